@@ -1,0 +1,178 @@
+/*
+ * mingpt_b200.h -- C ABI of libmingpt_b200.so: the sm_100a (B200) kernels behind the training step of
+ * aponte411/minGPT-distributed (GPT forward/backward in mingpt/model.py, optimizer + gradient clipping in
+ * mingpt/trainer.py).
+ *
+ * The reference has no FFI of its own (it is pure Python on top of torch), so every entry point below
+ * cites the reference line -- or the torch call that line makes -- whose arithmetic it replaces.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless stated otherwise; the library never allocates, frees or
+ *     retains memory past the call (the caller -- PyTorch's caching allocator in this repo -- owns it);
+ *   - `stream` is a cudaStream_t passed as void*; all work is asynchronous on that stream;
+ *   - return value 0 = ok, negative = error (mgb_last_error() gives a thread-local message);
+ *     nothing throws across the boundary and nothing falls back to another implementation;
+ *   - "bf16" buffers are __nv_bfloat16, row-major with an explicit leading dimension in ELEMENTS;
+ *   - entry points are re-entrant: forward ops are called from the Python thread, backward ops from
+ *     autograd's device thread.
+ */
+#ifndef MINGPT_B200_H_
+#define MINGPT_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* mgb_stream_t;
+
+enum {
+    MGB_OK = 0,
+    MGB_ERR_BAD_SHAPE = -1,
+    MGB_ERR_BAD_ALIGN = -2,
+    MGB_ERR_BAD_DTYPE = -3,
+    MGB_ERR_UNSUPPORTED = -4,
+    MGB_ERR_LAUNCH = -5,
+    MGB_ERR_DRIVER = -6,
+    MGB_ERR_TOO_LARGE = -7
+};
+
+enum { MGB_ACT_NONE = 0, MGB_ACT_GELU_TANH = 1, MGB_ACT_GELU_ERF = 2 };
+
+/* attention mask modes.
+ *   CAUSAL         scores[i,j] = -inf for j > i  (the README / north_star "CausalSelfAttention")
+ *   ADD_TRIL_ONES  scores[i,j] += 1.0 for j <= i, nothing masked: what mingpt/model.py:142-145,164 really
+ *                  computes, because a FLOAT attn_mask is ADDED by nn.MultiheadAttention
+ *                  (torch/nn/functional.py:6638-6643)
+ *   NONE           plain bidirectional softmax */
+enum { MGB_MASK_NONE = 0, MGB_MASK_CAUSAL = 1, MGB_MASK_ADD_TRIL_ONES = 2 };
+
+const char* mgb_last_error(void);
+int mgb_version(void);
+/* number of kernels this library has launched in the calling process (bench.py's gpu_launches) */
+int64_t mgb_launch_count(void);
+
+/* ---------------------------------------------------------------------------------------------------
+ * GEMM: D[m,n] = epilogue(alpha * sum_k A(m,k) B(n,k)), bf16 inputs, fp32 accumulate (tcgen05 + TMEM).
+ * Replaces nn.Linear forward/backward: mingpt/model.py:138 (c_proj), :180-181 (mlp.0, mlp.1), :249 (head),
+ * torch/nn/functional.py:6478 (MHA in-proj), :6653 (MHA out_proj), and autograd's dgrad/wgrad of each
+ * (mingpt/trainer.py:127).
+ *   a_mn_major = 0: A stored [m][k] (k contiguous, lda between rows of m)
+ *   a_mn_major = 1: A stored [k][m] (m contiguous, lda between rows of k)       -- same for B with n
+ * epilogue, in this order:  v = alpha*acc;  v += bias[n];  preact[m,n] = bf16(v) (if preact);
+ *   v = act(v);  v *= act'(gate[m,n]) (if gate; gate_kind selects the derivative);  v += residual[m,n];
+ *   D = v  (bf16 or fp32)   or   D += v (fp32, atomic; required for split_k > 1)
+ * ------------------------------------------------------------------------------------------------- */
+typedef struct mgb_gemm_args {
+    const void* a; int64_t lda; int32_t a_mn_major;
+    const void* b; int64_t ldb; int32_t b_mn_major;
+    void* d; int64_t ldd; int32_t d_f32; int32_t accumulate;
+    int64_t m, n, k;
+    const float* bias;
+    const void* residual; int64_t ldr;
+    int32_t act;
+    void* preact; int64_t ldp;
+    const void* gate; int64_t ldg; int32_t gate_kind;
+    int32_t split_k;   /* 0 = auto */
+    int32_t block_n;   /* 0 = auto; else 64/128/192/256 */
+    float alpha;       /* 0 is read as 1 */
+} mgb_gemm_args;
+int mgb_gemm_bf16(const mgb_gemm_args* args, mgb_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * LayerNorm (nn.LayerNorm, eps 1e-5, biased variance, affine): mingpt/model.py:176,178,248 applied at
+ * :187-188,312.  x,y bf16 [rows, cols]; gamma/beta fp32; mean/rstd fp32 [rows] saved for backward.
+ * ------------------------------------------------------------------------------------------------- */
+int mgb_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
+                      int64_t rows, int32_t cols, float eps, mgb_stream_t stream);
+/* dx = (dres ? dres : 0) + LN'(dy); dgamma += sum_rows(dy * xhat); dbeta += sum_rows(dy)  (fp32, atomic).
+ * `dres` fuses the residual-stream gradient of Block.forward (mingpt/model.py:187-188). dx may alias dres. */
+int mgb_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
+                      const void* dres, void* dx, float* dgamma, float* dbeta, int64_t rows, int32_t cols,
+                      mgb_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Embedding (GPTEmbedding.forward, mingpt/model.py:222-231 as repaired: wte[idx] + wpe[:, :T]).
+ * idx int64 [B,T]; wte bf16 [vocab, C]; wpe bf16 [block_size, C]; out bf16 [B,T,C].
+ * An index outside [0, vocab) sets *err_flag (int32, device, may be NULL) and produces zeros.
+ * ------------------------------------------------------------------------------------------------- */
+int mgb_embedding_fwd(const int64_t* idx, const void* wte, const void* wpe, void* out, int64_t B, int64_t T,
+                      int32_t C, int64_t vocab, int32_t* err_flag, mgb_stream_t stream);
+/* dwte[idx[b,t], :] += dx[b,t,:] (fp32 atomics);  dwpe[t,:] += sum_b dx[b,t,:] */
+int mgb_embedding_bwd(const int64_t* idx, const void* dx, float* dwte, float* dwpe, int64_t B, int64_t T,
+                      int32_t C, int64_t vocab, mgb_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Fused attention (flash-style: online softmax, no T x T tensor in HBM). Replaces
+ * torch/nn/functional.py:6630-6647 (scale, baddbmm with mask, softmax, bmm) called from
+ * mingpt/model.py:160-165.
+ * qkv bf16 [B, T, 3, H, d] (the in-proj output, untouched); out bf16 [B, T, H, d]; lse fp32 [B, H, T]
+ * (natural-log sum-exp of the masked/biased scaled scores).  d in {16, 32, 64}.
+ * ------------------------------------------------------------------------------------------------- */
+int mgb_attention_fwd(const void* qkv, void* out, float* lse, int32_t B, int32_t T, int32_t H, int32_t d,
+                      int32_t mask_mode, float scale, mgb_stream_t stream);
+/* Backward with recompute. delta fp32 [B,H,T] and dq_accum fp32 [B,T,H,d] are caller-provided scratch
+ * (dq_accum is zeroed by the call); dqkv bf16 [B,T,3,H,d] is fully overwritten. */
+int mgb_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                      float* dq_accum, void* dqkv, int32_t B, int32_t T, int32_t H, int32_t d, int32_t mask_mode,
+                      float scale, mgb_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Cross entropy (F.cross_entropy(..., ignore_index=-1), mean over valid targets: mingpt/model.py:316-318).
+ * In place on a chunk of bf16 logits [rows, ld] (only the first `vocab` columns are meaningful):
+ *   row_loss[r] = lse - logit[target]   (0 for ignored rows)
+ *   logits[r,:] <- (softmax - onehot) * grad_scale / max(*n_valid, 1)    (0 for ignored rows), bf16
+ * n_valid is a DEVICE int32 holding the number of non-ignored targets of the WHOLE batch.
+ * With write_grad = 0 the logits are left untouched (evaluation).
+ * ------------------------------------------------------------------------------------------------- */
+int mgb_cross_entropy_fwd_bwd(void* logits, int64_t ld, const int64_t* targets, float* row_loss,
+                              const int32_t* n_valid, int64_t rows, int64_t vocab, float grad_scale,
+                              int32_t write_grad, int32_t* err_flag, mgb_stream_t stream);
+int mgb_count_valid_targets(const int64_t* targets, int64_t n, int32_t* n_valid, mgb_stream_t stream);
+/* loss = sum(row_loss) / max(*n_valid, 1); deterministic single-block tree reduction */
+int mgb_loss_finalize(const float* row_loss, int64_t rows, const int32_t* n_valid, float* loss,
+                      mgb_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Small HBM-bound helpers of the backward pass.
+ * ------------------------------------------------------------------------------------------------- */
+/* out[c] += sum_r x[r, c]   (bias gradients; fp32 atomics) */
+int mgb_colsum_bf16(const void* x, int64_t ld, int64_t rows, int64_t cols, float* out, mgb_stream_t stream);
+/* dz = dy * act'(z)   (nn.GELU backward when the activation is not fused into a GEMM epilogue) */
+int mgb_act_bwd_bf16(const void* dy, const void* z, void* dz, int64_t n, int32_t act, mgb_stream_t stream);
+/* y = x + act(z) or act(z) (elementwise forward used by tests and the unfused path) */
+int mgb_act_fwd_bf16(const void* z, const void* res, void* y, int64_t n, int32_t act, mgb_stream_t stream);
+int mgb_cast_f32_to_bf16(const float* src, void* dst, int64_t n, mgb_stream_t stream);
+int mgb_cast_bf16_to_f32(const void* src, float* dst, int64_t n, mgb_stream_t stream);
+/* dst += alpha * src (fp32) */
+int mgb_axpy_f32(float* dst, const float* src, float alpha, int64_t n, mgb_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Gradient clipping + AdamW.
+ *   clip_grad_norm: mingpt/trainer.py:129-130 -> torch/nn/utils/clip_grad.py (global L2 norm,
+ *                   coef = max_norm / (norm + 1e-6) clamped to 1)
+ *   AdamW step:     mingpt/trainer.py:132 -> torch/optim/adam.py (decoupled weight decay, eps 1e-8,
+ *                   bias correction), groups from create_optimizer (mingpt/model.py:62-122)
+ * mgb_sumsq_f32 ACCUMULATES sum(x^2) into *out (fp32, device; zero it first with cudaMemsetAsync).
+ * mgb_adamw_multi updates every tensor described by `table` in ONE launch.  The clip coefficient is
+ * computed on the device from *gradnorm_sq (may be NULL = no clipping) so no host sync is needed:
+ *   g = grad * grad_scale;  norm = sqrt(*gradnorm_sq) * grad_scale;  g *= min(1, max_norm/(norm+1e-6))
+ * ------------------------------------------------------------------------------------------------- */
+typedef struct mgb_adamw_chunk {
+    int64_t offset;      /* element offset into the flat fp32 param / grad / m / v buffers */
+    int32_t numel;       /* elements in this chunk (<= chunk size chosen by the caller) */
+    float weight_decay;  /* this tensor's decay (0 for the no-decay group) */
+} mgb_adamw_chunk;
+int mgb_sumsq_f32(const float* x, int64_t n, float* out, mgb_stream_t stream);
+int mgb_adamw_multi(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, void* params_bf16,
+                    const mgb_adamw_chunk* table /*device*/, int32_t num_chunks, float lr, float beta1, float beta2,
+                    float eps, int32_t step, float grad_scale, const float* gradnorm_sq, float max_norm,
+                    mgb_stream_t stream);
+/* grads *= min(1, max_norm / (sqrt(*gradnorm_sq) + 1e-6))  -- for callers that keep a foreign optimizer */
+int mgb_clip_scale_f32(float* grads, int64_t n, const float* gradnorm_sq, float max_norm, mgb_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MINGPT_B200_H_ */

@@ -1,0 +1,523 @@
+// Fused (flash-style) self-attention, forward and backward with recompute.
+//
+// Replaces the need_weights=True slow path of nn.MultiheadAttention that the reference runs
+// (mingpt/model.py:160-165 -> torch/nn/functional.py:6630-6647): q*scale, baddbmm(mask, q, k^T),
+// softmax, bmm(P, V) -- which materialises (B*H, T, T) fp32 tensors -- with an online-softmax kernel that
+// keeps the T x T scores on chip.  Reads Q/K/V straight from the packed in-proj output [B,T,3,H,d] and
+// writes the context token-major [B,T,H,d] so the out-projection GEMM consumes it without a transpose.
+//
+// This is the warp-level tensor-core path (mma.sync m16n8k16, ldmatrix, cp.async double buffering) used
+// for every head size the reference's presets produce (d = 16 gpt-nano, 32 gpt-mini, 64 gpt2 family).
+//
+// mask modes (see mingpt_b200.h): CAUSAL, ADD_TRIL_ONES (the reference's as-written float mask), NONE.
+#include "common.cuh"
+#include "mingpt_b200.h"
+
+namespace mgb {
+namespace attn {
+
+constexpr int BM = 64;   // queries per CTA (fwd) / per inner step (bwd)
+constexpr int BN = 64;   // keys per inner step (fwd) / per CTA (bwd)
+constexpr int NTHREADS = 128;
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr float LN2 = 0.6931471805599453f;
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, bool pred) {
+    const uint32_t s = smem_u32(smem);
+    const int sz = pred ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(gmem), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], const void* p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(smem_u32(p)));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], const void* p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(smem_u32(p)));
+}
+__device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, "
+        "{%0, %1, %2, %3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// 64 rows x D bf16 from global (row stride ld) into smem (row stride D+8); rows >= T are zero-filled.
+template <int D>
+__device__ __forceinline__ void load_tile(__nv_bfloat16* s, const __nv_bfloat16* gbase, int64_t ld, int t0, int T) {
+    constexpr int CH = D / 8;
+    constexpr int LDS = D + 8;
+    for (int i = threadIdx.x; i < 64 * CH; i += NTHREADS) {
+        const int r = i / CH, c = i - r * CH;
+        const int t = t0 + r;
+        const bool ok = t < T;
+        cp_async16(s + r * LDS + c * 8, gbase + (int64_t)(ok ? t : 0) * ld + c * 8, ok);
+    }
+}
+
+// =====================================================================================
+// forward
+// =====================================================================================
+template <int D>
+__global__ void __launch_bounds__(NTHREADS)
+attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, float* __restrict__ lse,
+                int T, int H, int mask_mode, float scale_log2) {
+    constexpr int LDS = D + 8;
+    constexpr int KD = D / 16;   // k-steps over the head dim
+    constexpr int ND = D / 8;    // n-tiles over the head dim
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    __nv_bfloat16* sQ = reinterpret_cast<__nv_bfloat16*>(smem_raw);
+    __nv_bfloat16* sK = sQ + 64 * LDS;        // [2][64*LDS]
+    __nv_bfloat16* sV = sK + 2 * 64 * LDS;    // [2][64*LDS]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, t4 = lane & 3;
+    const int b = blockIdx.y / H, h = blockIdx.y % H;
+    const int qb = gridDim.x - 1 - blockIdx.x;   // heavy (late) causal blocks first
+    const int q0 = qb * BM;
+    const int64_t ld = (int64_t)3 * H * D;
+    const __nv_bfloat16* qbase = qkv + (int64_t)b * T * ld + (int64_t)h * D;
+    const __nv_bfloat16* kbase = qbase + (int64_t)H * D;
+    const __nv_bfloat16* vbase = qbase + (int64_t)2 * H * D;
+    const bool causal = mask_mode == MGB_MASK_CAUSAL;
+    const bool tril = mask_mode == MGB_MASK_ADD_TRIL_ONES;
+    const int nkv_all = (T + BN - 1) / BN;
+    const int nkv = causal ? min(qb + 1, nkv_all) : nkv_all;
+
+    load_tile<D>(sQ, qbase, ld, q0, T);
+    load_tile<D>(sK, kbase, ld, 0, T);
+    load_tile<D>(sV, vbase, ld, 0, T);
+    cp_async_commit();
+
+    float o[ND][4];
+#pragma unroll
+    for (int n = 0; n < ND; ++n) { o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f; }
+    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+    uint32_t qf[KD][4];
+    const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
+
+    for (int j = 0; j < nkv; ++j) {
+        cp_async_wait_all();
+        __syncthreads();
+        const int buf = j & 1;
+        if (j == 0) {
+#pragma unroll
+            for (int kk = 0; kk < KD; ++kk)
+                ldsm_x4(qf[kk], sQ + (warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * LDS + kk * 16 + (lane >> 4) * 8);
+        }
+        if (j + 1 < nkv) {
+            load_tile<D>(sK + (buf ^ 1) * 64 * LDS, kbase, ld, (j + 1) * BN, T);
+            load_tile<D>(sV + (buf ^ 1) * 64 * LDS, vbase, ld, (j + 1) * BN, T);
+            cp_async_commit();
+        }
+        const __nv_bfloat16* cK = sK + buf * 64 * LDS;
+        const __nv_bfloat16* cV = sV + buf * 64 * LDS;
+
+        float s[8][4];
+#pragma unroll
+        for (int n = 0; n < 8; ++n) { s[n][0] = s[n][1] = s[n][2] = s[n][3] = 0.f; }
+#pragma unroll
+        for (int kk = 0; kk < KD; ++kk) {
+#pragma unroll
+            for (int nb = 0; nb < 4; ++nb) {
+                uint32_t bf[4];
+                ldsm_x4(bf, cK + (nb * 16 + (lane & 7) + (lane >> 4) * 8) * LDS + kk * 16 + ((lane >> 3) & 1) * 8);
+                mma16816(s[2 * nb], qf[kk], bf[0], bf[1]);
+                mma16816(s[2 * nb + 1], qf[kk], bf[2], bf[3]);
+            }
+        }
+        // scale (log2 domain), additive tril bias, masking
+        float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+        for (int n = 0; n < 8; ++n) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int col = j * BN + n * 8 + 2 * t4 + (e & 1);
+                const int row = (e < 2) ? r0 : r1;
+                float v = s[n][e] * scale_log2;
+                if (tril && col <= row) v += LOG2E;
+                if (col >= T || (causal && col > row)) v = -INFINITY;
+                s[n][e] = v;
+                if (e < 2) mx0 = fmaxf(mx0, v); else mx1 = fmaxf(mx1, v);
+            }
+        }
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
+        // fully-masked rows (only padding rows >= T): keep everything at zero without NaNs
+        const float ms0 = (mn0 == -INFINITY) ? 0.f : mn0, ms1 = (mn1 == -INFINITY) ? 0.f : mn1;
+        const float c0 = exp2f(m0 - ms0), c1 = exp2f(m1 - ms1);
+        m0 = mn0; m1 = mn1;
+        float rs0 = 0.f, rs1 = 0.f;
+#pragma unroll
+        for (int n = 0; n < 8; ++n) {
+            s[n][0] = exp2f(s[n][0] - ms0); s[n][1] = exp2f(s[n][1] - ms0);
+            s[n][2] = exp2f(s[n][2] - ms1); s[n][3] = exp2f(s[n][3] - ms1);
+            rs0 += s[n][0] + s[n][1];
+            rs1 += s[n][2] + s[n][3];
+        }
+        l0 = l0 * c0 + rs0;
+        l1 = l1 * c1 + rs1;
+#pragma unroll
+        for (int n = 0; n < ND; ++n) { o[n][0] *= c0; o[n][1] *= c0; o[n][2] *= c1; o[n][3] *= c1; }
+        // O += P V
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+            uint32_t a[4];
+            a[0] = pack_bf16x2(s[2 * kk][0], s[2 * kk][1]);
+            a[1] = pack_bf16x2(s[2 * kk][2], s[2 * kk][3]);
+            a[2] = pack_bf16x2(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+            a[3] = pack_bf16x2(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+#pragma unroll
+            for (int nb = 0; nb < KD; ++nb) {
+                uint32_t bf[4];
+                ldsm_x4_t(bf, cV + (kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * LDS + nb * 16 + (lane >> 4) * 8);
+                mma16816(o[2 * nb], a, bf[0], bf[1]);
+                mma16816(o[2 * nb + 1], a, bf[2], bf[3]);
+            }
+        }
+    }
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    const float i0 = l0 > 0.f ? 1.f / l0 : 0.f, i1 = l1 > 0.f ? 1.f / l1 : 0.f;
+    const int64_t od = (int64_t)H * D;
+    if (r0 < T) {
+        __nv_bfloat16* orow = out + ((int64_t)b * T + r0) * od + (int64_t)h * D;
+#pragma unroll
+        for (int n = 0; n < ND; ++n)
+            *reinterpret_cast<uint32_t*>(orow + n * 8 + 2 * t4) = pack_bf16x2(o[n][0] * i0, o[n][1] * i0);
+        if (t4 == 0) lse[((int64_t)b * H + h) * T + r0] = (m0 + log2f(l0)) * LN2;
+    }
+    if (r1 < T) {
+        __nv_bfloat16* orow = out + ((int64_t)b * T + r1) * od + (int64_t)h * D;
+#pragma unroll
+        for (int n = 0; n < ND; ++n)
+            *reinterpret_cast<uint32_t*>(orow + n * 8 + 2 * t4) = pack_bf16x2(o[n][2] * i1, o[n][3] * i1);
+        if (t4 == 0) lse[((int64_t)b * H + h) * T + r1] = (m1 + log2f(l1)) * LN2;
+    }
+}
+
+// =====================================================================================
+// backward
+// =====================================================================================
+// delta[b,h,t] = sum_e dO[b,t,h,e] * O[b,t,h,e]
+template <int D>
+__global__ void __launch_bounds__(256)
+attn_bwd_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ dout,
+                      float* __restrict__ delta, int64_t B, int64_t T, int H) {
+    const int64_t total = B * T * H;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int h = (int)(i % H);
+        const int64_t bt = i / H;
+        const int64_t b = bt / T, t = bt - b * T;
+        float s = 0.f;
+#pragma unroll
+        for (int c = 0; c < D / 8; ++c) {
+            const uint4 a = ldg128(o + i * D + c * 8), d = ldg128(dout + i * D + c * 8);
+            const uint32_t wa[4] = {a.x, a.y, a.z, a.w}, wd[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 fa = unpack_bf16x2(wa[e]), fd = unpack_bf16x2(wd[e]);
+                s += fa.x * fd.x + fa.y * fd.y;
+            }
+        }
+        delta[(b * H + h) * T + t] = s;
+    }
+}
+
+template <int D>
+__global__ void __launch_bounds__(NTHREADS)
+attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dout,
+                const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_accum,
+                __nv_bfloat16* __restrict__ dqkv, int T, int H, int mask_mode, float scale, float scale_log2) {
+    constexpr int LDS = D + 8;
+    constexpr int LDP = 64 + 8;
+    constexpr int KD = D / 16;
+    constexpr int ND = D / 8;
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    __nv_bfloat16* sK = reinterpret_cast<__nv_bfloat16*>(smem_raw);
+    __nv_bfloat16* sV = sK + 64 * LDS;
+    __nv_bfloat16* sQ = sV + 64 * LDS;
+    __nv_bfloat16* sdO = sQ + 64 * LDS;
+    __nv_bfloat16* sdS = sdO + 64 * LDS;                        // [64 queries][LDP] keys
+    float* sLse = reinterpret_cast<float*>(sdS + 64 * LDP);     // [64], already * log2e
+    float* sDelta = sLse + 64;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, t4 = lane & 3;
+    const int b = blockIdx.y / H, h = blockIdx.y % H;
+    const int kb = blockIdx.x;
+    const int k0 = kb * BN;
+    const int64_t ld = (int64_t)3 * H * D;
+    const int64_t od = (int64_t)H * D;
+    const __nv_bfloat16* qbase = qkv + (int64_t)b * T * ld + (int64_t)h * D;
+    const __nv_bfloat16* kbase = qbase + od;
+    const __nv_bfloat16* vbase = qbase + 2 * od;
+    const __nv_bfloat16* dobase = dout + (int64_t)b * T * od + (int64_t)h * D;
+    const bool causal = mask_mode == MGB_MASK_CAUSAL;
+    const bool tril = mask_mode == MGB_MASK_ADD_TRIL_ONES;
+    const int nq = (T + BM - 1) / BM;
+    const int i_begin = causal ? kb : 0;
+
+    load_tile<D>(sK, kbase, ld, k0, T);
+    load_tile<D>(sV, vbase, ld, k0, T);
+    cp_async_commit();
+    cp_async_wait_all();
+    __syncthreads();
+
+    uint32_t kf[KD][4], vf[KD][4];
+#pragma unroll
+    for (int kk = 0; kk < KD; ++kk) {
+        const int off = (warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * LDS + kk * 16 + (lane >> 4) * 8;
+        ldsm_x4(kf[kk], sK + off);
+        ldsm_x4(vf[kk], sV + off);
+    }
+    float dk[ND][4], dv[ND][4];
+#pragma unroll
+    for (int n = 0; n < ND; ++n) {
+        dk[n][0] = dk[n][1] = dk[n][2] = dk[n][3] = 0.f;
+        dv[n][0] = dv[n][1] = dv[n][2] = dv[n][3] = 0.f;
+    }
+    const int kr0 = k0 + warp * 16 + g, kr1 = kr0 + 8;   // this thread's two key rows
+
+    for (int i = i_begin; i < nq; ++i) {
+        __syncthreads();   // previous step finished with sQ / sdO / sdS / sLse
+        load_tile<D>(sQ, qbase, ld, i * BM, T);
+        load_tile<D>(sdO, dobase, od, i * BM, T);
+        cp_async_commit();
+        if (threadIdx.x < 64) {
+            const int t = i * BM + threadIdx.x;
+            const int64_t idx = ((int64_t)b * H + h) * T + t;
+            sLse[threadIdx.x] = (t < T) ? lse[idx] * LOG2E : INFINITY;
+            sDelta[threadIdx.x] = (t < T) ? delta[idx] : 0.f;
+        }
+        cp_async_wait_all();
+        __syncthreads();
+
+        // S^T = K Q^T and dP^T = V dO^T : [16 keys x 64 queries] per warp
+        float st[8][4], dp[8][4];
+#pragma unroll
+        for (int n = 0; n < 8; ++n) {
+            st[n][0] = st[n][1] = st[n][2] = st[n][3] = 0.f;
+            dp[n][0] = dp[n][1] = dp[n][2] = dp[n][3] = 0.f;
+        }
+#pragma unroll
+        for (int kk = 0; kk < KD; ++kk) {
+#pragma unroll
+            for (int nb = 0; nb < 4; ++nb) {
+                const int off = (nb * 16 + (lane & 7) + (lane >> 4) * 8) * LDS + kk * 16 + ((lane >> 3) & 1) * 8;
+                uint32_t bq[4], bo[4];
+                ldsm_x4(bq, sQ + off);
+                ldsm_x4(bo, sdO + off);
+                mma16816(st[2 * nb], kf[kk], bq[0], bq[1]);
+                mma16816(st[2 * nb + 1], kf[kk], bq[2], bq[3]);
+                mma16816(dp[2 * nb], vf[kk], bo[0], bo[1]);
+                mma16816(dp[2 * nb + 1], vf[kk], bo[2], bo[3]);
+            }
+        }
+        // P^T (into st) and scaled dS^T (into dp)
+#pragma unroll
+        for (int n = 0; n < 8; ++n) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int ql = n * 8 + 2 * t4 + (e & 1);
+                const int q = i * BM + ql;
+                const int key = (e < 2) ? kr0 : kr1;
+                float sl = st[n][e] * scale_log2;
+                if (tril && key <= q) sl += LOG2E;
+                const bool masked = (key >= T) || (q >= T) || (causal && key > q);
+                const float p = masked ? 0.f : exp2f(sl - sLse[ql]);
+                st[n][e] = p;
+                dp[n][e] = p * (dp[n][e] - sDelta[ql]) * scale;
+            }
+        }
+        // dV += P^T dO ; dK += dS^T Q   (reduction over the 64 queries)
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+            uint32_t ap[4], ad[4];
+            ap[0] = pack_bf16x2(st[2 * kk][0], st[2 * kk][1]);
+            ap[1] = pack_bf16x2(st[2 * kk][2], st[2 * kk][3]);
+            ap[2] = pack_bf16x2(st[2 * kk + 1][0], st[2 * kk + 1][1]);
+            ap[3] = pack_bf16x2(st[2 * kk + 1][2], st[2 * kk + 1][3]);
+            ad[0] = pack_bf16x2(dp[2 * kk][0], dp[2 * kk][1]);
+            ad[1] = pack_bf16x2(dp[2 * kk][2], dp[2 * kk][3]);
+            ad[2] = pack_bf16x2(dp[2 * kk + 1][0], dp[2 * kk + 1][1]);
+            ad[3] = pack_bf16x2(dp[2 * kk + 1][2], dp[2 * kk + 1][3]);
+#pragma unroll
+            for (int nb = 0; nb < KD; ++nb) {
+                const int off = (kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * LDS + nb * 16 + (lane >> 4) * 8;
+                uint32_t bo[4], bq[4];
+                ldsm_x4_t(bo, sdO + off);
+                ldsm_x4_t(bq, sQ + off);
+                mma16816(dv[2 * nb], ap, bo[0], bo[1]);
+                mma16816(dv[2 * nb + 1], ap, bo[2], bo[3]);
+                mma16816(dk[2 * nb], ad, bq[0], bq[1]);
+                mma16816(dk[2 * nb + 1], ad, bq[2], bq[3]);
+            }
+        }
+        // dS (query-major) to shared memory for the dQ product
+#pragma unroll
+        for (int n = 0; n < 8; ++n) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int ql = n * 8 + 2 * t4 + (e & 1);
+                const int kl = warp * 16 + g + ((e < 2) ? 0 : 8);
+                sdS[ql * LDP + kl] = __float2bfloat16(dp[n][e]);
+            }
+        }
+        __syncthreads();
+        // dQ_i (partial over this key block) = dS K : warp takes 16 query rows
+        float dq[ND][4];
+#pragma unroll
+        for (int n = 0; n < ND; ++n) { dq[n][0] = dq[n][1] = dq[n][2] = dq[n][3] = 0.f; }
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+            uint32_t a[4];
+            ldsm_x4(a, sdS + (warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * LDP + kk * 16 + (lane >> 4) * 8);
+#pragma unroll
+            for (int nb = 0; nb < KD; ++nb) {
+                uint32_t bk[4];
+                ldsm_x4_t(bk, sK + (kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * LDS + nb * 16 + (lane >> 4) * 8);
+                mma16816(dq[2 * nb], a, bk[0], bk[1]);
+                mma16816(dq[2 * nb + 1], a, bk[2], bk[3]);
+            }
+        }
+        const int qr0 = i * BM + warp * 16 + g, qr1 = qr0 + 8;
+        if (qr0 < T) {
+            float* dst = dq_accum + ((int64_t)b * T + qr0) * od + (int64_t)h * D;
+#pragma unroll
+            for (int n = 0; n < ND; ++n) {
+                atomicAdd(dst + n * 8 + 2 * t4, dq[n][0]);
+                atomicAdd(dst + n * 8 + 2 * t4 + 1, dq[n][1]);
+            }
+        }
+        if (qr1 < T) {
+            float* dst = dq_accum + ((int64_t)b * T + qr1) * od + (int64_t)h * D;
+#pragma unroll
+            for (int n = 0; n < ND; ++n) {
+                atomicAdd(dst + n * 8 + 2 * t4, dq[n][2]);
+                atomicAdd(dst + n * 8 + 2 * t4 + 1, dq[n][3]);
+            }
+        }
+    }
+    // dK, dV for this key block
+    if (kr0 < T) {
+        __nv_bfloat16* row = dqkv + ((int64_t)b * T + kr0) * ld + (int64_t)h * D;
+#pragma unroll
+        for (int n = 0; n < ND; ++n) {
+            *reinterpret_cast<uint32_t*>(row + od + n * 8 + 2 * t4) = pack_bf16x2(dk[n][0], dk[n][1]);
+            *reinterpret_cast<uint32_t*>(row + 2 * od + n * 8 + 2 * t4) = pack_bf16x2(dv[n][0], dv[n][1]);
+        }
+    }
+    if (kr1 < T) {
+        __nv_bfloat16* row = dqkv + ((int64_t)b * T + kr1) * ld + (int64_t)h * D;
+#pragma unroll
+        for (int n = 0; n < ND; ++n) {
+            *reinterpret_cast<uint32_t*>(row + od + n * 8 + 2 * t4) = pack_bf16x2(dk[n][2], dk[n][3]);
+            *reinterpret_cast<uint32_t*>(row + 2 * od + n * 8 + 2 * t4) = pack_bf16x2(dv[n][2], dv[n][3]);
+        }
+    }
+}
+
+// dqkv[b,t,0,h,:] = bf16(dq_accum[b,t,h,:])
+__global__ void __launch_bounds__(256)
+attn_dq_convert_kernel(const float* __restrict__ dq_accum, __nv_bfloat16* __restrict__ dqkv, int64_t BT, int64_t HD) {
+    const int64_t nch = HD >> 3;
+    const int64_t total = BT * nch;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = i / nch, ch = i - row * nch;
+        const float4 a = *reinterpret_cast<const float4*>(dq_accum + row * HD + ch * 8);
+        const float4 c = *reinterpret_cast<const float4*>(dq_accum + row * HD + ch * 8 + 4);
+        stg128(dqkv + row * 3 * HD + ch * 8,
+               make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(c.x, c.y), pack_bf16x2(c.z, c.w)));
+    }
+}
+
+template <int D>
+static int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int mask_mode, float scale,
+                      cudaStream_t s) {
+    constexpr int smem = (64 + 4 * 64) * (D + 8) * 2;
+    dim3 grid((T + BM - 1) / BM, B * H);
+    attn_fwd_kernel<D><<<grid, NTHREADS, smem, s>>>((const __nv_bfloat16*)qkv, (__nv_bfloat16*)out, lse, T, H, mask_mode,
+                                                   scale * LOG2E);
+    return 0;
+}
+template <int D>
+static int launch_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                      float* dq_accum, void* dqkv, int B, int T, int H, int mask_mode, float scale, cudaStream_t s) {
+    const int64_t rows = (int64_t)B * T * H;
+    int g = (int)((rows + 255) / 256);
+    if (g > num_sms() * 16) g = num_sms() * 16;
+    attn_bwd_delta_kernel<D><<<g, 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, B, T, H);
+    constexpr int smem = 4 * 64 * (D + 8) * 2 + 64 * (64 + 8) * 2 + 2 * 64 * 4;
+    static bool attr_set = false;
+    if (!attr_set && smem > 48 * 1024) {
+        cudaFuncSetAttribute(attn_bwd_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        attr_set = true;
+    }
+    dim3 grid((T + BN - 1) / BN, B * H);
+    attn_bwd_kernel<D><<<grid, NTHREADS, smem, s>>>((const __nv_bfloat16*)qkv, (const __nv_bfloat16*)dout, lse, delta,
+                                                   dq_accum, (__nv_bfloat16*)dqkv, T, H, mask_mode, scale, scale * LOG2E);
+    const int64_t chunks = (int64_t)B * T * (H * D / 8);
+    int g2 = (int)((chunks + 255) / 256);
+    if (g2 > num_sms() * 16) g2 = num_sms() * 16;
+    attn_dq_convert_kernel<<<g2, 256, 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, (int64_t)B * T, (int64_t)H * D);
+    return 0;
+}
+
+}  // namespace attn
+}  // namespace mgb
+
+using namespace mgb;
+
+static int check_attn_shape(const char* who, int B, int T, int H, int d, int mask_mode) {
+    if (B <= 0 || T <= 0 || H <= 0) { set_last_error("attention: non-positive B/T/H"); return kErrBadShape; }
+    if (d != 16 && d != 32 && d != 64) { set_last_error("attention: head dim must be 16, 32 or 64"); return kErrUnsupported; }
+    if (mask_mode < 0 || mask_mode > 2) { set_last_error("attention: bad mask mode"); return kErrBadShape; }
+    if ((int64_t)B * H > 65535) { set_last_error("attention: B*H exceeds 65535"); return kErrTooLarge; }
+    (void)who;
+    return kOk;
+}
+
+extern "C" int mgb_attention_fwd(const void* qkv, void* out, float* lse, int32_t B, int32_t T, int32_t H, int32_t d,
+                                 int32_t mask_mode, float scale, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    int rc = check_attn_shape("fwd", B, T, H, d, mask_mode);
+    if (rc) return rc;
+    if (((uintptr_t)qkv % 16) || ((uintptr_t)out % 16)) { set_last_error("attention: pointers must be 16-byte aligned"); return kErrBadAlign; }
+    if (d == 64) attn::launch_fwd<64>(qkv, out, lse, B, T, H, mask_mode, scale, s);
+    else if (d == 32) attn::launch_fwd<32>(qkv, out, lse, B, T, H, mask_mode, scale, s);
+    else attn::launch_fwd<16>(qkv, out, lse, B, T, H, mask_mode, scale, s);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+extern "C" int mgb_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                                 float* dq_accum, void* dqkv, int32_t B, int32_t T, int32_t H, int32_t d,
+                                 int32_t mask_mode, float scale, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    int rc = check_attn_shape("bwd", B, T, H, d, mask_mode);
+    if (rc) return rc;
+    if (((uintptr_t)qkv % 16) || ((uintptr_t)out % 16) || ((uintptr_t)dout % 16) || ((uintptr_t)dqkv % 16) ||
+        ((uintptr_t)dq_accum % 16)) {
+        set_last_error("attention: pointers must be 16-byte aligned"); return kErrBadAlign;
+    }
+    cudaMemsetAsync(dq_accum, 0, (size_t)B * T * H * d * sizeof(float), s);
+    if (d == 64) attn::launch_bwd<64>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
+    else if (d == 32) attn::launch_bwd<32>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
+    else attn::launch_bwd<16>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
+    count_launch(3);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}

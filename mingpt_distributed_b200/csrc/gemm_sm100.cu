@@ -1,0 +1,488 @@
+// BF16 GEMM for sm_100a: TMA -> shared memory (SWIZZLE_128B) -> tcgen05.mma -> TMEM -> fused epilogue.
+//
+// Replaces every nn.Linear / F.linear call on the reference's training step
+// (mingpt/model.py:138,180-181,249 and torch/nn/functional.py:6478,6653 inside
+// nn.MultiheadAttention) and their autograd backward (dgrad + wgrad).
+//
+//   D[m, n] = epilogue( sum_k A(m, k) * B(n, k) )
+//
+// A and B are BF16 and may each be "K-major" (reduction index contiguous in memory) or
+// "MN-major" (output index contiguous), so the three layouts of a linear layer map onto one kernel:
+//   forward  Y = X W^T      : A = X  [M,K] K-major,  B = W  [N,K] K-major
+//   dgrad    dX = dY W      : A = dY [M,N] K-major,  B = W  [N,K] viewed as [Kred=N, Nout=K] MN-major
+//   wgrad    dW = dY^T X    : A = dY [M,N] viewed as [Kred=M, Mout=N] MN-major, B = X likewise MN-major
+//
+// One persistent CTA per SM, warp specialised:
+//   warp 0      TMA producer        (one lane)
+//   warp 1      tcgen05.mma issuer  (one lane)
+//   warp 2      TMEM allocator
+//   warps 4-11  epilogue: tcgen05.ld -> bias / GELU / gate / residual -> global stores
+// Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1.
+#include "common.cuh"
+#include "mingpt_b200.h"
+
+#include <mutex>
+
+namespace mgb {
+namespace gemm {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;   // 64 bf16 = 128 bytes = one SWIZZLE_128B row
+constexpr int UMMA_K = 16;
+constexpr int MAX_BLOCK_N = 256;
+constexpr int kStages = 4;
+constexpr int kEpiWarps = 8;
+constexpr int kThreads = 128 + kEpiWarps * 32;
+constexpr int kTmemCols = 512;
+constexpr int kAccStride = 256;   // TMEM column offset between the two accumulator stages
+
+constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;        // 16 KiB
+constexpr int B_STAGE_BYTES = MAX_BLOCK_N * BLOCK_K * 2;    // 32 KiB
+constexpr int ATOM_BYTES = 64 * BLOCK_K * 2;                // one 64-wide MN-major atom: 8 KiB
+constexpr int SMEM_BYTES = kStages * (A_STAGE_BYTES + B_STAGE_BYTES) + 1024 /*align slack*/ + 256 /*barriers*/;
+
+struct Params {
+    int64_t M, N, K;
+    int32_t a_mn, b_mn;
+    int32_t block_n;
+    int32_t split_k;
+    int32_t num_m_tiles, num_n_tiles, k_blocks_total, k_blocks_per_split;
+    // epilogue
+    void* d;
+    int64_t ldd;
+    int32_t d_f32;
+    int32_t accumulate;
+    const float* bias;
+    const __nv_bfloat16* residual;
+    int64_t ldr;
+    int32_t act;
+    __nv_bfloat16* preact;
+    int64_t ldp;
+    const __nv_bfloat16* gate;
+    int64_t ldg;
+    int32_t gate_kind;
+    float alpha;
+};
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+    if (act == MGB_ACT_GELU_TANH) return gelu_tanh_f(v);
+    if (act == MGB_ACT_GELU_ERF) return gelu_erf_f(v);
+    return v;
+}
+__device__ __forceinline__ float apply_gate(float g, int kind) {
+    return kind == MGB_ACT_GELU_TANH ? gelu_tanh_grad_f(g) : gelu_erf_grad_f(g);
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+            const Params p) {
+    extern __shared__ uint8_t smem_raw[];
+    // SWIZZLE_128B tiles need 1024-byte alignment.
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + kStages * A_STAGE_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * (A_STAGE_BYTES + B_STAGE_BYTES));
+    uint64_t* full_bar = bars;                  // [kStages]
+    uint64_t* empty_bar = bars + kStages;       // [kStages]
+    uint64_t* tmem_full = bars + 2 * kStages;   // [2]
+    uint64_t* tmem_empty = tmem_full + 2;       // [2]
+    uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full[s], 1);
+            mbar_init(&tmem_empty[s], kEpiWarps);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_base_ptr, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_base_ptr;
+
+    const int tiles = p.num_m_tiles * p.num_n_tiles;
+    const int units = tiles * p.split_k;
+    const int block_n = p.block_n;
+    const uint32_t stage_tx = A_STAGE_BYTES + (uint32_t)block_n * BLOCK_K * 2;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0;
+            for (int u = blockIdx.x; u < units; u += gridDim.x) {
+                const int split = u / tiles;
+                const int t = u - split * tiles;
+                const int m0 = (t / p.num_n_tiles) * BLOCK_M;
+                const int n0 = (t % p.num_n_tiles) * block_n;
+                const int kb0 = split * p.k_blocks_per_split;
+                const int kb1 = min(kb0 + p.k_blocks_per_split, p.k_blocks_total);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
+                    uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
+                    uint8_t* sb = smem_b + stage * B_STAGE_BYTES;
+                    const int k0 = kb * BLOCK_K;
+                    if (!p.a_mn) {
+                        tma_load_2d(sa, &tmap_a, &full_bar[stage], k0, m0);
+                    } else {
+                        tma_load_2d(sa, &tmap_a, &full_bar[stage], m0, k0);
+                        tma_load_2d(sa + ATOM_BYTES, &tmap_a, &full_bar[stage], m0 + 64, k0);
+                    }
+                    if (!p.b_mn) {
+                        tma_load_2d(sb, &tmap_b, &full_bar[stage], k0, n0);
+                    } else {
+                        for (int a = 0; a < block_n / 64; ++a)
+                            tma_load_2d(sb + a * ATOM_BYTES, &tmap_b, &full_bar[stage], n0 + a * 64, k0);
+                    }
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_bf16(BLOCK_M, block_n, p.a_mn, p.b_mn);
+            // K-major: 8-row groups are 1024 B apart (SBO), LBO unused; advance 32 B per UMMA_K.
+            // MN-major: 8 k-rows of 128 B per group (SBO = 1024), 64-wide atoms BLOCK_K*128 B apart (LBO);
+            //           advance 16 k-rows = 2048 B per UMMA_K.
+            const uint32_t a_lbo = p.a_mn ? ATOM_BYTES : 0, b_lbo = p.b_mn ? ATOM_BYTES : 0;
+            const uint32_t a_kstep = p.a_mn ? UMMA_K * 128 : UMMA_K * 2;
+            const uint32_t b_kstep = p.b_mn ? UMMA_K * 128 : UMMA_K * 2;
+            uint32_t stage = 0, phase = 0;
+            uint32_t acc = 0, acc_phase = 0;
+            for (int u = blockIdx.x; u < units; u += gridDim.x) {
+                const int split = u / tiles;
+                const int kb0 = split * p.k_blocks_per_split;
+                const int kb1 = min(kb0 + p.k_blocks_per_split, p.k_blocks_total);
+                mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * kAccStride;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem_a + stage * A_STAGE_BYTES);
+                    const uint32_t sb = smem_u32(smem_b + stage * B_STAGE_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                        const uint64_t da = make_smem_desc_sw128(sa + k * a_kstep, a_lbo, 1024);
+                        const uint64_t db = make_smem_desc_sw128(sb + k * b_kstep, b_lbo, 1024);
+                        umma_bf16_ss(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[stage]);   // frees the smem slot when these MMAs retire
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&tmem_full[acc]);         // accumulator ready for the epilogue
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else if (warp >= 4) {
+        // ===================== epilogue =====================
+        const int ew = warp - 4;
+        const int quarter = warp & 3;           // TMEM lane quarter this warp may access
+        const int half = ew >> 2;               // which half of the tile's columns
+        const int cols_per_warp = block_n >> 1; // multiple of 32
+        const bool vec_ok = ((p.ldd & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.d) & 15) == 0) &&
+                            (!p.residual || (((p.ldr & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.residual) & 15) == 0))) &&
+                            (!p.preact || (((p.ldp & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.preact) & 15) == 0))) &&
+                            (!p.gate || (((p.ldg & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.gate) & 15) == 0)));
+        uint32_t acc = 0, acc_phase = 0;
+        for (int u = blockIdx.x; u < units; u += gridDim.x) {
+            const int split = u / tiles;
+            const int t = u - split * tiles;
+            const int m0 = (t / p.num_n_tiles) * BLOCK_M;
+            const int n0 = (t % p.num_n_tiles) * block_n;
+            mbar_wait(&tmem_full[acc], acc_phase);
+            tc_fence_after();
+            const int64_t row = (int64_t)m0 + quarter * 32 + lane;
+            const bool row_ok = row < p.M;
+            const uint32_t taddr0 = tmem_base + acc * kAccStride + ((uint32_t)(quarter * 32) << 16) +
+                                    (uint32_t)(half * cols_per_warp);
+            const int nchunks = cols_per_warp >> 5;
+            for (int c = 0; c < nchunks; ++c) {
+                uint32_t r[32];
+                __syncwarp();   // tcgen05.ld is .sync.aligned: reconverge after the predicated body below
+                tmem_ld_32x32b_x32(taddr0 + c * 32, r);
+                tmem_ld_wait();
+                if (c == nchunks - 1) {
+                    // all TMEM reads of this accumulator stage are done: hand it back to the MMA warp
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+                }
+                const int64_t col0 = (int64_t)n0 + half * cols_per_warp + c * 32;
+                if (row_ok && col0 < p.N) {
+                float v[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+                const bool full = (col0 + 32 <= p.N) && vec_ok;
+                if (p.bias) {
+                    if (col0 + 32 <= p.N) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + col0 + j);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (col0 + j < p.N) v[j] += __ldg(p.bias + col0 + j);
+                    }
+                }
+                if (full) {
+                    if (p.preact) {
+                        __nv_bfloat16* dst = p.preact + row * p.ldp + col0;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            uint4 o;
+                            o.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]);
+                            o.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
+                            o.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]);
+                            o.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+                            stg128(dst + q * 8, o);
+                        }
+                    }
+                    if (p.act) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], p.act);
+                    }
+                    if (p.gate) {
+                        const __nv_bfloat16* g = p.gate + row * p.ldg + col0;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            uint4 gi = ldg128(g + q * 8);
+                            const uint32_t gw[4] = {gi.x, gi.y, gi.z, gi.w};
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                float2 f = unpack_bf16x2(gw[e]);
+                                v[q * 8 + e * 2 + 0] *= apply_gate(f.x, p.gate_kind);
+                                v[q * 8 + e * 2 + 1] *= apply_gate(f.y, p.gate_kind);
+                            }
+                        }
+                    }
+                    if (p.residual) {
+                        const __nv_bfloat16* rs = p.residual + row * p.ldr + col0;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            uint4 ri = ldg128(rs + q * 8);
+                            const uint32_t rw[4] = {ri.x, ri.y, ri.z, ri.w};
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                float2 f = unpack_bf16x2(rw[e]);
+                                v[q * 8 + e * 2 + 0] += f.x;
+                                v[q * 8 + e * 2 + 1] += f.y;
+                            }
+                        }
+                    }
+                    if (p.d_f32) {
+                        float* dst = reinterpret_cast<float*>(p.d) + row * p.ldd + col0;
+                        if (p.accumulate) {
+#pragma unroll
+                            for (int q = 0; q < 8; ++q)
+                                red_add_f32x4(dst + q * 4, v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+                        } else {
+#pragma unroll
+                            for (int q = 0; q < 8; ++q)
+                                *reinterpret_cast<float4*>(dst + q * 4) =
+                                    make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+                        }
+                    } else {
+                        __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.d) + row * p.ldd + col0;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            uint4 o;
+                            o.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]);
+                            o.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
+                            o.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]);
+                            o.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+                            stg128(dst + q * 8, o);
+                        }
+                    }
+                } else {
+                    // ragged tail / unaligned leading dimension: scalar path
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const int64_t col = col0 + j;
+                        if (col >= p.N) continue;
+                        float x = v[j];
+                        if (p.preact) p.preact[row * p.ldp + col] = __float2bfloat16(x);
+                        if (p.act) x = apply_act(x, p.act);
+                        if (p.gate) x *= apply_gate(__bfloat162float(p.gate[row * p.ldg + col]), p.gate_kind);
+                        if (p.residual) x += __bfloat162float(p.residual[row * p.ldr + col]);
+                        if (p.d_f32) {
+                            float* dst = reinterpret_cast<float*>(p.d) + row * p.ldd + col;
+                            if (p.accumulate) atomicAdd(dst, x);
+                            else *dst = x;
+                        } else {
+                            reinterpret_cast<__nv_bfloat16*>(p.d)[row * p.ldd + col] = __float2bfloat16(x);
+                        }
+                    }
+                }
+                }   // row_ok && col0 < N
+            }
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ----------------------------------------------------------------------------
+// host side
+// ----------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* sym = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(sym);
+    });
+    return fn;
+}
+
+// 2-D bf16 tensor map: `inner` contiguous elements, `outer` rows with `ld` elements between rows.
+static int make_map_2d(CUtensorMap* out, const void* base, int64_t inner, int64_t outer, int64_t ld,
+                       int box_inner, int box_outer) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) { set_last_error("cuTensorMapEncodeTiled not available"); return kErrDriver; }
+    cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_last_error("cuTensorMapEncodeTiled failed (check 16-byte alignment of base and leading dimension)");
+        return kErrDriver;
+    }
+    return kOk;
+}
+
+static int g_num_sms = 0;
+static std::once_flag g_attr_once;
+
+static int pick_block_n(int64_t M, int64_t N, int b_mn, int num_sms) {
+    // minimise (waves * block_n): quantisation-aware choice among the legal UMMA N sizes
+    const int cands[4] = {256, 192, 128, 64};
+    int best = 128;
+    double best_cost = 1e30;
+    const int64_t mt = ceil_div64(M, BLOCK_M);
+    for (int i = 0; i < 4; ++i) {
+        const int bn = cands[i];
+        if (bn > 64 && bn - 64 >= N) continue;   // do not pad N by more than one 64-wide atom
+        const int64_t nt = ceil_div64(N, bn);
+        const int64_t waves = ceil_div64(mt * nt, num_sms);
+        // per-tile cost ~ bn (MMA time) + fixed overhead; narrower tiles are less smem-efficient
+        const double cost = (double)waves * (bn + 24.0);
+        if (cost < best_cost) { best_cost = cost; best = bn; }
+    }
+    (void)b_mn;
+    return best;
+}
+
+}  // namespace gemm
+}  // namespace mgb
+
+using namespace mgb;
+using namespace mgb::gemm;
+
+extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    if (!a || !a->a || !a->b || !a->d) { set_last_error("gemm: null pointer"); return kErrBadShape; }
+    if (a->m <= 0 || a->n <= 0 || a->k <= 0) { set_last_error("gemm: non-positive dimension"); return kErrBadShape; }
+    if (a->m > INT32_MAX - 256 || a->n > INT32_MAX - 256 || a->k > INT32_MAX - 256) {
+        set_last_error("gemm: dimension too large"); return kErrTooLarge;
+    }
+    if ((a->lda & 7) || (a->ldb & 7) || (reinterpret_cast<uintptr_t>(a->a) & 15) ||
+        (reinterpret_cast<uintptr_t>(a->b) & 15)) {
+        set_last_error("gemm: A/B base must be 16-byte aligned and lda/ldb multiples of 8 elements (TMA)");
+        return kErrBadAlign;
+    }
+    if (a->accumulate && !a->d_f32) { set_last_error("gemm: accumulate requires fp32 D"); return kErrBadDtype; }
+    if (a->split_k > 1 && !a->accumulate) { set_last_error("gemm: split_k > 1 requires accumulate"); return kErrUnsupported; }
+
+    std::call_once(g_attr_once, [] {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaFuncSetAttribute(gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    });
+    const int num_sms = g_num_sms > 0 ? g_num_sms : 148;
+
+    Params p{};
+    p.M = a->m; p.N = a->n; p.K = a->k;
+    p.a_mn = a->a_mn_major ? 1 : 0;
+    p.b_mn = a->b_mn_major ? 1 : 0;
+    int bn = a->block_n;
+    if (bn == 0) bn = pick_block_n(a->m, a->n, p.b_mn, num_sms);
+    if (bn != 64 && bn != 128 && bn != 192 && bn != 256) { set_last_error("gemm: block_n must be 64/128/192/256"); return kErrBadShape; }
+    p.block_n = bn;
+    p.num_m_tiles = (int)ceil_div64(a->m, BLOCK_M);
+    p.num_n_tiles = (int)ceil_div64(a->n, bn);
+    p.k_blocks_total = (int)ceil_div64(a->k, BLOCK_K);
+    int split = a->split_k;
+    const int tiles = p.num_m_tiles * p.num_n_tiles;
+    if (split <= 0) {
+        split = 1;
+        if (a->accumulate) {
+            // fill the machine: choose the split whose unit count wastes the least of the last wave,
+            // keeping at least 8 k-blocks per unit
+            const int max_split = p.k_blocks_total / 8 > 0 ? p.k_blocks_total / 8 : 1;
+            double best = 1e30;
+            for (int s = 1; s <= max_split && s <= 64; ++s) {
+                const int64_t units = (int64_t)tiles * s;
+                const int64_t waves = ceil_div64(units, num_sms);
+                const int kbs = (int)ceil_div64(p.k_blocks_total, s);
+                const double cost = (double)waves * (kbs + 6.0);
+                if (cost < best - 1e-9) { best = cost; split = s; }
+            }
+        }
+    }
+    if (split > p.k_blocks_total) split = p.k_blocks_total;
+    p.k_blocks_per_split = (int)ceil_div64(p.k_blocks_total, split);
+    p.split_k = (int)ceil_div64(p.k_blocks_total, p.k_blocks_per_split);   // no empty splits
+    p.d = a->d; p.ldd = a->ldd; p.d_f32 = a->d_f32; p.accumulate = a->accumulate;
+    p.bias = a->bias;
+    p.residual = reinterpret_cast<const __nv_bfloat16*>(a->residual); p.ldr = a->ldr;
+    p.act = a->act;
+    p.preact = reinterpret_cast<__nv_bfloat16*>(a->preact); p.ldp = a->ldp;
+    p.gate = reinterpret_cast<const __nv_bfloat16*>(a->gate); p.ldg = a->ldg; p.gate_kind = a->gate_kind;
+    p.alpha = a->alpha == 0.0f ? 1.0f : a->alpha;
+
+    CUtensorMap ta, tb;
+    int rc;
+    if (!p.a_mn) rc = make_map_2d(&ta, a->a, a->k, a->m, a->lda, BLOCK_K, BLOCK_M);
+    else         rc = make_map_2d(&ta, a->a, a->m, a->k, a->lda, 64, BLOCK_K);
+    if (rc) return rc;
+    if (!p.b_mn) rc = make_map_2d(&tb, a->b, a->k, a->n, a->ldb, BLOCK_K, bn);
+    else         rc = make_map_2d(&tb, a->b, a->n, a->k, a->ldb, 64, BLOCK_K);
+    if (rc) return rc;
+
+    const int64_t units = (int64_t)tiles * p.split_k;
+    const int grid = (int)(units < num_sms ? units : num_sms);
+    gemm_kernel<<<grid, kThreads, SMEM_BYTES, stream>>>(ta, tb, p);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}

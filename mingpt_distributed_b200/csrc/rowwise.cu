@@ -1,0 +1,536 @@
+// HBM-bound row-wise kernels of the training step: LayerNorm fwd/bwd, embedding fwd/bwd,
+// cross-entropy (in place on a logits chunk). Single pass over the data, 16-byte vector accesses,
+// fp32 statistics.
+#include "common.cuh"
+#include "mingpt_b200.h"
+
+namespace mgb {
+
+// =====================================================================================
+// LayerNorm  (nn.LayerNorm: mingpt/model.py:176,178,248)
+// =====================================================================================
+constexpr int LN_WARPS = 8;
+
+// One warp per row; the row lives in registers (MAXCH 16-byte chunks per lane).
+template <int MAXCH>
+__global__ void __launch_bounds__(LN_WARPS * 32)
+ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
+              __nv_bfloat16* __restrict__ y, float* __restrict__ mean, float* __restrict__ rstd, int64_t rows,
+              int cols, float eps) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nch = cols >> 3;
+    const float inv_cols = 1.0f / (float)cols;
+    for (int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp; row < rows; row += (int64_t)gridDim.x * LN_WARPS) {
+        const __nv_bfloat16* xr = x + row * cols;
+        uint4 buf[MAXCH];
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < MAXCH; ++i) {
+            const int ch = lane + 32 * i;
+            if (ch < nch) {
+                buf[i] = ldg128(xr + ch * 8);
+                const uint32_t w[4] = {buf[i].x, buf[i].y, buf[i].z, buf[i].w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) { float2 f = unpack_bf16x2(w[e]); s += f.x + f.y; }
+            }
+        }
+        const float mu = warp_sum(s) * inv_cols;
+        float q = 0.f;
+#pragma unroll
+        for (int i = 0; i < MAXCH; ++i) {
+            const int ch = lane + 32 * i;
+            if (ch < nch) {
+                const uint32_t w[4] = {buf[i].x, buf[i].y, buf[i].z, buf[i].w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    float2 f = unpack_bf16x2(w[e]);
+                    q += (f.x - mu) * (f.x - mu) + (f.y - mu) * (f.y - mu);
+                }
+            }
+        }
+        const float rs = rsqrtf(warp_sum(q) * inv_cols + eps);
+        if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+        __nv_bfloat16* yr = y + row * cols;
+#pragma unroll
+        for (int i = 0; i < MAXCH; ++i) {
+            const int ch = lane + 32 * i;
+            if (ch < nch) {
+                const uint32_t w[4] = {buf[i].x, buf[i].y, buf[i].z, buf[i].w};
+                const float4 g0 = *reinterpret_cast<const float4*>(gamma + ch * 8);
+                const float4 g1 = *reinterpret_cast<const float4*>(gamma + ch * 8 + 4);
+                const float4 b0 = *reinterpret_cast<const float4*>(beta + ch * 8);
+                const float4 b1 = *reinterpret_cast<const float4*>(beta + ch * 8 + 4);
+                const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+                const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+                uint32_t o[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    float2 f = unpack_bf16x2(w[e]);
+                    o[e] = pack_bf16x2((f.x - mu) * rs * gg[2 * e] + bb[2 * e],
+                                       (f.y - mu) * rs * gg[2 * e + 1] + bb[2 * e + 1]);
+                }
+                stg128(yr + ch * 8, make_uint4(o[0], o[1], o[2], o[3]));
+            }
+        }
+    }
+}
+
+// any cols (scalar accesses): ragged widths such as C = 50
+__global__ void __launch_bounds__(LN_WARPS * 32)
+ln_fwd_generic_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+                      const float* __restrict__ beta, __nv_bfloat16* __restrict__ y, float* __restrict__ mean,
+                      float* __restrict__ rstd, int64_t rows, int cols, float eps) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp; row < rows; row += (int64_t)gridDim.x * LN_WARPS) {
+        const __nv_bfloat16* xr = x + row * cols;
+        float s = 0.f;
+        for (int c = lane; c < cols; c += 32) s += __bfloat162float(xr[c]);
+        const float mu = warp_sum(s) / (float)cols;
+        float q = 0.f;
+        for (int c = lane; c < cols; c += 32) { float d = __bfloat162float(xr[c]) - mu; q += d * d; }
+        const float rs = rsqrtf(warp_sum(q) / (float)cols + eps);
+        if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+        for (int c = lane; c < cols; c += 32)
+            y[row * cols + c] = __float2bfloat16((__bfloat162float(xr[c]) - mu) * rs * gamma[c] + beta[c]);
+    }
+}
+
+template <int MAXCH>
+__global__ void __launch_bounds__(LN_WARPS * 32)
+ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+              const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd,
+              const __nv_bfloat16* dres, __nv_bfloat16* dx, float* __restrict__ dgamma, float* __restrict__ dbeta,
+              int64_t rows, int cols) {
+    extern __shared__ float ln_smem[];   // [2][cols] CTA-level dgamma / dbeta accumulators
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nch = cols >> 3;
+    const float inv_cols = 1.0f / (float)cols;
+    for (int c = threadIdx.x; c < 2 * cols; c += blockDim.x) ln_smem[c] = 0.f;
+    __syncthreads();
+
+    float gam[MAXCH][8], dg[MAXCH][8], db[MAXCH][8];
+#pragma unroll
+    for (int i = 0; i < MAXCH; ++i) {
+        const int ch = lane + 32 * i;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            gam[i][e] = (ch < nch) ? gamma[ch * 8 + e] : 0.f;
+            dg[i][e] = 0.f;
+            db[i][e] = 0.f;
+        }
+    }
+    for (int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp; row < rows; row += (int64_t)gridDim.x * LN_WARPS) {
+        const float mu = mean[row], rs = rstd[row];
+        float xh[MAXCH][8], gdy[MAXCH][8];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < MAXCH; ++i) {
+            const int ch = lane + 32 * i;
+            if (ch < nch) {
+                const uint4 vx = ldg128(x + row * cols + ch * 8);
+                const uint4 vd = ldg128(dy + row * cols + ch * 8);
+                const uint32_t wx[4] = {vx.x, vx.y, vx.z, vx.w};
+                const uint32_t wd[4] = {vd.x, vd.y, vd.z, vd.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float2 fx = unpack_bf16x2(wx[e]);
+                    const float2 fd = unpack_bf16x2(wd[e]);
+                    const float h0 = (fx.x - mu) * rs, h1 = (fx.y - mu) * rs;
+                    xh[i][2 * e] = h0; xh[i][2 * e + 1] = h1;
+                    dg[i][2 * e] += fd.x * h0; dg[i][2 * e + 1] += fd.y * h1;
+                    db[i][2 * e] += fd.x;      db[i][2 * e + 1] += fd.y;
+                    const float g0 = fd.x * gam[i][2 * e], g1 = fd.y * gam[i][2 * e + 1];
+                    gdy[i][2 * e] = g0; gdy[i][2 * e + 1] = g1;
+                    s1 += g0 + g1;
+                    s2 += g0 * h0 + g1 * h1;
+                }
+            }
+        }
+        const float m1 = warp_sum(s1) * inv_cols;
+        const float m2 = warp_sum(s2) * inv_cols;
+#pragma unroll
+        for (int i = 0; i < MAXCH; ++i) {
+            const int ch = lane + 32 * i;
+            if (ch < nch) {
+                float r[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) r[e] = rs * (gdy[i][e] - m1 - xh[i][e] * m2);
+                if (dres) {
+                    const uint4 vr = ldg128(dres + row * cols + ch * 8);
+                    const uint32_t wr[4] = {vr.x, vr.y, vr.z, vr.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float2 f = unpack_bf16x2(wr[e]);
+                        r[2 * e] += f.x; r[2 * e + 1] += f.y;
+                    }
+                }
+                stg128(dx + row * cols + ch * 8,
+                       make_uint4(pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]),
+                                  pack_bf16x2(r[6], r[7])));
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < MAXCH; ++i) {
+        const int ch = lane + 32 * i;
+        if (ch < nch) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                atomicAdd(&ln_smem[ch * 8 + e], dg[i][e]);
+                atomicAdd(&ln_smem[cols + ch * 8 + e], db[i][e]);
+            }
+        }
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < cols; c += blockDim.x) {
+        atomicAdd(dgamma + c, ln_smem[c]);
+        atomicAdd(dbeta + c, ln_smem[cols + c]);
+    }
+}
+
+__global__ void __launch_bounds__(LN_WARPS * 32)
+ln_bwd_generic_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                      const float* __restrict__ gamma, const float* __restrict__ mean,
+                      const float* __restrict__ rstd, const __nv_bfloat16* dres, __nv_bfloat16* dx,
+                      float* __restrict__ dgamma, float* __restrict__ dbeta, int64_t rows, int cols) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp; row < rows; row += (int64_t)gridDim.x * LN_WARPS) {
+        const float mu = mean[row], rs = rstd[row];
+        float s1 = 0.f, s2 = 0.f;
+        for (int c = lane; c < cols; c += 32) {
+            const float h = (__bfloat162float(x[row * cols + c]) - mu) * rs;
+            const float g = __bfloat162float(dy[row * cols + c]) * gamma[c];
+            s1 += g; s2 += g * h;
+        }
+        const float m1 = warp_sum(s1) / (float)cols, m2 = warp_sum(s2) / (float)cols;
+        for (int c = lane; c < cols; c += 32) {
+            const float h = (__bfloat162float(x[row * cols + c]) - mu) * rs;
+            const float d = __bfloat162float(dy[row * cols + c]);
+            float r = rs * (d * gamma[c] - m1 - h * m2);
+            if (dres) r += __bfloat162float(dres[row * cols + c]);
+            dx[row * cols + c] = __float2bfloat16(r);
+            atomicAdd(dgamma + c, d * h);
+            atomicAdd(dbeta + c, d);
+        }
+    }
+}
+
+// =====================================================================================
+// Embedding  (GPTEmbedding.forward, mingpt/model.py:222-231)
+// =====================================================================================
+__global__ void __launch_bounds__(256)
+embedding_fwd_kernel(const int64_t* __restrict__ idx, const __nv_bfloat16* __restrict__ wte,
+                     const __nv_bfloat16* __restrict__ wpe, __nv_bfloat16* __restrict__ out, int64_t BT, int64_t T,
+                     int C, int64_t vocab, int32_t* err_flag) {
+    const int nch = C >> 3;
+    const int64_t total = BT * nch;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = i / nch;
+        const int ch = (int)(i - row * nch);
+        const int64_t t = row % T;
+        const int64_t tok = idx[row];
+        uint4 o = make_uint4(0, 0, 0, 0);
+        if (tok >= 0 && tok < vocab) {
+            const uint4 a = ldg128(wte + tok * C + ch * 8);
+            const uint4 b = ldg128(wpe + t * C + ch * 8);
+            const uint32_t wa[4] = {a.x, a.y, a.z, a.w}, wb[4] = {b.x, b.y, b.z, b.w};
+            uint32_t r[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 fa = unpack_bf16x2(wa[e]), fb = unpack_bf16x2(wb[e]);
+                r[e] = pack_bf16x2(fa.x + fb.x, fa.y + fb.y);
+            }
+            o = make_uint4(r[0], r[1], r[2], r[3]);
+        } else if (err_flag && ch == 0) {
+            atomicExch(err_flag, 1);
+        }
+        stg128(out + row * C + ch * 8, o);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+embedding_fwd_scalar_kernel(const int64_t* __restrict__ idx, const __nv_bfloat16* __restrict__ wte,
+                            const __nv_bfloat16* __restrict__ wpe, __nv_bfloat16* __restrict__ out, int64_t BT,
+                            int64_t T, int C, int64_t vocab, int32_t* err_flag) {
+    const int64_t total = BT * C;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = i / C;
+        const int c = (int)(i - row * C);
+        const int64_t tok = idx[row];
+        float v = 0.f;
+        if (tok >= 0 && tok < vocab) v = __bfloat162float(wte[tok * C + c]) + __bfloat162float(wpe[(row % T) * C + c]);
+        else if (err_flag && c == 0) atomicExch(err_flag, 1);
+        out[i] = __float2bfloat16(v);
+    }
+}
+
+// dwte: one thread per (row, 4 columns), fp32 vector atomics into the touched table row.
+__global__ void __launch_bounds__(256)
+embedding_bwd_wte_kernel(const int64_t* __restrict__ idx, const __nv_bfloat16* __restrict__ dx,
+                         float* __restrict__ dwte, int64_t BT, int C, int64_t vocab) {
+    const int64_t total = BT * C;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = i / C;
+        const int c = (int)(i - row * C);
+        const int64_t tok = idx[row];
+        if (tok >= 0 && tok < vocab) atomicAdd(dwte + tok * C + c, __bfloat162float(dx[i]));
+    }
+}
+// dwpe[t, c] += sum_b dx[b, t, c]: no atomics needed inside one launch, but the buffer accumulates
+__global__ void __launch_bounds__(256)
+embedding_bwd_wpe_kernel(const __nv_bfloat16* __restrict__ dx, float* __restrict__ dwpe, int64_t B, int64_t T,
+                         int C) {
+    const int64_t total = T * C;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int64_t b = 0; b < B; ++b) s += __bfloat162float(dx[b * total + i]);
+        dwpe[i] += s;
+    }
+}
+
+// =====================================================================================
+// Cross entropy, in place  (F.cross_entropy ignore_index=-1: mingpt/model.py:316-318)
+// =====================================================================================
+constexpr int CE_THREADS = 512;
+
+__device__ __forceinline__ float block_reduce_max(float v, float* sh) {
+    v = warp_max(v);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float r = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : -INFINITY;
+    if (threadIdx.x < 32) { r = warp_max(r); if (threadIdx.x == 0) sh[0] = r; }
+    __syncthreads();
+    r = sh[0];
+    __syncthreads();
+    return r;
+}
+__device__ __forceinline__ float block_reduce_sum(float v, float* sh) {
+    v = warp_sum(v);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float r = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0.f;
+    if (threadIdx.x < 32) { r = warp_sum(r); if (threadIdx.x == 0) sh[0] = r; }
+    __syncthreads();
+    r = sh[0];
+    __syncthreads();
+    return r;
+}
+
+__global__ void __launch_bounds__(CE_THREADS)
+cross_entropy_kernel(__nv_bfloat16* logits, int64_t ld, const int64_t* __restrict__ targets,
+                     float* __restrict__ row_loss, const int32_t* __restrict__ n_valid, int64_t vocab,
+                     float grad_scale, int write_grad, int32_t* err_flag) {
+    __shared__ float sh[32];
+    const int64_t row = blockIdx.x;
+    __nv_bfloat16* lr = logits + row * ld;
+    int64_t tgt = targets[row];
+    bool ignored = (tgt == -1);
+    if (!ignored && (tgt < 0 || tgt >= vocab)) {
+        if (err_flag && threadIdx.x == 0) atomicExch(err_flag, 2);
+        ignored = true;
+    }
+    const bool vec = ((ld & 7) == 0) && ((reinterpret_cast<uintptr_t>(logits) & 15) == 0);
+    const int64_t vmain = vec ? (vocab & ~int64_t(7)) : 0;
+    if (ignored) {
+        if (threadIdx.x == 0) row_loss[row] = 0.f;
+        if (write_grad) {
+            for (int64_t c = (int64_t)threadIdx.x * 8; c < vmain; c += (int64_t)blockDim.x * 8)
+                stg128(lr + c, make_uint4(0, 0, 0, 0));
+            for (int64_t c = vmain + threadIdx.x; c < ld; c += blockDim.x) lr[c] = __float2bfloat16(0.f);
+        }
+        return;
+    }
+    // pass 1: online max / sum-exp
+    float m = -INFINITY, s = 0.f;
+    for (int64_t c = (int64_t)threadIdx.x * 8; c < vmain; c += (int64_t)blockDim.x * 8) {
+        const uint4 v = ldg128(lr + c);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        float f[8];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { float2 t = unpack_bf16x2(w[e]); f[2 * e] = t.x; f[2 * e + 1] = t.y; }
+        float lm = f[0];
+#pragma unroll
+        for (int e = 1; e < 8; ++e) lm = fmaxf(lm, f[e]);
+        if (lm > m) { s *= __expf(m - lm); m = lm; }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) s += __expf(f[e] - m);
+    }
+    for (int64_t c = vmain + threadIdx.x; c < vocab; c += blockDim.x) {
+        const float f = __bfloat162float(lr[c]);
+        if (f > m) { s *= __expf(m - f); m = f; }
+        s += __expf(f - m);
+    }
+    const float gm = block_reduce_max(m, sh);
+    s = (m == -INFINITY) ? 0.f : s * __expf(m - gm);
+    const float gs = block_reduce_sum(s, sh);
+    const float lse = gm + logf(gs);
+    if (threadIdx.x == 0) row_loss[row] = lse - __bfloat162float(lr[tgt]);
+    if (!write_grad) return;
+    __syncthreads();   // the target logit was read above; now the row may be overwritten
+    const int nv = max(*n_valid, 1);
+    const float sc = grad_scale / (float)nv;
+    for (int64_t c = (int64_t)threadIdx.x * 8; c < vmain; c += (int64_t)blockDim.x * 8) {
+        const uint4 v = ldg128(lr + c);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        float f[8];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { float2 t = unpack_bf16x2(w[e]); f[2 * e] = t.x; f[2 * e + 1] = t.y; }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = (__expf(f[e] - lse) - ((c + e) == tgt ? 1.f : 0.f)) * sc;
+        stg128(lr + c, make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
+                                  pack_bf16x2(f[6], f[7])));
+    }
+    for (int64_t c = vmain + threadIdx.x; c < ld; c += blockDim.x) {
+        float g = 0.f;
+        if (c < vocab) g = (__expf(__bfloat162float(lr[c]) - lse) - (c == tgt ? 1.f : 0.f)) * sc;
+        lr[c] = __float2bfloat16(g);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+count_valid_kernel(const int64_t* __restrict__ targets, int64_t n, int32_t* out) {
+    __shared__ int sh[8];
+    int c = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        c += (targets[i] != -1) ? 1 : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int w = 0; w < 8; ++w) t += sh[w];
+        atomicAdd(out, t);
+    }
+}
+
+__global__ void __launch_bounds__(1024)
+loss_finalize_kernel(const float* __restrict__ row_loss, int64_t rows, const int32_t* __restrict__ n_valid,
+                     float* loss) {
+    __shared__ float sh[32];
+    float s = 0.f;
+    for (int64_t i = threadIdx.x; i < rows; i += blockDim.x) s += row_loss[i];
+    const float t = block_reduce_sum(s, sh);
+    if (threadIdx.x == 0) *loss = t / (float)max(*n_valid, 1);
+}
+
+}  // namespace mgb
+
+using namespace mgb;
+
+static int grid_for(int64_t work_items, int per_block, int max_blocks) {
+    int64_t g = (work_items + per_block - 1) / per_block;
+    if (g < 1) g = 1;
+    if (g > max_blocks) g = max_blocks;
+    return (int)g;
+}
+
+extern "C" int mgb_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean,
+                                 float* rstd, int64_t rows, int32_t cols, float eps, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    if (rows < 0 || cols <= 0) { set_last_error("layernorm_fwd: bad shape"); return kErrBadShape; }
+    if (rows == 0) return kOk;
+    const int grid = grid_for(rows, LN_WARPS, num_sms() * 8);
+    auto X = (const __nv_bfloat16*)x; auto Y = (__nv_bfloat16*)y;
+    const bool vec = (cols % 8 == 0) && cols <= 2048 && ((uintptr_t)x % 16 == 0) && ((uintptr_t)y % 16 == 0) &&
+                     ((uintptr_t)gamma % 16 == 0) && ((uintptr_t)beta % 16 == 0);
+    if (!vec) ln_fwd_generic_kernel<<<grid, LN_WARPS * 32, 0, s>>>(X, gamma, beta, Y, mean, rstd, rows, cols, eps);
+    else if (cols <= 256) ln_fwd_kernel<1><<<grid, LN_WARPS * 32, 0, s>>>(X, gamma, beta, Y, mean, rstd, rows, cols, eps);
+    else if (cols <= 512) ln_fwd_kernel<2><<<grid, LN_WARPS * 32, 0, s>>>(X, gamma, beta, Y, mean, rstd, rows, cols, eps);
+    else if (cols <= 1024) ln_fwd_kernel<4><<<grid, LN_WARPS * 32, 0, s>>>(X, gamma, beta, Y, mean, rstd, rows, cols, eps);
+    else ln_fwd_kernel<8><<<grid, LN_WARPS * 32, 0, s>>>(X, gamma, beta, Y, mean, rstd, rows, cols, eps);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+extern "C" int mgb_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean,
+                                 const float* rstd, const void* dres, void* dx, float* dgamma, float* dbeta,
+                                 int64_t rows, int32_t cols, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    if (rows < 0 || cols <= 0) { set_last_error("layernorm_bwd: bad shape"); return kErrBadShape; }
+    if (rows == 0) return kOk;
+    auto DY = (const __nv_bfloat16*)dy; auto X = (const __nv_bfloat16*)x;
+    auto DR = (const __nv_bfloat16*)dres; auto DX = (__nv_bfloat16*)dx;
+    const bool vec = (cols % 8 == 0) && cols <= 2048 && ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0) &&
+                     ((uintptr_t)dx % 16 == 0) && (!dres || (uintptr_t)dres % 16 == 0);
+    // persistent: each CTA owns register accumulators for dgamma/dbeta, flushed once
+    const int grid = grid_for(rows, LN_WARPS * 4, num_sms() * 2);
+    const size_t smem = (size_t)2 * cols * sizeof(float);
+    if (!vec) ln_bwd_generic_kernel<<<grid, LN_WARPS * 32, 0, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, dbeta, rows, cols);
+    else if (cols <= 256) ln_bwd_kernel<1><<<grid, LN_WARPS * 32, smem, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, dbeta, rows, cols);
+    else if (cols <= 512) ln_bwd_kernel<2><<<grid, LN_WARPS * 32, smem, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, dbeta, rows, cols);
+    else if (cols <= 1024) ln_bwd_kernel<4><<<grid, LN_WARPS * 32, smem, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, dbeta, rows, cols);
+    else ln_bwd_kernel<8><<<grid, LN_WARPS * 32, smem, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, dbeta, rows, cols);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+extern "C" int mgb_embedding_fwd(const int64_t* idx, const void* wte, const void* wpe, void* out, int64_t B,
+                                 int64_t T, int32_t C, int64_t vocab, int32_t* err_flag, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    if (B < 0 || T < 0 || C <= 0 || vocab <= 0) { set_last_error("embedding_fwd: bad shape"); return kErrBadShape; }
+    if (B * T == 0) return kOk;
+    const bool vec = (C % 8 == 0) && ((uintptr_t)wte % 16 == 0) && ((uintptr_t)wpe % 16 == 0) && ((uintptr_t)out % 16 == 0);
+    if (vec) {
+        const int grid = grid_for(B * T * (C / 8), 256, num_sms() * 16);
+        embedding_fwd_kernel<<<grid, 256, 0, s>>>(idx, (const __nv_bfloat16*)wte, (const __nv_bfloat16*)wpe,
+                                                  (__nv_bfloat16*)out, B * T, T, C, vocab, err_flag);
+    } else {
+        const int grid = grid_for(B * T * C, 256, num_sms() * 16);
+        embedding_fwd_scalar_kernel<<<grid, 256, 0, s>>>(idx, (const __nv_bfloat16*)wte, (const __nv_bfloat16*)wpe,
+                                                         (__nv_bfloat16*)out, B * T, T, C, vocab, err_flag);
+    }
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+extern "C" int mgb_embedding_bwd(const int64_t* idx, const void* dx, float* dwte, float* dwpe, int64_t B, int64_t T,
+                                 int32_t C, int64_t vocab, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    if (B < 0 || T < 0 || C <= 0 || vocab <= 0) { set_last_error("embedding_bwd: bad shape"); return kErrBadShape; }
+    if (B * T == 0) return kOk;
+    embedding_bwd_wte_kernel<<<grid_for(B * T * C, 256, num_sms() * 16), 256, 0, s>>>(
+        idx, (const __nv_bfloat16*)dx, dwte, B * T, C, vocab);
+    embedding_bwd_wpe_kernel<<<grid_for(T * C, 256, num_sms() * 16), 256, 0, s>>>((const __nv_bfloat16*)dx, dwpe, B, T, C);
+    count_launch(2);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+extern "C" int mgb_cross_entropy_fwd_bwd(void* logits, int64_t ld, const int64_t* targets, float* row_loss,
+                                         const int32_t* n_valid, int64_t rows, int64_t vocab, float grad_scale,
+                                         int32_t write_grad, int32_t* err_flag, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    if (rows < 0 || vocab <= 0 || ld < vocab) { set_last_error("cross_entropy: bad shape"); return kErrBadShape; }
+    if (rows > INT32_MAX) { set_last_error("cross_entropy: too many rows"); return kErrTooLarge; }
+    if (rows == 0) return kOk;
+    cross_entropy_kernel<<<(int)rows, CE_THREADS, 0, s>>>((__nv_bfloat16*)logits, ld, targets, row_loss, n_valid, vocab,
+                                                         grad_scale, write_grad, err_flag);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+extern "C" int mgb_count_valid_targets(const int64_t* targets, int64_t n, int32_t* n_valid, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    if (n < 0) { set_last_error("count_valid: bad shape"); return kErrBadShape; }
+    cudaMemsetAsync(n_valid, 0, sizeof(int32_t), s);
+    if (n == 0) return kOk;
+    count_valid_kernel<<<grid_for(n, 256 * 8, num_sms() * 4), 256, 0, s>>>(targets, n, n_valid);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+extern "C" int mgb_loss_finalize(const float* row_loss, int64_t rows, const int32_t* n_valid, float* loss,
+                                 mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    if (rows < 0) { set_last_error("loss_finalize: bad shape"); return kErrBadShape; }
+    loss_finalize_kernel<<<1, 1024, 0, s>>>(row_loss, rows, n_valid, loss);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
