@@ -147,6 +147,10 @@ int mgb_cast_f32_to_bf16(const float* src, void* dst, int64_t n, mgb_stream_t st
 int mgb_cast_bf16_to_f32(const void* src, float* dst, int64_t n, mgb_stream_t stream);
 /* dst += alpha * src (fp32) */
 int mgb_axpy_f32(float* dst, const float* src, float alpha, int64_t n, mgb_stream_t stream);
+/* Same with alpha read from DEVICE memory, and x *= *alpha for bf16: they apply the upstream gradient of the
+ * scalar loss (loss.backward() at mingpt/trainer.py:127 hands it over as a device tensor) without a host sync. */
+int mgb_axpy_f32_dev(float* dst, const float* src, const float* alpha, int64_t n, mgb_stream_t stream);
+int mgb_scale_bf16_dev(void* x, int64_t n, const float* alpha, mgb_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------------
  * Gradient clipping + AdamW.

@@ -162,6 +162,37 @@ axpy_kernel(float* __restrict__ dst, const float* __restrict__ src, float alpha,
         for (int64_t i = (n4 << 2) + threadIdx.x; i < n; i += blockDim.x) dst[i] += alpha * src[i];
 }
 
+__global__ void __launch_bounds__(256)
+axpy_dev_kernel(float* __restrict__ dst, const float* __restrict__ src, const float* __restrict__ alpha_p, int64_t n) {
+    const float alpha = *alpha_p;
+    const int64_t n4 = n >> 2;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        float4 d = reinterpret_cast<float4*>(dst)[i];
+        const float4 s = reinterpret_cast<const float4*>(src)[i];
+        d.x += alpha * s.x; d.y += alpha * s.y; d.z += alpha * s.z; d.w += alpha * s.w;
+        reinterpret_cast<float4*>(dst)[i] = d;
+    }
+    if (blockIdx.x == 0)
+        for (int64_t i = (n4 << 2) + threadIdx.x; i < n; i += blockDim.x) dst[i] += alpha * src[i];
+}
+__global__ void __launch_bounds__(256)
+scale_bf16_dev_kernel(__nv_bfloat16* __restrict__ x, int64_t n, const float* __restrict__ alpha_p) {
+    const float alpha = *alpha_p;
+    if (alpha == 1.0f) return;
+    const int64_t n8 = n >> 3;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+        const uint4 v = ldg128(x + i * 8);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        uint32_t o[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { const float2 f = unpack_bf16x2(w[e]); o[e] = pack_bf16x2(f.x * alpha, f.y * alpha); }
+        stg128(x + i * 8, make_uint4(o[0], o[1], o[2], o[3]));
+    }
+    if (blockIdx.x == 0)
+        for (int64_t i = (n8 << 3) + threadIdx.x; i < n; i += blockDim.x)
+            x[i] = __float2bfloat16(__bfloat162float(x[i]) * alpha);
+}
+
 // ---------------------------------------------------------------------------
 // bias gradient: out[c] += sum_r x[r, c]
 // block = 8 warps; a warp covers 256 columns (8 per lane), warps take interleaved rows of a 256-row slab
@@ -320,6 +351,27 @@ extern "C" int mgb_axpy_f32(float* dst, const float* src, float alpha, int64_t n
     if (((uintptr_t)src % 16) || ((uintptr_t)dst % 16)) { set_last_error("axpy: pointers must be 16-byte aligned"); return kErrBadAlign; }
     if (n == 0) return kOk;
     axpy_kernel<<<grid_for(n, 256 * 8, num_sms() * 8), 256, 0, s>>>(dst, src, alpha, n);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+extern "C" int mgb_axpy_f32_dev(float* dst, const float* src, const float* alpha, int64_t n, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    if (n < 0 || !alpha) { set_last_error("axpy_dev: bad arguments"); return kErrBadShape; }
+    if (((uintptr_t)src % 16) || ((uintptr_t)dst % 16)) { set_last_error("axpy_dev: pointers must be 16-byte aligned"); return kErrBadAlign; }
+    if (n == 0) return kOk;
+    axpy_dev_kernel<<<grid_for(n, 256 * 8, num_sms() * 8), 256, 0, s>>>(dst, src, alpha, n);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+extern "C" int mgb_scale_bf16_dev(void* x, int64_t n, const float* alpha, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    if (n < 0 || !alpha) { set_last_error("scale_dev: bad arguments"); return kErrBadShape; }
+    if ((uintptr_t)x % 16) { set_last_error("scale_dev: x must be 16-byte aligned"); return kErrBadAlign; }
+    if (n == 0) return kOk;
+    scale_bf16_dev_kernel<<<grid_for(n, 256 * 8, num_sms() * 8), 256, 0, s>>>((__nv_bfloat16*)x, n, alpha);
     count_launch(1);
     MGB_CHECK_LAUNCH();
     return kOk;

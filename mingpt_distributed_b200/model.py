@@ -1,0 +1,753 @@
+"""GPT language model with the reference's API (mingpt/model.py) and a B200-native training step.
+
+Public surface kept from the reference (file:line = /root/reference/mingpt/model.py):
+  GPTConfig :38-51, OptimizerConfig :54-59, create_optimizer :62-122, print_model_size :21-33,
+  GPT.__init__ :237-259, GPT.forward(inputs, targets=None) -> (logits, loss) :309-320, GPT.generate :322-356
+and the spellings its README (README.md:29-54) and the task's north_star use:
+  GPT.get_default_config(), GPT(config), model.configure_optimizers(train_config).
+
+Two module graphs share one set of kernels ("fidelity decision"):
+  variant="reference"  the graph mingpt/model.py really builds: float tril mask ADDED to the scores
+                       (nothing is masked), MHA out_proj followed by a second c_proj, MLP = Linear ->
+                       Linear -> GELU(erf); parameter names and initialisation identical to the reference,
+                       so its snapshots load and `torch.manual_seed(s); GPT(cfg)` gives the same weights.
+  variant="mingpt"     the graph the README / north_star describe: causal attention, c_attn / c_proj,
+                       c_fc -> NewGELU(tanh) -> c_proj, lm_head; parameter names of upstream minGPT.
+
+nn.Parameters stay ordinary fp32 leaves (state_dict, parameters(), foreign optimizers all work) but live
+as views of ONE flat fp32 buffer, with a flat bf16 shadow for the GEMM operands and a flat fp32 gradient
+buffer the backward pass accumulates into -- the layout the fused AdamW and the bucketed all-reduce use.
+The forward/backward themselves are hand-scheduled launches of the C-ABI kernels (ops.py); there is no
+PyTorch-math path on the device side.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Callable, Dict, List, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from . import ops
+
+PRESETS = {
+    # names follow the huggingface naming conventions (mingpt/model.py:269-294)
+    "openai-gpt": dict(n_layer=12, n_head=12, n_embed=768),
+    "gpt2": dict(n_layer=12, n_head=12, n_embed=768),
+    "gpt2-medium": dict(n_layer=24, n_head=16, n_embed=1024),
+    "gpt2-large": dict(n_layer=36, n_head=20, n_embed=1280),
+    "gpt2-xl": dict(n_layer=48, n_head=25, n_embed=1600),
+    "gopher-44m": dict(n_layer=8, n_head=16, n_embed=512),
+    "gpt-mini": dict(n_layer=6, n_head=6, n_embed=192),
+    "gpt-micro": dict(n_layer=4, n_head=4, n_embed=128),
+    "gpt-nano": dict(n_layer=3, n_head=3, n_embed=48),
+}
+
+
+def print_model_size(model: nn.Module):
+    """params + buffers in MB (mingpt/model.py:21-33)"""
+    size = sum(p.numel() * p.element_size() for p in model.parameters())
+    size += sum(b.numel() * b.element_size() for b in model.buffers())
+    print(f"Model size (MB): {size / 1024**2:.3f}")
+
+
+@dataclass
+class GPTConfig:
+    """mingpt/model.py:38-51. `n_embd` is accepted as an alias of `n_embed` (the reference's YAML and preset
+    table spell it that way, mingpt/gpt2_config.yaml:4 / model.py:273-293, and crash on it: SURVEY D4, D6)."""
+    model_type: Optional[str] = "gpt2"
+    n_layer: Optional[int] = None
+    n_head: Optional[int] = None
+    n_embed: Optional[int] = None
+    vocab_size: int = 50257
+    block_size: int = 1024
+    embed_drop: float = 0.1
+    resid_drop: float = 0.1
+    attn_drop: float = 0.1
+    n_embd: Optional[int] = None
+    variant: str = "mingpt"
+
+    def __post_init__(self):
+        if self.n_embed is None and self.n_embd is not None:
+            self.n_embed = self.n_embd
+        self.n_embd = self.n_embed
+
+
+@dataclass
+class OptimizerConfig:
+    """mingpt/model.py:54-59"""
+    learning_rate: float = 3e-4
+    weight_decay: float = 0.1
+    betas: tuple = (0.9, 0.95)
+
+
+class CfgNode:
+    """Minimal attribute bag in the spirit of upstream minGPT's CfgNode (README.md:31-38 usage)."""
+
+    def __init__(self, **kw):
+        self.__dict__.update(kw)
+
+    def merge_from_dict(self, d):
+        self.__dict__.update(d)
+
+    def to_dict(self):
+        return dict(self.__dict__)
+
+    def __repr__(self):
+        return "CfgNode(" + ", ".join(f"{k}={v!r}" for k, v in self.__dict__.items()) + ")"
+
+
+def _to_gpt_config(config) -> GPTConfig:
+    if isinstance(config, GPTConfig):
+        return config
+    d = config.to_dict() if hasattr(config, "to_dict") else dict(vars(config))
+    return GPTConfig(
+        model_type=d.get("model_type", None),
+        n_layer=d.get("n_layer"), n_head=d.get("n_head"),
+        n_embed=d.get("n_embed", d.get("n_embd")),
+        vocab_size=d.get("vocab_size", 50257), block_size=d.get("block_size", 1024),
+        embed_drop=d.get("embed_drop", d.get("embd_pdrop", 0.1)),
+        resid_drop=d.get("resid_drop", d.get("resid_pdrop", 0.1)),
+        attn_drop=d.get("attn_drop", d.get("attn_pdrop", 0.1)),
+        variant=d.get("variant", "mingpt"),
+    )
+
+
+# ---------------------------------------------------------------------------------------------------
+# parameter containers.  They are real torch modules of the same classes the reference instantiates, so
+# construction consumes the RNG exactly as the reference does and module-type based code (the reference's
+# own create_optimizer, mingpt/model.py:70-93) classifies the parameters identically.  Their forward()
+# is never used: the compute goes through the engine below.
+# ---------------------------------------------------------------------------------------------------
+class _RefEmbedding(nn.Module):          # GPTEmbedding, mingpt/model.py:193-231
+    def __init__(self, cfg):
+        super().__init__()
+        self.token_embedding = nn.Embedding(cfg.vocab_size, cfg.n_embed)
+        self.pos_embedding = nn.Parameter(torch.zeros(1, cfg.block_size, cfg.n_embed))
+        self.drop = nn.Dropout(cfg.embed_drop)
+
+
+class _RefAttention(nn.Module):          # MultiHeadSelfAttention, mingpt/model.py:125-168
+    def __init__(self, cfg):
+        super().__init__()
+        assert cfg.n_embed % cfg.n_head == 0
+        self.c_proj = nn.Linear(cfg.n_embed, cfg.n_embed)
+        self.resid_drop = nn.Dropout(cfg.resid_drop)
+        # the reference also registers a (1,1,T,T) float `mask` buffer per layer (model.py:142-145); the
+        # attention kernel applies it implicitly, so it is not materialised (nor broadcast by DDP).
+        self.attn = nn.MultiheadAttention(embed_dim=cfg.n_embed, num_heads=cfg.n_head, dropout=cfg.attn_drop,
+                                          batch_first=True)
+
+
+class _RefBlock(nn.Module):              # Block, mingpt/model.py:171-189
+    def __init__(self, cfg):
+        super().__init__()
+        self.ln_1 = nn.LayerNorm(cfg.n_embed)
+        self.attn = _RefAttention(cfg)
+        self.ln_2 = nn.LayerNorm(cfg.n_embed)
+        self.mlp = nn.Sequential(nn.Linear(cfg.n_embed, 4 * cfg.n_embed), nn.Linear(4 * cfg.n_embed, cfg.n_embed),
+                                 nn.GELU(), nn.Dropout(cfg.resid_drop))
+
+
+class _MinAttention(nn.Module):          # upstream minGPT CausalSelfAttention (README.md:10-15)
+    def __init__(self, cfg):
+        super().__init__()
+        assert cfg.n_embed % cfg.n_head == 0
+        self.c_attn = nn.Linear(cfg.n_embed, 3 * cfg.n_embed)
+        self.c_proj = nn.Linear(cfg.n_embed, cfg.n_embed)
+        self.attn_dropout = nn.Dropout(cfg.attn_drop)
+        self.resid_dropout = nn.Dropout(cfg.resid_drop)
+
+
+class _MinBlock(nn.Module):
+    def __init__(self, cfg):
+        super().__init__()
+        self.ln_1 = nn.LayerNorm(cfg.n_embed)
+        self.attn = _MinAttention(cfg)
+        self.ln_2 = nn.LayerNorm(cfg.n_embed)
+        self.mlp = nn.ModuleDict(dict(c_fc=nn.Linear(cfg.n_embed, 4 * cfg.n_embed),
+                                      c_proj=nn.Linear(4 * cfg.n_embed, cfg.n_embed),
+                                      dropout=nn.Dropout(cfg.resid_drop)))
+
+
+_ALIGN = 64  # elements: every parameter starts 256-byte (fp32) / 128-byte (bf16 shadow) aligned
+
+
+class LazyLogits:
+    """What forward() returns as `logits` when a loss is requested on the fused path: the full
+    (B, T, vocab) tensor is only produced if somebody asks (mingpt/trainer.py:122 discards it)."""
+
+    def __init__(self, model, ws, generation):
+        self._model, self._ws, self._gen = model, ws, generation
+        self.shape = torch.Size((ws.B, ws.T, model.vocab_size))
+        self.dtype = torch.float32
+
+    def size(self, dim=None):
+        return self.shape if dim is None else self.shape[dim]
+
+    def materialize(self) -> torch.Tensor:
+        if self._ws.generation != self._gen:
+            raise RuntimeError("LazyLogits is stale: the model ran another forward since it was returned")
+        return self._model._head_logits(self._ws)
+
+    def view(self, *shape):
+        return self.materialize().view(*shape)
+
+    def __getitem__(self, item):
+        return self.materialize()[item]
+
+    @classmethod
+    def __torch_function__(cls, func, types, args=(), kwargs=None):
+        kwargs = kwargs or {}
+        conv = lambda a: a.materialize() if isinstance(a, LazyLogits) else a
+        return func(*[conv(a) for a in args], **{k: conv(v) for k, v in kwargs.items()})
+
+
+class _Workspace:
+    """Activation / gradient scratch for one (B, T): allocated once through torch's caching allocator and
+    reused every step, so the step performs no allocation (and can be captured in a CUDA graph)."""
+
+    def __init__(self, model: "GPT", B: int, T: int):
+        dev = model._flat.device
+        C, L, H, V = model.n_embed, model.n_layer, model.n_head, model.vocab_size
+        M = B * T
+        self.B, self.T, self.M = B, T, M
+        self.generation = 0
+        bf = lambda *s: torch.empty(*s, dtype=torch.bfloat16, device=dev)
+        f32 = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
+        ref = model.variant == "reference"
+        self.x = [bf(M, C) for _ in range(L + 1)]
+        self.xmid = [bf(M, C) for _ in range(L)]
+        self.ln1 = [bf(M, C) for _ in range(L)]
+        self.ln2 = [bf(M, C) for _ in range(L)]
+        self.stats = [[f32(M) for _ in range(4)] for _ in range(L)]  # ln1 mean/rstd, ln2 mean/rstd
+        self.qkv = [bf(M, 3 * C) for _ in range(L)]
+        self.att = [bf(M, C) for _ in range(L)]
+        self.att_o = [bf(M, C) for _ in range(L)] if ref else None
+        self.lse = [f32(B, H, T) for _ in range(L)]
+        self.fc_pre = [bf(M, 4 * C) for _ in range(L)]
+        self.fc_act = [bf(M, 4 * C) for _ in range(L)] if not ref else None
+        self.z = [bf(M, C) for _ in range(L)] if ref else None
+        self.lnf = bf(M, C)
+        self.lnf_stats = [f32(M), f32(M)]
+        # head / loss
+        self.chunk = min(M, model.head_chunk_rows)
+        self.vpad = (V + 63) // 64 * 64
+        self.logits = bf(self.chunk, self.vpad)
+        self.row_loss = f32(M)
+        self.n_valid = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.loss = f32(())
+        self.err_flag = torch.zeros(1, dtype=torch.int32, device=dev)
+        # backward scratch
+        self.dlnf = bf(M, C)
+        self.head_dw = f32(V, C)
+        self.dx_a, self.dx_b = bf(M, C), bf(M, C)
+        self.dln = bf(M, C)
+        self.datt = bf(M, C)
+        self.datt2 = bf(M, C) if ref else None
+        self.dz = bf(M, C) if ref else None
+        self.dfc = bf(M, 4 * C)
+        self.dqkv = bf(M, 3 * C)
+        self.dq_acc = f32(M, C)
+        self.delta = f32(B, H, T)
+        self.idx = None
+        self.has_head_grads = False
+
+
+class _LossFn(torch.autograd.Function):
+    """Ties the fused forward to autograd: loss.backward() (mingpt/trainer.py:127) lands here and runs
+    the hand-scheduled backward, which writes into the flat gradient buffer and sets p.grad views."""
+
+    @staticmethod
+    def forward(ctx, anchor, model, ws):
+        ctx.model, ctx.ws, ctx.gen = model, ws, ws.generation
+        return ws.loss.clone()
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        if ctx.ws.generation != ctx.gen:
+            raise RuntimeError("backward() after another forward reused the activation workspace")
+        ctx.model._backward(ctx.ws, grad_loss.contiguous().float())
+        return None, None, None
+
+
+class GPT(nn.Module):
+    """GPT Language Model (mingpt/model.py:234-356)."""
+
+    @staticmethod
+    def get_default_config() -> CfgNode:
+        """README.md:31-38 spelling of the configuration object."""
+        return CfgNode(model_type="gpt", n_layer=None, n_head=None, n_embd=None, vocab_size=None, block_size=None,
+                       embd_pdrop=0.1, resid_pdrop=0.1, attn_pdrop=0.1, variant="mingpt")
+
+    def __init__(self, config, variant: Optional[str] = None, head_chunk_rows: int = 8192, verbose: bool = True):
+        super().__init__()
+        config = _to_gpt_config(config)
+        if variant is not None:
+            config.variant = variant
+        config = self._set_model_config(config, verbose)
+        if config.variant not in ("reference", "mingpt"):
+            raise ValueError("variant must be 'reference' or 'mingpt'")
+        self.config = config
+        self.variant = config.variant
+        self.block_size = config.block_size
+        self.vocab_size = config.vocab_size
+        self.n_layer, self.n_head, self.n_embed = config.n_layer, config.n_head, config.n_embed
+        self.head_dim = config.n_embed // config.n_head
+        self.head_chunk_rows = head_chunk_rows
+        self.drop_p = (config.embed_drop, config.resid_drop, config.attn_drop)
+        L = config.n_layer
+        if self.variant == "reference":
+            # construction order == mingpt/model.py:243-249
+            self.embedding = _RefEmbedding(config)
+            self.blocks = nn.Sequential(*[_RefBlock(config) for _ in range(L)])
+            self.ln_ff = nn.LayerNorm(config.n_embed)
+            self.head = nn.Linear(config.n_embed, config.vocab_size, bias=False)
+        else:
+            self.transformer = nn.ModuleDict(dict(
+                wte=nn.Embedding(config.vocab_size, config.n_embed),
+                wpe=nn.Embedding(config.block_size, config.n_embed),
+                drop=nn.Dropout(config.embed_drop),
+                h=nn.ModuleList([_MinBlock(config) for _ in range(L)]),
+                ln_f=nn.LayerNorm(config.n_embed)))
+            self.lm_head = nn.Linear(config.n_embed, config.vocab_size, bias=False)
+        # mingpt/model.py:251-256
+        self.apply(self._init_weights)
+        for name, param in self.named_parameters():
+            if name.endswith("c_proj.weight"):
+                param.data.normal_(mean=0.0, std=0.02 / math.sqrt(2 * L))
+        if verbose:
+            print(f"Number of parameters: {sum(p.numel() for p in self.parameters())}")
+            print_model_size(self)
+        # engine state
+        self._roles: Dict[str, str] = self._role_table()
+        self._flat = self._flat_bf16 = self._flat_grad = None
+        self._spans: Dict[str, Tuple[int, int]] = {}
+        self._shadow_token = None
+        self._workspaces: Dict[Tuple[int, int], _Workspace] = {}
+        self._anchor = None
+        self._layer_done_hook: Optional[Callable[[int], None]] = None
+        self.loss_scale_hint = 1.0
+        self._flatten()
+
+    # ------------------------------------------------------------------ configuration
+    @staticmethod
+    def _set_model_config(config: GPTConfig, verbose=True) -> GPTConfig:
+        """mingpt/model.py:261-296 with the intended semantics: explicit n_layer/n_head/n_embed win,
+        otherwise the preset named by model_type fills them in (the reference does neither: SURVEY D4/D5)."""
+        params_given = all(v is not None for v in (config.n_layer, config.n_head, config.n_embed))
+        if not params_given:
+            if config.model_type not in PRESETS:
+                raise ValueError("give n_layer/n_head/n_embed or a known model_type: " + ", ".join(PRESETS))
+            for k, v in PRESETS[config.model_type].items():
+                if getattr(config, k) is None:
+                    setattr(config, k, v)
+        config.n_embd = config.n_embed
+        if config.vocab_size is None or config.block_size is None:
+            raise ValueError("vocab_size and block_size must be set")
+        if verbose:
+            print(config)
+        return config
+
+    @staticmethod
+    def _init_weights(module):
+        """mingpt/model.py:298-307"""
+        if isinstance(module, nn.Linear):
+            module.weight.data.normal_(mean=0.0, std=0.02)
+            if module.bias is not None:
+                module.bias.data.zero_()
+        elif isinstance(module, nn.Embedding):
+            module.weight.data.normal_(mean=0.0, std=0.02)
+        elif isinstance(module, nn.LayerNorm):
+            module.bias.data.zero_()
+            module.weight.data.fill_(1.0)
+
+    def _role_table(self) -> Dict[str, str]:
+        """engine role -> parameter name"""
+        r = {}
+        if self.variant == "reference":
+            r["wte"], r["wpe"] = "embedding.token_embedding.weight", "embedding.pos_embedding"
+            for i in range(self.n_layer):
+                b = f"blocks.{i}."
+                r.update({f"{i}.ln1_w": b + "ln_1.weight", f"{i}.ln1_b": b + "ln_1.bias",
+                          f"{i}.qkv_w": b + "attn.attn.in_proj_weight", f"{i}.qkv_b": b + "attn.attn.in_proj_bias",
+                          f"{i}.o_w": b + "attn.attn.out_proj.weight", f"{i}.o_b": b + "attn.attn.out_proj.bias",
+                          f"{i}.proj_w": b + "attn.c_proj.weight", f"{i}.proj_b": b + "attn.c_proj.bias",
+                          f"{i}.ln2_w": b + "ln_2.weight", f"{i}.ln2_b": b + "ln_2.bias",
+                          f"{i}.fc_w": b + "mlp.0.weight", f"{i}.fc_b": b + "mlp.0.bias",
+                          f"{i}.fc2_w": b + "mlp.1.weight", f"{i}.fc2_b": b + "mlp.1.bias"})
+            r.update({"lnf_w": "ln_ff.weight", "lnf_b": "ln_ff.bias", "head_w": "head.weight"})
+        else:
+            r["wte"], r["wpe"] = "transformer.wte.weight", "transformer.wpe.weight"
+            for i in range(self.n_layer):
+                b = f"transformer.h.{i}."
+                r.update({f"{i}.ln1_w": b + "ln_1.weight", f"{i}.ln1_b": b + "ln_1.bias",
+                          f"{i}.qkv_w": b + "attn.c_attn.weight", f"{i}.qkv_b": b + "attn.c_attn.bias",
+                          f"{i}.proj_w": b + "attn.c_proj.weight", f"{i}.proj_b": b + "attn.c_proj.bias",
+                          f"{i}.ln2_w": b + "ln_2.weight", f"{i}.ln2_b": b + "ln_2.bias",
+                          f"{i}.fc_w": b + "mlp.c_fc.weight", f"{i}.fc_b": b + "mlp.c_fc.bias",
+                          f"{i}.fc2_w": b + "mlp.c_proj.weight", f"{i}.fc2_b": b + "mlp.c_proj.bias"})
+            r.update({"lnf_w": "transformer.ln_f.weight", "lnf_b": "transformer.ln_f.bias", "head_w": "lm_head.weight"})
+        return r
+
+    # ------------------------------------------------------------------ flat storage
+    def _flatten(self, device=None):
+        """(Re)pack every parameter into one flat fp32 buffer; Parameter objects keep their identity."""
+        named = list(self.named_parameters())
+        device = device if device is not None else named[0][1].device
+        off, spans = 0, {}
+        for name, p in named:
+            spans[name] = (off, p.numel())
+            off += (p.numel() + _ALIGN - 1) // _ALIGN * _ALIGN
+        flat = torch.zeros(off, dtype=torch.float32, device=device)
+        for name, p in named:
+            o, n = spans[name]
+            view = flat[o:o + n].view(p.shape)
+            view.copy_(p.data)
+            p.data = view
+        self._flat, self._spans, self._total = flat, spans, off
+        self._flat_bf16 = self._flat_grad = None
+        self._shadow_token = None
+        self._workspaces = {}
+        self._layer_spans = self._compute_layer_spans()
+
+    def _apply(self, fn, recurse=True):
+        out = super()._apply(fn, recurse)
+        first = next(self.parameters(), None)
+        if first is not None and self._flat is not None:
+            if any(p.dtype != torch.float32 for p in self.parameters()):
+                raise RuntimeError("GPT keeps fp32 master parameters (bf16 compute copies are internal); "
+                                   "do not cast the module")
+            self._flatten(first.device)
+        return out
+
+    def _compute_layer_spans(self) -> List[Tuple[int, int]]:
+        """[start, end) element ranges of the flat buffers: embeddings, each block, final norm + head."""
+        names = [n for n, _ in self.named_parameters()]
+        def group(n):
+            parts = n.split(".")
+            if self.variant == "reference":
+                return 1 + int(parts[1]) if parts[0] == "blocks" else (0 if parts[0] == "embedding" else self.n_layer + 1)
+            if parts[0] == "transformer" and parts[1] == "h":
+                return 1 + int(parts[2])
+            return 0 if (parts[0] == "transformer" and parts[1] in ("wte", "wpe")) else self.n_layer + 1
+        spans: Dict[int, List[int]] = {}
+        for n in names:
+            o, k = self._spans[n]
+            g = group(n)
+            end = o + (k + _ALIGN - 1) // _ALIGN * _ALIGN
+            s = spans.setdefault(g, [o, end])
+            s[0], s[1] = min(s[0], o), max(s[1], end)
+        return [tuple(spans[g]) for g in sorted(spans)]
+
+    def _param_token(self):
+        return sum(p._version for p in self.parameters())
+
+    def mark_params_dirty(self):
+        """Call after modifying parameters through `.data` (invisible to version counters)."""
+        self._shadow_token = None
+
+    def _ensure_device_state(self):
+        if not self._flat.is_cuda:
+            raise RuntimeError("this GPT runs on a CUDA (B200) device only: call model.to('cuda') first "
+                               "(there is no CPU compute path)")
+        if self._flat_bf16 is None:
+            self._flat_bf16 = torch.empty(self._total, dtype=torch.bfloat16, device=self._flat.device)
+            self._shadow_token = None
+        if self._flat_grad is None:
+            self._flat_grad = torch.zeros(self._total, dtype=torch.float32, device=self._flat.device)
+        if self._anchor is None or self._anchor.device != self._flat.device:
+            self._anchor = torch.zeros((), device=self._flat.device, requires_grad=True)
+        tok = self._param_token()
+        if self._shadow_token != tok:
+            ops.cast_f32_to_bf16(self._flat, self._flat_bf16)
+            self._shadow_token = tok
+
+    def _w(self, role: str, bf16: bool = False) -> torch.Tensor:
+        name = self._roles[role]
+        o, n = self._spans[name]
+        src = self._flat_bf16 if bf16 else self._flat
+        shape = self._shape_of[name]
+        return src[o:o + n].view(shape)
+
+    def _g(self, role: str) -> torch.Tensor:
+        name = self._roles[role]
+        o, n = self._spans[name]
+        return self._flat_grad[o:o + n].view(self._shape_of[name])
+
+    @property
+    def _shape_of(self):
+        cache = self.__dict__.get("_shape_cache")
+        if cache is None:
+            cache = {n: p.shape for n, p in self.named_parameters()}
+            self.__dict__["_shape_cache"] = cache
+        return cache
+
+    def _ws(self, B: int, T: int) -> _Workspace:
+        ws = self._workspaces.get((B, T))
+        if ws is None:
+            ws = _Workspace(self, B, T)
+            self._workspaces[(B, T)] = ws
+        return ws
+
+    # ------------------------------------------------------------------ forward
+    def _check_dropout(self):
+        if self.training and any(p > 0 for p in self.drop_p):
+            raise NotImplementedError(
+                "dropout > 0 in training mode is not implemented on the fused B200 path yet: construct the "
+                "config with embed_drop=resid_drop=attn_drop=0 or call model.eval()")
+
+    def _trunk(self, ws: _Workspace, idx: torch.Tensor):
+        """embeddings -> blocks -> final LayerNorm (mingpt/model.py:310-312 up to ln_ff)"""
+        B, T = idx.shape
+        C, H, d, L = self.n_embed, self.n_head, self.head_dim, self.n_layer
+        ref = self.variant == "reference"
+        mask = ops.MASK_ADD_TRIL_ONES if ref else ops.MASK_CAUSAL
+        W = lambda r: self._w(r, bf16=True)
+        P = lambda r: self._w(r)
+        wpe = W("wpe").view(-1, C)
+        ops.embedding_fwd(idx, W("wte"), wpe, ws.x[0], ws.err_flag)
+        for l in range(L):
+            s = ws.stats[l]
+            ops.layernorm_fwd(ws.x[l], P(f"{l}.ln1_w"), P(f"{l}.ln1_b"), ws.ln1[l], s[0], s[1])
+            ops.linear_fwd(ws.ln1[l], W(f"{l}.qkv_w"), ws.qkv[l], bias=P(f"{l}.qkv_b"))
+            ops.attention_fwd(ws.qkv[l], ws.att[l], ws.lse[l], B, T, H, d, mask)
+            a_in = ws.att[l]
+            if ref:  # nn.MultiheadAttention's own out_proj, then the extra c_proj (model.py:147-154,167)
+                ops.linear_fwd(ws.att[l], W(f"{l}.o_w"), ws.att_o[l], bias=P(f"{l}.o_b"))
+                a_in = ws.att_o[l]
+            ops.linear_fwd(a_in, W(f"{l}.proj_w"), ws.xmid[l], bias=P(f"{l}.proj_b"), residual=ws.x[l])
+            ops.layernorm_fwd(ws.xmid[l], P(f"{l}.ln2_w"), P(f"{l}.ln2_b"), ws.ln2[l], s[2], s[3])
+            if ref:  # Linear -> Linear -> GELU(erf) (model.py:179-184)
+                ops.linear_fwd(ws.ln2[l], W(f"{l}.fc_w"), ws.fc_pre[l], bias=P(f"{l}.fc_b"))
+                ops.linear_fwd(ws.fc_pre[l], W(f"{l}.fc2_w"), ws.x[l + 1], bias=P(f"{l}.fc2_b"), act=ops.ACT_GELU_ERF,
+                               preact=ws.z[l], residual=ws.xmid[l])
+            else:    # c_fc + NewGELU epilogue, then c_proj + residual epilogue
+                ops.linear_fwd(ws.ln2[l], W(f"{l}.fc_w"), ws.fc_act[l], bias=P(f"{l}.fc_b"), act=ops.ACT_GELU_TANH,
+                               preact=ws.fc_pre[l])
+                ops.linear_fwd(ws.fc_act[l], W(f"{l}.fc2_w"), ws.x[l + 1], bias=P(f"{l}.fc2_b"), residual=ws.xmid[l])
+        ops.layernorm_fwd(ws.x[L], P("lnf_w"), P("lnf_b"), ws.lnf, ws.lnf_stats[0], ws.lnf_stats[1])
+
+    def _head_loss(self, ws: _Workspace, targets: torch.Tensor, need_grad: bool):
+        """head + cross_entropy (mingpt/model.py:312,316-318) in row chunks; the bf16 logits of a chunk are
+        turned into dlogits in place and consumed by the head's dgrad/wgrad right away, so the full
+        (B*T, vocab) logits / dlogits never exist."""
+        V, M = self.vocab_size, ws.M
+        tg = targets.reshape(-1)
+        hw = self._w("head_w", bf16=True)
+        ops.count_valid_targets(tg, ws.n_valid)
+        if need_grad:
+            ws.head_dw.zero_()
+        for r0 in range(0, M, ws.chunk):
+            rows = min(ws.chunk, M - r0)
+            lg_full = ws.logits[:rows]
+            lg = lg_full[:, :V]
+            ops.linear_fwd(ws.lnf[r0:r0 + rows], hw, lg)
+            ops.cross_entropy_fwd_bwd(lg_full, tg[r0:r0 + rows], ws.row_loss[r0:r0 + rows], ws.n_valid, V,
+                                      write_grad=need_grad, err_flag=ws.err_flag)
+            if need_grad:
+                ops.linear_dgrad(lg, hw, ws.dlnf[r0:r0 + rows])
+                ops.linear_wgrad(lg, ws.lnf[r0:r0 + rows], ws.head_dw, accumulate=True)
+        ops.loss_finalize(ws.row_loss, ws.n_valid, ws.loss)
+        ws.has_head_grads = need_grad
+
+    def _head_logits(self, ws: _Workspace, last_only: bool = False) -> torch.Tensor:
+        V, C = self.vocab_size, self.n_embed
+        hw = self._w("head_w", bf16=True)
+        if last_only:
+            x = ws.lnf.view(ws.B, ws.T, C)[:, -1, :].contiguous()
+            out = torch.empty(ws.B, V, dtype=torch.float32, device=x.device)
+            ops.linear_fwd(x, hw, out)
+            return out
+        out = torch.empty(ws.M, V, dtype=torch.float32, device=ws.lnf.device)
+        ops.linear_fwd(ws.lnf, hw, out)
+        return out.view(ws.B, ws.T, V)
+
+    def forward(self, inputs: torch.Tensor, targets: Optional[torch.Tensor] = None):
+        """mingpt/model.py:309-320: returns (logits, loss); loss is None without targets.
+        With targets the logits come back as a LazyLogits handle (materialised on first use)."""
+        if inputs.dim() != 2:
+            raise ValueError("inputs must be (batch, seq)")
+        B, T = inputs.shape
+        assert T <= self.block_size, "Sequence length must be less than or equal to block size for positional embeddings."
+        self._ensure_device_state()
+        self._check_dropout()
+        if not inputs.is_cuda:
+            raise RuntimeError("inputs must be on the model's CUDA device")
+        idx = inputs.contiguous()
+        if idx.dtype != torch.int64:
+            idx = idx.long()
+        ws = self._ws(B, T)
+        ws.generation += 1
+        ws.idx = idx
+        self._trunk(ws, idx)
+        if targets is None:
+            return self._head_logits(ws), None
+        tg = targets.contiguous()
+        if tg.dtype != torch.int64:
+            tg = tg.long()
+        need_grad = torch.is_grad_enabled()
+        self._head_loss(ws, tg, need_grad)
+        logits = LazyLogits(self, ws, ws.generation)
+        if need_grad:
+            loss = _LossFn.apply(self._anchor, self, ws)
+        else:
+            loss = ws.loss.clone()
+        return logits, loss
+
+    # ------------------------------------------------------------------ backward
+    def _prepare_grads(self):
+        """Gradient accumulation semantics of .grad: tensors whose .grad is None (fresh model, or
+        optimizer.zero_grad(set_to_none=True) as in mingpt/trainer.py:125) start from zero."""
+        params = list(self.named_parameters())
+        missing = [n for n, p in params if p.grad is None]
+        if len(missing) == len(params):
+            self._flat_grad.zero_()
+        else:
+            for n in missing:
+                o, k = self._spans[n]
+                self._flat_grad[o:o + k].zero_()
+        for n, p in params:
+            if p.grad is None:
+                o, k = self._spans[n]
+                p.grad = self._flat_grad[o:o + k].view(p.shape)
+
+    def _backward(self, ws: _Workspace, grad_loss: torch.Tensor):
+        if not ws.has_head_grads:
+            raise RuntimeError("backward() needs a forward that ran with gradients enabled")
+        B, T, M = ws.B, ws.T, ws.M
+        C, H, d, L = self.n_embed, self.n_head, self.head_dim, self.n_layer
+        ref = self.variant == "reference"
+        mask = ops.MASK_ADD_TRIL_ONES if ref else ops.MASK_CAUSAL
+        W = lambda r: self._w(r, bf16=True)
+        P = lambda r: self._w(r)
+        G = self._g
+        self._prepare_grads()
+        # upstream gradient of the scalar loss, applied on the device (no host sync)
+        ops.scale_bf16_dev(ws.dlnf, grad_loss)
+        ops.axpy(G("head_w"), ws.head_dw, grad_loss)
+        ops.layernorm_bwd(ws.dlnf, ws.x[L], P("lnf_w"), ws.lnf_stats[0], ws.lnf_stats[1], ws.dx_a, G("lnf_w"), G("lnf_b"))
+        if self._layer_done_hook is not None:
+            self._layer_done_hook(L + 1)
+        dx = ws.dx_a
+        for l in range(L - 1, -1, -1):
+            s = ws.stats[l]
+            if ref:
+                ops.act_bwd(dx, ws.z[l], ws.dz, ops.ACT_GELU_ERF)
+                ops.colsum(ws.dz, G(f"{l}.fc2_b"))
+                ops.linear_wgrad(ws.dz, ws.fc_pre[l], G(f"{l}.fc2_w"))
+                ops.linear_dgrad(ws.dz, W(f"{l}.fc2_w"), ws.dfc)
+            else:
+                ops.colsum(dx, G(f"{l}.fc2_b"))
+                ops.linear_wgrad(dx, ws.fc_act[l], G(f"{l}.fc2_w"))
+                ops.linear_dgrad(dx, W(f"{l}.fc2_w"), ws.dfc, gate=ws.fc_pre[l], gate_kind=ops.ACT_GELU_TANH)
+            ops.colsum(ws.dfc, G(f"{l}.fc_b"))
+            ops.linear_wgrad(ws.dfc, ws.ln2[l], G(f"{l}.fc_w"))
+            ops.linear_dgrad(ws.dfc, W(f"{l}.fc_w"), ws.dln)
+            ops.layernorm_bwd(ws.dln, ws.xmid[l], P(f"{l}.ln2_w"), s[2], s[3], ws.dx_b, G(f"{l}.ln2_w"), G(f"{l}.ln2_b"), dres=dx)
+            dxm = ws.dx_b
+            a_in = ws.att_o[l] if ref else ws.att[l]
+            ops.colsum(dxm, G(f"{l}.proj_b"))
+            ops.linear_wgrad(dxm, a_in, G(f"{l}.proj_w"))
+            ops.linear_dgrad(dxm, W(f"{l}.proj_w"), ws.datt)
+            datt = ws.datt
+            if ref:
+                ops.colsum(ws.datt, G(f"{l}.o_b"))
+                ops.linear_wgrad(ws.datt, ws.att[l], G(f"{l}.o_w"))
+                ops.linear_dgrad(ws.datt, W(f"{l}.o_w"), ws.datt2)
+                datt = ws.datt2
+            ops.attention_bwd(ws.qkv[l], ws.att[l], datt, ws.lse[l], ws.delta, ws.dq_acc, ws.dqkv, B, T, H, d, mask)
+            ops.colsum(ws.dqkv, G(f"{l}.qkv_b"))
+            ops.linear_wgrad(ws.dqkv, ws.ln1[l], G(f"{l}.qkv_w"))
+            ops.linear_dgrad(ws.dqkv, W(f"{l}.qkv_w"), ws.dln)
+            ops.layernorm_bwd(ws.dln, ws.x[l], P(f"{l}.ln1_w"), s[0], s[1], ws.dx_a, G(f"{l}.ln1_w"), G(f"{l}.ln1_b"), dres=dxm)
+            dx = ws.dx_a
+            if self._layer_done_hook is not None:
+                self._layer_done_hook(l + 1)
+        gwpe = G("wpe").view(-1, C)
+        ops.embedding_bwd(ws.idx, dx, G("wte"), gwpe)
+        if self._layer_done_hook is not None:
+            self._layer_done_hook(0)
+        ws.has_head_grads = False
+
+    # ------------------------------------------------------------------ optimizer / generate
+    def configure_optimizers(self, train_config):
+        """README.md / upstream spelling of create_optimizer (mingpt/model.py:62-122)."""
+        oc = OptimizerConfig(learning_rate=getattr(train_config, "learning_rate", 3e-4),
+                             weight_decay=getattr(train_config, "weight_decay", 0.1),
+                             betas=tuple(getattr(train_config, "betas", (0.9, 0.95))))
+        return create_optimizer(self, oc)
+
+    @torch.no_grad()
+    def generate(self, idx, max_new_tokens, temperature=1.0, do_sample=False, top_k=None):
+        """mingpt/model.py:322-356 (full-window recompute per token, as the reference does), except that
+        only the last position goes through the head GEMM."""
+        was_training = self.training
+        if any(p > 0 for p in self.drop_p):
+            self.eval()
+        try:
+            for _ in range(max_new_tokens):
+                idx_cond = idx if idx.size(1) <= self.block_size else idx[:, -self.block_size:]
+                self._ensure_device_state()
+                B, T = idx_cond.shape
+                ws = self._ws(B, T)
+                ws.generation += 1
+                self._trunk(ws, idx_cond.contiguous().long())
+                logits = self._head_logits(ws, last_only=True) / temperature
+                if top_k is not None:
+                    v, _ = torch.topk(logits, top_k)
+                    logits[logits < v[:, [-1]]] = -float("Inf")
+                probs = torch.softmax(logits, dim=-1)
+                if do_sample:
+                    idx_next = torch.multinomial(probs, num_samples=1)
+                else:
+                    _, idx_next = torch.topk(probs, k=1, dim=-1)
+                idx = torch.cat((idx, idx_next), dim=1)
+        finally:
+            self.train(was_training)
+        return idx
+
+    # ------------------------------------------------------------------ snapshots
+    def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
+        """Reference snapshots carry one `blocks.N.attn.mask` buffer per layer (mingpt/model.py:142-145,
+        saved by mingpt/trainer.py:155); they are implicit here and dropped on load."""
+        sd = {k: v for k, v in state_dict.items() if not k.endswith(".attn.mask")}
+        out = super().load_state_dict(sd, strict=strict, assign=False)
+        self._shadow_token = None
+        return out
+
+
+def param_groups(model: nn.Module) -> Tuple[List[str], List[str]]:
+    """Names in the decay / no-decay groups, by the rules of mingpt/model.py:68-104."""
+    decay, no_decay = set(), set()
+    for mn, m in model.named_modules():
+        for pn, _ in m.named_parameters():
+            fpn = f"{mn}.{pn}" if mn else pn
+            if pn.endswith("bias"):
+                no_decay.add(fpn)
+            elif pn.endswith("weight") and isinstance(m, nn.Linear):
+                decay.add(fpn)
+            elif pn.endswith("in_proj_weight"):
+                decay.add(fpn)
+            elif pn.endswith("weight") and isinstance(m, (nn.LayerNorm, nn.Embedding)):
+                no_decay.add(fpn)
+            elif pn.endswith("pos_embedding"):
+                no_decay.add(fpn)
+    names = {n for n, _ in model.named_parameters()}
+    assert not (decay & no_decay), f"parameters {decay & no_decay} made it into both decay/no_decay sets!"
+    assert not (names - (decay | no_decay)), f"parameters {names - (decay | no_decay)} were not separated into either decay/no_decay set!"
+    return sorted(decay), sorted(no_decay)
+
+
+def create_optimizer(model: nn.Module, optimizer_config: OptimizerConfig):
+    """mingpt/model.py:62-122: two groups (decay / no decay), AdamW(lr, betas). Returns the fused
+    multi-tensor AdamW (same param_groups / state_dict layout as torch.optim.AdamW)."""
+    from .optim import FusedAdamW
+    decay, no_decay = param_groups(model)
+    pd = dict(model.named_parameters())
+    groups = [
+        {"params": [pd[n] for n in decay], "weight_decay": optimizer_config.weight_decay},
+        {"params": [pd[n] for n in no_decay], "weight_decay": 0.0},
+    ]
+    return FusedAdamW(groups, lr=optimizer_config.learning_rate, betas=tuple(optimizer_config.betas), model=model)

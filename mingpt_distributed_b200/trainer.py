@@ -1,0 +1,241 @@
+"""Training loop with the reference's interface (mingpt/trainer.py) on the fused B200 step.
+
+GPTTrainer(config, model, optimizer, train_dataset, test_dataset=None).train() -- mingpt/trainer.py:40-183
+Trainer(config, model, train_dataset).run()                                   -- README.md:47-53 spelling
+
+One step (mingpt/trainer.py:118-133) = forward -> zero_grad(set_to_none=True) -> backward -> clip ->
+optimizer.step -> loss.  Kept: that order and its numerics.  Changed for B200: the clip's norm reduction
+and coefficient are fused into the AdamW launch, gradients are all-reduced per bucket on a side stream
+while backward runs (parallel.DataParallel instead of torch DDP), the two H2D copies are non-blocking from
+pinned memory, and the loss is only read back (a device->host sync) when it is printed, not every batch.
+"""
+from __future__ import annotations
+
+import os
+import time
+from collections import defaultdict
+from dataclasses import asdict, dataclass
+from typing import Any, Dict, Optional
+
+import torch
+import torch.distributed as dist
+from torch.utils.data import DataLoader, Dataset
+from torch.utils.data.distributed import DistributedSampler
+
+from .model import CfgNode
+from .optim import FusedAdamW, clip_grad_norm_
+from .parallel import DataParallel
+
+
+@dataclass
+class GPTTrainerConfig:
+    """mingpt/trainer.py:21-29"""
+    max_epochs: Optional[int] = None
+    batch_size: Optional[int] = None
+    learning_rate: Optional[float] = None   # unused by the reference as well (LR comes from OptimizerConfig)
+    grad_norm_clip: Optional[float] = None
+    dl_num_workers: Optional[int] = None
+    snapshot_path: Optional[str] = None
+    save_every: Optional[int] = None
+
+
+@dataclass
+class ModelSnapshot:
+    """mingpt/trainer.py:33-37"""
+    model_state: "Dict[str, torch.Tensor]"
+    optimizer_state: Dict[str, Any]
+    final_epoch: int
+
+
+def train_step(model, optimizer, inputs, labels, grad_norm_clip: Optional[float], dp: Optional[DataParallel] = None,
+               accumulate: bool = False, loss_div: float = 1.0, zero_grad: bool = False) -> torch.Tensor:
+    """The hot path: mingpt/trainer.py:122-132 on device tensors. Returns the loss as a DEVICE scalar.
+    `accumulate=True` runs forward/backward only (no all-reduce, no update): gradient accumulation.
+    `zero_grad=True` drops the gradients between forward and backward, where the reference does (:125)."""
+    fwd = dp if dp is not None else model
+    logits, loss = fwd(inputs, labels)
+    if zero_grad:
+        optimizer.zero_grad(set_to_none=True)
+    if accumulate and dp is not None:
+        with dp.no_sync():
+            (loss / loss_div if loss_div != 1.0 else loss).backward()
+        return loss.detach()
+    (loss / loss_div if loss_div != 1.0 else loss).backward()
+    if accumulate:
+        return loss.detach()
+    scale = 1.0
+    if dp is not None:
+        dp.finish_backward()
+        scale = dp.grad_scale
+    if isinstance(optimizer, FusedAdamW):
+        clip = grad_norm_clip is not None and grad_norm_clip > 0
+        norm_sq = optimizer.grad_norm_sq() if clip else None
+        optimizer.step(grad_scale=scale, gradnorm_sq=norm_sq, max_norm=float(grad_norm_clip) if clip else 0.0)
+    else:
+        if scale != 1.0:
+            model._flat_grad.mul_(scale)
+        if grad_norm_clip is not None and grad_norm_clip > 0:
+            clip_grad_norm_(model, grad_norm_clip)
+        optimizer.step()
+    return loss.detach()
+
+
+class GPTTrainer:
+    """Same constructor and methods as the reference's GPTTrainer (mingpt/trainer.py:40-183)."""
+
+    def __init__(self, config: GPTTrainerConfig, model: torch.nn.Module, optimizer: Any, train_dataset: Dataset,
+                 test_dataset: Dataset = None):
+        # torchrun / srun environment contract (mingpt/trainer.py:53-54, mingpt/slurm/slurm_run.sh:17-23)
+        self.local_rank = int(os.environ.get("LOCAL_RANK", 0))
+        self.global_rank = int(os.environ.get("RANK", 0))
+        self.config = config
+        self.train_dataset = train_dataset
+        self.test_dataset = test_dataset
+        self.train_loader = self._prepare_dataloader(train_dataset)
+        self.test_loader = self._prepare_dataloader(test_dataset) if test_dataset else None
+        self.device = torch.device("cuda", self.local_rank)
+        torch.cuda.set_device(self.device)
+        self.model = model.to(self.device)
+        self.optimizer = optimizer
+        self.save_every = config.save_every if config.save_every else 1
+        self.last_epoch = 0
+        if self.config.snapshot_path is None:
+            self.config.snapshot_path = "gpt_snapshot.pt"
+        self._load_snapshot()
+        self.raw_model = self.model
+        self.dp = None
+        if dist.is_initialized() and dist.get_world_size() > 1:
+            self.dp = DataParallel(self.model, device_ids=[self.local_rank])
+            self.model = self.dp
+        self.tokens_seen = 0
+
+    def _prepare_dataloader(self, dataset: Dataset):
+        if dist.is_initialized():
+            sampler = DistributedSampler(dataset)
+        else:
+            sampler = DistributedSampler(dataset, num_replicas=1, rank=0)
+        workers = self.config.dl_num_workers or 0
+        return DataLoader(dataset, batch_size=self.config.batch_size, pin_memory=True, shuffle=False,
+                          num_workers=workers, sampler=sampler)
+
+    # ---------------------------------------------------------------- snapshots (mingpt/trainer.py:83-116,149-167)
+    def _load_snapshot(self):
+        path = self.config.snapshot_path
+        try:
+            if "://" in path:
+                import fsspec
+                with fsspec.open(path) as f:
+                    snapshot_data = torch.load(f, map_location="cpu")
+            else:
+                snapshot_data = torch.load(path, map_location="cpu")
+        except FileNotFoundError:
+            print("Model snapshot not found. You need to train your model from scratch.")
+            return
+        snap = ModelSnapshot(**snapshot_data)
+        self.model.load_state_dict(snap.model_state)
+        self.optimizer.load_state_dict(snap.optimizer_state)
+        self.last_epoch = snap.final_epoch
+        print(f"Resuming training from epoch: {self.last_epoch}")
+
+    def _save_snapshot(self, epoch: int) -> None:
+        model = self.model.module if hasattr(self.model, "module") else self.model
+        snapshot = dict(model_state=model.state_dict(), optimizer_state=self.optimizer.state_dict(), final_epoch=epoch)
+        path = self.config.snapshot_path
+        if "://" in path:
+            import fsspec
+            with fsspec.open(path, "wb") as f:
+                torch.save(snapshot, f)
+        else:
+            torch.save(snapshot, path)
+        print(f"Model snapshot taken and saved at epoch {epoch}")
+
+    # ---------------------------------------------------------------- step / epoch
+    def _run_batch(self, inputs, labels, train: bool = True):
+        """mingpt/trainer.py:118-133. Returns the loss as a device scalar (float() it to sync)."""
+        if not train:
+            with torch.no_grad():
+                _, loss = self.model(inputs, labels)
+            return loss
+        return train_step(self.raw_model, self.optimizer, inputs, labels, self.config.grad_norm_clip, self.dp,
+                          zero_grad=True)
+
+    def _run_epoch(self, epoch: int, dataloader: DataLoader, train: bool = True) -> None:
+        t0, tok0 = time.time(), self.tokens_seen
+        for idx, (x, y) in enumerate(dataloader):
+            inputs = x.to(self.device, non_blocking=True)
+            labels = y.to(self.device, non_blocking=True)
+            loss = self._run_batch(inputs, labels, train)
+            self.tokens_seen += inputs.numel()
+            if idx % 100 == 0:
+                lv = float(loss)   # the only device->host sync
+                dt = max(time.time() - t0, 1e-9)
+                print(f"[GPU{self.local_rank}] Epoch {epoch},{'Training' if train else 'Test'} loss {lv} "
+                      f"| {(self.tokens_seen - tok0) / dt:.0f} tok/s/rank")
+
+    def train(self) -> None:
+        for epoch in range(self.last_epoch, self.config.max_epochs):
+            self._run_epoch(epoch, self.train_loader, True)
+            if self.local_rank == 0 and epoch % self.save_every == 0:
+                self._save_snapshot(epoch)
+            if self.test_loader is not None:
+                self._run_epoch(epoch, self.test_loader, False)
+
+
+class Trainer:
+    """The README.md:47-53 / upstream minGPT spelling: Trainer(config, model, dataset).run(), iteration
+    based, with callbacks. Uses the same fused step."""
+
+    @staticmethod
+    def get_default_config() -> CfgNode:
+        return CfgNode(device="auto", num_workers=4, max_iters=None, batch_size=64, learning_rate=3e-4,
+                       betas=(0.9, 0.95), weight_decay=0.1, grad_norm_clip=1.0)
+
+    def __init__(self, config, model, train_dataset):
+        self.config = config
+        self.model = model
+        self.train_dataset = train_dataset
+        self.callbacks = defaultdict(list)
+        self.optimizer = None
+        if config.device == "auto":
+            self.device = torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0)))
+        else:
+            self.device = torch.device(config.device)
+        self.model = self.model.to(self.device)
+        print("running on device", self.device)
+        self.iter_num, self.iter_time, self.iter_dt = 0, 0.0, 0.0
+        self.loss = None
+
+    def add_callback(self, onevent: str, callback):
+        self.callbacks[onevent].append(callback)
+
+    def set_callback(self, onevent: str, callback):
+        self.callbacks[onevent] = [callback]
+
+    def trigger_callbacks(self, onevent: str):
+        for cb in self.callbacks.get(onevent, []):
+            cb(self)
+
+    def run(self):
+        model, config = self.model, self.config
+        self.optimizer = model.configure_optimizers(config)
+        dp = DataParallel(model) if dist.is_initialized() and dist.get_world_size() > 1 else None
+        sampler = torch.utils.data.RandomSampler(self.train_dataset, replacement=True, num_samples=int(1e10))
+        loader = DataLoader(self.train_dataset, sampler=sampler, shuffle=False, pin_memory=True,
+                            batch_size=config.batch_size, num_workers=config.num_workers)
+        model.train()
+        self.iter_num, self.iter_time = 0, time.time()
+        it = iter(loader)
+        while True:
+            try:
+                batch = next(it)
+            except StopIteration:
+                it = iter(loader)
+                batch = next(it)
+            x, y = [t.to(self.device, non_blocking=True) for t in batch]
+            self.loss = train_step(model, self.optimizer, x, y, config.grad_norm_clip, dp, zero_grad=True)
+            self.trigger_callbacks("on_batch_end")
+            self.iter_num += 1
+            tnow = time.time()
+            self.iter_dt, self.iter_time = tnow - self.iter_time, tnow
+            if config.max_iters is not None and self.iter_num >= config.max_iters:
+                break

@@ -1,0 +1,156 @@
+"""Host-side logic and the drop-in API, no GPU: construction / initialisation parity, state_dict layout,
+optimizer groups, config loading, dataset semantics, bucket planning, and that the C-ABI library loads
+and exports every symbol include/mingpt_b200.h declares (no compute calls)."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+import mingpt_distributed_b200 as m
+from conftest import ROOT, load_golden
+from mingpt_distributed_b200 import _lib
+
+NANO = dict(model_type=None, n_layer=3, n_head=3, n_embed=48, vocab_size=65, block_size=128, embed_drop=0.0,
+            resid_drop=0.0, attn_drop=0.0)
+
+
+def test_reference_variant_init_is_bit_identical_to_reference():
+    fx = load_golden("ref_nano")
+    torch.manual_seed(0)
+    g = m.GPT(m.GPTConfig(variant="reference", **NANO), verbose=False)
+    sd = g.state_dict()
+    assert list(sd.keys()) == list(fx["state_dict"].keys())
+    for k, v in fx["state_dict"].items():
+        assert torch.equal(sd[k], v), k
+
+
+def test_parameter_counts():
+    # as-written / mingpt-variant parameter counts
+    ref = m.GPT(m.GPTConfig(variant="reference", **NANO), verbose=False)
+    mg = m.GPT(m.GPTConfig(variant="mingpt", **NANO), verbose=False)
+    assert sum(p.numel() for p in ref.parameters()) == 104352
+    assert sum(p.numel() for p in mg.parameters()) == 97296
+
+
+def test_presets_and_aliases():
+    g = m.GPT(m.GPTConfig(model_type="gpt-mini", vocab_size=65, block_size=256), verbose=False)
+    assert (g.n_layer, g.n_head, g.n_embed) == (6, 6, 192)
+    g = m.GPT(m.GPTConfig(model_type=None, n_layer=2, n_head=2, n_embd=32, vocab_size=11, block_size=8), verbose=False)
+    assert g.n_embed == 32
+    with pytest.raises(ValueError):
+        m.GPT(m.GPTConfig(model_type="nope", vocab_size=11, block_size=8), verbose=False)
+
+
+def test_readme_api_spelling():
+    cfg = m.GPT.get_default_config()
+    cfg.model_type, cfg.vocab_size, cfg.block_size = "gpt-nano", 65, 128
+    g = m.GPT(cfg, verbose=False)
+    assert g.variant == "mingpt" and "lm_head.weight" in g.state_dict()
+    tc = m.Trainer.get_default_config()
+    opt = g.configure_optimizers(tc)
+    assert isinstance(opt, m.FusedAdamW) and opt.defaults["betas"] == (0.9, 0.95)
+
+
+def test_flat_storage_views_and_state_dict_roundtrip():
+    g = m.GPT(m.GPTConfig(variant="reference", **NANO), verbose=False)
+    base = g._flat.data_ptr()
+    for n, p in g.named_parameters():
+        o, k = g._spans[n]
+        assert p.data_ptr() == base + 4 * o and p.numel() == k and o % 64 == 0
+    sd = {k: v.clone() for k, v in g.state_dict().items()}
+    # a reference snapshot also carries per-layer mask buffers (mingpt/model.py:142-145): must load
+    sd["blocks.0.attn.mask"] = torch.ones(1, 1, 128, 128)
+    g2 = m.GPT(m.GPTConfig(variant="reference", **NANO), verbose=False)
+    g2.load_state_dict(sd)
+    for k, v in g2.state_dict().items():
+        assert torch.equal(v, sd[k])
+    spans = g._layer_spans
+    assert len(spans) == g.n_layer + 2 and spans[0][0] == 0 and spans[-1][1] == g._total
+    assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+
+
+def test_param_groups_match_reference_rules():
+    for variant, want in (("reference", (16, 31)), ("mingpt", (13, 28))):
+        g = m.GPT(m.GPTConfig(variant=variant, **NANO), verbose=False)
+        d, nd = m.param_groups(g)
+        assert (len(d), len(nd)) == want
+        opt = m.create_optimizer(g, m.OptimizerConfig())
+        assert [gr["weight_decay"] for gr in opt.param_groups] == [0.1, 0.0]
+        assert opt.defaults["lr"] == 3e-4 and opt.defaults["eps"] == 1e-8
+        names = {id(p): n for n, p in g.named_parameters()}
+        assert [names[id(p)] for p in opt.param_groups[0]["params"]] == d   # sorted by name, model.py:107-116
+
+
+def test_optimizer_state_dict_layout_matches_torch_adamw():
+    g = m.GPT(m.GPTConfig(variant="mingpt", **NANO), verbose=False)
+    ours = m.create_optimizer(g, m.OptimizerConfig()).state_dict()
+    d, nd = m.param_groups(g)
+    pd = dict(g.named_parameters())
+    theirs = torch.optim.AdamW([{"params": [pd[n] for n in d], "weight_decay": 0.1},
+                                {"params": [pd[n] for n in nd], "weight_decay": 0.0}], lr=3e-4, betas=(0.9, 0.95)).state_dict()
+    for a, b in zip(ours["param_groups"], theirs["param_groups"]):
+        assert a["params"] == b["params"]
+        for k in ("lr", "betas", "eps", "weight_decay"):
+            assert a[k] == b[k]
+
+
+def test_cpu_forward_fails_loudly():
+    g = m.GPT(m.GPTConfig(variant="mingpt", **NANO), verbose=False)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        g(torch.zeros(1, 8, dtype=torch.long))
+
+
+def test_config_loader_accepts_reference_yaml(tmp_path):
+    ref_yaml = os.path.join(ROOT, "mingpt_distributed_b200", "gpt2_config.yaml")
+    gc, oc, dc, tc = m.load_config(ref_yaml, ["gpt_config.n_layer=2", "trainer_config.batch_size=8"])
+    assert gc.n_layer == 2 and gc.n_embed == 512 and gc.n_head == 8     # n_embd in the YAML
+    assert oc.learning_rate == 3e-4 and tc.batch_size == 8 and dc.block_size == 128
+    # the reference's own file (hydra section ignored, s3 paths kept as strings)
+    p = tmp_path / "ref.yaml"
+    p.write_text("gpt_config:\n  n_layer: 8\n  n_head: 8\n  n_embd: 512\noptimizer_config:\n  weight_decay: 0.1\n"
+                 "  learning_rate: 0.0003\ndata_config:\n  path: s3://bucket\n  block_size: 128\n  truncate: 0.05\n"
+                 "trainer_config:\n  max_epochs: 10\n  batch_size: 64\n  dl_num_workers: 4\n  grad_norm_clip: 1.0\n"
+                 "  snapshot_path: s3://bucket/gpt_snapshot.pt\n  save_every: 3\nhydra:\n  run:\n    dir: ./\n")
+    gc, oc, dc, tc = m.load_config(str(p))
+    assert gc.n_embed == 512 and tc.save_every == 3 and dc.path == "s3://bucket"
+    with pytest.raises(TypeError):
+        m.load_config(str(p), ["gpt_config.bogus=1"])
+
+
+def test_char_dataset_matches_reference_fixture(tmp_path):
+    fx = load_golden("ref_char_dataset")
+    path = tmp_path / "corpus.txt"
+    path.write_bytes(fx["corpus"])
+    ds = m.CharDataset(m.DataConfig(path=str(path), block_size=fx["block_size"], train_split=0.9, truncate=fx["truncate"]))
+    assert len(ds) == fx["length"] and ds.vocab_size == fx["vocab_size"] and ds.stoi == fx["stoi"]
+    for i, (x, y) in fx["items"].items():
+        a, b = ds[i]
+        assert torch.equal(a, x) and torch.equal(b, y) and a.dtype == torch.int64
+    empty = m.CharDataset(m.DataConfig(path=str(path), block_size=4, truncate=0.0))
+    assert empty.vocab_size == 0 and empty.__len__() == -4     # the reference's arithmetic on an empty corpus
+
+
+def test_plan_buckets_reverse_order_and_coverage():
+    spans = [(0, 100), (100, 300), (300, 500), (500, 700), (700, 1000)]
+    b = m.plan_buckets(spans, cap_elems=350)
+    assert b[0][1] == 1000 and b[-1][0] == 0
+    assert [x[2] for x in b] == sorted([x[2] for x in b], reverse=True)
+    covered = sorted((s, e) for s, e, _ in b)
+    assert covered[0][0] == 0 and all(a[1] == c[0] for a, c in zip(covered, covered[1:])) and covered[-1][1] == 1000
+    assert len(m.plan_buckets(spans, cap_elems=10**9)) == 1
+
+
+def test_cabi_library_exports_every_declared_symbol():
+    header = open(os.path.join(ROOT, "include", "mingpt_b200.h")).read()
+    declared = set(re.findall(r"\b(mgb_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) >= 20
+    if not os.path.exists(_lib.LIB_PATH):
+        _lib.build()
+    handle = ctypes.CDLL(_lib.LIB_PATH)
+    for name in declared:
+        assert hasattr(handle, name), name
+    assert declared == set(_lib.SIGNATURES) | set(_lib.INTROSPECTION)
+    assert handle.mgb_version() == 100
+    assert ctypes.sizeof(_lib.GemmArgs) == 176 and ctypes.sizeof(_lib.AdamWChunk) == 16
