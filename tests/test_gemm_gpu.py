@@ -1,0 +1,157 @@
+"""tcgen05 GEMM (mgb_gemm_bf16 through the C ABI) against torch fp32 matmul on the same bf16 inputs:
+the three operand layouts of a linear layer (forward, dgrad, wgrad), ragged shapes, every epilogue,
+split-K accumulation. Tolerance: bf16 outputs 2e-2 relative (north_star, BF16 inputs), fp32 outputs 1e-3."""
+import pytest
+import torch
+
+from conftest import report
+
+pytestmark = pytest.mark.gpu
+
+LAYOUTS = {"fwd_kk": (False, False), "dgrad_kmn": (False, True), "wgrad_mnmn": (True, True)}
+SHAPES = [(128, 64, 64), (128, 256, 64), (256, 256, 128), (128, 128, 256), (300, 200, 136), (1024, 768, 768),
+          (520, 2304, 768), (64, 48, 48), (77, 65, 48), (2048, 768, 3072)]
+
+
+def _mk(M, N, K, a_mn, b_mn, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    a = (torch.randn((K, M) if a_mn else (M, K), device="cuda", generator=g) * 0.5).bfloat16()
+    b = (torch.randn((K, N) if b_mn else (N, K), device="cuda", generator=g) * 0.5).bfloat16()
+    A = a.float().t() if a_mn else a.float()
+    B = b.float().t() if b_mn else b.float()
+    return a, b, A @ B.t()
+
+
+def _tma_ok(M, N, K, a_mn, b_mn):
+    return (M if a_mn else K) % 8 == 0 and (N if b_mn else K) % 8 == 0
+
+
+def _check(name, got, want, rtol):
+    got, want = got.float(), want.float()
+    scale = want.abs().max().item() + 1e-12
+    err = (got - want).abs()
+    bad = (err > rtol * (want.abs() + 0.05 * scale)).nonzero()
+    report(name, max_abs_err=err.max().item(), scale=scale, bad=int(bad.shape[0]))
+    assert bad.shape[0] == 0, (f"{name}: {bad.shape[0]}/{got.numel()} elements off, max err {err.max().item():.4g} "
+                               f"(scale {scale:.3g}); first bad {bad[:6].tolist()} got {got[tuple(bad[0])].item()} want {want[tuple(bad[0])].item()}")
+
+
+@pytest.mark.parametrize("layout", list(LAYOUTS))
+@pytest.mark.parametrize("shape", SHAPES[:5])
+def test_gemm_small(layout, shape):
+    from mingpt_distributed_b200 import ops
+    M, N, K = shape
+    a_mn, b_mn = LAYOUTS[layout]
+    if not _tma_ok(M, N, K, a_mn, b_mn):
+        pytest.skip("TMA needs 16-byte row pitch")
+    a, b, want = _mk(M, N, K, a_mn, b_mn)
+    out = torch.empty(M, N, dtype=torch.float32, device="cuda")
+    ops.gemm(a, b, out, a_mn=a_mn, b_mn=b_mn)
+    torch.cuda.synchronize()
+    _check(f"gemm_{layout}_{M}x{N}x{K}", out, want, 1e-3)
+
+
+@pytest.mark.parametrize("layout", list(LAYOUTS))
+@pytest.mark.parametrize("shape", SHAPES[5:])
+@pytest.mark.parametrize("block_n", [0, 64, 128, 192, 256])
+def test_gemm_large_and_tile_sizes(layout, shape, block_n):
+    from mingpt_distributed_b200 import ops
+    M, N, K = shape
+    a_mn, b_mn = LAYOUTS[layout]
+    if not _tma_ok(M, N, K, a_mn, b_mn):
+        pytest.skip("TMA needs 16-byte row pitch")
+    if block_n and shape != SHAPES[5] and shape != SHAPES[8]:
+        pytest.skip("tile sweep on two shapes only")
+    a, b, want = _mk(M, N, K, a_mn, b_mn, seed=1)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    ops.gemm(a, b, out, a_mn=a_mn, b_mn=b_mn, block_n=block_n)
+    torch.cuda.synchronize()
+    _check(f"gemm_{layout}_{M}x{N}x{K}_bn{block_n}", out, want, 2e-2)
+
+
+@pytest.mark.parametrize("act", [0, 1, 2])
+@pytest.mark.parametrize("N", [768, 65])
+def test_gemm_forward_epilogues(act, N):
+    """bias + {none, NewGELU(tanh), GELU(erf)} + residual + saved pre-activation: mingpt/model.py:179-188"""
+    from mingpt_distributed_b200 import ops
+    M, K = 384, 256
+    a, b, acc = _mk(M, N, K, False, False, seed=2)
+    bias = torch.randn(N, device="cuda")
+    res = torch.randn(M, N, device="cuda").bfloat16()
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    pre = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    ops.gemm(a, b, out, bias=bias, act=act, residual=res, preact=pre)
+    torch.cuda.synchronize()
+    z = acc + bias
+    y = z if act == 0 else torch.nn.functional.gelu(z, approximate="tanh" if act == 1 else "none")
+    _check(f"gemm_epi_pre_act{act}_N{N}", pre, z, 2e-2)
+    _check(f"gemm_epi_out_act{act}_N{N}", out, y + res.float(), 2e-2)
+
+
+@pytest.mark.parametrize("kind", [1, 2])
+def test_gemm_dgrad_gate_epilogue(kind):
+    """dX = (dY W) * gelu'(pre): the fused backward of c_fc's activation"""
+    from mingpt_distributed_b200 import ops
+    M, N, K = 256, 512, 384     # dY [M,N], W [N,K] -> dX [M,K]
+    g = torch.Generator(device="cuda").manual_seed(3)
+    dy = (torch.randn(M, N, device="cuda", generator=g) * 0.5).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) * 0.1).bfloat16()
+    pre = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    out = torch.empty(M, K, dtype=torch.bfloat16, device="cuda")
+    ops.linear_dgrad(dy, w, out, gate=pre, gate_kind=kind)
+    torch.cuda.synchronize()
+    p = pre.float().requires_grad_(True)
+    torch.nn.functional.gelu(p, approximate="tanh" if kind == 1 else "none").sum().backward()
+    _check(f"gemm_gate{kind}", out, (dy.float() @ w.float()) * p.grad, 2e-2)
+
+
+@pytest.mark.parametrize("split_k", [0, 1, 3, 8])
+def test_gemm_wgrad_split_k_accumulates(split_k):
+    """dW += dY^T X with fp32 atomics: two calls must add up (gradient accumulation), any split"""
+    from mingpt_distributed_b200 import ops
+    M, N, K = 4096, 768, 256    # dY [M,N], X [M,K] -> dW [N,K]
+    g = torch.Generator(device="cuda").manual_seed(4)
+    dy = (torch.randn(M, N, device="cuda", generator=g) * 0.1).bfloat16()
+    x = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    dw = torch.zeros(N, K, dtype=torch.float32, device="cuda")
+    ops.linear_wgrad(dy, x, dw, split_k=split_k)
+    ops.linear_wgrad(dy, x, dw, split_k=split_k)
+    torch.cuda.synchronize()
+    _check(f"gemm_wgrad_split{split_k}", dw, 2 * (dy.float().t() @ x.float()), 1e-3)
+
+
+def test_gemm_strided_views_and_padded_vocab():
+    """the head: logits chunk written into a wider (padded) buffer, then used as a K-major A operand whose
+    reduction length (the vocabulary) is not a multiple of anything"""
+    from mingpt_distributed_b200 import ops
+    M, V, C, Vpad = 256, 1000 + 1, 128, 1024
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.randn(M, C, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(V, C, device="cuda", generator=g) * 0.2).bfloat16()
+    buf = torch.full((M, Vpad), 7.0, dtype=torch.bfloat16, device="cuda")
+    ops.linear_fwd(x, w, buf[:, :V])
+    torch.cuda.synchronize()
+    _check("gemm_head_logits", buf[:, :V], x.float() @ w.float().t(), 2e-2)
+    assert (buf[:, V:] == 7.0).all()          # nothing written beyond N
+    dx = torch.empty(M, C, dtype=torch.bfloat16, device="cuda")
+    ops.linear_dgrad(buf[:, :V], w, dx)        # K = V = 1001: TMA zero-fills the ragged tail
+    dw = torch.zeros(V, C, dtype=torch.float32, device="cuda")
+    ops.linear_wgrad(buf[:, :V], x, dw)
+    torch.cuda.synchronize()
+    lg = buf[:, :V].float()
+    _check("gemm_head_dgrad", dx, lg @ w.float(), 2e-2)
+    _check("gemm_head_wgrad", dw, lg.t() @ x.float(), 1e-3)
+
+
+def test_gemm_rejects_bad_arguments():
+    from mingpt_distributed_b200 import ops
+    a = torch.zeros(128, 60, dtype=torch.bfloat16, device="cuda")   # row pitch 120 B: not TMA-able
+    b = torch.zeros(64, 60, dtype=torch.bfloat16, device="cuda")
+    out = torch.empty(128, 64, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(RuntimeError, match="16-byte|multiples of 8"):
+        ops.gemm(a, b, out)
+    with pytest.raises(RuntimeError, match="accumulate"):
+        ops.gemm(torch.zeros(128, 64, dtype=torch.bfloat16, device="cuda"), torch.zeros(64, 64, dtype=torch.bfloat16, device="cuda"),
+                 out, accumulate=True)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        ops.gemm(a.cpu(), b.cpu(), out.cpu())
