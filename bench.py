@@ -1,0 +1,292 @@
+#!/usr/bin/env python
+"""bench.py -- train tokens/s of the fused B200 training step on the configuration BASELINE.json's
+metric is quoted on: GPT-2 124M (12 x 12 x 768, vocab 50257, block_size 1024), bf16 compute, synthetic
+tokens, data parallel over N GPUs (weak scaling: per-GPU batch fixed).
+
+    python bench.py --gpus N --steps K --warmup W            # our arm  (N > 1: launched by torchrun)
+    python bench.py --impl reference --steps K --warmup W    # the reference's arithmetic on the host cores
+
+One "step" = forward, backward (gradient all-reduce overlapped when N > 1), global-norm clip + AdamW:
+exactly GPTTrainer._run_batch (mingpt/trainer.py:118-133).  Prints ONE JSON line (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch
+
+GPT2 = dict(n_layer=12, n_head=12, n_embed=768, vocab_size=50257, block_size=1024)
+NOMINAL_BF16 = 2.25e15
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return dict(bf16_burst=p.get("bf16_tflops", 1590.0), bf16_sustained=p.get("bf16_tflops_sustained", 1400.0),
+                    hbm=p.get("hbm_gbs", 6650.0), source="MEASURED_PEAKS.json")
+    return dict(bf16_burst=1590.0, bf16_sustained=1400.0, hbm=6650.0, source="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for name, val in zip(names, r[5:9]):
+                    if val.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        return dict(sm_mhz=statistics.median(sm) if sm else None, sm_max_mhz=max(mx) if mx else None,
+                    reasons=sorted(reasons), samples=len(sm))
+
+
+def make_tokens(B, T, V, seed):
+    g = torch.Generator().manual_seed(seed)
+    tok = torch.randint(0, V, (B, T + 1), generator=g)
+    return tok[:, :-1].contiguous(), tok[:, 1:].contiguous()
+
+
+# ----------------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the oracle (a port of the reference's arithmetic) on the host cores
+# ----------------------------------------------------------------------------------------------------
+def cpu_oracle_tokens_per_s(variant: str, steps: int, warmup: int, budget_s: float, B: int = 1, T: int = 1024):
+    from oracle import gpt_oracle as go
+    import mingpt_distributed_b200 as m
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(0)
+    model = m.GPT(m.GPTConfig(model_type=None, embed_drop=0.0, resid_drop=0.0, attn_drop=0.0, variant=variant, **GPT2), verbose=False)
+    tr = go.OracleTrainer(model.state_dict(), GPT2["n_head"], variant)
+    del model
+    times = []
+    t_start = time.time()
+    for i in range(warmup + steps):
+        x, y = make_tokens(B, T, GPT2["vocab_size"], 1234 + i)
+        t0 = time.time()
+        tr.run_batch(x, y)
+        dt = time.time() - t0
+        if i >= warmup:
+            times.append(dt)
+        if time.time() - t_start > budget_s and len(times) >= 1:
+            break
+    ms = 1000.0 * sum(times) / len(times)
+    return B * T / (ms / 1000.0), ms, cores, len(times), f"{len(times)} steps of B={B} x T={T} tokens, fp32, torch {torch.__version__} CPU, {cores} threads"
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    budget = 150.0
+    val, ms, cores, n, sample = cpu_oracle_tokens_per_s("reference", args.steps, min(args.warmup, 1), budget)
+    line = dict(impl="reference", metric="train_tokens_per_s", value=val, unit="tokens/s", n_gpus=args.gpus, steps=n,
+                warmup=min(args.warmup, 1), ms_per_step=ms, higher_is_better=True, scaling="weak", vs_baseline=None,
+                dtype="f32", data="synthetic",
+                config=dict(workload="gpt2-124M train step (L12 H12 C768 V50257 T1024)", global_batch=1, seq_len=1024,
+                            parallelism="cpu", note="the reference's as-written graph (oracle port of mingpt/model.py + trainer.py:118-133; "
+                                                    "the reference itself is CUDA+NCCL-only and absent from this box)"),
+                cpu_baseline=dict(value=val, unit="tokens/s", cores=cores, kind="port", sample=sample),
+                e2e=dict(value=val, unit="tokens/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
+    print(json.dumps(line))
+
+
+# ----------------------------------------------------------------------------------------------------
+# our arm
+# ----------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--batch", type=int, default=32, help="sequences per GPU per step")
+    ap.add_argument("--seq", type=int, default=1024)
+    ap.add_argument("--variant", default="mingpt")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-budget", type=float, default=25.0)
+    ap.add_argument("--profile-gemm", action="store_true", default=True)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
+
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+
+    import torch.distributed as dist
+    import mingpt_distributed_b200 as m
+    from mingpt_distributed_b200 import _lib, ops
+    from oracle import gpt_oracle as go
+
+    rank = int(os.environ.get("RANK", 0))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, T, V = args.batch, args.seq, GPT2["vocab_size"]
+
+    torch.manual_seed(0)
+    cfg = m.GPTConfig(model_type=None, embed_drop=0.0, resid_drop=0.0, attn_drop=0.0, variant=args.variant, **GPT2)
+    model = m.GPT(cfg, verbose=False)
+    opt = m.create_optimizer(model, m.OptimizerConfig())
+    model = model.to(dev)
+    dp = m.DataParallel(model) if world > 1 else None
+
+    nbatches = 4
+    host = [make_tokens(B, T, V, 1234 + rank + 100 * i) for i in range(nbatches)]
+    pinned = [(x.pin_memory(), y.pin_memory()) for x, y in host]
+    resident = [(x.to(dev), y.to(dev)) for x, y in host]
+
+    def step_resident(i):
+        x, y = resident[i % nbatches]
+        return m.train_step(model, opt, x, y, 1.0, dp, zero_grad=True)
+
+    def step_e2e(i):
+        x, y = pinned[i % nbatches]
+        xd, yd = x.to(dev, non_blocking=True), y.to(dev, non_blocking=True)
+        return m.train_step(model, opt, xd, yd, 1.0, dp, zero_grad=True).item()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        n0 = _lib.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = t.item()
+        return ms, _lib.launch_count() - n0
+
+    for i in range(args.warmup):
+        step_resident(i)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms_total, launches = timed(step_resident, args.steps)
+    for i in range(2):
+        step_e2e(i)
+    ms_e2e, _ = timed(step_e2e, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_step = ms_total / args.steps
+    tokens_per_step = world * B * T
+    value = tokens_per_step / (ms_step / 1000.0)
+    e2e_value = tokens_per_step / (ms_e2e / args.steps / 1000.0)
+
+    # roofline of the dominant kernel (the tcgen05 GEMM): every launch of two extra steps bracketed by CUDA events
+    roof = None
+    peaks = measured_peaks()
+    if args.profile_gemm:
+        records = []
+        orig = ops.gemm
+
+        def timed_gemm(a, b, out, **kw):
+            M, N = out.shape
+            K = a.shape[0] if kw.get("a_mn") else a.shape[1]
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            r = orig(a, b, out, **kw)
+            e.record()
+            records.append((2.0 * M * N * K, s, e))
+            return r
+
+        ops.gemm = timed_gemm
+        try:
+            step_resident(0)
+            records.clear()
+            t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+            t0.record()
+            for i in range(2):
+                step_resident(i)
+            t1.record()
+            torch.cuda.synchronize()
+        finally:
+            ops.gemm = orig
+        flops = sum(r[0] for r in records)
+        gemm_ms = sum(r[1].elapsed_time(r[2]) for r in records)
+        step_ms_instr = t0.elapsed_time(t1)
+        achieved = flops / (gemm_ms / 1000.0) / 1e12
+        roof = dict(bound="tensor", kernel="mgb::gemm::gemm_kernel (all %d launches of a step)" % (len(records) // 2),
+                    achieved=achieved, peak=peaks["bf16_sustained"], unit="TFLOP/s", frac=achieved / peaks["bf16_sustained"],
+                    peak_source=peaks["source"] + " bf16_tflops_sustained (kernel timed inside a long step)",
+                    frac_of_nominal=achieved * 1e12 / NOMINAL_BF16, traffic=None,
+                    share_of_step=gemm_ms / step_ms_instr, flops_per_launch_avg=flops / max(len(records), 1),
+                    ms_per_launch_avg=gemm_ms / max(len(records), 1))
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v_ref, ms_ref, cores, n, sample = cpu_oracle_tokens_per_s("reference", 2, 1, args.cpu_budget)
+        cpu = dict(value=v_ref, unit="tokens/s", cores=cores, kind="port",
+                   sample="reference's as-written graph via the oracle port: " + sample)
+
+    if rank == 0:
+        f_tok = go.flops_per_token(GPT2["n_layer"], GPT2["n_embed"], V, T, args.variant)
+        line = dict(metric="train_tokens_per_s", value=value, unit="tokens/s", n_gpus=world, steps=args.steps,
+                    warmup=args.warmup, ms_per_step=ms_step, higher_is_better=True, scaling="weak", vs_baseline=None,
+                    dtype="bf16", data="synthetic",
+                    config=dict(workload=f"gpt2-124M train step (L12 H12 C768 V50257 T{T}), variant={args.variant}, "
+                                         "fp32 master weights + AdamW state, bf16 GEMM/attention operands",
+                                global_batch=world * B, seq_len=T, parallelism=f"dp{world}",
+                                l2="per-step working set (>10 GB of activations + 2 GB of parameters/state) is far larger than the 126 MB L2"),
+                    mfu=dict(flops_per_token=f_tok, of_nominal_2p25pf=value * f_tok / (world * NOMINAL_BF16),
+                             of_measured_sustained=value * f_tok / (world * peaks["bf16_sustained"] * 1e12)),
+                    clocks=clocks,
+                    e2e=dict(value=e2e_value, unit="tokens/s", h2d_bytes_per_step=2 * B * T * 8, d2h_bytes_per_step=4,
+                             ms_per_step=ms_e2e / args.steps),
+                    gpu_launches=launches, roofline=roof, cpu_baseline=cpu)
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -180,7 +180,16 @@ def test_fixture_trajectory_and_generate_reference_variant():
     dev = max(abs(a - b) / b for a, b in zip(losses, fx["traj"]))
     report("fixture_traj10", max_rel_dev=dev)
     assert dev < 1e-2
-    worst = max(_rel(p.detach(), fx["state_dict_after"][n]) for n, p in model.named_parameters() if fx["state_dict_after"][n].norm() > 0)
+    C = cfg["n_embed"]
+    worst = 0.0
+    for n, p in model.named_parameters():
+        want, got = fx["state_dict_after"][n], p.detach().cpu()
+        if n.endswith("in_proj_bias"):
+            # the key bias has an analytically ZERO gradient (softmax is shift invariant), so Adam turns pure
+            # rounding noise into +-lr steps there, in the reference as much as here: compare q and v parts
+            want, got = torch.cat([want[:C], want[2 * C:]]), torch.cat([got[:C], got[2 * C:]])
+        if want.norm() > 0:
+            worst = max(worst, _rel(got, want))
     report("fixture_params_after10", worst_rel=worst)
     assert worst < 2e-2
     out = model.generate(fx["prompt"].cuda(), 12)
@@ -248,7 +257,8 @@ def test_gpt2_124m_full_size_properties():
     tok = torch.randint(0, 50257, (4, 1025), generator=g).cuda()
     x, y = tok[:, :-1].contiguous(), tok[:, 1:].contiguous()
     _, loss = model(x, y)
-    assert abs(loss.item() - math.log(50257)) < 0.15
+    # logits at init have std ~ 0.02 * sqrt(768) = 0.55, so E[loss] = ln V + sigma^2 / 2 ~ 10.82 + 0.15
+    assert abs(loss.item() - (math.log(50257) + 0.15)) < 0.1
     loss.backward()
     g1 = model._flat_grad.clone()
     assert torch.isfinite(g1).all() and g1.abs().max().item() > 0

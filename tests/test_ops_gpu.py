@@ -58,11 +58,14 @@ def test_layernorm_custom_op_autograd():
     import mingpt_distributed_b200.ops  # registers torch.ops.mingpt_b200
     x = torch.randn(4, 16, 64, device="cuda").bfloat16().requires_grad_(True)
     g = torch.ones(64, device="cuda", requires_grad=True); b = torch.zeros(64, device="cuda", requires_grad=True)
+    w = torch.randn(4, 16, 64, device="cuda").bfloat16()
     y, _, _ = torch.ops.mingpt_b200.layernorm(x, g, b, 1e-5)
-    y.float().pow(2).sum().backward()
+    (y.float() * w.float()).sum().backward()
     xf = x.detach().float().requires_grad_(True)
-    F.layer_norm(xf, (64,), g.detach(), b.detach()).pow(2).sum().backward()
+    gf = g.detach().clone().requires_grad_(True)
+    (F.layer_norm(xf, (64,), gf, b.detach()) * w.float()).sum().backward()
     _close("ln_customop_dx", x.grad, xf.grad, 3e-2)
+    _close("ln_customop_dgamma", g.grad, gf.grad, 1e-2)
 
 
 # ------------------------------------------------------------------ embedding
