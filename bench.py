@@ -144,6 +144,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=25.0)
     ap.add_argument("--profile-gemm", action="store_true", default=True)
+    ap.add_argument("--quick", action="store_true", help="timed loop only (for runs under ncu): no e2e, roofline or cpu legs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -213,9 +214,13 @@ def main():
     if rank == 0:
         sampler.start()
     ms_total, launches = timed(step_resident, args.steps)
-    for i in range(2):
-        step_e2e(i)
-    ms_e2e, _ = timed(step_e2e, args.steps)
+    if args.quick:
+        ms_e2e = ms_total
+        args.profile_gemm, args.no_cpu_baseline = False, True
+    else:
+        for i in range(2):
+            step_e2e(i)
+        ms_e2e, _ = timed(step_e2e, args.steps)
     clocks = sampler.stop() if rank == 0 else None
     ms_step = ms_total / args.steps
     tokens_per_step = world * B * T

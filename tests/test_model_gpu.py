@@ -189,9 +189,14 @@ def test_fixture_trajectory_and_generate_reference_variant():
             # rounding noise into +-lr steps there, in the reference as much as here: compare q and v parts
             want, got = torch.cat([want[:C], want[2 * C:]]), torch.cat([got[:C], got[2 * C:]])
         if want.norm() > 0:
-            worst = max(worst, _rel(got, want))
+            r = _rel(got, want)
+            report("fixture_after10_" + n, rel=r, norm=want.norm().item())
+            # tensors that start at ZERO (biases, pos_embedding) are nothing but 10 Adam steps of size ~lr:
+            # m / sqrt(v) turns the bf16 noise of small gradient entries into O(lr) differences
+            starts_at_zero = fx["state_dict"][n].abs().max().item() == 0
+            assert r < (0.12 if starts_at_zero else 2e-2), f"{n}: {r:.4f}"
+            worst = max(worst, r)
     report("fixture_params_after10", worst_rel=worst)
-    assert worst < 2e-2
     out = model.generate(fx["prompt"].cuda(), 12)
     assert out.shape == fx["generated"].shape and torch.equal(out[:, :8].cpu(), fx["prompt"])
 
