@@ -118,6 +118,18 @@ int mgb_attention_bwd(const void* qkv, const void* out, const void* dout, const 
                       float* dq_accum, void* dqkv, int32_t B, int32_t T, int32_t H, int32_t d, int32_t mask_mode,
                       float scale, mgb_stream_t stream);
 
+/* No counterpart in the reference. mgb_attention_bwd for callers that have no scratch to give: a plugin
+ * inside a process whose device pool is fixed at start-up, or an FFI stub that only forwards pointers and
+ * owns no allocator. delta and the dQ accumulator live in a fixed 17 MiB __device__ array inside the library
+ * (held by every GPU that loads it, until exit); the call allocates nothing. Limits and rules:
+ *   - B*T*H*d <= 4194304, otherwise MGB_ERR_TOO_LARGE (use mgb_attention_bwd);
+ *   - the first call on each device looks up the array's address; make that call before any stream capture;
+ *   - all calls share the one array (it is cleared as needed at the start of each call), so two calls that
+ *     overlap on the GPU -- different streams, or different threads on one device -- race: serialise them. */
+int mgb_attention_bwd_noalloc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                              int32_t B, int32_t T, int32_t H, int32_t d, int32_t mask_mode, float scale,
+                              mgb_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------------
  * Cross entropy (F.cross_entropy(..., ignore_index=-1), mean over valid targets: mingpt/model.py:316-318).
  * In place on a chunk of bf16 logits [rows, ld] (only the first `vocab` columns are meaningful):

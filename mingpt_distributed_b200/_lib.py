@@ -54,6 +54,7 @@ SIGNATURES = {
     "mgb_embedding_bwd": [_P, _P, _P, _P, _I64, _I64, _I32, _I64, _P],
     "mgb_attention_fwd": [_P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _P],
     "mgb_attention_bwd": [_P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _P],
+    "mgb_attention_bwd_noalloc": [_P, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _P],
     "mgb_cross_entropy_fwd_bwd": [_P, _I64, _P, _P, _P, _I64, _I64, _F, _I32, _P, _P],
     "mgb_count_valid_targets": [_P, _I64, _P, _P],
     "mgb_loss_finalize": [_P, _I64, _P, _P, _P],

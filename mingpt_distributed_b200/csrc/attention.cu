@@ -13,6 +13,8 @@
 #include "common.cuh"
 #include "mingpt_b200.h"
 
+#include <mutex>
+
 namespace mgb {
 namespace attn {
 
@@ -514,6 +516,81 @@ extern "C" int mgb_attention_bwd(const void* qkv, const void* out, const void* d
         set_last_error("attention: pointers must be 16-byte aligned"); return kErrBadAlign;
     }
     cudaMemsetAsync(dq_accum, 0, (size_t)B * T * H * d * sizeof(float), s);
+    if (d == 64) attn::launch_bwd<64>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
+    else if (d == 32) attn::launch_bwd<32>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
+    else attn::launch_bwd<16>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
+    count_launch(3);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+// =====================================================================================
+// attention backward for callers that cannot give us scratch memory
+// =====================================================================================
+// mgb_attention_bwd needs two scratch arrays from its caller (delta and the fp32 dQ accumulator). Some
+// callers have nowhere to get them: a plugin living inside a serving process whose device pool was
+// carved up at start-up, or a thin FFI stub (ctypes / cgo style) that merely forwards
+// the pointers it was handed and owns no allocator. For them the scratch lives here, in one fixed array
+// that every GPU loading this library keeps until the process exits.
+namespace mgb {
+namespace attn {
+
+constexpr int64_t kNoAllocMaxElems = 4194304;                        // B*T*H*d, e.g. 4 x 1024 x 1024
+constexpr int64_t kNoAllocDeltaElems = kNoAllocMaxElems / 16;        // B*H*T at the smallest head size (16)
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocMaxElems + kNoAllocDeltaElems];   // 17 MiB
+
+constexpr int kMaxDevices = 64;
+static float* g_noalloc_ptr[kMaxDevices] = {};
+static std::mutex g_noalloc_mu;
+
+// In host code `g_noalloc_scratch` is only a handle for the symbol, not a device address: resolve it once
+// per device (with that device current) and hand the real pointer to the kernels.
+static int noalloc_scratch(float** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+        set_last_error("attention_bwd_noalloc: cannot identify the current device");
+        return kErrDriver;
+    }
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            set_last_error(e != cudaSuccess ? cudaGetErrorString(e) : "cudaGetSymbolAddress returned null");
+            return kErrDriver;
+        }
+        g_noalloc_ptr[dev] = static_cast<float*>(p);
+    }
+    *out = g_noalloc_ptr[dev];
+    return kOk;
+}
+
+}  // namespace attn
+}  // namespace mgb
+
+extern "C" int mgb_attention_bwd_noalloc(const void* qkv, const void* out, const void* dout, const float* lse,
+                                         void* dqkv, int32_t B, int32_t T, int32_t H, int32_t d, int32_t mask_mode,
+                                         float scale, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    int rc = check_attn_shape("bwd_noalloc", B, T, H, d, mask_mode);
+    if (rc) return rc;
+    if (((uintptr_t)qkv % 16) || ((uintptr_t)out % 16) || ((uintptr_t)dout % 16) || ((uintptr_t)dqkv % 16)) {
+        set_last_error("attention: pointers must be 16-byte aligned"); return kErrBadAlign;
+    }
+    const int64_t elems = (int64_t)B * T * H * d;
+    if (elems > attn::kNoAllocMaxElems) {
+        set_last_error("attention_bwd_noalloc: B*T*H*d exceeds the built-in scratch (4194304 elements); "
+                       "use mgb_attention_bwd with caller-provided scratch");
+        return kErrTooLarge;
+    }
+    float* scratch = nullptr;
+    rc = attn::noalloc_scratch(&scratch);
+    if (rc) return rc;
+    float* dq_accum = scratch;                                  // [B,T,H,d]; must start at zero
+    float* delta = scratch + attn::kNoAllocMaxElems;            // [B,H,T];   fully overwritten
+    // the array still holds the previous call's partial sums: clear the part this call accumulates into
+    cudaMemsetAsync(dq_accum, 0, (size_t)elems * sizeof(float), s);
     if (d == 64) attn::launch_bwd<64>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
     else if (d == 32) attn::launch_bwd<32>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
     else attn::launch_bwd<16>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);

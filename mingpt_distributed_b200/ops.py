@@ -146,6 +146,16 @@ def attention_bwd(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, d, mask_m
     return dqkv
 
 
+def attention_bwd_noalloc(qkv, out, dout, lse, dqkv, B, T, H, d, mask_mode, scale=None):
+    """attention_bwd for callers with no scratch to offer (a plugin in a process with a fixed device pool, a
+    pointer-forwarding FFI stub): delta / dQ accumulator come from a fixed array inside the library, so B*T*H*d
+    is capped at 4194304 and overlapping calls on one GPU must be serialised (see mingpt_b200.h)."""
+    _chk_cuda(qkv, out, dout, lse, dqkv)
+    scale = 1.0 / math.sqrt(d) if scale is None else scale
+    check(_lib.lib().mgb_attention_bwd_noalloc(_p(qkv), _p(out), _p(dout), _p(lse), _p(dqkv), B, T, H, d, mask_mode, scale, _stream()), "attention_bwd_noalloc")
+    return dqkv
+
+
 def cross_entropy_fwd_bwd(logits, targets, row_loss, n_valid, vocab, grad_scale=1.0, write_grad=True, err_flag=None):
     """in place on bf16 logits [rows, ld]; see mgb_cross_entropy_fwd_bwd"""
     _chk_cuda(logits, targets, row_loss, n_valid)
