@@ -39,6 +39,7 @@ enum {
 };
 
 enum { MGB_ACT_NONE = 0, MGB_ACT_GELU_TANH = 1, MGB_ACT_GELU_ERF = 2 };
+enum { MGB_GEMM_ENGINE_SINGLE = 1024, MGB_GEMM_ENGINE_PAIR = 2048 };
 
 /* attention mask modes.
  *   CAUSAL         scores[i,j] = -inf for j > i  (the README / north_star "CausalSelfAttention")
@@ -52,6 +53,10 @@ const char* mgb_last_error(void);
 int mgb_version(void);
 /* number of kernels this library has launched in the calling process (bench.py's gpu_launches) */
 int64_t mgb_launch_count(void);
+/* Tuning / test knobs (process-wide). Keys: "gemm_single" (1 = always use the single-CTA tile engine),
+ * "gemm_direct_store" (1 = CTA-pair engine writes D from registers instead of through TMA). Returns the
+ * previous value, or -1 for an unknown key. Both engines compute the same result. */
+int mgb_set_option(const char* key, int value);
 
 /* ---------------------------------------------------------------------------------------------------
  * GEMM: D[m,n] = epilogue(alpha * sum_k A(m,k) B(n,k)), bf16 inputs, fp32 accumulate (tcgen05 + TMEM).
@@ -63,6 +68,9 @@ int64_t mgb_launch_count(void);
  * epilogue, in this order:  v = alpha*acc;  v += bias[n];  preact[m,n] = bf16(v) (if preact);
  *   v = act(v);  v *= act'(gate[m,n]) (if gate; gate_kind selects the derivative);  v += residual[m,n];
  *   D = v  (bf16 or fp32)   or   D += v (fp32, atomic; required for split_k > 1)
+ * D rows are written in 16-byte units: when n is not a multiple of 8 (bf16) / 4 (fp32) AND ldd leaves room
+ * after column n, the rest of the last unit (at most 7 / 3 elements) is overwritten too (with the epilogue of
+ * a zero accumulator). With ldd == n (a dense D) nothing outside the matrix is ever touched.
  * ------------------------------------------------------------------------------------------------- */
 typedef struct mgb_gemm_args {
     const void* a; int64_t lda; int32_t a_mn_major;
@@ -75,7 +83,9 @@ typedef struct mgb_gemm_args {
     void* preact; int64_t ldp;
     const void* gate; int64_t ldg; int32_t gate_kind;
     int32_t split_k;   /* 0 = auto */
-    int32_t block_n;   /* 0 = auto; else 64/128/192/256 */
+    int32_t block_n;   /* 0 = auto; else tile width 64/128/192/256, optionally OR-ed with an engine request:
+                          MGB_GEMM_ENGINE_SINGLE (128-row tiles, one CTA) or MGB_GEMM_ENGINE_PAIR (256-row tiles,
+                          two CTAs, tcgen05 cta_group::2). Both engines compute the same result. */
     float alpha;       /* 0 is read as 1 */
 } mgb_gemm_args;
 int mgb_gemm_bf16(const mgb_gemm_args* args, mgb_stream_t stream);

@@ -69,6 +69,7 @@ SIGNATURES = {
     "mgb_sumsq_f32": [_P, _I64, _P, _P],
     "mgb_adamw_multi": [_P, _P, _P, _P, _P, _P, _I32, _F, _F, _F, _F, _I32, _F, _P, _F, _P],
     "mgb_clip_scale_f32": [_P, _I64, _P, _F, _P],
+    "mgb_set_option": [C.c_char_p, _I32],
 }
 INTROSPECTION = {"mgb_last_error": C.c_char_p, "mgb_version": C.c_int, "mgb_launch_count": C.c_int64}
 
@@ -120,6 +121,14 @@ def check(rc: int, what: str = "") -> None:
     if rc != 0:
         msg = lib().mgb_last_error().decode("utf-8", "replace")
         raise RuntimeError(f"mingpt_b200 {what} failed (code {rc}): {msg}")
+
+
+def set_option(key: str, value: int) -> int:
+    """process-wide tuning knob (see mgb_set_option); returns the previous value"""
+    prev = lib().mgb_set_option(key.encode(), int(value))
+    if prev < 0:
+        raise KeyError(key)
+    return prev
 
 
 def launch_count() -> int:

@@ -1,0 +1,525 @@
+// BF16 GEMM, CTA-pair edition: two SMs of a cluster cooperate on one 256 x BLOCK_N tile
+// (tcgen05.mma.cta_group::2). Same contract as gemm_sm100.cu (see mingpt_b200.h, mgb_gemm_bf16).
+//
+// Why pairs: with both operands in shared memory a single-CTA 128 x 256 MMA needs ~190 B/clk of shared
+// memory traffic (operand reads + TMA fills) against the SM's 128 B/clk, which caps the tensor pipe near
+// 65 % (measured 62 % in profiles/r1_a). In a pair each SM stages its own 128 rows of A but only HALF of
+// B; the other half is read from the peer's shared memory by the hardware, so traffic per SM drops by a
+// third while the tile -- and the work per MMA instruction -- doubles.
+//
+// Per CTA:  warp 0 TMA producer (own A rows, own half of B; bytes are credited to the LEADER's barrier),
+//           warp 1 MMA issuer (leader CTA only; commits are multicast to both CTAs' barriers),
+//           warp 2 TMEM allocator, warps 4-11 epilogue for this CTA's 128 rows.
+// Epilogue: all global traffic of the epilogue goes through 128B-swizzled shared-memory boxes and TMA:
+//           the residual / gate tile is TMA-LOADED into the box while the tile's MMAs still run, each
+//           thread then updates its own row in place (TMEM -> registers -> bias, GELU, gate, residual) and
+//           one thread TMA-STORES the box (or TMA-reduce-adds it in fp32 for split-K / accumulation).
+#include "gemm_common.cuh"
+
+namespace mgb {
+namespace gemm {
+
+constexpr int kMaxStages = 8;
+constexpr int kBoxBytes = 128 * 128;          // 128 rows x 128 bytes
+constexpr int kNumBoxes = 4;                  // two per epilogue half
+constexpr int kSmemLimit = 232448;            // 227 KiB
+
+// Fallback epilogue for outputs TMA cannot address (row pitch not a multiple of 16 bytes): registers -> global.
+__device__ __forceinline__ void epilogue_direct(const Params& p, float (&v)[32], int64_t row, int64_t col0,
+                                                bool vec_ok) {
+    const bool full = (col0 + 32 <= p.N) && vec_ok;
+    if (full) {
+        if (p.preact) {
+            __nv_bfloat16* dst = p.preact + row * p.ldp + col0;
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                stg128(dst + q * 8, make_uint4(pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
+                                               pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7])));
+        }
+        if (p.act) act_inplace(v, p.act);
+        if (p.gate) {
+            const __nv_bfloat16* g = p.gate + row * p.ldg + col0;
+            uint32_t gw[16];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const uint4 gi = ldg128(g + q * 8);
+                gw[q * 4 + 0] = gi.x; gw[q * 4 + 1] = gi.y; gw[q * 4 + 2] = gi.z; gw[q * 4 + 3] = gi.w;
+            }
+            gate_inplace(v, gw, p.gate_kind);
+        }
+        if (p.residual) {
+            const __nv_bfloat16* rs = p.residual + row * p.ldr + col0;
+            uint32_t rw[16];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const uint4 ri = ldg128(rs + q * 8);
+                rw[q * 4 + 0] = ri.x; rw[q * 4 + 1] = ri.y; rw[q * 4 + 2] = ri.z; rw[q * 4 + 3] = ri.w;
+            }
+            add_bf16_inplace(v, rw);
+        }
+        if (p.d_f32) {
+            float* dst = reinterpret_cast<float*>(p.d) + row * p.ldd + col0;
+            if (p.accumulate) {
+#pragma unroll
+                for (int q = 0; q < 8; ++q) red_add_f32x4(dst + q * 4, v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+            } else {
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    *reinterpret_cast<float4*>(dst + q * 4) = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+            }
+        } else {
+            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.d) + row * p.ldd + col0;
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                stg128(dst + q * 8, make_uint4(pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
+                                               pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7])));
+        }
+    } else {
+        const bool tanh_kind = p.act == MGB_ACT_GELU_TANH;
+        const bool gate_tanh = p.gate_kind == MGB_ACT_GELU_TANH;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const int64_t col = col0 + j;
+            if (col >= p.N) continue;
+            float x = v[j];
+            if (p.preact) p.preact[row * p.ldp + col] = __float2bfloat16(x);
+            if (p.act) x = tanh_kind ? gelu_tanh_f(x) : gelu_erf_f(x);
+            if (p.gate) {
+                const float g = __bfloat162float(p.gate[row * p.ldg + col]);
+                x *= gate_tanh ? gelu_tanh_grad_f(g) : gelu_erf_grad_f(g);
+            }
+            if (p.residual) x += __bfloat162float(p.residual[row * p.ldr + col]);
+            if (p.d_f32) {
+                float* dst = reinterpret_cast<float*>(p.d) + row * p.ldd + col;
+                if (p.accumulate) atomicAdd(dst, x);
+                else *dst = x;
+            } else {
+                reinterpret_cast<__nv_bfloat16*>(p.d)[row * p.ldd + col] = __float2bfloat16(x);
+            }
+        }
+    }
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                 const __grid_constant__ CUtensorMap tmap_d, const __grid_constant__ CUtensorMap tmap_p,
+                 const __grid_constant__ CUtensorMap tmap_x, const Params p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int block_n = p.block_n;
+    const int nb = block_n >> 1;                               // B columns staged by this CTA
+    const uint32_t stage_bytes = BLOCK_M * BLOCK_K * 2 + (uint32_t)nb * BLOCK_K * 2;
+    uint8_t* boxes = smem + p.num_stages * stage_bytes;        // kNumBoxes x 16 KiB, 1024-aligned
+    uint64_t* bars = reinterpret_cast<uint64_t*>(boxes + kNumBoxes * kBoxBytes);
+    uint64_t* full_bar = bars;                       // [kMaxStages]  (leader's copy is the live one)
+    uint64_t* empty_bar = bars + kMaxStages;         // [kMaxStages]
+    uint64_t* tmem_full = bars + 2 * kMaxStages;     // [2]
+    uint64_t* tmem_empty = tmem_full + 2;            // [2]           (leader's copy is the live one)
+    uint64_t* aux_bar = tmem_empty + 2;              // [kNumBoxes]   residual / gate tile landed in box i
+    uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(aux_bar + kNumBoxes);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    const int cluster_id = blockIdx.x >> 1;
+    const int num_clusters = gridDim.x >> 1;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+        if (p.tma_store) {
+            tma_prefetch_desc(&tmap_d);
+            if (p.preact) tma_prefetch_desc(&tmap_p);
+            if (p.tma_aux) tma_prefetch_desc(&tmap_x);
+        }
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < p.num_stages; ++s) {
+            mbar_init(&full_bar[s], 2);      // leader's arrive.expect_tx + the peer's remote arrive
+            mbar_init(&empty_bar[s], 1);     // one multicast commit
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full[s], 1);
+            mbar_init(&tmem_empty[s], 2 * kEpiWarps);   // epilogue warps of BOTH CTAs
+        }
+        for (int s = 0; s < kNumBoxes; ++s) mbar_init(&aux_bar[s], 1);
+        fence_mbar_init();
+    }
+    if (warp == 2) tmem_alloc_cg2(tmem_base_ptr, kTmemCols);
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_base_ptr;
+
+    const int tiles = p.num_m_tiles * p.num_n_tiles;
+    const int units = tiles * p.split_k;
+
+    if (warp == 0) {
+        // ===================== TMA producer (both CTAs) =====================
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0;
+            for (int u = cluster_id; u < units; u += num_clusters) {
+                const int split = u / tiles;
+                const int t = u - split * tiles;
+                const int m0 = (t / p.num_n_tiles) * (2 * BLOCK_M) + (int)rank * BLOCK_M;
+                const int n0 = (t % p.num_n_tiles) * block_n + (int)rank * nb;
+                const int kb0 = split * p.k_blocks_per_split;
+                const int kb1 = min(kb0 + p.k_blocks_per_split, p.k_blocks_total);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * stage_bytes);
+                    else mbar_arrive_cluster(&full_bar[stage], 0);
+                    uint8_t* sa = smem + stage * stage_bytes;
+                    uint8_t* sb = sa + BLOCK_M * BLOCK_K * 2;
+                    const int k0 = kb * BLOCK_K;
+                    if (!p.a_mn) {
+                        tma_load_2d_cg2(sa, &tmap_a, &full_bar[stage], k0, m0);
+                    } else {
+                        tma_load_2d_cg2(sa, &tmap_a, &full_bar[stage], m0, k0);
+                        tma_load_2d_cg2(sa + ATOM_BYTES, &tmap_a, &full_bar[stage], m0 + 64, k0);
+                    }
+                    if (!p.b_mn) {
+                        tma_load_2d_cg2(sb, &tmap_b, &full_bar[stage], k0, n0);
+                    } else {
+                        for (int a = 0; a < nb / 64; ++a)
+                            tma_load_2d_cg2(sb + a * ATOM_BYTES, &tmap_b, &full_bar[stage], n0 + a * 64, k0);
+                    }
+                    if (++stage == (uint32_t)p.num_stages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (leader CTA only) =====================
+        if (leader && lane == 0) {
+            const uint32_t idesc = make_idesc_bf16(2 * BLOCK_M, block_n, p.a_mn, p.b_mn);
+            const uint32_t a_lbo = p.a_mn ? ATOM_BYTES : 0, b_lbo = p.b_mn ? ATOM_BYTES : 0;
+            const uint32_t a_kstep = p.a_mn ? UMMA_K * 128 : UMMA_K * 2;
+            const uint32_t b_kstep = p.b_mn ? UMMA_K * 128 : UMMA_K * 2;
+            uint32_t stage = 0, phase = 0;
+            uint32_t acc = 0, acc_phase = 0;
+            for (int u = cluster_id; u < units; u += num_clusters) {
+                const int split = u / tiles;
+                const int kb0 = split * p.k_blocks_per_split;
+                const int kb1 = min(kb0 + p.k_blocks_per_split, p.k_blocks_total);
+                mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * kAccStride;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+                    const uint32_t sb = sa + BLOCK_M * BLOCK_K * 2;
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                        const uint64_t da = make_smem_desc_sw128(sa + k * a_kstep, a_lbo, 1024);
+                        const uint64_t db = make_smem_desc_sw128(sb + k * b_kstep, b_lbo, 1024);
+                        umma_bf16_ss_cg2(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit_cg2_mc(&empty_bar[stage], 0x3);   // frees this stage in both CTAs
+                    if (++stage == (uint32_t)p.num_stages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit_cg2_mc(&tmem_full[acc], 0x3);         // accumulators ready in both CTAs
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else if (warp >= 4) {
+        // ===================== epilogue (both CTAs, own 128 rows) =====================
+        const int ew = warp - 4;
+        const int quarter = warp & 3;
+        const int half = ew >> 2;
+        const bool elected = (quarter == 0) && (lane == 0);
+        const int r_local = quarter * 32 + lane;
+        const uint32_t swz = (uint32_t)(r_local & 7);
+        const bool vec_ok = ((p.ldd & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.d) & 15) == 0) &&
+                            (!p.residual || (((p.ldr & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.residual) & 15) == 0))) &&
+                            (!p.preact || (((p.ldp & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.preact) & 15) == 0))) &&
+                            (!p.gate || (((p.ldg & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.gate) & 15) == 0)));
+        const bool bias_vec = p.bias && ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
+        const bool two_out = p.tma_store && p.preact != nullptr;
+        const int aux = p.tma_aux;                                // 0 none, 1 residual, 2 gate: TMA-loaded in place
+        const int slice_cols = p.d_f32 ? 32 : 64;                 // columns per 128-byte output slice
+        const int nslices = block_n / slice_cols;
+        const int chunks_per_slice = slice_cols >> 5;
+        uint8_t* box_base = boxes + half * 2 * kBoxBytes;
+        uint64_t* aux_b = aux_bar + half * 2;
+        uint32_t buf = 0;
+        uint32_t aux_ph = 0;                                      // bit b: parity the next load into box b completes
+        uint32_t acc = 0, acc_phase = 0;
+        for (int u = cluster_id; u < units; u += num_clusters) {
+            const int split = u / tiles;
+            const int t = u - split * tiles;
+            const int m0 = (t / p.num_n_tiles) * (2 * BLOCK_M) + (int)rank * BLOCK_M;
+            const int n0 = (t % p.num_n_tiles) * block_n;
+            if (aux && elected) {
+                // bf16 output => at most two slices per half and tile, one per box. Fetch their residual / gate
+                // tiles now, while the tile's MMAs still run. Every thread of this half is past the previous
+                // tile's last named barrier, so nobody touches the boxes until the loads land.
+                bulk_wait_read<0>();
+                uint32_t b = buf;
+                for (int sl = half; sl < nslices; sl += 2, b ^= 1) {
+                    mbar_arrive_expect_tx(&aux_b[b], kBoxBytes);
+                    tma_load_2d(box_base + b * kBoxBytes, &tmap_x, &aux_b[b], n0 + sl * slice_cols, m0);
+                }
+            }
+            mbar_wait(&tmem_full[acc], acc_phase);
+            tc_fence_after();
+            const int64_t row = (int64_t)m0 + r_local;
+            const bool row_ok = row < p.M;
+            const uint32_t taddr_row = tmem_base + acc * kAccStride + ((uint32_t)(quarter * 32) << 16);
+            bool released = false;
+            for (int sl = half; sl < nslices; sl += 2) {
+                uint8_t* box = box_base + buf * kBoxBytes;
+                uint8_t* box2 = box_base + (buf ^ 1) * kBoxBytes;
+                if (p.tma_store && !aux) {
+                    // the box written two slices ago (or both, when two outputs share the ring) must have been read
+                    if (elected) { if (two_out) bulk_wait_read<0>(); else bulk_wait_read<1>(); }
+                    named_bar_sync(1 + half, 128);
+                }
+                if (aux) {
+                    mbar_wait(&aux_b[buf], (aux_ph >> buf) & 1u);
+                    aux_ph ^= (1u << buf);
+                }
+                uint8_t* rowp = box + r_local * 128;
+                for (int ch = 0; ch < chunks_per_slice; ++ch) {
+                    const int ccol = sl * slice_cols + ch * 32;      // column inside the tile
+                    uint32_t r[32];
+                    __syncwarp();
+                    tmem_ld_32x32b_x32(taddr_row + (uint32_t)ccol, r);
+                    tmem_ld_wait();
+                    if (sl + 2 >= nslices && ch == chunks_per_slice - 1) {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive_cluster(&tmem_empty[acc], 0);
+                        released = true;
+                    }
+                    const int64_t col0 = (int64_t)n0 + ccol;
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+                    if (p.bias) {
+                        if (bias_vec && col0 + 32 <= p.N) {
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) {
+                                const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0) + q);
+                                v[q * 4 + 0] += b4.x; v[q * 4 + 1] += b4.y; v[q * 4 + 2] += b4.z; v[q * 4 + 3] += b4.w;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (col0 + j < p.N) v[j] += __ldg(p.bias + col0 + j);
+                        }
+                    }
+                    if (!p.tma_store) {
+                        if (row_ok && col0 < p.N) epilogue_direct(p, v, row, col0, vec_ok);
+                        continue;
+                    }
+                    // ---- staged path: everything below touches shared memory only ----
+                    if (two_out) {
+                        uint8_t* rowp2 = box2 + r_local * 128;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const uint32_t j = (uint32_t)(ch * 4 + q);
+                            *reinterpret_cast<uint4*>(rowp2 + ((j ^ swz) << 4)) =
+                                make_uint4(pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
+                                           pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]));
+                        }
+                    }
+                    if (p.act) act_inplace(v, p.act);
+                    if (aux) {
+                        // this thread's 64 bytes of the TMA-loaded residual / gate tile (swizzled like the output)
+                        uint32_t xw[16];
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const uint32_t j = (uint32_t)(ch * 4 + q);
+                            const uint4 xi = *reinterpret_cast<const uint4*>(rowp + ((j ^ swz) << 4));
+                            xw[q * 4 + 0] = xi.x; xw[q * 4 + 1] = xi.y; xw[q * 4 + 2] = xi.z; xw[q * 4 + 3] = xi.w;
+                        }
+                        if (aux == 2) gate_inplace(v, xw, p.gate_kind);
+                        else add_bf16_inplace(v, xw);
+                    }
+                    if (p.gate && aux != 2 && row_ok) {
+                        const __nv_bfloat16* g = p.gate + row * p.ldg + col0;
+                        uint32_t gw[16];
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            uint4 gi = make_uint4(0, 0, 0, 0);
+                            if (col0 + q * 8 < p.N) gi = ldg128(g + q * 8);
+                            gw[q * 4 + 0] = gi.x; gw[q * 4 + 1] = gi.y; gw[q * 4 + 2] = gi.z; gw[q * 4 + 3] = gi.w;
+                        }
+                        gate_inplace(v, gw, p.gate_kind);
+                    }
+                    if (p.residual && aux != 1 && row_ok) {
+                        const __nv_bfloat16* rs = p.residual + row * p.ldr + col0;
+                        uint32_t rw[16];
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            uint4 ri = make_uint4(0, 0, 0, 0);
+                            if (col0 + q * 8 < p.N) ri = ldg128(rs + q * 8);
+                            rw[q * 4 + 0] = ri.x; rw[q * 4 + 1] = ri.y; rw[q * 4 + 2] = ri.z; rw[q * 4 + 3] = ri.w;
+                        }
+                        add_bf16_inplace(v, rw);
+                    }
+                    if (p.d_f32) {
+#pragma unroll
+                        for (int q = 0; q < 8; ++q)
+                            *reinterpret_cast<float4*>(rowp + (((uint32_t)q ^ swz) << 4)) =
+                                make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const uint32_t j = (uint32_t)(ch * 4 + q);
+                            *reinterpret_cast<uint4*>(rowp + ((j ^ swz) << 4)) =
+                                make_uint4(pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
+                                           pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]));
+                        }
+                    }
+                }
+                if (p.tma_store) {
+                    fence_proxy_async_smem();
+                    named_bar_sync(1 + half, 128);
+                    if (elected) {
+                        const int c0 = n0 + sl * slice_cols;
+                        if (c0 < p.N && m0 < p.M) {
+                            if (p.accumulate) tma_reduce_add_2d(&tmap_d, box, c0, m0);
+                            else tma_store_2d(&tmap_d, box, c0, m0);
+                            if (two_out) tma_store_2d(&tmap_p, box2, c0, m0);
+                        }
+                        bulk_commit();
+                    }
+                    if (!two_out) buf ^= 1;
+                }
+            }
+            if (!released) {   // this half had no slice in the tile (narrow tiles): still hand TMEM back
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(&tmem_empty[acc], 0);
+            }
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+        if (p.tma_store && elected) bulk_wait<0>();
+    }
+
+    __syncwarp();
+    tc_fence_before();
+    cluster_sync_all();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc_cg2(tmem_base, kTmemCols);
+    }
+}
+
+// ----------------------------------------------------------------------------
+// host side
+// ----------------------------------------------------------------------------
+static int pick_block_n_pair(int64_t M, int64_t N, int b_mn, bool accumulate, int num_clusters) {
+    // K-major B: 64/128/192/256 (each CTA stages block_n/2 rows); MN-major B: 64-wide atoms per CTA -> 128/256.
+    // Cost = waves x time per tile; narrow tiles move more operand bytes per flop (efficiency factors measured
+    // with tools/gemm_probe.py). With split-K available (accumulate) the widest tile always wins.
+    if (accumulate) return N > 128 ? 256 : 128;
+    const int cands[4] = {256, 192, 128, 64};
+    const double eff[4] = {1.0, 0.93, 0.70, 0.45};
+    int best = 128;
+    double best_cost = 1e30;
+    const int64_t mt = ceil_div64(M, 2 * BLOCK_M);
+    for (int i = 0; i < 4; ++i) {
+        const int bn = cands[i];
+        if (b_mn && (bn == 192 || bn == 64)) continue;
+        if (bn > 64 && bn - 64 >= N && !(b_mn && bn == 128)) continue;
+        const int64_t nt = ceil_div64(N, bn);
+        const int64_t waves = ceil_div64(mt * nt, num_clusters);
+        const double cost = (double)waves * (bn / eff[i] + 8.0);
+        if (cost < best_cost) { best_cost = cost; best = bn; }
+    }
+    return best;
+}
+
+static bool tma_ok(const void* base, int64_t ld, int elem_bytes) {
+    return base && ((ld * elem_bytes) % 16 == 0) && ((reinterpret_cast<uintptr_t>(base) & 15) == 0);
+}
+
+int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t stream) {
+    static std::once_flag once;
+    std::call_once(once, [] {
+        cudaFuncSetAttribute(gemm_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+    });
+    const int num_clusters = num_sms / 2;
+    int bn = a->block_n;
+    if (bn == 0) bn = pick_block_n_pair(a->m, a->n, p.b_mn, a->accumulate != 0, num_clusters);
+    if (bn != 64 && bn != 128 && bn != 192 && bn != 256) { set_last_error("gemm: block_n must be 64/128/192/256"); return kErrBadShape; }
+    if (p.b_mn && (bn == 64 || bn == 192)) bn = (bn == 64) ? 128 : 256;
+    p.block_n = bn;
+    p.num_m_tiles = (int)ceil_div64(a->m, 2 * BLOCK_M);
+    p.num_n_tiles = (int)ceil_div64(a->n, bn);
+    p.k_blocks_total = (int)ceil_div64(a->k, BLOCK_K);
+    const int tiles = p.num_m_tiles * p.num_n_tiles;
+    int split = a->split_k;
+    if (split <= 0) {
+        split = 1;
+        if (a->accumulate) {
+            const int max_split = p.k_blocks_total / 8 > 0 ? p.k_blocks_total / 8 : 1;
+            double best = 1e30;
+            for (int s = 1; s <= max_split && s <= 64; ++s) {
+                const int64_t units = (int64_t)tiles * s;
+                const int64_t waves = ceil_div64(units, num_clusters);
+                const int kbs = (int)ceil_div64(p.k_blocks_total, s);
+                const double cost = (double)waves * (kbs + 6.0);
+                if (cost < best - 1e-9) { best = cost; split = s; }
+            }
+        }
+    }
+    if (split > p.k_blocks_total) split = p.k_blocks_total;
+    p.k_blocks_per_split = (int)ceil_div64(p.k_blocks_total, split);
+    p.split_k = (int)ceil_div64(p.k_blocks_total, p.k_blocks_per_split);
+
+    // D (and the saved pre-activation) leave through TMA when their row pitch allows it; one bf16 side input
+    // (gate, else residual) is TMA-loaded in place when the output is bf16 and there is a single output.
+    p.tma_store = tma_ok(a->d, a->ldd, a->d_f32 ? 4 : 2) && (!a->preact || tma_ok(a->preact, a->ldp, 2)) &&
+                  !(a->preact && a->d_f32);
+    if (g_opt_gemm_direct_store.load(std::memory_order_relaxed)) p.tma_store = 0;
+    p.tma_aux = 0;
+    if (p.tma_store && !a->d_f32 && !a->preact) {
+        if (a->gate && tma_ok(a->gate, a->ldg, 2)) p.tma_aux = 2;
+        else if (a->residual && tma_ok(a->residual, a->ldr, 2)) p.tma_aux = 1;
+    }
+
+    const int nb = bn / 2;
+    const uint32_t stage_bytes = BLOCK_M * BLOCK_K * 2 + (uint32_t)nb * BLOCK_K * 2;
+    const int fixed = kNumBoxes * kBoxBytes + 1024 + 512;
+    int stages = (kSmemLimit - fixed) / (int)stage_bytes;
+    if (stages > kMaxStages) stages = kMaxStages;
+    p.num_stages = stages;
+    const int smem_bytes = stages * (int)stage_bytes + fixed;
+
+    CUtensorMap ta, tb, td, tp, tx;
+    int rc;
+    if (!p.a_mn) rc = make_map_2d(&ta, a->a, a->k, a->m, a->lda, BLOCK_K, BLOCK_M);
+    else         rc = make_map_2d(&ta, a->a, a->m, a->k, a->lda, 64, BLOCK_K);
+    if (rc) return rc;
+    if (!p.b_mn) rc = make_map_2d(&tb, a->b, a->k, a->n, a->ldb, BLOCK_K, nb);
+    else         rc = make_map_2d(&tb, a->b, a->n, a->k, a->ldb, 64, BLOCK_K);
+    if (rc) return rc;
+    td = ta; tp = ta; tx = ta;   // placeholders when unused
+    if (p.tma_store) {
+        rc = make_map_2d(&td, a->d, a->n, a->m, a->ldd, a->d_f32 ? 32 : 64, BLOCK_M, a->d_f32 != 0);
+        if (rc) return rc;
+        if (a->preact) {
+            rc = make_map_2d(&tp, a->preact, a->n, a->m, a->ldp, 64, BLOCK_M);
+            if (rc) return rc;
+        }
+        if (p.tma_aux) {
+            rc = p.tma_aux == 2 ? make_map_2d(&tx, a->gate, a->n, a->m, a->ldg, 64, BLOCK_M)
+                                : make_map_2d(&tx, a->residual, a->n, a->m, a->ldr, 64, BLOCK_M);
+            if (rc) return rc;
+        }
+    }
+    const int64_t units = (int64_t)tiles * p.split_k;
+    const int clusters = (int)(units < num_clusters ? units : num_clusters);
+    gemm_pair_kernel<<<2 * clusters, kThreads, smem_bytes, stream>>>(ta, tb, td, tp, tx, p);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+}  // namespace gemm
+}  // namespace mgb

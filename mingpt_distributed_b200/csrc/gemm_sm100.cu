@@ -18,60 +18,17 @@
 //   warp 2      TMEM allocator
 //   warps 4-11  epilogue: tcgen05.ld -> bias / GELU / gate / residual -> global stores
 // Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1.
-#include "common.cuh"
-#include "mingpt_b200.h"
+#include "gemm_common.cuh"
 
-#include <mutex>
+#include <cstdlib>
 
 namespace mgb {
 namespace gemm {
 
-constexpr int BLOCK_M = 128;
-constexpr int BLOCK_K = 64;   // 64 bf16 = 128 bytes = one SWIZZLE_128B row
-constexpr int UMMA_K = 16;
-constexpr int MAX_BLOCK_N = 256;
 constexpr int kStages = 4;
-constexpr int kEpiWarps = 8;
-constexpr int kThreads = 128 + kEpiWarps * 32;
-constexpr int kTmemCols = 512;
-constexpr int kAccStride = 256;   // TMEM column offset between the two accumulator stages
-
 constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;        // 16 KiB
 constexpr int B_STAGE_BYTES = MAX_BLOCK_N * BLOCK_K * 2;    // 32 KiB
-constexpr int ATOM_BYTES = 64 * BLOCK_K * 2;                // one 64-wide MN-major atom: 8 KiB
 constexpr int SMEM_BYTES = kStages * (A_STAGE_BYTES + B_STAGE_BYTES) + 1024 /*align slack*/ + 256 /*barriers*/;
-
-struct Params {
-    int64_t M, N, K;
-    int32_t a_mn, b_mn;
-    int32_t block_n;
-    int32_t split_k;
-    int32_t num_m_tiles, num_n_tiles, k_blocks_total, k_blocks_per_split;
-    // epilogue
-    void* d;
-    int64_t ldd;
-    int32_t d_f32;
-    int32_t accumulate;
-    const float* bias;
-    const __nv_bfloat16* residual;
-    int64_t ldr;
-    int32_t act;
-    __nv_bfloat16* preact;
-    int64_t ldp;
-    const __nv_bfloat16* gate;
-    int64_t ldg;
-    int32_t gate_kind;
-    float alpha;
-};
-
-__device__ __forceinline__ float apply_act(float v, int act) {
-    if (act == MGB_ACT_GELU_TANH) return gelu_tanh_f(v);
-    if (act == MGB_ACT_GELU_ERF) return gelu_erf_f(v);
-    return v;
-}
-__device__ __forceinline__ float apply_gate(float g, int kind) {
-    return kind == MGB_ACT_GELU_TANH ? gelu_tanh_grad_f(g) : gelu_erf_grad_f(g);
-}
 
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
@@ -250,37 +207,26 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
                             stg128(dst + q * 8, o);
                         }
                     }
-                    if (p.act) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], p.act);
-                    }
+                    if (p.act) act_inplace(v, p.act);
                     if (p.gate) {
                         const __nv_bfloat16* g = p.gate + row * p.ldg + col0;
+                        uint32_t gw[16];
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
-                            uint4 gi = ldg128(g + q * 8);
-                            const uint32_t gw[4] = {gi.x, gi.y, gi.z, gi.w};
-#pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                float2 f = unpack_bf16x2(gw[e]);
-                                v[q * 8 + e * 2 + 0] *= apply_gate(f.x, p.gate_kind);
-                                v[q * 8 + e * 2 + 1] *= apply_gate(f.y, p.gate_kind);
-                            }
+                            const uint4 gi = ldg128(g + q * 8);
+                            gw[q * 4 + 0] = gi.x; gw[q * 4 + 1] = gi.y; gw[q * 4 + 2] = gi.z; gw[q * 4 + 3] = gi.w;
                         }
+                        gate_inplace(v, gw, p.gate_kind);
                     }
                     if (p.residual) {
                         const __nv_bfloat16* rs = p.residual + row * p.ldr + col0;
+                        uint32_t rw[16];
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
-                            uint4 ri = ldg128(rs + q * 8);
-                            const uint32_t rw[4] = {ri.x, ri.y, ri.z, ri.w};
-#pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                float2 f = unpack_bf16x2(rw[e]);
-                                v[q * 8 + e * 2 + 0] += f.x;
-                                v[q * 8 + e * 2 + 1] += f.y;
-                            }
+                            const uint4 ri = ldg128(rs + q * 8);
+                            rw[q * 4 + 0] = ri.x; rw[q * 4 + 1] = ri.y; rw[q * 4 + 2] = ri.z; rw[q * 4 + 3] = ri.w;
                         }
+                        add_bf16_inplace(v, rw);
                     }
                     if (p.d_f32) {
                         float* dst = reinterpret_cast<float*>(p.d) + row * p.ldd + col0;
@@ -343,42 +289,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
 // ----------------------------------------------------------------------------
 // host side
 // ----------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode_fn() {
-    static EncodeTiledFn fn = nullptr;
-    static std::once_flag once;
-    std::call_once(once, [] {
-        void* sym = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess &&
-            q == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<EncodeTiledFn>(sym);
-    });
-    return fn;
-}
-
-// 2-D bf16 tensor map: `inner` contiguous elements, `outer` rows with `ld` elements between rows.
-static int make_map_2d(CUtensorMap* out, const void* base, int64_t inner, int64_t outer, int64_t ld,
-                       int box_inner, int box_outer) {
-    EncodeTiledFn enc = get_encode_fn();
-    if (!enc) { set_last_error("cuTensorMapEncodeTiled not available"); return kErrDriver; }
-    cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
-    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-    cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
-    cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) {
-        set_last_error("cuTensorMapEncodeTiled failed (check 16-byte alignment of base and leading dimension)");
-        return kErrDriver;
-    }
-    return kOk;
-}
-
 static int g_num_sms = 0;
 static std::once_flag g_attr_once;
 
@@ -434,8 +344,26 @@ extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
     p.M = a->m; p.N = a->n; p.K = a->k;
     p.a_mn = a->a_mn_major ? 1 : 0;
     p.b_mn = a->b_mn_major ? 1 : 0;
-    int bn = a->block_n;
-    if (bn == 0) bn = pick_block_n(a->m, a->n, p.b_mn, num_sms);
+    p.d = a->d; p.ldd = a->ldd; p.d_f32 = a->d_f32; p.accumulate = a->accumulate;
+    p.bias = a->bias;
+    p.residual = reinterpret_cast<const __nv_bfloat16*>(a->residual); p.ldr = a->ldr;
+    p.act = a->act;
+    p.preact = reinterpret_cast<__nv_bfloat16*>(a->preact); p.ldp = a->ldp;
+    p.gate = reinterpret_cast<const __nv_bfloat16*>(a->gate); p.ldg = a->ldg; p.gate_kind = a->gate_kind;
+    p.alpha = a->alpha == 0.0f ? 1.0f : a->alpha;
+
+    // Two tile engines, chosen by shape: CTA pairs (cta_group::2, 256-row tiles, halves the shared-memory
+    // traffic per MMA) whenever there are at least two 128-row tiles; the single-CTA kernel for short M.
+    // block_n carries an optional engine request in its high bits (see mingpt_b200.h)
+    const int engine = a->block_n & (MGB_GEMM_ENGINE_SINGLE | MGB_GEMM_ENGINE_PAIR);
+    mgb_gemm_args a_local = *a;
+    a_local.block_n = a->block_n & ~(MGB_GEMM_ENGINE_SINGLE | MGB_GEMM_ENGINE_PAIR);
+    const bool want_pair = engine == MGB_GEMM_ENGINE_PAIR ||
+                           (engine == 0 && a->m > BLOCK_M && !g_opt_gemm_single.load(std::memory_order_relaxed));
+    if (want_pair) return launch_gemm_pair(&a_local, p, num_sms, stream);
+
+    int bn = a_local.block_n;
+    if (bn == 0) bn = (a->accumulate && a->n > 128) ? 256 : pick_block_n(a->m, a->n, p.b_mn, num_sms);
     if (bn != 64 && bn != 128 && bn != 192 && bn != 256) { set_last_error("gemm: block_n must be 64/128/192/256"); return kErrBadShape; }
     p.block_n = bn;
     p.num_m_tiles = (int)ceil_div64(a->m, BLOCK_M);
@@ -462,14 +390,6 @@ extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
     if (split > p.k_blocks_total) split = p.k_blocks_total;
     p.k_blocks_per_split = (int)ceil_div64(p.k_blocks_total, split);
     p.split_k = (int)ceil_div64(p.k_blocks_total, p.k_blocks_per_split);   // no empty splits
-    p.d = a->d; p.ldd = a->ldd; p.d_f32 = a->d_f32; p.accumulate = a->accumulate;
-    p.bias = a->bias;
-    p.residual = reinterpret_cast<const __nv_bfloat16*>(a->residual); p.ldr = a->ldr;
-    p.act = a->act;
-    p.preact = reinterpret_cast<__nv_bfloat16*>(a->preact); p.ldp = a->ldp;
-    p.gate = reinterpret_cast<const __nv_bfloat16*>(a->gate); p.ldg = a->ldg; p.gate_kind = a->gate_kind;
-    p.alpha = a->alpha == 0.0f ? 1.0f : a->alpha;
-
     CUtensorMap ta, tb;
     int rc;
     if (!p.a_mn) rc = make_map_2d(&ta, a->a, a->k, a->m, a->lda, BLOCK_K, BLOCK_M);

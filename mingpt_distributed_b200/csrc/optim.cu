@@ -285,6 +285,16 @@ static int grid_for(int64_t work_items, int per_block, int max_blocks) {
 extern "C" const char* mgb_last_error(void) { return g_err; }
 extern "C" int mgb_version(void) { return 100; }
 extern "C" int64_t mgb_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+namespace mgb {
+std::atomic<int> g_opt_gemm_single{0};
+std::atomic<int> g_opt_gemm_direct_store{0};
+}
+extern "C" int mgb_set_option(const char* key, int value) {
+    if (!key) return -1;
+    if (!std::strcmp(key, "gemm_single")) return mgb::g_opt_gemm_single.exchange(value);
+    if (!std::strcmp(key, "gemm_direct_store")) return mgb::g_opt_gemm_direct_store.exchange(value);
+    return -1;
+}
 
 extern "C" int mgb_sumsq_f32(const float* x, int64_t n, float* out, mgb_stream_t s_) {
     cudaStream_t s = (cudaStream_t)s_;

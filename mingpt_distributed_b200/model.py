@@ -281,7 +281,7 @@ class GPT(nn.Module):
         return CfgNode(model_type="gpt", n_layer=None, n_head=None, n_embd=None, vocab_size=None, block_size=None,
                        embd_pdrop=0.1, resid_pdrop=0.1, attn_pdrop=0.1, variant="mingpt")
 
-    def __init__(self, config, variant: Optional[str] = None, head_chunk_rows: int = 8192, verbose: bool = True):
+    def __init__(self, config, variant: Optional[str] = None, head_chunk_rows: int = 16384, verbose: bool = True):
         super().__init__()
         config = _to_gpt_config(config)
         if variant is not None:

@@ -132,7 +132,8 @@ def test_gemm_strided_views_and_padded_vocab():
     ops.linear_fwd(x, w, buf[:, :V])
     torch.cuda.synchronize()
     _check("gemm_head_logits", buf[:, :V], x.float() @ w.float().t(), 2e-2)
-    assert (buf[:, V:] == 7.0).all()          # nothing written beyond N
+    V8 = (V + 7) // 8 * 8
+    assert (buf[:, V8:] == 7.0).all()         # D is written in 16-byte units: nothing beyond the unit holding N-1
     dx = torch.empty(M, C, dtype=torch.bfloat16, device="cuda")
     ops.linear_dgrad(buf[:, :V], w, dx)        # K = V = 1001: TMA zero-fills the ragged tail
     dw = torch.zeros(V, C, dtype=torch.float32, device="cuda")
@@ -155,3 +156,49 @@ def test_gemm_rejects_bad_arguments():
                  out, accumulate=True)
     with pytest.raises(RuntimeError, match="CUDA"):
         ops.gemm(a.cpu(), b.cpu(), out.cpu())
+
+
+@pytest.mark.parametrize("engine", [1024, 2048])          # MGB_GEMM_ENGINE_SINGLE / _PAIR
+@pytest.mark.parametrize("layout", list(LAYOUTS))
+def test_gemm_both_tile_engines_agree(engine, layout):
+    """the single-CTA and the CTA-pair (cta_group::2) engines on the same problems, incl. ragged M and N"""
+    from mingpt_distributed_b200 import ops
+    for (M, N, K) in [(520, 776, 320), (1024, 768, 768), (136, 72, 64)]:
+        a_mn, b_mn = LAYOUTS[layout]
+        if not _tma_ok(M, N, K, a_mn, b_mn):
+            continue
+        a, b, want = _mk(M, N, K, a_mn, b_mn, seed=7)
+        out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+        ops.gemm(a, b, out, a_mn=a_mn, b_mn=b_mn, block_n=engine)
+        torch.cuda.synchronize()
+        _check(f"gemm_engine{engine}_{layout}_{M}x{N}x{K}", out, want, 2e-2)
+
+
+@pytest.mark.parametrize("engine", [1024, 2048])
+def test_gemm_single_side_input_epilogues(engine):
+    """bias + residual (block output) and gelu' gate (fused c_fc backward), one side input each: on the
+    CTA-pair engine the side tile arrives by TMA and is updated in place in shared memory"""
+    from mingpt_distributed_b200 import ops
+    M, N, K = 768, 512, 192
+    a, b, acc = _mk(M, N, K, False, False, seed=8)
+    bias = torch.randn(N, device="cuda")
+    side = torch.randn(M, N, device="cuda").bfloat16()
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    ops.gemm(a, b, out, bias=bias, residual=side, block_n=engine)
+    torch.cuda.synchronize()
+    _check(f"gemm_residual_engine{engine}", out, acc + bias + side.float(), 2e-2)
+    for kind, approx in ((1, "tanh"), (2, "none")):
+        ops.gemm(a, b, out, gate=side, gate_kind=kind, block_n=engine)
+        torch.cuda.synchronize()
+        s = side.float().requires_grad_(True)
+        torch.nn.functional.gelu(s, approximate=approx).sum().backward()
+        _check(f"gemm_gate{kind}_engine{engine}", out, acc * s.grad, 2e-2)
+    # many tiles per CTA pair: exercises the box ring / barrier phases across tiles
+    M2 = 256 * 74 * 2 + 256
+    a2 = (torch.randn(M2, 64, device="cuda") * 0.5).bfloat16()
+    b2 = (torch.randn(128, 64, device="cuda") * 0.5).bfloat16()
+    side2 = torch.randn(M2, 128, device="cuda").bfloat16()
+    out2 = torch.empty(M2, 128, dtype=torch.bfloat16, device="cuda")
+    ops.gemm(a2, b2, out2, residual=side2, block_n=engine)
+    torch.cuda.synchronize()
+    _check(f"gemm_residual_manytiles_engine{engine}", out2, a2.float() @ b2.float().t() + side2.float(), 2e-2)
