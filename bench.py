@@ -152,6 +152,11 @@ def main():
         run_reference_arm(args)
         return
 
+    # libraries (NCCL's version banner, ...) may write to fd 1: keep stdout clean for the ONE JSON line
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
     import torch.distributed as dist
     import mingpt_distributed_b200 as m
     from mingpt_distributed_b200 import _lib, ops
@@ -288,7 +293,9 @@ def main():
                     e2e=dict(value=e2e_value, unit="tokens/s", h2d_bytes_per_step=2 * B * T * 8, d2h_bytes_per_step=4,
                              ms_per_step=ms_e2e / args.steps),
                     gpu_launches=launches, roofline=roof, cpu_baseline=cpu)
-        print(json.dumps(line))
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 

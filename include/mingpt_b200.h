@@ -54,8 +54,9 @@ int mgb_version(void);
 /* number of kernels this library has launched in the calling process (bench.py's gpu_launches) */
 int64_t mgb_launch_count(void);
 /* Tuning / test knobs (process-wide). Keys: "gemm_single" (1 = always use the single-CTA tile engine),
- * "gemm_direct_store" (1 = CTA-pair engine writes D from registers instead of through TMA). Returns the
- * previous value, or -1 for an unknown key. Both engines compute the same result. */
+ * "gemm_direct_store" (1 = CTA-pair engine writes D from registers instead of through TMA), "attn_mma"
+ * (1 = head size 64 also uses the mma.sync attention kernels instead of the tcgen05 ones). Returns the
+ * previous value, or -1 for an unknown key. Every alternative computes the same result. */
 int mgb_set_option(const char* key, int value);
 
 /* ---------------------------------------------------------------------------------------------------

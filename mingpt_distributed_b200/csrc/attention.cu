@@ -13,9 +13,16 @@
 #include "common.cuh"
 #include "mingpt_b200.h"
 
+#include <atomic>
 #include <mutex>
 
 namespace mgb {
+extern std::atomic<int> g_opt_attn_mma;
+namespace attn_tc {   // tcgen05 / TMEM kernels for head size 64 (attention_sm100.cu)
+int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream);
+int launch_bwd_main(const void* qkv, const void* dout, const float* lse, const float* delta, float* dq_accum,
+                    void* dqkv, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream);
+}
 namespace attn {
 
 constexpr int BM = 64;   // queries per CTA (fwd) / per inner step (bwd)
@@ -467,9 +474,14 @@ static int launch_bwd(const void* qkv, const void* out, const void* dout, const 
         cudaFuncSetAttribute(attn_bwd_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         attr_set = true;
     }
-    dim3 grid((T + BN - 1) / BN, B * H);
-    attn_bwd_kernel<D><<<grid, NTHREADS, smem, s>>>((const __nv_bfloat16*)qkv, (const __nv_bfloat16*)dout, lse, delta,
-                                                   dq_accum, (__nv_bfloat16*)dqkv, T, H, mask_mode, scale, scale * LOG2E);
+    if (D == 64 && !g_opt_attn_mma.load(std::memory_order_relaxed)) {
+        const int rc = attn_tc::launch_bwd_main(qkv, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
+        if (rc) return rc;
+    } else {
+        dim3 grid((T + BN - 1) / BN, B * H);
+        attn_bwd_kernel<D><<<grid, NTHREADS, smem, s>>>((const __nv_bfloat16*)qkv, (const __nv_bfloat16*)dout, lse, delta,
+                                                       dq_accum, (__nv_bfloat16*)dqkv, T, H, mask_mode, scale, scale * LOG2E);
+    }
     const int64_t chunks = (int64_t)B * T * (H * D / 8);
     int g2 = (int)((chunks + 255) / 256);
     if (g2 > num_sms() * 16) g2 = num_sms() * 16;
@@ -497,7 +509,11 @@ extern "C" int mgb_attention_fwd(const void* qkv, void* out, float* lse, int32_t
     int rc = check_attn_shape("fwd", B, T, H, d, mask_mode);
     if (rc) return rc;
     if (((uintptr_t)qkv % 16) || ((uintptr_t)out % 16)) { set_last_error("attention: pointers must be 16-byte aligned"); return kErrBadAlign; }
-    if (d == 64) attn::launch_fwd<64>(qkv, out, lse, B, T, H, mask_mode, scale, s);
+    if (d == 64 && !g_opt_attn_mma.load(std::memory_order_relaxed)) {
+        // gpt2-family head size: tcgen05 / TMEM kernel (attention_sm100.cu)
+        rc = attn_tc::launch_fwd(qkv, out, lse, B, T, H, mask_mode, scale, s);
+        if (rc) return rc;
+    } else if (d == 64) attn::launch_fwd<64>(qkv, out, lse, B, T, H, mask_mode, scale, s);
     else if (d == 32) attn::launch_fwd<32>(qkv, out, lse, B, T, H, mask_mode, scale, s);
     else attn::launch_fwd<16>(qkv, out, lse, B, T, H, mask_mode, scale, s);
     count_launch(1);

@@ -1,0 +1,577 @@
+// Fused attention forward on the 5th-generation tensor cores (tcgen05 + TMEM + TMA), head size 64 --
+// the head size of every gpt2 preset (gpt2 / medium / large / xl). Other head sizes (16, 32: gpt-nano,
+// gpt-mini) stay on the mma.sync kernels in attention.cu.
+//
+// One CTA = 128 queries of one (batch, head); keys/values stream through in blocks of 128.
+//   S = Q K^T   : tcgen05.mma 128x128x64 (Q, K K-major, SWIZZLE_128B), fp32 S in TMEM columns [0,128)
+//   softmax     : warps 0-3, ONE THREAD PER QUERY ROW (TMEM lane == row): row max / sum need no shuffles;
+//                 online softmax in the log2 domain; P (bf16 pairs) is written back to TMEM columns [128,192)
+//   O += P V    : tcgen05.mma 128x64x128 with the A operand (P) read FROM TMEM and V as the MN-major B
+//                 operand straight from the TMA tile; fp32 O in TMEM columns [192,256); O is only rescaled
+//                 when the running max grows by more than 2^8
+// warp 4 = TMA producer, warp 5 = MMA issuer + TMEM allocator. 48 KiB of shared memory and 256 TMEM columns
+// per CTA, so two CTAs share an SM: one does softmax while the other's MMAs run.
+#include "gemm_common.cuh"
+
+namespace mgb {
+namespace attn_tc {
+
+constexpr int BQ = 128, BKV = 128, D = 64;
+constexpr int kThreads = 192;
+constexpr int TILE_BYTES = 128 * 128;            // 128 rows x 64 bf16
+constexpr int SMEM_BYTES = 3 * TILE_BYTES + 1024 + 256;   // Q, K, V + align slack + barriers
+constexpr uint32_t kTmemCols = 256;
+constexpr uint32_t kColS = 0, kColP = 128, kColO = 192;
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr float LN2 = 0.6931471805599453f;
+constexpr float kRescaleThreshold = 8.0f;         // log2 units: P stays below 2^8 between rescales
+
+__device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+          "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
+          "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]),
+          "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+        : "memory");
+}
+
+__global__ void __launch_bounds__(kThreads, 2)
+attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __restrict__ out,
+                   float* __restrict__ lse, int T, int H, int mask_mode, float scale_log2) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem;
+    uint8_t* sK = smem + TILE_BYTES;
+    uint8_t* sV = smem + 2 * TILE_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 3 * TILE_BYTES);
+    uint64_t* q_full = bars + 0;
+    uint64_t* k_full = bars + 1;
+    uint64_t* k_empty = bars + 2;
+    uint64_t* v_full = bars + 3;
+    uint64_t* v_empty = bars + 4;
+    uint64_t* s_full = bars + 5;
+    uint64_t* p_ready = bars + 6;
+    uint64_t* pv_done = bars + 7;
+    uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(bars + 8);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = blockIdx.y / H, h = blockIdx.y % H;
+    const int qb = gridDim.x - 1 - blockIdx.x;       // heavy (late) causal blocks first
+    const int q0 = qb * BQ;
+    const int C = H * D;
+    const bool causal = mask_mode == MGB_MASK_CAUSAL;
+    const bool tril = mask_mode == MGB_MASK_ADD_TRIL_ONES;
+    const int nkv_all = (T + BKV - 1) / BKV;
+    const int nkv = causal ? min(qb + 1, nkv_all) : nkv_all;
+    const int row0 = b * T;                          // first row of this sequence in the [B*T, 3C] view
+
+    if (warp == 4 && lane == 0) {
+        tma_prefetch_desc(&tmap_qkv);
+        mbar_init(q_full, 1); mbar_init(k_full, 1); mbar_init(k_empty, 1); mbar_init(v_full, 1); mbar_init(v_empty, 1);
+        mbar_init(s_full, 1); mbar_init(p_ready, 4); mbar_init(pv_done, 1);
+        fence_mbar_init();
+    }
+    if (warp == 5) tmem_alloc(tmem_base_ptr, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_base_ptr;
+
+    if (warp == 4) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            mbar_arrive_expect_tx(q_full, TILE_BYTES);
+            tma_load_2d(sQ, &tmap_qkv, q_full, h * D, row0 + q0);
+            for (int j = 0; j < nkv; ++j) {
+                const uint32_t ph = (uint32_t)(j & 1);
+                mbar_wait(k_empty, ph ^ 1);           // S_{j-1} has consumed the previous K
+                mbar_arrive_expect_tx(k_full, TILE_BYTES);
+                tma_load_2d(sK, &tmap_qkv, k_full, C + h * D, row0 + j * BKV);
+                mbar_wait(v_empty, ph ^ 1);           // P V_{j-1} has consumed the previous V
+                mbar_arrive_expect_tx(v_full, TILE_BYTES);
+                tma_load_2d(sV, &tmap_qkv, v_full, 2 * C + h * D, row0 + j * BKV);
+            }
+        }
+    } else if (warp == 5) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc_s = make_idesc_bf16(BQ, BKV, 0, 0);   // S: 128 x 128, both K-major
+            const uint32_t idesc_o = make_idesc_bf16(BQ, D, 0, 1);     // O: 128 x 64, V MN-major
+            const uint32_t aQ = smem_u32(sQ), aK = smem_u32(sK), aV = smem_u32(sV);
+            mbar_wait(q_full, 0);
+            mbar_wait(k_full, 0);
+            tc_fence_after();
+#pragma unroll
+            for (int k = 0; k < D / 16; ++k)
+                umma_bf16_ss(tmem_base + kColS, make_smem_desc_sw128(aQ + k * 32, 0, 1024),
+                             make_smem_desc_sw128(aK + k * 32, 0, 1024), idesc_s, k > 0 ? 1u : 0u);
+            umma_commit(k_empty);
+            umma_commit(s_full);
+            for (int j = 0; j < nkv; ++j) {
+                const uint32_t ph = (uint32_t)(j & 1);
+                mbar_wait(p_ready, ph);               // P_j in TMEM, O rescaled if needed, S consumed
+                mbar_wait(v_full, ph);
+                tc_fence_after();
+#pragma unroll
+                for (int kk = 0; kk < BKV / 16; ++kk)   // A = P from TMEM: 16 bf16 = 8 packed columns per step
+                    umma_bf16_ts(tmem_base + kColO, tmem_base + kColP + kk * 8,
+                                 make_smem_desc_sw128(aV + kk * 2048, TILE_BYTES, 1024), idesc_o,
+                                 (j > 0 || kk > 0) ? 1u : 0u);
+                umma_commit(v_empty);
+                umma_commit(pv_done);
+                if (j + 1 < nkv) {
+                    mbar_wait(k_full, ph ^ 1);
+                    tc_fence_after();
+#pragma unroll
+                    for (int k = 0; k < D / 16; ++k)
+                        umma_bf16_ss(tmem_base + kColS, make_smem_desc_sw128(aQ + k * 32, 0, 1024),
+                                     make_smem_desc_sw128(aK + k * 32, 0, 1024), idesc_s, k > 0 ? 1u : 0u);
+                    umma_commit(k_empty);
+                    umma_commit(s_full);
+                }
+            }
+        }
+    } else {
+        // ===================== softmax: one thread per query row =====================
+        const int r = warp * 32 + lane;              // row inside the tile == TMEM lane
+        const int q = q0 + r;
+        const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16);
+        float m_run = -INFINITY, l_run = 0.f;
+        for (int j = 0; j < nkv; ++j) {
+            const uint32_t ph = (uint32_t)(j & 1);
+            const int kvalid = min(BKV, T - j * BKV);            // keys of this block that exist
+            const bool diag = (j == qb);
+            const bool need_mask = (kvalid < BKV) || (causal && diag);
+            const float bias_all = (tril && j < qb) ? LOG2E : 0.f;
+            const bool bias_diag = tril && diag;
+            const bool fast = !need_mask && !bias_diag;
+            mbar_wait(s_full, ph);
+            tc_fence_after();
+            // ---- pass 1: row maximum of this block (log2 domain); 64 columns per TMEM round trip ----
+            float mx = -INFINITY;
+#pragma unroll 1
+            for (int c = 0; c < 2; ++c) {
+                uint32_t s0[32], s1[32];
+                tmem_ld_32x32b_x32(taddr + kColS + c * 64, s0);
+                tmem_ld_32x32b_x32(taddr + kColS + c * 64 + 32, s1);
+                tmem_ld_wait();
+                if (fast) {
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) mx = fmaxf(mx, fmaxf(__uint_as_float(s0[e]), __uint_as_float(s1[e])));
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 64; ++e) {
+                        const int col = c * 64 + e;
+                        float x = fmaf(__uint_as_float(e < 32 ? s0[e & 31] : s1[e & 31]), scale_log2, bias_all);
+                        if (bias_diag && col <= r) x += LOG2E;
+                        if (col >= kvalid || (causal && diag && col > r)) x = -INFINITY;
+                        mx = fmaxf(mx, x);
+                    }
+                }
+            }
+            if (fast) mx = fmaf(mx, scale_log2, bias_all);
+            // ---- running max with lazy rescale ----
+            float factor = 1.0f;
+            const bool grow = mx > m_run + kRescaleThreshold;    // also true on the first block (m_run = -inf)
+            if (grow) {
+                factor = exp2f(m_run - mx);                      // 0 on the first block
+                m_run = mx;
+                l_run *= factor;
+            }
+            if (j > 0) {
+                mbar_wait(pv_done, ph ^ 1);                      // P V_{j-1} finished: P columns free, O stable
+                tc_fence_after();
+                if (__any_sync(0xffffffffu, grow)) {
+#pragma unroll 1
+                    for (int c = 0; c < 2; ++c) {
+                        uint32_t ov[32];
+                        tmem_ld_32x32b_x32(taddr + kColO + c * 32, ov);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) ov[e] = __float_as_uint(__uint_as_float(ov[e]) * factor);
+                        tmem_st_32x32b_x32(taddr + kColO + c * 32, ov);
+                    }
+                }
+            }
+            // ---- pass 2: P = exp2(x - m_run), row sum, bf16 pairs back into TMEM ----
+            const float off = bias_all - m_run;
+            float rs = 0.f;
+#pragma unroll 1
+            for (int c = 0; c < 2; ++c) {
+                uint32_t s0[32], s1[32];
+                tmem_ld_32x32b_x32(taddr + kColS + c * 64, s0);
+                tmem_ld_32x32b_x32(taddr + kColS + c * 64 + 32, s1);
+                tmem_ld_wait();
+                uint32_t pk[32];
+                if (fast) {
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) {
+                        const float a0 = exp2f(fmaf(__uint_as_float(s0[2 * e]), scale_log2, off));
+                        const float a1 = exp2f(fmaf(__uint_as_float(s0[2 * e + 1]), scale_log2, off));
+                        const float b0 = exp2f(fmaf(__uint_as_float(s1[2 * e]), scale_log2, off));
+                        const float b1 = exp2f(fmaf(__uint_as_float(s1[2 * e + 1]), scale_log2, off));
+                        rs += (a0 + a1) + (b0 + b1);
+                        pk[e] = pack_bf16x2(a0, a1);
+                        pk[16 + e] = pack_bf16x2(b0, b1);
+                    }
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) {
+                        float pv[2];
+#pragma unroll
+                        for (int t2 = 0; t2 < 2; ++t2) {
+                            const int idx = 2 * e + t2;                       // 0..63 inside this 64-column group
+                            const int col = c * 64 + idx;
+                            float x = fmaf(__uint_as_float(idx < 32 ? s0[idx & 31] : s1[idx & 31]), scale_log2, off);
+                            if (bias_diag && col <= r) x += LOG2E;
+                            const bool dead = col >= kvalid || (causal && diag && col > r);
+                            pv[t2] = dead ? 0.f : exp2f(x);
+                        }
+                        rs += pv[0] + pv[1];
+                        pk[e] = pack_bf16x2(pv[0], pv[1]);
+                    }
+                }
+                tmem_st_32x32b_x32(taddr + kColP + c * 32, pk);
+            }
+            l_run += rs;
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(p_ready);
+        }
+        // ---- epilogue: O / l, log-sum-exp ----
+        mbar_wait(pv_done, (uint32_t)((nkv - 1) & 1));
+        tc_fence_after();
+        const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
+        __nv_bfloat16* orow = out + ((int64_t)(row0 + q)) * C + (int64_t)h * D;
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+            uint32_t ov[32];
+            __syncwarp();
+            tmem_ld_32x32b_x32(taddr + kColO + c * 32, ov);
+            tmem_ld_wait();
+            if (q < T) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    stg128(orow + c * 32 + u * 8,
+                           make_uint4(pack_bf16x2(__uint_as_float(ov[u * 8 + 0]) * inv, __uint_as_float(ov[u * 8 + 1]) * inv),
+                                      pack_bf16x2(__uint_as_float(ov[u * 8 + 2]) * inv, __uint_as_float(ov[u * 8 + 3]) * inv),
+                                      pack_bf16x2(__uint_as_float(ov[u * 8 + 4]) * inv, __uint_as_float(ov[u * 8 + 5]) * inv),
+                                      pack_bf16x2(__uint_as_float(ov[u * 8 + 6]) * inv, __uint_as_float(ov[u * 8 + 7]) * inv)));
+            }
+        }
+        if (q < T) lse[((int64_t)b * H + h) * T + q] = (m_run + log2f(l_run)) * LN2;
+    }
+
+    __syncwarp();
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 5) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int mask_mode, float scale,
+               cudaStream_t stream) {
+    static std::once_flag once;
+    std::call_once(once, [] {
+        cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    });
+    CUtensorMap tm;
+    const int64_t C3 = (int64_t)3 * H * D;
+    int rc = gemm::make_map_2d(&tm, qkv, C3, (int64_t)B * T, C3, 64, 128);
+    if (rc) return rc;
+    dim3 grid((T + BQ - 1) / BQ, B * H);
+    attn_fwd_tc_kernel<<<grid, kThreads, SMEM_BYTES, stream>>>(tm, (__nv_bfloat16*)out, lse, T, H, mask_mode,
+                                                               scale * LOG2E);
+    return kOk;
+}
+
+// =====================================================================================================
+// backward (recompute), head size 64
+// =====================================================================================================
+// One CTA = one block of 128 keys of one (batch, head); it walks over the query blocks that see those keys.
+// Everything is computed TRANSPOSED (rows = keys) so that a thread owns one key row in TMEM and the
+// recomputed P^T / dS^T are directly the A operands of the dV / dK products:
+//   S^T  = K Q^T          tcgen05.mma 128x128x64   TMEM cols [  0,128)
+//   dP^T = V dO^T         tcgen05.mma 128x128x64   TMEM cols [128,256)
+//   P^T  = exp2(S^T*c - lse_q), dS^T = P^T (dP^T - delta_q) * scale      (8 warps, thread = key row, half the queries each)
+//   dV  += P^T dO         A = P^T from TMEM cols [256,320), B = dO tile as MN-major operand; TMEM cols [384,448)
+//   dK  += dS^T Q         A = dS^T from shared memory (K-major view), B = Q tile (MN-major);  TMEM cols [320,384)
+//   dQ_i = dS K           A = the SAME shared-memory dS^T read as an MN-major operand, B = K tile (MN-major);
+//                         TMEM cols [448,512), drained with fp32 vector atomics into dq_accum
+// tcgen05.mma instructions of one thread execute in order, so "S^T of the next query block is done" implies
+// every product of the current block is done: no extra barriers guard the P^T / dS^T / dQ buffers.
+constexpr int kBwdThreads = 320;                  // 8 elementwise warps + TMA warp + MMA warp
+constexpr uint32_t kBwdTmemCols = 512;
+constexpr uint32_t cST = 0, cDPT = 128, cPT = 256, cDK = 320, cDV = 384, cDQ = 448;
+constexpr int BWD_SMEM = 8 * TILE_BYTES + 2 * 128 * 8 + 1024 + 256;   // K, V, 2x(Q,dO), dS^T (2 atoms), lse/delta x2
+
+__device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+          "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
+
+__global__ void __launch_bounds__(kBwdThreads, 1)
+attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do,
+                   const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_accum,
+                   __nv_bfloat16* __restrict__ dqkv, int T, int H, int mask_mode, float scale, float scale_log2) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sK = smem;
+    uint8_t* sV = smem + TILE_BYTES;
+    uint8_t* sQ = smem + 2 * TILE_BYTES;             // [2] stages: Q at +0, dO at +TILE_BYTES
+    uint8_t* sdS = smem + 6 * TILE_BYTES;            // dS^T: two 64-query atoms of 128 key rows x 128 B
+    float2* sLD = reinterpret_cast<float2*>(smem + 8 * TILE_BYTES);     // [2][128] (lse * log2e, delta)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 8 * TILE_BYTES + 2 * 128 * 8);
+    uint64_t* kv_full = bars + 0;
+    uint64_t* qdo_full = bars + 1;     // [2]
+    uint64_t* qdo_empty = bars + 3;    // [2]
+    uint64_t* s_full = bars + 5;
+    uint64_t* p_ready = bars + 6;
+    uint64_t* all_done = bars + 7;
+    uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(bars + 8);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = blockIdx.y / H, h = blockIdx.y % H;
+    const int kb = blockIdx.x;
+    const int k0 = kb * BKV;
+    const int C = H * D;
+    const bool causal = mask_mode == MGB_MASK_CAUSAL;
+    const bool tril = mask_mode == MGB_MASK_ADD_TRIL_ONES;
+    const int nq = (T + BQ - 1) / BQ;
+    const int i_begin = causal ? kb : 0;
+    const int nblk = nq - i_begin;
+    const int row0 = b * T;
+
+    if (warp == 8 && lane == 0) {
+        tma_prefetch_desc(&tmap_qkv);
+        tma_prefetch_desc(&tmap_do);
+        mbar_init(kv_full, 1);
+        for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
+        mbar_init(s_full, 1); mbar_init(p_ready, 8); mbar_init(all_done, 1);
+        fence_mbar_init();
+    }
+    if (warp == 9) tmem_alloc(tmem_base_ptr, kBwdTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_base_ptr;
+
+    if (warp == 8) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            mbar_arrive_expect_tx(kv_full, 2 * TILE_BYTES);
+            tma_load_2d(sK, &tmap_qkv, kv_full, C + h * D, row0 + k0);
+            tma_load_2d(sV, &tmap_qkv, kv_full, 2 * C + h * D, row0 + k0);
+            for (int n = 0; n < nblk; ++n) {
+                const int st = n & 1;
+                const uint32_t ph = (uint32_t)((n >> 1) & 1);
+                mbar_wait(&qdo_empty[st], ph ^ 1);
+                mbar_arrive_expect_tx(&qdo_full[st], 2 * TILE_BYTES);
+                const int qrow = row0 + (i_begin + n) * BQ;
+                tma_load_2d(sQ + st * 2 * TILE_BYTES, &tmap_qkv, &qdo_full[st], h * D, qrow);
+                tma_load_2d(sQ + st * 2 * TILE_BYTES + TILE_BYTES, &tmap_do, &qdo_full[st], h * D, qrow);
+            }
+        }
+    } else if (warp == 9) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc_kk = make_idesc_bf16(128, 128, 0, 0);   // S^T, dP^T
+            const uint32_t idesc_kn = make_idesc_bf16(128, D, 0, 1);     // dV (A in TMEM), dK (A K-major smem)
+            const uint32_t idesc_nn = make_idesc_bf16(128, D, 1, 1);     // dQ (A = dS^T read MN-major)
+            const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aS = smem_u32(sdS);
+            mbar_wait(kv_full, 0);
+            for (int n = 0; n < nblk; ++n) {
+                const int st = n & 1;
+                const uint32_t aQ = smem_u32(sQ + st * 2 * TILE_BYTES), aO = aQ + TILE_BYTES;
+                mbar_wait(&qdo_full[st], (uint32_t)((n >> 1) & 1));
+                tc_fence_after();
+#pragma unroll
+                for (int k = 0; k < D / 16; ++k)
+                    umma_bf16_ss(tmem_base + cST, make_smem_desc_sw128(aK + k * 32, 0, 1024),
+                                 make_smem_desc_sw128(aQ + k * 32, 0, 1024), idesc_kk, k > 0 ? 1u : 0u);
+#pragma unroll
+                for (int k = 0; k < D / 16; ++k)
+                    umma_bf16_ss(tmem_base + cDPT, make_smem_desc_sw128(aV + k * 32, 0, 1024),
+                                 make_smem_desc_sw128(aO + k * 32, 0, 1024), idesc_kk, k > 0 ? 1u : 0u);
+                umma_commit(s_full);
+                mbar_wait(p_ready, (uint32_t)(n & 1));
+                tc_fence_after();
+#pragma unroll
+                for (int kk = 0; kk < BQ / 16; ++kk)     // dV += P^T dO   (reduction over the 128 queries)
+                    umma_bf16_ts(tmem_base + cDV, tmem_base + cPT + kk * 8,
+                                 make_smem_desc_sw128(aO + kk * 2048, TILE_BYTES, 1024), idesc_kn,
+                                 (n > 0 || kk > 0) ? 1u : 0u);
+#pragma unroll
+                for (int kk = 0; kk < BQ / 16; ++kk)     // dK += dS^T Q
+                    umma_bf16_ss(tmem_base + cDK,
+                                 make_smem_desc_sw128(aS + (kk >> 2) * TILE_BYTES + (kk & 3) * 32, 0, 1024),
+                                 make_smem_desc_sw128(aQ + kk * 2048, TILE_BYTES, 1024), idesc_kn,
+                                 (n > 0 || kk > 0) ? 1u : 0u);
+#pragma unroll
+                for (int kk = 0; kk < BKV / 16; ++kk)    // dQ_i = dS K    (reduction over the 128 keys)
+                    umma_bf16_ss(tmem_base + cDQ, make_smem_desc_sw128(aS + kk * 2048, TILE_BYTES, 1024),
+                                 make_smem_desc_sw128(aK + kk * 2048, TILE_BYTES, 1024), idesc_nn, kk > 0 ? 1u : 0u);
+                umma_commit(&qdo_empty[st]);
+            }
+            umma_commit(all_done);
+        }
+    } else {
+        // ===================== elementwise warps: thread = key row, warpgroup = half of the queries ==========
+        const int quarter = warp & 3, wg = warp >> 2;
+        const int r = quarter * 32 + lane;               // key row inside the block == TMEM lane
+        const int key = k0 + r;
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+        const uint32_t swz = (uint32_t)(r & 7);
+        const int etid = threadIdx.x;                    // 0..255
+        const int64_t od = (int64_t)C;
+
+        auto drain_dq = [&](int iq) {
+            // dQ rows = queries of block iq (TMEM lane = query row); this warpgroup takes 32 of the 64 features
+            uint32_t dv[32];
+            __syncwarp();
+            tmem_ld_32x32b_x32(taddr + cDQ + wg * 32, dv);
+            tmem_ld_wait();
+            const int qrow = iq * BQ + r;
+            if (qrow < T) {
+                float* dst = dq_accum + ((int64_t)(row0 + qrow)) * od + (int64_t)h * D + wg * 32;
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    red_add_f32x4(dst + u * 4, __uint_as_float(dv[u * 4]), __uint_as_float(dv[u * 4 + 1]),
+                                  __uint_as_float(dv[u * 4 + 2]), __uint_as_float(dv[u * 4 + 3]));
+            }
+        };
+
+        for (int n = 0; n < nblk; ++n) {
+            const int i = i_begin + n;
+            const int buf = n & 1;
+            // stage lse (log2 domain) / delta of this query block
+            if (etid < 128) {
+                const int t = i * BQ + etid;
+                float2 v = make_float2(INFINITY, 0.f);
+                if (t < T) {
+                    const int64_t idx = ((int64_t)b * H + h) * T + t;
+                    v = make_float2(lse[idx] * LOG2E, delta[idx]);
+                }
+                sLD[buf * 128 + etid] = v;
+            }
+            named_bar_sync(1, 256);
+            mbar_wait(s_full, (uint32_t)(n & 1));
+            tc_fence_after();
+            if (n > 0) drain_dq(i - 1);                  // S^T_n done  =>  dQ of the previous block is complete
+            const bool diag = causal && (i == kb);
+            const bool need_mask = diag || (k0 + BKV > T) || (i * BQ + BQ > T);
+            const float bias_all = (tril && i > kb) ? LOG2E : 0.f;
+            const bool bias_diag = tril && (i == kb);
+            const float2* ld = sLD + buf * 128 + wg * 64;
+#pragma unroll 1
+            for (int c = 0; c < 2; ++c) {
+                uint32_t sv[32], dp[32];
+                tmem_ld_32x32b_x32(taddr + cST + wg * 64 + c * 32, sv);
+                tmem_ld_32x32b_x32(taddr + cDPT + wg * 64 + c * 32, dp);
+                tmem_ld_wait();
+                uint32_t pk[16], dk[16];
+#pragma unroll
+                for (int e = 0; e < 16; ++e) {
+                    float pv[2], dsv[2];
+#pragma unroll
+                    for (int t2 = 0; t2 < 2; ++t2) {
+                        const int cl = c * 32 + 2 * e + t2;             // query column inside this warpgroup's half
+                        const int col = wg * 64 + cl;                   // query column inside the block
+                        const float2 ldv = ld[cl];
+                        float x = fmaf(__uint_as_float(sv[2 * e + t2]), scale_log2, bias_all - ldv.x);
+                        float p;
+                        if (!need_mask && !bias_diag) {
+                            p = exp2f(x);
+                        } else {
+                            const int qg = i * BQ + col;
+                            if (bias_diag && r <= col) x += LOG2E;
+                            const bool dead = (key >= T) || (qg >= T) || (diag && r > col);
+                            p = dead ? 0.f : exp2f(x);
+                        }
+                        pv[t2] = p;
+                        dsv[t2] = p * (__uint_as_float(dp[2 * e + t2]) - ldv.y) * scale;
+                    }
+                    pk[e] = pack_bf16x2(pv[0], pv[1]);
+                    dk[e] = pack_bf16x2(dsv[0], dsv[1]);
+                }
+                tmem_st_32x32b_x16(taddr + cPT + wg * 32 + c * 16, pk);
+                // dS^T row `r`, queries [wg*64 + c*32, +32): four 16-byte units of atom `wg`
+                uint8_t* rowp = sdS + wg * TILE_BYTES + r * 128;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const uint32_t jj = (uint32_t)(c * 4 + u);
+                    *reinterpret_cast<uint4*>(rowp + ((jj ^ swz) << 4)) =
+                        make_uint4(dk[u * 4 + 0], dk[u * 4 + 1], dk[u * 4 + 2], dk[u * 4 + 3]);
+                }
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(p_ready);
+        }
+        // ---- epilogue: last dQ, then dK / dV of this key block ----
+        mbar_wait(all_done, 0);
+        tc_fence_after();
+        drain_dq(i_begin + nblk - 1);
+        const int64_t ld3 = (int64_t)3 * C;
+        __nv_bfloat16* krow = dqkv + ((int64_t)(row0 + key)) * ld3 + C + (int64_t)h * D + wg * 32;
+#pragma unroll 1
+        for (int which = 0; which < 2; ++which) {        // 0: dK, 1: dV
+            uint32_t v[32];
+            __syncwarp();
+            tmem_ld_32x32b_x32(taddr + (which ? cDV : cDK) + wg * 32, v);
+            tmem_ld_wait();
+            if (key < T) {
+                __nv_bfloat16* dst = krow + (int64_t)which * C;
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    stg128(dst + u * 8,
+                           make_uint4(pack_bf16x2(__uint_as_float(v[u * 8 + 0]), __uint_as_float(v[u * 8 + 1])),
+                                      pack_bf16x2(__uint_as_float(v[u * 8 + 2]), __uint_as_float(v[u * 8 + 3])),
+                                      pack_bf16x2(__uint_as_float(v[u * 8 + 4]), __uint_as_float(v[u * 8 + 5])),
+                                      pack_bf16x2(__uint_as_float(v[u * 8 + 6]), __uint_as_float(v[u * 8 + 7]))));
+            }
+        }
+    }
+
+    __syncwarp();
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kBwdTmemCols);
+    }
+}
+
+// main backward kernel only: delta must be precomputed and dq_accum zeroed by the caller (attention.cu)
+int launch_bwd_main(const void* qkv, const void* dout, const float* lse, const float* delta, float* dq_accum,
+                    void* dqkv, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream) {
+    static std::once_flag once;
+    std::call_once(once, [] {
+        cudaFuncSetAttribute(attn_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
+    });
+    CUtensorMap tq, td;
+    const int64_t C = (int64_t)H * D, C3 = 3 * C;
+    int rc = gemm::make_map_2d(&tq, qkv, C3, (int64_t)B * T, C3, 64, 128);
+    if (rc) return rc;
+    rc = gemm::make_map_2d(&td, dout, C, (int64_t)B * T, C, 64, 128);
+    if (rc) return rc;
+    dim3 grid((T + BKV - 1) / BKV, B * H);
+    attn_bwd_tc_kernel<<<grid, kBwdThreads, BWD_SMEM, stream>>>(tq, td, lse, delta, dq_accum, (__nv_bfloat16*)dqkv, T, H,
+                                                                mask_mode, scale, scale * LOG2E);
+    return kOk;
+}
+
+}  // namespace attn_tc
+}  // namespace mgb

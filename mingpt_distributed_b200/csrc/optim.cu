@@ -288,11 +288,13 @@ extern "C" int64_t mgb_launch_count(void) { return g_launches.load(std::memory_o
 namespace mgb {
 std::atomic<int> g_opt_gemm_single{0};
 std::atomic<int> g_opt_gemm_direct_store{0};
+std::atomic<int> g_opt_attn_mma{0};
 }
 extern "C" int mgb_set_option(const char* key, int value) {
     if (!key) return -1;
     if (!std::strcmp(key, "gemm_single")) return mgb::g_opt_gemm_single.exchange(value);
     if (!std::strcmp(key, "gemm_direct_store")) return mgb::g_opt_gemm_direct_store.exchange(value);
+    if (!std::strcmp(key, "attn_mma")) return mgb::g_opt_attn_mma.exchange(value);
     return -1;
 }
 

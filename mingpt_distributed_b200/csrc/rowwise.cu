@@ -96,7 +96,7 @@ ln_fwd_generic_kernel(const __nv_bfloat16* __restrict__ x, const float* __restri
 }
 
 template <int MAXCH>
-__global__ void __launch_bounds__(LN_WARPS * 32)
+__global__ void __launch_bounds__(LN_WARPS * 32, MAXCH <= 3 ? 2 : 1)
 ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
               const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd,
               const __nv_bfloat16* dres, __nv_bfloat16* dx, float* __restrict__ dgamma, float* __restrict__ dbeta,
@@ -108,6 +108,8 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
     for (int c = threadIdx.x; c < 2 * cols; c += blockDim.x) ln_smem[c] = 0.f;
     __syncthreads();
 
+    // Register diet (occupancy is what hides the HBM latency here): gamma and the dgamma/dbeta partial sums
+    // stay in registers, x and dy stay PACKED (bf16) between the two passes and xhat is recomputed.
     float gam[MAXCH][8], dg[MAXCH][8], db[MAXCH][8];
 #pragma unroll
     for (int i = 0; i < MAXCH; ++i) {
@@ -121,26 +123,30 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
     }
     for (int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp; row < rows; row += (int64_t)gridDim.x * LN_WARPS) {
         const float mu = mean[row], rs = rstd[row];
-        float xh[MAXCH][8], gdy[MAXCH][8];
+        uint4 px[MAXCH], pd[MAXCH];
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
         for (int i = 0; i < MAXCH; ++i) {
             const int ch = lane + 32 * i;
             if (ch < nch) {
-                const uint4 vx = ldg128(x + row * cols + ch * 8);
-                const uint4 vd = ldg128(dy + row * cols + ch * 8);
-                const uint32_t wx[4] = {vx.x, vx.y, vx.z, vx.w};
-                const uint32_t wd[4] = {vd.x, vd.y, vd.z, vd.w};
+                px[i] = ldg128(x + row * cols + ch * 8);
+                pd[i] = ldg128(dy + row * cols + ch * 8);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < MAXCH; ++i) {
+            const int ch = lane + 32 * i;
+            if (ch < nch) {
+                const uint32_t wx[4] = {px[i].x, px[i].y, px[i].z, px[i].w};
+                const uint32_t wd[4] = {pd[i].x, pd[i].y, pd[i].z, pd[i].w};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     const float2 fx = unpack_bf16x2(wx[e]);
                     const float2 fd = unpack_bf16x2(wd[e]);
                     const float h0 = (fx.x - mu) * rs, h1 = (fx.y - mu) * rs;
-                    xh[i][2 * e] = h0; xh[i][2 * e + 1] = h1;
                     dg[i][2 * e] += fd.x * h0; dg[i][2 * e + 1] += fd.y * h1;
                     db[i][2 * e] += fd.x;      db[i][2 * e + 1] += fd.y;
                     const float g0 = fd.x * gam[i][2 * e], g1 = fd.y * gam[i][2 * e + 1];
-                    gdy[i][2 * e] = g0; gdy[i][2 * e + 1] = g1;
                     s1 += g0 + g1;
                     s2 += g0 * h0 + g1 * h1;
                 }
@@ -152,9 +158,17 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
         for (int i = 0; i < MAXCH; ++i) {
             const int ch = lane + 32 * i;
             if (ch < nch) {
+                const uint32_t wx[4] = {px[i].x, px[i].y, px[i].z, px[i].w};
+                const uint32_t wd[4] = {pd[i].x, pd[i].y, pd[i].z, pd[i].w};
                 float r[8];
 #pragma unroll
-                for (int e = 0; e < 8; ++e) r[e] = rs * (gdy[i][e] - m1 - xh[i][e] * m2);
+                for (int e = 0; e < 4; ++e) {
+                    const float2 fx = unpack_bf16x2(wx[e]);
+                    const float2 fd = unpack_bf16x2(wd[e]);
+                    const float h0 = (fx.x - mu) * rs, h1 = (fx.y - mu) * rs;
+                    r[2 * e] = rs * (fd.x * gam[i][2 * e] - m1 - h0 * m2);
+                    r[2 * e + 1] = rs * (fd.y * gam[i][2 * e + 1] - m1 - h1 * m2);
+                }
                 if (dres) {
                     const uint4 vr = ldg128(dres + row * cols + ch * 8);
                     const uint32_t wr[4] = {vr.x, vr.y, vr.z, vr.w};
@@ -455,12 +469,14 @@ extern "C" int mgb_layernorm_bwd(const void* dy, const void* x, const float* gam
     const bool vec = (cols % 8 == 0) && cols <= 2048 && ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0) &&
                      ((uintptr_t)dx % 16 == 0) && (!dres || (uintptr_t)dres % 16 == 0);
     // persistent: each CTA owns register accumulators for dgamma/dbeta, flushed once
-    const int grid = grid_for(rows, LN_WARPS * 4, num_sms() * 2);
+    const int grid = grid_for(rows, LN_WARPS * 4, num_sms() * (cols <= 768 ? 4 : 2));
     const size_t smem = (size_t)2 * cols * sizeof(float);
     if (!vec) ln_bwd_generic_kernel<<<grid, LN_WARPS * 32, 0, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, dbeta, rows, cols);
     else if (cols <= 256) ln_bwd_kernel<1><<<grid, LN_WARPS * 32, smem, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, dbeta, rows, cols);
     else if (cols <= 512) ln_bwd_kernel<2><<<grid, LN_WARPS * 32, smem, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, dbeta, rows, cols);
+    else if (cols <= 768) ln_bwd_kernel<3><<<grid, LN_WARPS * 32, smem, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, dbeta, rows, cols);
     else if (cols <= 1024) ln_bwd_kernel<4><<<grid, LN_WARPS * 32, smem, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, dbeta, rows, cols);
+    else if (cols <= 1536) ln_bwd_kernel<6><<<grid, LN_WARPS * 32, smem, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, dbeta, rows, cols);
     else ln_bwd_kernel<8><<<grid, LN_WARPS * 32, smem, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, dbeta, rows, cols);
     count_launch(1);
     MGB_CHECK_LAUNCH();
