@@ -309,7 +309,7 @@ int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int 
 constexpr int kBwdThreads = 320;                  // 8 elementwise warps + TMA warp + MMA warp
 constexpr uint32_t kBwdTmemCols = 512;
 constexpr uint32_t cST = 0, cDPT = 128, cPT = 256, cDK = 320, cDV = 384, cDQ = 448;
-constexpr int BWD_SMEM = 8 * TILE_BYTES + 2 * 128 * 8 + 1024 + 256;   // K, V, 2x(Q,dO), dS^T (2 atoms), lse/delta x2
+constexpr int BWD_SMEM = 10 * TILE_BYTES + 2 * 128 * 8 + 1024 + 256;   // K, V, 2x(Q,dO), dS^T (2 atoms), dQ staging x2, lse/delta x2
 
 __device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_t (&r)[16]) {
     asm volatile(
@@ -322,7 +322,7 @@ __device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_
 
 __global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do,
-                   const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_accum,
+                   const __grid_constant__ CUtensorMap tmap_dq, const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_accum,
                    __nv_bfloat16* __restrict__ dqkv, int T, int H, int mask_mode, float scale, float scale_log2) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -330,8 +330,9 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
     uint8_t* sV = smem + TILE_BYTES;
     uint8_t* sQ = smem + 2 * TILE_BYTES;             // [2] stages: Q at +0, dO at +TILE_BYTES
     uint8_t* sdS = smem + 6 * TILE_BYTES;            // dS^T: two 64-query atoms of 128 key rows x 128 B
-    float2* sLD = reinterpret_cast<float2*>(smem + 8 * TILE_BYTES);     // [2][128] (lse * log2e, delta)
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 8 * TILE_BYTES + 2 * 128 * 8);
+    uint8_t* sDQ = smem + 8 * TILE_BYTES;            // two boxes (one per warpgroup): 128 query rows x 32 fp32
+    float2* sLD = reinterpret_cast<float2*>(smem + 10 * TILE_BYTES);    // [2][128] (bias - lse*log2e, delta*scale)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 10 * TILE_BYTES + 2 * 128 * 8);
     uint64_t* kv_full = bars + 0;
     uint64_t* qdo_full = bars + 1;     // [2]
     uint64_t* qdo_empty = bars + 3;    // [2]
@@ -355,6 +356,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
     if (warp == 8 && lane == 0) {
         tma_prefetch_desc(&tmap_qkv);
         tma_prefetch_desc(&tmap_do);
+        tma_prefetch_desc(&tmap_dq);
         mbar_init(kv_full, 1);
         for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
         mbar_init(s_full, 1); mbar_init(p_ready, 8); mbar_init(all_done, 1);
@@ -433,34 +435,47 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
         const uint32_t swz = (uint32_t)(r & 7);
         const int etid = threadIdx.x;                    // 0..255
-        const int64_t od = (int64_t)C;
 
+        uint8_t* dq_box = sDQ + wg * TILE_BYTES;         // this warpgroup's 128 rows x 32 fp32 staging box
+        const bool wg_elected = (quarter == 0) && (lane == 0);
         auto drain_dq = [&](int iq) {
-            // dQ rows = queries of block iq (TMEM lane = query row); this warpgroup takes 32 of the 64 features
+            // dQ rows = queries of block iq (TMEM lane = query row); this warpgroup takes 32 of the 64 features.
+            // TMEM -> registers -> swizzled shared-memory box -> ONE TMA fp32 reduce-add per warpgroup (rows of
+            // queries >= T hold exact zeros because their P is zero, so adding them is harmless).
             uint32_t dv[32];
             __syncwarp();
             tmem_ld_32x32b_x32(taddr + cDQ + wg * 32, dv);
             tmem_ld_wait();
-            const int qrow = iq * BQ + r;
-            if (qrow < T) {
-                float* dst = dq_accum + ((int64_t)(row0 + qrow)) * od + (int64_t)h * D + wg * 32;
+            if (wg_elected) bulk_wait_read<0>();         // the previous reduce has finished reading the box
+            named_bar_sync(2 + wg, 128);
+            uint8_t* rowp = dq_box + r * 128;
 #pragma unroll
-                for (int u = 0; u < 8; ++u)
-                    red_add_f32x4(dst + u * 4, __uint_as_float(dv[u * 4]), __uint_as_float(dv[u * 4 + 1]),
-                                  __uint_as_float(dv[u * 4 + 2]), __uint_as_float(dv[u * 4 + 3]));
+            for (int u = 0; u < 8; ++u)
+                *reinterpret_cast<uint4*>(rowp + (((uint32_t)u ^ swz) << 4)) =
+                    make_uint4(dv[u * 4], dv[u * 4 + 1], dv[u * 4 + 2], dv[u * 4 + 3]);
+            fence_proxy_async_smem();
+            named_bar_sync(2 + wg, 128);
+            if (wg_elected) {
+                tma_reduce_add_2d(&tmap_dq, dq_box, h * D + wg * 32, row0 + iq * BQ);
+                bulk_commit();
             }
         };
 
         for (int n = 0; n < nblk; ++n) {
             const int i = i_begin + n;
             const int buf = n & 1;
-            // stage lse (log2 domain) / delta of this query block
+            const bool diag = causal && (i == kb);
+            const bool need_mask = diag || (k0 + BKV > T) || (i * BQ + BQ > T);
+            const float bias_all = (tril && i > kb) ? LOG2E : 0.f;
+            const bool bias_diag = tril && (i == kb);
+            // stage, per query of this block: (bias - lse) in the log2 domain and delta * scale, so the inner
+            // loop is  p = exp2(fma(s, c, a));  ds = p * fma(dp, scale, -b)
             if (etid < 128) {
                 const int t = i * BQ + etid;
-                float2 v = make_float2(INFINITY, 0.f);
+                float2 v = make_float2(-INFINITY, 0.f);   // queries past the end: p = 0
                 if (t < T) {
                     const int64_t idx = ((int64_t)b * H + h) * T + t;
-                    v = make_float2(lse[idx] * LOG2E, delta[idx]);
+                    v = make_float2(bias_all - lse[idx] * LOG2E, delta[idx] * scale);
                 }
                 sLD[buf * 128 + etid] = v;
             }
@@ -468,10 +483,6 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
             mbar_wait(s_full, (uint32_t)(n & 1));
             tc_fence_after();
             if (n > 0) drain_dq(i - 1);                  // S^T_n done  =>  dQ of the previous block is complete
-            const bool diag = causal && (i == kb);
-            const bool need_mask = diag || (k0 + BKV > T) || (i * BQ + BQ > T);
-            const float bias_all = (tril && i > kb) ? LOG2E : 0.f;
-            const bool bias_diag = tril && (i == kb);
             const float2* ld = sLD + buf * 128 + wg * 64;
 #pragma unroll 1
             for (int c = 0; c < 2; ++c) {
@@ -480,29 +491,35 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
                 tmem_ld_32x32b_x32(taddr + cDPT + wg * 64 + c * 32, dp);
                 tmem_ld_wait();
                 uint32_t pk[16], dk[16];
+                if (!need_mask && !bias_diag) {
 #pragma unroll
-                for (int e = 0; e < 16; ++e) {
-                    float pv[2], dsv[2];
-#pragma unroll
-                    for (int t2 = 0; t2 < 2; ++t2) {
-                        const int cl = c * 32 + 2 * e + t2;             // query column inside this warpgroup's half
-                        const int col = wg * 64 + cl;                   // query column inside the block
-                        const float2 ldv = ld[cl];
-                        float x = fmaf(__uint_as_float(sv[2 * e + t2]), scale_log2, bias_all - ldv.x);
-                        float p;
-                        if (!need_mask && !bias_diag) {
-                            p = exp2f(x);
-                        } else {
-                            const int qg = i * BQ + col;
-                            if (bias_diag && r <= col) x += LOG2E;
-                            const bool dead = (key >= T) || (qg >= T) || (diag && r > col);
-                            p = dead ? 0.f : exp2f(x);
-                        }
-                        pv[t2] = p;
-                        dsv[t2] = p * (__uint_as_float(dp[2 * e + t2]) - ldv.y) * scale;
+                    for (int e = 0; e < 16; ++e) {
+                        const float4 l4 = *reinterpret_cast<const float4*>(ld + c * 32 + 2 * e);   // (a0, b0, a1, b1)
+                        const float p0 = exp2f(fmaf(__uint_as_float(sv[2 * e]), scale_log2, l4.x));
+                        const float p1 = exp2f(fmaf(__uint_as_float(sv[2 * e + 1]), scale_log2, l4.z));
+                        pk[e] = pack_bf16x2(p0, p1);
+                        dk[e] = pack_bf16x2(p0 * fmaf(__uint_as_float(dp[2 * e]), scale, -l4.y),
+                                            p1 * fmaf(__uint_as_float(dp[2 * e + 1]), scale, -l4.w));
                     }
-                    pk[e] = pack_bf16x2(pv[0], pv[1]);
-                    dk[e] = pack_bf16x2(dsv[0], dsv[1]);
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) {
+                        float pv[2], dsv[2];
+#pragma unroll
+                        for (int t2 = 0; t2 < 2; ++t2) {
+                            const int cl = c * 32 + 2 * e + t2;         // query column inside this warpgroup's half
+                            const int col = wg * 64 + cl;               // query column inside the block
+                            const float2 ldv = ld[cl];
+                            float x = fmaf(__uint_as_float(sv[2 * e + t2]), scale_log2, ldv.x);
+                            if (bias_diag && r <= col) x += LOG2E;
+                            const bool dead = (key >= T) || (diag && r > col);   // queries >= T carry a = -inf
+                            const float p = dead ? 0.f : exp2f(x);
+                            pv[t2] = p;
+                            dsv[t2] = p * fmaf(__uint_as_float(dp[2 * e + t2]), scale, -ldv.y);
+                        }
+                        pk[e] = pack_bf16x2(pv[0], pv[1]);
+                        dk[e] = pack_bf16x2(dsv[0], dsv[1]);
+                    }
                 }
                 tmem_st_32x32b_x16(taddr + cPT + wg * 32 + c * 16, pk);
                 // dS^T row `r`, queries [wg*64 + c*32, +32): four 16-byte units of atom `wg`
@@ -532,6 +549,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
             __syncwarp();
             tmem_ld_32x32b_x32(taddr + (which ? cDV : cDK) + wg * 32, v);
             tmem_ld_wait();
+            if (which == 0 && wg_elected) bulk_wait<0>();   // all dQ reduce-adds have left shared memory
             if (key < T) {
                 __nv_bfloat16* dst = krow + (int64_t)which * C;
 #pragma unroll
@@ -561,14 +579,16 @@ int launch_bwd_main(const void* qkv, const void* dout, const float* lse, const f
     std::call_once(once, [] {
         cudaFuncSetAttribute(attn_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
     });
-    CUtensorMap tq, td;
+    CUtensorMap tq, td, tdq;
     const int64_t C = (int64_t)H * D, C3 = 3 * C;
     int rc = gemm::make_map_2d(&tq, qkv, C3, (int64_t)B * T, C3, 64, 128);
     if (rc) return rc;
     rc = gemm::make_map_2d(&td, dout, C, (int64_t)B * T, C, 64, 128);
     if (rc) return rc;
+    rc = gemm::make_map_2d(&tdq, dq_accum, C, (int64_t)B * T, C, 32, 128, /*f32=*/true);
+    if (rc) return rc;
     dim3 grid((T + BKV - 1) / BKV, B * H);
-    attn_bwd_tc_kernel<<<grid, kBwdThreads, BWD_SMEM, stream>>>(tq, td, lse, delta, dq_accum, (__nv_bfloat16*)dqkv, T, H,
+    attn_bwd_tc_kernel<<<grid, kBwdThreads, BWD_SMEM, stream>>>(tq, td, tdq, lse, delta, dq_accum, (__nv_bfloat16*)dqkv, T, H,
                                                                 mask_mode, scale, scale * LOG2E);
     return kOk;
 }
