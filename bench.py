@@ -145,6 +145,7 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=25.0)
     ap.add_argument("--profile-gemm", action="store_true", default=True)
     ap.add_argument("--quick", action="store_true", help="timed loop only (for runs under ncu): no e2e, roofline or cpu legs")
+    ap.add_argument("--no-graph", action="store_true", help="issue every kernel from Python instead of replaying a CUDA graph")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -183,14 +184,19 @@ def main():
     pinned = [(x.pin_memory(), y.pin_memory()) for x, y in host]
     resident = [(x.to(dev), y.to(dev)) for x, y in host]
 
+    stepper = m.GraphedTrainStep(model, opt, 1.0, dp, use_graph=not args.no_graph)
+
     def step_resident(i):
         x, y = resident[i % nbatches]
-        return m.train_step(model, opt, x, y, 1.0, dp, zero_grad=True)
+        return stepper(x, y)
 
     def step_e2e(i):
-        x, y = pinned[i % nbatches]
-        xd, yd = x.to(dev, non_blocking=True), y.to(dev, non_blocking=True)
-        return m.train_step(model, opt, xd, yd, 1.0, dp, zero_grad=True).item()
+        x, y = pinned[i % nbatches]          # pinned host tokens -> static device buffers (H2D inside the step)
+        return stepper(x, y).item()          # device -> host read of the loss every step
+
+    def step_eager(i):
+        x, y = resident[i % nbatches]
+        return m.train_step(model, opt, x, y, 1.0, dp, zero_grad=True)
 
     def barrier():
         if world > 1:
@@ -211,7 +217,10 @@ def main():
             t = torch.tensor([ms], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = t.item()
-        return ms, _lib.launch_count() - n0
+        n = _lib.launch_count() - n0
+        if n == 0:     # CUDA-graph replays: the kernels were recorded once, at capture
+            n = stepper.launches_per_replay((B, T)) * steps
+        return ms, n
 
     for i in range(args.warmup):
         step_resident(i)
@@ -251,12 +260,12 @@ def main():
 
         ops.gemm = timed_gemm
         try:
-            step_resident(0)
+            step_eager(0)
             records.clear()
             t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
             t0.record()
             for i in range(2):
-                step_resident(i)
+                step_eager(i)
             t1.record()
             torch.cuda.synchronize()
         finally:
@@ -286,6 +295,7 @@ def main():
                     config=dict(workload=f"gpt2-124M train step (L12 H12 C768 V50257 T{T}), variant={args.variant}, "
                                          "fp32 master weights + AdamW state, bf16 GEMM/attention operands",
                                 global_batch=world * B, seq_len=T, parallelism=f"dp{world}",
+                                launch="eager (one Python call per kernel)" if args.no_graph else "CUDA graph replay of the whole step",
                                 l2="per-step working set (>10 GB of activations + 2 GB of parameters/state) is far larger than the 126 MB L2"),
                     mfu=dict(flops_per_token=f_tok, of_nominal_2p25pf=value * f_tok / (world * NOMINAL_BF16),
                              of_measured_sustained=value * f_tok / (world * peaks["bf16_sustained"] * 1e12)),

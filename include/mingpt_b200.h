@@ -185,6 +185,9 @@ int mgb_scale_bf16_dev(void* x, int64_t n, const float* alpha, mgb_stream_t stre
  * mgb_adamw_multi updates every tensor described by `table` in ONE launch.  The clip coefficient is
  * computed on the device from *gradnorm_sq (may be NULL = no clipping) so no host sync is needed:
  *   g = grad * grad_scale;  norm = sqrt(*gradnorm_sq) * grad_scale;  g *= min(1, max_norm/(norm+1e-6))
+ * step_dev (DEVICE int32, may be NULL): when given, the step count for the bias corrections is read from it
+ * instead of `step`, so a captured CUDA graph of the training step can be replayed (host arguments are frozen
+ * at capture time; the caller increments *step_dev inside the graph).
  * ------------------------------------------------------------------------------------------------- */
 typedef struct mgb_adamw_chunk {
     int64_t offset;      /* element offset into the flat fp32 param / grad / m / v buffers */
@@ -195,7 +198,7 @@ int mgb_sumsq_f32(const float* x, int64_t n, float* out, mgb_stream_t stream);
 int mgb_adamw_multi(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, void* params_bf16,
                     const mgb_adamw_chunk* table /*device*/, int32_t num_chunks, float lr, float beta1, float beta2,
                     float eps, int32_t step, float grad_scale, const float* gradnorm_sq, float max_norm,
-                    mgb_stream_t stream);
+                    const int32_t* step_dev, mgb_stream_t stream);
 /* grads *= min(1, max_norm / (sqrt(*gradnorm_sq) + 1e-6))  -- for callers that keep a foreign optimizer */
 int mgb_clip_scale_f32(float* grads, int64_t n, const float* gradnorm_sq, float max_norm, mgb_stream_t stream);
 

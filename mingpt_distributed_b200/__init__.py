@@ -13,10 +13,10 @@ from .model import (GPT, CfgNode, GPTConfig, LazyLogits, OptimizerConfig, create
 from .char_dataset import CharDataset, DataConfig
 from .optim import FusedAdamW, clip_grad_norm_
 from .parallel import DataParallel, GradBuckets, plan_buckets
-from .trainer import GPTTrainer, GPTTrainerConfig, ModelSnapshot, Trainer, train_step
+from .trainer import GPTTrainer, GPTTrainerConfig, GraphedTrainStep, ModelSnapshot, Trainer, train_step
 from .config import load_config
 
 __all__ = ["GPT", "CfgNode", "GPTConfig", "LazyLogits", "OptimizerConfig", "create_optimizer", "param_groups",
            "print_model_size", "CharDataset", "DataConfig", "FusedAdamW", "clip_grad_norm_", "DataParallel",
-           "GradBuckets", "plan_buckets", "GPTTrainer", "GPTTrainerConfig", "ModelSnapshot", "Trainer",
+           "GradBuckets", "plan_buckets", "GPTTrainer", "GraphedTrainStep", "GPTTrainerConfig", "ModelSnapshot", "Trainer",
            "train_step", "load_config"]

@@ -67,7 +67,7 @@ SIGNATURES = {
     "mgb_axpy_f32_dev": [_P, _P, _P, _I64, _P],
     "mgb_scale_bf16_dev": [_P, _I64, _P, _P],
     "mgb_sumsq_f32": [_P, _I64, _P, _P],
-    "mgb_adamw_multi": [_P, _P, _P, _P, _P, _P, _I32, _F, _F, _F, _F, _I32, _F, _P, _F, _P],
+    "mgb_adamw_multi": [_P, _P, _P, _P, _P, _P, _I32, _F, _F, _F, _F, _I32, _F, _P, _F, _P, _P],
     "mgb_clip_scale_f32": [_P, _I64, _P, _F, _P],
     "mgb_set_option": [C.c_char_p, _I32],
 }

@@ -82,7 +82,15 @@ __global__ void __launch_bounds__(256)
 adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
              __nv_bfloat16* __restrict__ pb, const mgb_adamw_chunk* __restrict__ table, float lr, float beta1,
              float beta2, float eps, float step_size, float inv_bc2_sqrt, float grad_scale,
-             const float* gradnorm_sq, float max_norm) {
+             const float* gradnorm_sq, float max_norm, const int32_t* __restrict__ step_dev) {
+    if (step_dev) {
+        // step count lives on the device (CUDA-graph replay: host arguments are frozen at capture time)
+        const float t = (float)(*step_dev);
+        const float bc1 = 1.0f - powf(beta1, t);
+        const float bc2 = 1.0f - powf(beta2, t);
+        step_size = lr / bc1;
+        inv_bc2_sqrt = rsqrtf(bc2);
+    }
     const mgb_adamw_chunk ck = table[blockIdx.x];
     const float gs = grad_scale * clip_coef(gradnorm_sq, grad_scale, max_norm);
     const float decay = 1.0f - lr * ck.weight_decay;
@@ -322,17 +330,20 @@ extern "C" int mgb_clip_scale_f32(float* g, int64_t n, const float* gradnorm_sq,
 extern "C" int mgb_adamw_multi(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, void* params_bf16,
                                const mgb_adamw_chunk* table, int32_t num_chunks, float lr, float beta1, float beta2,
                                float eps, int32_t step, float grad_scale, const float* gradnorm_sq, float max_norm,
-                               mgb_stream_t s_) {
+                               const int32_t* step_dev, mgb_stream_t s_) {
     cudaStream_t s = (cudaStream_t)s_;
-    if (num_chunks < 0 || step < 1) { set_last_error("adamw: bad num_chunks/step"); return kErrBadShape; }
+    if (num_chunks < 0 || (!step_dev && step < 1)) { set_last_error("adamw: bad num_chunks/step"); return kErrBadShape; }
     if (num_chunks == 0) return kOk;
-    const double bc1 = 1.0 - std::pow((double)beta1, (double)step);
-    const double bc2 = 1.0 - std::pow((double)beta2, (double)step);
-    const float step_size = (float)((double)lr / bc1);
-    const float inv_bc2_sqrt = (float)(1.0 / std::sqrt(bc2));
+    float step_size = 0.f, inv_bc2_sqrt = 0.f;
+    if (!step_dev) {
+        const double bc1 = 1.0 - std::pow((double)beta1, (double)step);
+        const double bc2 = 1.0 - std::pow((double)beta2, (double)step);
+        step_size = (float)((double)lr / bc1);
+        inv_bc2_sqrt = (float)(1.0 / std::sqrt(bc2));
+    }
     adamw_kernel<<<num_chunks, 256, 0, s>>>(params, grads, exp_avg, exp_avg_sq, (__nv_bfloat16*)params_bf16, table, lr,
                                             beta1, beta2, eps, step_size, inv_bc2_sqrt, grad_scale, gradnorm_sq,
-                                            max_norm);
+                                            max_norm, step_dev);
     count_launch(1);
     MGB_CHECK_LAUNCH();
     return kOk;

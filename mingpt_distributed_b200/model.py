@@ -459,6 +459,7 @@ class GPT(nn.Module):
             self._flat_grad = torch.zeros(self._total, dtype=torch.float32, device=self._flat.device)
         if self._anchor is None or self._anchor.device != self._flat.device:
             self._anchor = torch.zeros((), device=self._flat.device, requires_grad=True)
+            self._one = torch.ones((), device=self._flat.device)
         tok = self._param_token()
         if self._shadow_token != tok:
             ops.cast_f32_to_bf16(self._flat, self._flat_bf16)
@@ -595,6 +596,26 @@ class GPT(nn.Module):
         else:
             loss = ws.loss.clone()
         return logits, loss
+
+    def forward_backward(self, inputs: torch.Tensor, targets: torch.Tensor,
+                         grad_scale: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """forward(inputs, targets) immediately followed by loss.backward(), without going through autograd:
+        the fast path of one training step (mingpt/trainer.py:122-127). Gradients land in p.grad exactly as
+        backward() would leave them. Performs no allocation and no host sync, so it can be captured in a CUDA
+        graph. Returns the loss as a device scalar that is OVERWRITTEN by the next call."""
+        B, T = inputs.shape
+        assert T <= self.block_size, "Sequence length must be less than or equal to block size for positional embeddings."
+        self._ensure_device_state()
+        self._check_dropout()
+        if inputs.dtype != torch.int64 or targets.dtype != torch.int64 or not inputs.is_contiguous() or not targets.is_contiguous():
+            raise RuntimeError("forward_backward expects contiguous int64 CUDA tensors")
+        ws = self._ws(B, T)
+        ws.generation += 1
+        ws.idx = inputs
+        self._trunk(ws, inputs)
+        self._head_loss(ws, targets, True)
+        self._backward(ws, self._one if grad_scale is None else grad_scale)
+        return ws.loss
 
     # ------------------------------------------------------------------ backward
     def _prepare_grads(self):

@@ -212,10 +212,10 @@ def clip_scale(g, gradnorm_sq, max_norm):
 
 
 def adamw_multi(params, grads, exp_avg, exp_avg_sq, params_bf16, table_dev, num_chunks, lr, beta1, beta2, eps, step,
-                grad_scale=1.0, gradnorm_sq=None, max_norm=0.0):
+                grad_scale=1.0, gradnorm_sq=None, max_norm=0.0, step_dev=None):
     check(_lib.lib().mgb_adamw_multi(_p(params), _p(grads), _p(exp_avg), _p(exp_avg_sq), _p(params_bf16), _p(table_dev),
                                      num_chunks, lr, beta1, beta2, eps, step, grad_scale, _p(gradnorm_sq), max_norm,
-                                     _stream()), "adamw")
+                                     _p(step_dev), _stream()), "adamw")
 
 
 def make_adamw_table(entries, chunk: int = 8192) -> torch.Tensor:

@@ -31,6 +31,7 @@ class FusedAdamW(torch.optim.Optimizer):
         self._step_t = torch.zeros((), dtype=torch.float32)   # shared by every parameter's state["step"]
         self._tables = {}
         self._norm_sq = None
+        self._step_dev = None      # device-side step counter (CUDA-graph replay)
 
     # ------------------------------------------------------------------ helpers
     def _flat_ready(self) -> bool:
@@ -113,12 +114,23 @@ class FusedAdamW(torch.optim.Optimizer):
         return out
 
     # ------------------------------------------------------------------ step
+    def begin_graph_mode(self):
+        """Call right before capturing a CUDA graph that contains step(graph_step=True): moves the step count
+        to a device counter the captured kernels read (host arguments are frozen at capture time)."""
+        m = self._model
+        self._step_dev = torch.tensor([int(self._step_t.item())], dtype=torch.int32, device=m._flat.device)
+
+    def note_replay(self):
+        """Call after each replay of such a graph: keeps the host-side step (state_dict) in sync."""
+        self._step_t += 1
+
     @torch.no_grad()
     def step(self, closure=None, *, grad_scale: float = 1.0, gradnorm_sq: Optional[torch.Tensor] = None,
-             max_norm: float = 0.0):
+             max_norm: float = 0.0, graph_step: bool = False):
         """One AdamW update. grad_scale multiplies every gradient (1/world_size after a SUM all-reduce,
         1/accumulation_steps, ...); gradnorm_sq (device scalar from grad_norm_sq()) + max_norm > 0 apply
-        clip_grad_norm's coefficient inside the same kernel."""
+        clip_grad_norm's coefficient inside the same kernel. graph_step=True: the step count is taken from
+        (and advanced in) device memory so the call can be captured in a CUDA graph and replayed."""
         loss = None
         if closure is not None:
             with torch.enable_grad():
@@ -132,15 +144,24 @@ class FusedAdamW(torch.optim.Optimizer):
             return loss
         self._ensure_state()
         self._sync_foreign_grads()
-        self._step_t += 1
-        step = int(self._step_t.item())
+        step_dev = None
+        if graph_step:
+            if self._step_dev is None:
+                self.begin_graph_mode()
+            self._step_dev += 1            # a device kernel: part of the captured graph
+            step_dev, step = self._step_dev, 1
+        else:
+            self._step_t += 1
+            step = int(self._step_t.item())
+            self._step_dev = None
         for gi, group in enumerate(self.param_groups):
             table, count = self._table(gi, group)
             if count == 0:
                 continue
             b1, b2 = group["betas"]
             ops.adamw_multi(m._flat, m._flat_grad, self._m, self._v, m._flat_bf16, table, count, float(group["lr"]),
-                            float(b1), float(b2), float(group["eps"]), step, grad_scale, gradnorm_sq, float(max_norm))
+                            float(b1), float(b2), float(group["eps"]), step, grad_scale, gradnorm_sq, float(max_norm),
+                            step_dev=step_dev)
         # the kernel refreshed the bf16 shadow: no recast needed before the next forward
         m._shadow_token = m._param_token()
         return loss
