@@ -94,7 +94,10 @@ class GraphedTrainStep:
         if not isinstance(optimizer, FusedAdamW):
             raise TypeError("GraphedTrainStep needs the FusedAdamW returned by create_optimizer")
         self.model, self.opt, self.clip, self.dp = model, optimizer, grad_norm_clip, dp
-        self.use_graph, self.warmup = use_graph, warmup
+        # With data parallelism the step stays eager: capturing the side-stream NCCL all-reduces together with
+        # the compute hung in testing on 2 x B200 (torch 2.11 / NCCL 2.28), and the all-reduce must overlap the
+        # backward, so it cannot simply be left outside the graph.
+        self.use_graph, self.warmup = (use_graph and dp is None), warmup
         self._states = {}
 
     def _body(self, st, graph_step: bool):
