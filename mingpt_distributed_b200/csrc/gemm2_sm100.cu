@@ -162,8 +162,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             for (int u = cluster_id; u < units; u += num_clusters) {
                 const int split = u / tiles;
                 const int t = u - split * tiles;
-                const int m0 = (t / p.num_n_tiles) * (2 * BLOCK_M) + (int)rank * BLOCK_M;
-                const int n0 = (t % p.num_n_tiles) * block_n + (int)rank * nb;
+                const int mt = p.m_fast ? (t % p.num_m_tiles) : (t / p.num_n_tiles);
+                const int nt = p.m_fast ? (t / p.num_m_tiles) : (t % p.num_n_tiles);
+                const int m0 = mt * (2 * BLOCK_M) + (int)rank * BLOCK_M;
+                const int n0 = nt * block_n + (int)rank * nb;
                 const int kb0 = split * p.k_blocks_per_split;
                 const int kb1 = min(kb0 + p.k_blocks_per_split, p.k_blocks_total);
                 for (int kb = kb0; kb < kb1; ++kb) {
@@ -249,8 +251,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         for (int u = cluster_id; u < units; u += num_clusters) {
             const int split = u / tiles;
             const int t = u - split * tiles;
-            const int m0 = (t / p.num_n_tiles) * (2 * BLOCK_M) + (int)rank * BLOCK_M;
-            const int n0 = (t % p.num_n_tiles) * block_n;
+            const int mt = p.m_fast ? (t % p.num_m_tiles) : (t / p.num_n_tiles);
+            const int nt = p.m_fast ? (t / p.num_m_tiles) : (t % p.num_n_tiles);
+            const int m0 = mt * (2 * BLOCK_M) + (int)rank * BLOCK_M;
+            const int n0 = nt * block_n;
             if (aux && elected) {
                 // bf16 output => at most two slices per half and tile, one per box. Fetch their residual / gate
                 // tiles now, while the tile's MMAs still run. Every thread of this half is past the previous
@@ -471,6 +475,10 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
     if (split > p.k_blocks_total) split = p.k_blocks_total;
     p.k_blocks_per_split = (int)ceil_div64(p.k_blocks_total, split);
     p.split_k = (int)ceil_div64(p.k_blocks_total, p.k_blocks_per_split);
+    // Raster order: concurrently running tiles share one operand tile and sweep the other operand, which is
+    // then re-read once per tile of the shared side. Sweep the SMALLER operand (it stays in the 126 MB L2):
+    // activations x weights -> n fastest; the head (16384 x 50257: weights larger than the activation chunk) -> m fastest.
+    p.m_fast = a->m < a->n ? 1 : 0;
 
     // D (and the saved pre-activation) leave through TMA when their row pitch allows it; one bf16 side input
     // (gate, else residual) is TMA-loaded in place when the output is bf16 and there is a single output.

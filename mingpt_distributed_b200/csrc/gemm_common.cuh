@@ -31,6 +31,7 @@ struct Params {
     int32_t num_m_tiles, num_n_tiles, k_blocks_total, k_blocks_per_split;
     int32_t num_stages;      // CTA-pair kernel only
     int32_t tma_store;       // CTA-pair kernel only: D (and preact) leave through smem + TMA
+    int32_t m_fast;          // CTA-pair kernel only: tile raster order (1 = m index fastest)
     int32_t tma_aux;         // CTA-pair kernel only: 1 residual / 2 gate arrives through TMA, updated in place
     // epilogue
     void* d;

@@ -205,7 +205,7 @@ scale_bf16_dev_kernel(__nv_bfloat16* __restrict__ x, int64_t n, const float* __r
 // bias gradient: out[c] += sum_r x[r, c]
 // block = 8 warps; a warp covers 256 columns (8 per lane), warps take interleaved rows of a 256-row slab
 // ---------------------------------------------------------------------------
-constexpr int CS_ROWS = 256;
+constexpr int CS_ROWS = 64;   // small slabs: a [32768 x 768] input still gives 1536 CTAs worth of loads in flight
 __global__ void __launch_bounds__(256)
 colsum_kernel(const __nv_bfloat16* __restrict__ x, int64_t ld, int64_t rows, int64_t cols, float* out) {
     __shared__ float sh[8][256 + 8];
@@ -215,6 +215,7 @@ colsum_kernel(const __nv_bfloat16* __restrict__ x, int64_t ld, int64_t rows, int
     const int64_t r1 = min(r0 + CS_ROWS, rows);
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (c0 < cols) {
+#pragma unroll 4
         for (int64_t r = r0 + warp; r < r1; r += 8) {
             const uint4 v = ldg128(x + r * ld + c0);
             const uint32_t w[4] = {v.x, v.y, v.z, v.w};

@@ -123,14 +123,15 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
     }
     for (int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp; row < rows; row += (int64_t)gridDim.x * LN_WARPS) {
         const float mu = mean[row], rs = rstd[row];
-        uint4 px[MAXCH], pd[MAXCH];
+        uint4 px[MAXCH], pd[MAXCH], pr[MAXCH];
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-        for (int i = 0; i < MAXCH; ++i) {
+        for (int i = 0; i < MAXCH; ++i) {      // all three input streams in flight before the first reduction
             const int ch = lane + 32 * i;
             if (ch < nch) {
                 px[i] = ldg128(x + row * cols + ch * 8);
                 pd[i] = ldg128(dy + row * cols + ch * 8);
+                pr[i] = dres ? ldg128(dres + row * cols + ch * 8) : make_uint4(0, 0, 0, 0);
             }
         }
 #pragma unroll
@@ -169,9 +170,8 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
                     r[2 * e] = rs * (fd.x * gam[i][2 * e] - m1 - h0 * m2);
                     r[2 * e + 1] = rs * (fd.y * gam[i][2 * e + 1] - m1 - h1 * m2);
                 }
-                if (dres) {
-                    const uint4 vr = ldg128(dres + row * cols + ch * 8);
-                    const uint32_t wr[4] = {vr.x, vr.y, vr.z, vr.w};
+                {
+                    const uint32_t wr[4] = {pr[i].x, pr[i].y, pr[i].z, pr[i].w};   // zeros when there is no dres
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
                         const float2 f = unpack_bf16x2(wr[e]);

@@ -1,0 +1,40 @@
+#!/usr/bin/env python
+"""2+ GPU check of the data-parallel step (run under torchrun on the GPU box):
+ (1) after backward + bucketed all-reduce, every rank's averaged gradient equals the gradient of the
+     concatenated global batch computed on one GPU;  (2) after the optimizer step all ranks hold identical
+     parameters;  (3) launches overlap: all-reduces are issued from the backward hooks.
+Prints one JSON line from rank 0."""
+import json, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch, torch.distributed as dist
+import mingpt_distributed_b200 as m
+
+rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+torch.manual_seed(0)
+cfg = m.GPTConfig(model_type=None, n_layer=4, n_head=4, n_embed=256, vocab_size=1000, block_size=128, embed_drop=0, resid_drop=0, attn_drop=0)
+model = m.GPT(cfg, verbose=False).cuda()
+opt = m.create_optimizer(model, m.OptimizerConfig())
+dp = m.DataParallel(model, bucket_cap_mb=1.0)
+g = torch.Generator().manual_seed(7)
+tok = torch.randint(0, 1000, (4 * world, 129), generator=g)
+xs, ys = tok[:, :-1].contiguous().cuda(), tok[:, 1:].contiguous().cuda()
+# reference: the whole global batch on this GPU (mean over all tokens == mean of per-rank means, equal sizes)
+_, loss_all = model(xs, ys); loss_all.backward()
+want = model._flat_grad.clone()
+for p in model.parameters(): p.grad = None
+# data parallel: this rank's shard, SUM all-reduce in buckets, scale 1/world folded into the optimizer
+_, loss = dp(xs[4 * rank:4 * rank + 4], ys[4 * rank:4 * rank + 4]); loss.backward()
+dp.finish_backward(); torch.cuda.synchronize()
+got = model._flat_grad * dp.grad_scale
+rel = ((got - want).norm() / want.norm()).item()
+opt.step(grad_scale=dp.grad_scale, gradnorm_sq=opt.grad_norm_sq(), max_norm=1.0)
+torch.cuda.synchronize()
+ref = model._flat.clone(); dist.broadcast(ref, src=0)
+same = bool(torch.equal(ref, model._flat))
+flags = torch.tensor([rel, float(same)], device="cuda"); dist.all_reduce(flags, op=dist.ReduceOp.MAX if False else dist.ReduceOp.MIN)
+if rank == 0:
+    print(json.dumps(dict(world=world, grad_rel_err_vs_global_batch=rel, params_identical_after_step=same,
+                          buckets=len(dp.buckets.buckets), allreduces_launched=dp.buckets.launched)))
+dist.destroy_process_group()
