@@ -270,6 +270,15 @@ def main():
             torch.cuda.synchronize()
         finally:
             ops.gemm = orig
+        # DRAM traffic per launch from the committed ncu --set full capture of every GEMM shape of the step
+        # (tools/gemm_ncu.py -> profiles/r1_gemm_shapes_ncu.json), weighted by how often each shape runs
+        traffic, traffic_alg = None, None
+        tpath = os.path.join(ROOT, "profiles", "r1_gemm_shapes_ncu.json")
+        if os.path.exists(tpath) and B == 32 and T == 1024 and args.variant == "mingpt":
+            shapes = json.load(open(tpath))
+            weights = [2 if s["name"].startswith("head") else GPT2["n_layer"] for s in shapes]
+            traffic = sum(w * s["dram_bytes"] for w, s in zip(weights, shapes)) / sum(weights)
+            traffic_alg = sum(w * s["algorithmic_bytes"] for w, s in zip(weights, shapes)) / sum(weights)
         flops = sum(r[0] for r in records)
         gemm_ms = sum(r[1].elapsed_time(r[2]) for r in records)
         step_ms_instr = t0.elapsed_time(t1)
@@ -277,7 +286,8 @@ def main():
         roof = dict(bound="tensor", kernel="mgb::gemm::gemm_kernel (all %d launches of a step)" % (len(records) // 2),
                     achieved=achieved, peak=peaks["bf16_sustained"], unit="TFLOP/s", frac=achieved / peaks["bf16_sustained"],
                     peak_source=peaks["source"] + " bf16_tflops_sustained (kernel timed inside a long step)",
-                    frac_of_nominal=achieved * 1e12 / NOMINAL_BF16, traffic=None,
+                    frac_of_nominal=achieved * 1e12 / NOMINAL_BF16, traffic=traffic, traffic_algorithmic=traffic_alg,
+                    traffic_source="profiles/r1_gemm_shapes_ncu.json (ncu --set full, dram read+write, mean per launch)",
                     share_of_step=gemm_ms / step_ms_instr, flops_per_launch_avg=flops / max(len(records), 1),
                     ms_per_launch_avg=gemm_ms / max(len(records), 1))
 
