@@ -145,6 +145,7 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=25.0)
     ap.add_argument("--profile-gemm", action="store_true", default=True)
     ap.add_argument("--quick", action="store_true", help="timed loop only (for runs under ncu): no e2e, roofline or cpu legs")
+    ap.add_argument("--dropout", type=float, default=0.0, help="embed/resid/attn dropout (reference default 0.1); headline is 0")
     ap.add_argument("--no-graph", action="store_true", help="issue every kernel from Python instead of replaying a CUDA graph")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
@@ -173,7 +174,8 @@ def main():
     B, T, V = args.batch, args.seq, GPT2["vocab_size"]
 
     torch.manual_seed(0)
-    cfg = m.GPTConfig(model_type=None, embed_drop=0.0, resid_drop=0.0, attn_drop=0.0, variant=args.variant, **GPT2)
+    cfg = m.GPTConfig(model_type=None, embed_drop=args.dropout, resid_drop=args.dropout, attn_drop=args.dropout,
+                      variant=args.variant, **GPT2)
     model = m.GPT(cfg, verbose=False)
     opt = m.create_optimizer(model, m.OptimizerConfig())
     model = model.to(dev)
@@ -304,7 +306,7 @@ def main():
                     dtype="bf16", data="synthetic",
                     config=dict(workload=f"gpt2-124M train step (L12 H12 C768 V50257 T{T}), variant={args.variant}, "
                                          "fp32 master weights + AdamW state, bf16 GEMM/attention operands",
-                                global_batch=world * B, seq_len=T, parallelism=f"dp{world}",
+                                global_batch=world * B, seq_len=T, parallelism=f"dp{world}", dropout=args.dropout,
                                 launch="CUDA graph replay of the whole step" if stepper.use_graph else "eager (one Python call per kernel)",
                                 l2="per-step working set (>10 GB of activations + 2 GB of parameters/state) is far larger than the 126 MB L2"),
                     mfu=dict(flops_per_token=f_tok, of_nominal_2p25pf=value * f_tok / (world * NOMINAL_BF16),

@@ -129,6 +129,27 @@ int mgb_attention_bwd(const void* qkv, const void* out, const void* dout, const 
                       float* dq_accum, void* dqkv, int32_t B, int32_t T, int32_t H, int32_t d, int32_t mask_mode,
                       float scale, mgb_stream_t stream);
 
+/* Dropout (the reference trains with p = 0.1 at four sites and never calls eval(): mingpt/model.py:49-51,140,
+ * 150,183,215). Masks are counter based (Philox4x32-10 over (seed, site, element)) and never stored: the
+ * backward regenerates them. *seed_dev is a DEVICE uint64 the caller changes every step; `site` tells the
+ * dropouts of one step apart. An element is kept with probability 1 - round(p * 65536) / 65536.
+ *   mgb_dropout_bf16:   y = (res ? res : 0) + (keep ? x / (1-p) : 0)     (embedding / residual dropouts, and
+ *                       their backward: call it on the incoming gradient with res = NULL)
+ *   mgb_attention_*_dropout: mgb_attention_fwd / _bwd with dropout on the softmax probabilities
+ *                       (torch/nn/functional.py:6644-6645); p_drop = 0 forwards to the plain entry points
+ *   mgb_attention_dropout_mask: the uint8 keep mask [B,H,T,T] those kernels use (for tests) */
+int mgb_dropout_bf16(const void* x, const void* res, void* y, int64_t n, float p, const uint64_t* seed_dev,
+                     uint32_t site, mgb_stream_t stream);
+int mgb_attention_fwd_dropout(const void* qkv, void* out, float* lse, int32_t B, int32_t T, int32_t H, int32_t d,
+                              int32_t mask_mode, float scale, float p_drop, const uint64_t* seed_dev, uint32_t site,
+                              mgb_stream_t stream);
+int mgb_attention_bwd_dropout(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                              float* dq_accum, void* dqkv, int32_t B, int32_t T, int32_t H, int32_t d,
+                              int32_t mask_mode, float scale, float p_drop, const uint64_t* seed_dev, uint32_t site,
+                              mgb_stream_t stream);
+int mgb_attention_dropout_mask(void* keep, int32_t B, int32_t T, int32_t H, float p_drop, const uint64_t* seed_dev,
+                               uint32_t site, mgb_stream_t stream);
+
 /* No counterpart in the reference. mgb_attention_bwd for callers that have no scratch to give: a plugin
  * inside a process whose device pool is fixed at start-up, or an FFI stub that only forwards pointers and
  * owns no allocator. delta and the dQ accumulator live in a fixed 17 MiB __device__ array inside the library

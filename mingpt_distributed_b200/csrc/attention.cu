@@ -11,6 +11,7 @@
 //
 // mask modes (see mingpt_b200.h): CAUSAL, ADD_TRIL_ONES (the reference's as-written float mask), NONE.
 #include "common.cuh"
+#include "dropout.cuh"
 #include "mingpt_b200.h"
 
 #include <atomic>
@@ -76,7 +77,8 @@ __device__ __forceinline__ void load_tile(__nv_bfloat16* s, const __nv_bfloat16*
 template <int D>
 __global__ void __launch_bounds__(NTHREADS)
 attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, float* __restrict__ lse,
-                int T, int H, int mask_mode, float scale_log2) {
+                int T, int H, int mask_mode, float scale_log2, uint32_t drop_thresh, float inv_keep,
+                const uint64_t* __restrict__ seed_dev, uint32_t site) {
     constexpr int LDS = D + 8;
     constexpr int KD = D / 16;   // k-steps over the head dim
     constexpr int ND = D / 8;    // n-tiles over the head dim
@@ -175,6 +177,23 @@ attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict
         }
         l0 = l0 * c0 + rs0;
         l1 = l1 * c1 + rs1;
+        if (drop_thresh) {
+            // attention-probability dropout (nn.MultiheadAttention dropout=attn_drop, mingpt/model.py:150 ->
+            // torch/nn/functional.py:6644-6645): the softmax normaliser keeps every key, P V only the kept ones
+            const uint64_t seed = *seed_dev;
+            const uint64_t t8 = (uint64_t)((T + 7) >> 3);
+            const uint64_t g0 = ((uint64_t)blockIdx.y * T + (uint64_t)r0) * t8 + (uint64_t)(j * (BN / 8));
+            const uint64_t g1 = g0 + 8 * t8;
+#pragma unroll
+            for (int n = 0; n < 8; ++n) {
+                const uint32_t ka = dropout_keep8(seed, site, g0 + n, drop_thresh) >> (2 * t4);
+                const uint32_t kb = dropout_keep8(seed, site, g1 + n, drop_thresh) >> (2 * t4);
+                s[n][0] = (ka & 1u) ? s[n][0] * inv_keep : 0.f;
+                s[n][1] = (ka & 2u) ? s[n][1] * inv_keep : 0.f;
+                s[n][2] = (kb & 1u) ? s[n][2] * inv_keep : 0.f;
+                s[n][3] = (kb & 2u) ? s[n][3] * inv_keep : 0.f;
+            }
+        }
 #pragma unroll
         for (int n = 0; n < ND; ++n) { o[n][0] *= c0; o[n][1] *= c0; o[n][2] *= c1; o[n][3] *= c1; }
         // O += P V
@@ -248,7 +267,8 @@ template <int D>
 __global__ void __launch_bounds__(NTHREADS)
 attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dout,
                 const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_accum,
-                __nv_bfloat16* __restrict__ dqkv, int T, int H, int mask_mode, float scale, float scale_log2) {
+                __nv_bfloat16* __restrict__ dqkv, int T, int H, int mask_mode, float scale, float scale_log2,
+                uint32_t drop_thresh, float inv_keep, const uint64_t* __restrict__ seed_dev, uint32_t site) {
     constexpr int LDS = D + 8;
     constexpr int LDP = 64 + 8;
     constexpr int KD = D / 16;
@@ -346,8 +366,16 @@ attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __re
                 if (tril && key <= q) sl += LOG2E;
                 const bool masked = (key >= T) || (q >= T) || (causal && key > q);
                 const float p = masked ? 0.f : exp2f(sl - sLse[ql]);
-                st[n][e] = p;
-                dp[n][e] = p * (dp[n][e] - sDelta[ql]) * scale;
+                float pd = p, dpe = dp[n][e];
+                if (drop_thresh) {
+                    // same mask as the forward: element (query q, key) of this (batch, head)
+                    const uint64_t grp = ((uint64_t)blockIdx.y * T + (uint64_t)q) * (uint64_t)((T + 7) >> 3) + (uint64_t)(key >> 3);
+                    const bool keep = (q < T) && ((dropout_keep8(*seed_dev, site, grp, drop_thresh) >> (key & 7)) & 1u);
+                    pd = keep ? p * inv_keep : 0.f;       // what multiplied V in the forward
+                    dpe = keep ? dpe * inv_keep : 0.f;    // d(loss)/d(softmax prob)
+                }
+                st[n][e] = pd;
+                dp[n][e] = p * (dpe - sDelta[ql]) * scale;
             }
         }
         // dV += P^T dO ; dK += dS^T Q   (reduction over the 64 queries)
@@ -454,16 +482,21 @@ attn_dq_convert_kernel(const float* __restrict__ dq_accum, __nv_bfloat16* __rest
 
 template <int D>
 static int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int mask_mode, float scale,
-                      cudaStream_t s) {
+                      cudaStream_t s, float p_drop = 0.f, const uint64_t* seed_dev = nullptr, uint32_t site = 0) {
     constexpr int smem = (64 + 4 * 64) * (D + 8) * 2;
     dim3 grid((T + BM - 1) / BM, B * H);
+    const uint32_t thresh = p_drop > 0.f ? dropout_thresh16(p_drop) : 0u;
+    const float inv_keep = thresh ? 65536.0f / (65536.0f - (float)thresh) : 1.0f;
     attn_fwd_kernel<D><<<grid, NTHREADS, smem, s>>>((const __nv_bfloat16*)qkv, (__nv_bfloat16*)out, lse, T, H, mask_mode,
-                                                   scale * LOG2E);
+                                                   scale * LOG2E, thresh, inv_keep, seed_dev, site);
     return 0;
 }
 template <int D>
 static int launch_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
-                      float* dq_accum, void* dqkv, int B, int T, int H, int mask_mode, float scale, cudaStream_t s) {
+                      float* dq_accum, void* dqkv, int B, int T, int H, int mask_mode, float scale, cudaStream_t s,
+                      float p_drop = 0.f, const uint64_t* seed_dev = nullptr, uint32_t site = 0) {
+    const uint32_t thresh = p_drop > 0.f ? dropout_thresh16(p_drop) : 0u;
+    const float inv_keep = thresh ? 65536.0f / (65536.0f - (float)thresh) : 1.0f;
     const int64_t rows = (int64_t)B * T * H;
     int g = (int)((rows + 255) / 256);
     if (g > num_sms() * 16) g = num_sms() * 16;
@@ -474,13 +507,14 @@ static int launch_bwd(const void* qkv, const void* out, const void* dout, const 
         cudaFuncSetAttribute(attn_bwd_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         attr_set = true;
     }
-    if (D == 64 && !g_opt_attn_mma.load(std::memory_order_relaxed)) {
+    if (D == 64 && !thresh && !g_opt_attn_mma.load(std::memory_order_relaxed)) {
         const int rc = attn_tc::launch_bwd_main(qkv, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
         if (rc) return rc;
     } else {
         dim3 grid((T + BN - 1) / BN, B * H);
         attn_bwd_kernel<D><<<grid, NTHREADS, smem, s>>>((const __nv_bfloat16*)qkv, (const __nv_bfloat16*)dout, lse, delta,
-                                                       dq_accum, (__nv_bfloat16*)dqkv, T, H, mask_mode, scale, scale * LOG2E);
+                                                       dq_accum, (__nv_bfloat16*)dqkv, T, H, mask_mode, scale, scale * LOG2E,
+                                                       thresh, inv_keep, seed_dev, site);
     }
     const int64_t chunks = (int64_t)B * T * (H * D / 8);
     int g2 = (int)((chunks + 255) / 256);
@@ -611,6 +645,80 @@ extern "C" int mgb_attention_bwd_noalloc(const void* qkv, const void* out, const
     else if (d == 32) attn::launch_bwd<32>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
     else attn::launch_bwd<16>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
     count_launch(3);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+// =====================================================================================
+// attention with dropout on the probabilities (training with attn_drop > 0, the reference's default 0.1)
+// =====================================================================================
+namespace mgb {
+namespace attn {
+// keep[b,h,q,k] (uint8) exactly as the kernels above generate it: lets tests rebuild the computation in torch
+__global__ void __launch_bounds__(256)
+attn_dropout_mask_kernel(uint8_t* __restrict__ keep, int64_t BH, int T, uint32_t thresh, const uint64_t* seed_dev,
+                         uint32_t site) {
+    const int64_t t8 = (T + 7) >> 3;
+    const int64_t groups = BH * T * t8;
+    const uint64_t seed = *seed_dev;
+    for (int64_t gidx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; gidx < groups; gidx += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t m = dropout_keep8(seed, site, (uint64_t)gidx, thresh);
+        const int64_t row = gidx / t8;                 // (bh * T + q)
+        const int k0 = (int)(gidx - row * t8) * 8;
+        for (int i = 0; i < 8 && k0 + i < T; ++i) keep[row * T + k0 + i] = (m >> i) & 1u;
+    }
+}
+}  // namespace attn
+}  // namespace mgb
+
+extern "C" int mgb_attention_fwd_dropout(const void* qkv, void* out, float* lse, int32_t B, int32_t T, int32_t H,
+                                         int32_t d, int32_t mask_mode, float scale, float p_drop,
+                                         const uint64_t* seed_dev, uint32_t site, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    int rc = check_attn_shape("fwd_dropout", B, T, H, d, mask_mode);
+    if (rc) return rc;
+    if (!(p_drop >= 0.f && p_drop < 1.f) || (p_drop > 0.f && !seed_dev)) { set_last_error("attention: bad dropout arguments"); return kErrBadShape; }
+    if (((uintptr_t)qkv % 16) || ((uintptr_t)out % 16)) { set_last_error("attention: pointers must be 16-byte aligned"); return kErrBadAlign; }
+    if (p_drop == 0.f) return mgb_attention_fwd(qkv, out, lse, B, T, H, d, mask_mode, scale, s_);
+    if (d == 64) attn::launch_fwd<64>(qkv, out, lse, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
+    else if (d == 32) attn::launch_fwd<32>(qkv, out, lse, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
+    else attn::launch_fwd<16>(qkv, out, lse, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+extern "C" int mgb_attention_bwd_dropout(const void* qkv, const void* out, const void* dout, const float* lse,
+                                         float* delta, float* dq_accum, void* dqkv, int32_t B, int32_t T, int32_t H,
+                                         int32_t d, int32_t mask_mode, float scale, float p_drop,
+                                         const uint64_t* seed_dev, uint32_t site, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    int rc = check_attn_shape("bwd_dropout", B, T, H, d, mask_mode);
+    if (rc) return rc;
+    if (!(p_drop >= 0.f && p_drop < 1.f) || (p_drop > 0.f && !seed_dev)) { set_last_error("attention: bad dropout arguments"); return kErrBadShape; }
+    if (p_drop == 0.f) return mgb_attention_bwd(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, d, mask_mode, scale, s_);
+    if (((uintptr_t)qkv % 16) || ((uintptr_t)out % 16) || ((uintptr_t)dout % 16) || ((uintptr_t)dqkv % 16) ||
+        ((uintptr_t)dq_accum % 16)) {
+        set_last_error("attention: pointers must be 16-byte aligned"); return kErrBadAlign;
+    }
+    cudaMemsetAsync(dq_accum, 0, (size_t)B * T * H * d * sizeof(float), s);
+    if (d == 64) attn::launch_bwd<64>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
+    else if (d == 32) attn::launch_bwd<32>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
+    else attn::launch_bwd<16>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
+    count_launch(3);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+extern "C" int mgb_attention_dropout_mask(void* keep, int32_t B, int32_t T, int32_t H, float p_drop,
+                                          const uint64_t* seed_dev, uint32_t site, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    if (B <= 0 || T <= 0 || H <= 0 || !seed_dev || !(p_drop >= 0.f && p_drop < 1.f)) { set_last_error("dropout_mask: bad arguments"); return kErrBadShape; }
+    const int64_t groups = (int64_t)B * H * T * ((T + 7) / 8);
+    int g = (int)((groups + 255) / 256);
+    if (g > num_sms() * 32) g = num_sms() * 32;
+    attn::attn_dropout_mask_kernel<<<g, 256, 0, s>>>((uint8_t*)keep, (int64_t)B * H, T, dropout_thresh16(p_drop), seed_dev, site);
+    count_launch(1);
     MGB_CHECK_LAUNCH();
     return kOk;
 }

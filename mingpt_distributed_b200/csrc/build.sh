@@ -10,7 +10,7 @@ FLAGS=(-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17
        -Xcompiler -fPIC -I"$ROOT/include" -I"$HERE" "$@")
 OBJS=()
 pids=()
-for f in gemm_sm100 gemm2_sm100 rowwise optim attention attention_sm100; do
+for f in gemm_sm100 gemm2_sm100 rowwise optim attention attention_sm100 dropout; do
   # the optimizer / norm kernels keep IEEE division and sqrt (parity with torch.optim.AdamW); the rest use fast math
   FM=(--use_fast_math); [ "$f" = optim ] && FM=()
   "$NVCC" "${FLAGS[@]}" "${FM[@]}" -c "$HERE/$f.cu" -o "$HERE/$f.o" &

@@ -1,0 +1,63 @@
+// Elementwise dropout for the three non-attention dropout sites of the reference (embeddings
+// mingpt/model.py:215,231; after c_proj :140,167; after the MLP :183), fused with the residual add that
+// follows it:   y = (res ? res : 0) + (keep ? x / (1 - p) : 0)
+// The mask is a pure function of (seed, site, element index): the backward pass calls the same kernel on the
+// incoming gradient (res = NULL) and gets the same mask, nothing is stored.
+#include "common.cuh"
+#include "dropout.cuh"
+#include "mingpt_b200.h"
+
+namespace mgb {
+
+__global__ void __launch_bounds__(256)
+dropout_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* res, __nv_bfloat16* y, int64_t n,
+               uint32_t thresh, float inv_keep, const uint64_t* __restrict__ seed_dev, uint32_t site) {
+    const uint64_t seed = *seed_dev;
+    const int64_t groups = (n + 7) >> 3;
+    for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t keep = dropout_keep8(seed, site, (uint64_t)g, thresh);
+        const int64_t i0 = g * 8;
+        if (i0 + 8 <= n) {
+            const uint4 vx = ldg128(x + i0);
+            uint4 vr = make_uint4(0, 0, 0, 0);
+            if (res) vr = ldg128(res + i0);
+            const uint32_t wx[4] = {vx.x, vx.y, vx.z, vx.w}, wr[4] = {vr.x, vr.y, vr.z, vr.w};
+            uint32_t o[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 fx = unpack_bf16x2(wx[e]), fr = unpack_bf16x2(wr[e]);
+                const float a = ((keep >> (2 * e)) & 1u) ? fx.x * inv_keep : 0.f;
+                const float b = ((keep >> (2 * e + 1)) & 1u) ? fx.y * inv_keep : 0.f;
+                o[e] = pack_bf16x2(a + fr.x, b + fr.y);
+            }
+            stg128(y + i0, make_uint4(o[0], o[1], o[2], o[3]));
+        } else {
+            for (int e = 0; i0 + e < n; ++e) {
+                float v = ((keep >> e) & 1u) ? __bfloat162float(x[i0 + e]) * inv_keep : 0.f;
+                if (res) v += __bfloat162float(res[i0 + e]);
+                y[i0 + e] = __float2bfloat16(v);
+            }
+        }
+    }
+}
+
+}  // namespace mgb
+
+using namespace mgb;
+
+extern "C" int mgb_dropout_bf16(const void* x, const void* res, void* y, int64_t n, float p, const uint64_t* seed_dev,
+                                uint32_t site, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    if (n < 0 || !(p >= 0.f && p < 1.f) || !seed_dev) { set_last_error("dropout: bad arguments"); return kErrBadShape; }
+    if (((uintptr_t)x % 16) || ((uintptr_t)y % 16) || (res && ((uintptr_t)res % 16))) { set_last_error("dropout: pointers must be 16-byte aligned"); return kErrBadAlign; }
+    if (n == 0) return kOk;
+    const uint32_t thresh = dropout_thresh16(p);
+    const float inv_keep = 65536.0f / (65536.0f - (float)thresh);
+    int64_t g = ((n + 7) / 8 + 255) / 256;
+    if (g > (int64_t)num_sms() * 16) g = (int64_t)num_sms() * 16;
+    dropout_kernel<<<(int)g, 256, 0, s>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)res, (__nv_bfloat16*)y, n, thresh,
+                                         inv_keep, seed_dev, site);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}

@@ -253,6 +253,16 @@ class _Workspace:
         self.delta = f32(B, H, T)
         self.idx = None
         self.has_head_grads = False
+        self.drop = (0.0, 0.0, 0.0)      # dropout probabilities used by the forward that filled this workspace
+        self.tmp = self.dtmp = None
+        self._mc = (M, C, dev)
+
+    def ensure_dropout_buffers(self):
+        """GEMM output before residual dropout, and the masked gradient of it (training with dropout only)"""
+        if self.tmp is None:
+            M, C, dev = self._mc
+            self.tmp = torch.empty(M, C, dtype=torch.bfloat16, device=dev)
+            self.dtmp = torch.empty(M, C, dtype=torch.bfloat16, device=dev)
 
 
 class _LossFn(torch.autograd.Function):
@@ -328,6 +338,7 @@ class GPT(nn.Module):
         self._workspaces: Dict[Tuple[int, int], _Workspace] = {}
         self._anchor = None
         self._layer_done_hook: Optional[Callable[[int], None]] = None
+        self._rng_seed: Optional[torch.Tensor] = None   # device int64: dropout seed, advanced once per training forward
         self.loss_scale_hint = 1.0
         self._flatten()
 
@@ -493,11 +504,22 @@ class GPT(nn.Module):
         return ws
 
     # ------------------------------------------------------------------ forward
-    def _check_dropout(self):
-        if self.training and any(p > 0 for p in self.drop_p):
-            raise NotImplementedError(
-                "dropout > 0 in training mode is not implemented on the fused B200 path yet: construct the "
-                "config with embed_drop=resid_drop=attn_drop=0 or call model.eval()")
+    SITE_EMBED = 0xFFFF
+
+    def _dropout_now(self, ws: "_Workspace") -> Tuple[float, float, float]:
+        """(embed, resid, attn) dropout probabilities in force for this forward: the config's values in
+        training mode (the reference never leaves it: mingpt/trainer.py:118-122,180-183), zeros in eval mode.
+        Draws a fresh seed for the step; masks are regenerated from it in backward (nothing is stored)."""
+        if not self.training or not any(p > 0 for p in self.drop_p):
+            ws.drop = (0.0, 0.0, 0.0)
+            return ws.drop
+        if self._rng_seed is None or self._rng_seed.device != self._flat.device:
+            # follows torch.manual_seed(): drawn from the default CPU generator once, then advanced on the device
+            self._rng_seed = torch.randint(0, 2 ** 62, (1,), dtype=torch.int64).to(self._flat.device)
+        self._rng_seed += 1
+        ws.ensure_dropout_buffers()
+        ws.drop = self.drop_p
+        return ws.drop
 
     def _trunk(self, ws: _Workspace, idx: torch.Tensor):
         """embeddings -> blocks -> final LayerNorm (mingpt/model.py:310-312 up to ln_ff)"""
@@ -508,26 +530,46 @@ class GPT(nn.Module):
         W = lambda r: self._w(r, bf16=True)
         P = lambda r: self._w(r)
         wpe = W("wpe").view(-1, C)
+        pe, pr, pa = self._dropout_now(ws)
+        seed = self._rng_seed
         ops.embedding_fwd(idx, W("wte"), wpe, ws.x[0], ws.err_flag)
+        if pe > 0:   # nn.Dropout(embed_drop), mingpt/model.py:215,231
+            ops.dropout(ws.x[0], None, ws.x[0], pe, seed, self.SITE_EMBED)
         for l in range(L):
             s = ws.stats[l]
             ops.layernorm_fwd(ws.x[l], P(f"{l}.ln1_w"), P(f"{l}.ln1_b"), ws.ln1[l], s[0], s[1])
             ops.linear_fwd(ws.ln1[l], W(f"{l}.qkv_w"), ws.qkv[l], bias=P(f"{l}.qkv_b"))
-            ops.attention_fwd(ws.qkv[l], ws.att[l], ws.lse[l], B, T, H, d, mask)
+            if pa > 0:   # dropout on the attention probabilities, mingpt/model.py:150
+                ops.attention_fwd_dropout(ws.qkv[l], ws.att[l], ws.lse[l], B, T, H, d, mask, pa, seed, 4 * l)
+            else:
+                ops.attention_fwd(ws.qkv[l], ws.att[l], ws.lse[l], B, T, H, d, mask)
             a_in = ws.att[l]
             if ref:  # nn.MultiheadAttention's own out_proj, then the extra c_proj (model.py:147-154,167)
                 ops.linear_fwd(ws.att[l], W(f"{l}.o_w"), ws.att_o[l], bias=P(f"{l}.o_b"))
                 a_in = ws.att_o[l]
-            ops.linear_fwd(a_in, W(f"{l}.proj_w"), ws.xmid[l], bias=P(f"{l}.proj_b"), residual=ws.x[l])
+            if pr > 0:   # resid_drop after c_proj (model.py:140,167), then the residual add (:187)
+                ops.linear_fwd(a_in, W(f"{l}.proj_w"), ws.tmp, bias=P(f"{l}.proj_b"))
+                ops.dropout(ws.tmp, ws.x[l], ws.xmid[l], pr, seed, 4 * l + 1)
+            else:
+                ops.linear_fwd(a_in, W(f"{l}.proj_w"), ws.xmid[l], bias=P(f"{l}.proj_b"), residual=ws.x[l])
             ops.layernorm_fwd(ws.xmid[l], P(f"{l}.ln2_w"), P(f"{l}.ln2_b"), ws.ln2[l], s[2], s[3])
-            if ref:  # Linear -> Linear -> GELU(erf) (model.py:179-184)
+            if ref:  # Linear -> Linear -> GELU(erf) -> Dropout (model.py:179-184)
                 ops.linear_fwd(ws.ln2[l], W(f"{l}.fc_w"), ws.fc_pre[l], bias=P(f"{l}.fc_b"))
-                ops.linear_fwd(ws.fc_pre[l], W(f"{l}.fc2_w"), ws.x[l + 1], bias=P(f"{l}.fc2_b"), act=ops.ACT_GELU_ERF,
-                               preact=ws.z[l], residual=ws.xmid[l])
-            else:    # c_fc + NewGELU epilogue, then c_proj + residual epilogue
+                if pr > 0:
+                    ops.linear_fwd(ws.fc_pre[l], W(f"{l}.fc2_w"), ws.tmp, bias=P(f"{l}.fc2_b"), act=ops.ACT_GELU_ERF,
+                                   preact=ws.z[l])
+                    ops.dropout(ws.tmp, ws.xmid[l], ws.x[l + 1], pr, seed, 4 * l + 2)
+                else:
+                    ops.linear_fwd(ws.fc_pre[l], W(f"{l}.fc2_w"), ws.x[l + 1], bias=P(f"{l}.fc2_b"),
+                                   act=ops.ACT_GELU_ERF, preact=ws.z[l], residual=ws.xmid[l])
+            else:    # c_fc + NewGELU epilogue, then c_proj (+ dropout) + residual
                 ops.linear_fwd(ws.ln2[l], W(f"{l}.fc_w"), ws.fc_act[l], bias=P(f"{l}.fc_b"), act=ops.ACT_GELU_TANH,
                                preact=ws.fc_pre[l])
-                ops.linear_fwd(ws.fc_act[l], W(f"{l}.fc2_w"), ws.x[l + 1], bias=P(f"{l}.fc2_b"), residual=ws.xmid[l])
+                if pr > 0:
+                    ops.linear_fwd(ws.fc_act[l], W(f"{l}.fc2_w"), ws.tmp, bias=P(f"{l}.fc2_b"))
+                    ops.dropout(ws.tmp, ws.xmid[l], ws.x[l + 1], pr, seed, 4 * l + 2)
+                else:
+                    ops.linear_fwd(ws.fc_act[l], W(f"{l}.fc2_w"), ws.x[l + 1], bias=P(f"{l}.fc2_b"), residual=ws.xmid[l])
         ops.layernorm_fwd(ws.x[L], P("lnf_w"), P("lnf_b"), ws.lnf, ws.lnf_stats[0], ws.lnf_stats[1])
 
     def _head_loss(self, ws: _Workspace, targets: torch.Tensor, need_grad: bool):
@@ -573,7 +615,6 @@ class GPT(nn.Module):
         B, T = inputs.shape
         assert T <= self.block_size, "Sequence length must be less than or equal to block size for positional embeddings."
         self._ensure_device_state()
-        self._check_dropout()
         if not inputs.is_cuda:
             raise RuntimeError("inputs must be on the model's CUDA device")
         idx = inputs.contiguous()
@@ -606,7 +647,6 @@ class GPT(nn.Module):
         B, T = inputs.shape
         assert T <= self.block_size, "Sequence length must be less than or equal to block size for positional embeddings."
         self._ensure_device_state()
-        self._check_dropout()
         if inputs.dtype != torch.int64 or targets.dtype != torch.int64 or not inputs.is_contiguous() or not targets.is_contiguous():
             raise RuntimeError("forward_backward expects contiguous int64 CUDA tensors")
         ws = self._ws(B, T)
@@ -652,33 +692,47 @@ class GPT(nn.Module):
         if self._layer_done_hook is not None:
             self._layer_done_hook(L + 1)
         dx = ws.dx_a
+        pe, pr, pa = ws.drop
+        seed = self._rng_seed
         for l in range(L - 1, -1, -1):
             s = ws.stats[l]
+            dmlp = dx          # gradient of the MLP branch output: through its dropout mask when there is one
+            if pr > 0:
+                ops.dropout(dx, None, ws.dtmp, pr, seed, 4 * l + 2)
+                dmlp = ws.dtmp
             if ref:
-                ops.act_bwd(dx, ws.z[l], ws.dz, ops.ACT_GELU_ERF)
+                ops.act_bwd(dmlp, ws.z[l], ws.dz, ops.ACT_GELU_ERF)
                 ops.colsum(ws.dz, G(f"{l}.fc2_b"))
                 ops.linear_wgrad(ws.dz, ws.fc_pre[l], G(f"{l}.fc2_w"))
                 ops.linear_dgrad(ws.dz, W(f"{l}.fc2_w"), ws.dfc)
             else:
-                ops.colsum(dx, G(f"{l}.fc2_b"))
-                ops.linear_wgrad(dx, ws.fc_act[l], G(f"{l}.fc2_w"))
-                ops.linear_dgrad(dx, W(f"{l}.fc2_w"), ws.dfc, gate=ws.fc_pre[l], gate_kind=ops.ACT_GELU_TANH)
+                ops.colsum(dmlp, G(f"{l}.fc2_b"))
+                ops.linear_wgrad(dmlp, ws.fc_act[l], G(f"{l}.fc2_w"))
+                ops.linear_dgrad(dmlp, W(f"{l}.fc2_w"), ws.dfc, gate=ws.fc_pre[l], gate_kind=ops.ACT_GELU_TANH)
             ops.colsum(ws.dfc, G(f"{l}.fc_b"))
             ops.linear_wgrad(ws.dfc, ws.ln2[l], G(f"{l}.fc_w"))
             ops.linear_dgrad(ws.dfc, W(f"{l}.fc_w"), ws.dln)
             ops.layernorm_bwd(ws.dln, ws.xmid[l], P(f"{l}.ln2_w"), s[2], s[3], ws.dx_b, G(f"{l}.ln2_w"), G(f"{l}.ln2_b"), dres=dx)
             dxm = ws.dx_b
             a_in = ws.att_o[l] if ref else ws.att[l]
-            ops.colsum(dxm, G(f"{l}.proj_b"))
-            ops.linear_wgrad(dxm, a_in, G(f"{l}.proj_w"))
-            ops.linear_dgrad(dxm, W(f"{l}.proj_w"), ws.datt)
+            dproj = dxm
+            if pr > 0:
+                ops.dropout(dxm, None, ws.dtmp, pr, seed, 4 * l + 1)
+                dproj = ws.dtmp
+            ops.colsum(dproj, G(f"{l}.proj_b"))
+            ops.linear_wgrad(dproj, a_in, G(f"{l}.proj_w"))
+            ops.linear_dgrad(dproj, W(f"{l}.proj_w"), ws.datt)
             datt = ws.datt
             if ref:
                 ops.colsum(ws.datt, G(f"{l}.o_b"))
                 ops.linear_wgrad(ws.datt, ws.att[l], G(f"{l}.o_w"))
                 ops.linear_dgrad(ws.datt, W(f"{l}.o_w"), ws.datt2)
                 datt = ws.datt2
-            ops.attention_bwd(ws.qkv[l], ws.att[l], datt, ws.lse[l], ws.delta, ws.dq_acc, ws.dqkv, B, T, H, d, mask)
+            if pa > 0:
+                ops.attention_bwd_dropout(ws.qkv[l], ws.att[l], datt, ws.lse[l], ws.delta, ws.dq_acc, ws.dqkv, B, T, H, d,
+                                          mask, pa, seed, 4 * l)
+            else:
+                ops.attention_bwd(ws.qkv[l], ws.att[l], datt, ws.lse[l], ws.delta, ws.dq_acc, ws.dqkv, B, T, H, d, mask)
             ops.colsum(ws.dqkv, G(f"{l}.qkv_b"))
             ops.linear_wgrad(ws.dqkv, ws.ln1[l], G(f"{l}.qkv_w"))
             ops.linear_dgrad(ws.dqkv, W(f"{l}.qkv_w"), ws.dln)
@@ -687,6 +741,8 @@ class GPT(nn.Module):
             if self._layer_done_hook is not None:
                 self._layer_done_hook(l + 1)
         gwpe = G("wpe").view(-1, C)
+        if pe > 0:
+            ops.dropout(dx, None, dx, pe, seed, self.SITE_EMBED)
         ops.embedding_bwd(ws.idx, dx, G("wte"), gwpe)
         if self._layer_done_hook is not None:
             self._layer_done_hook(0)

@@ -156,6 +156,30 @@ def attention_bwd_noalloc(qkv, out, dout, lse, dqkv, B, T, H, d, mask_mode, scal
     return dqkv
 
 
+def dropout(x, res, y, p, seed_dev, site):
+    """y = (res or 0) + dropout_p(x); mask = f(*seed_dev, site, element). Also its own backward (res=None)."""
+    _chk_cuda(x, res, y, seed_dev)
+    check(_lib.lib().mgb_dropout_bf16(_p(x), _p(res), _p(y), x.numel(), float(p), _p(seed_dev), int(site), _stream()), "dropout")
+    return y
+
+
+def attention_fwd_dropout(qkv, out, lse, B, T, H, d, mask_mode, p, seed_dev, site, scale=None):
+    scale = 1.0 / math.sqrt(d) if scale is None else scale
+    check(_lib.lib().mgb_attention_fwd_dropout(_p(qkv), _p(out), _p(lse), B, T, H, d, mask_mode, scale, float(p), _p(seed_dev), int(site), _stream()), "attention_fwd_dropout")
+    return out
+
+
+def attention_bwd_dropout(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, d, mask_mode, p, seed_dev, site, scale=None):
+    scale = 1.0 / math.sqrt(d) if scale is None else scale
+    check(_lib.lib().mgb_attention_bwd_dropout(_p(qkv), _p(out), _p(dout), _p(lse), _p(delta), _p(dq_accum), _p(dqkv), B, T, H, d, mask_mode, scale, float(p), _p(seed_dev), int(site), _stream()), "attention_bwd_dropout")
+    return dqkv
+
+
+def attention_dropout_mask(keep, B, T, H, p, seed_dev, site):
+    check(_lib.lib().mgb_attention_dropout_mask(_p(keep), B, T, H, float(p), _p(seed_dev), int(site), _stream()), "attention_dropout_mask")
+    return keep
+
+
 def cross_entropy_fwd_bwd(logits, targets, row_loss, n_valid, vocab, grad_scale=1.0, write_grad=True, err_flag=None):
     """in place on bf16 logits [rows, ld]; see mgb_cross_entropy_fwd_bwd"""
     _chk_cuda(logits, targets, row_loss, n_valid)

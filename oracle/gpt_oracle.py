@@ -38,7 +38,12 @@ def _layer_norm(x, sd, prefix):
     return F.layer_norm(x, (x.shape[-1],), sd[prefix + ".weight"], sd[prefix + ".bias"], 1e-5)
 
 
-def _attention_core(q, k, v, mode: str):
+def _drop(x, keep, p):
+    """nn.Dropout with a GIVEN keep mask (the CUDA path exports its counter-based masks for the tests)"""
+    return x if keep is None else x * keep.to(x.dtype) / (1.0 - p)
+
+
+def _attention_core(q, k, v, mode: str, keep=None, p: float = 0.0):
     """q,k,v (B,H,T,d).  mode 'add_tril_ones': what nn.MultiheadAttention does with the FLOAT tril mask the
     reference passes (mingpt/model.py:142-145,164 -> torch/nn/functional.py:6630-6647): q is scaled, the
     mask is ADDED to the scores, softmax, P@V -- nothing is masked.  mode 'causal': -inf above the diagonal."""
@@ -50,6 +55,7 @@ def _attention_core(q, k, v, mode: str):
     elif mode == "causal":
         att = att.masked_fill(tril == 0, float("-inf"))
     att = torch.softmax(att, dim=-1)
+    att = _drop(att, keep, p)          # dropout on the probabilities (torch/nn/functional.py:6644-6645)
     return att @ v
 
 
@@ -58,12 +64,17 @@ def _split_heads(t, n_head):
     return t.view(B, T, n_head, C // n_head).transpose(1, 2)
 
 
-def forward_reference(sd: StateDict, n_head: int, idx: torch.Tensor, targets: Optional[torch.Tensor] = None):
-    """GPT.forward of the repaired reference (mingpt/model.py:309-320), dropout = 0.
+def forward_reference(sd: StateDict, n_head: int, idx: torch.Tensor, targets: Optional[torch.Tensor] = None,
+                      masks: Optional[dict] = None, drop=(0.0, 0.0, 0.0)):
+    """GPT.forward of the repaired reference (mingpt/model.py:309-320). Dropout (embed, resid, attn = `drop`)
+    is applied with the keep masks given in `masks` ({"embed", ("attn", l), ("resid1", l), ("resid2", l)}).
     Keys are the reference's state_dict names."""
     B, T = idx.shape
+    masks = masks or {}
+    pe, pr, pa = drop
     # GPTEmbedding.forward, mingpt/model.py:222-231 (with repairs D2/D3: pos_embedding[:, :T, :])
     x = sd["embedding.token_embedding.weight"][idx] + sd["embedding.pos_embedding"][:, :T, :]
+    x = _drop(x, masks.get("embed"), pe)
     n_layer = 1 + max(int(k.split(".")[1]) for k in sd if k.startswith("blocks."))
     for i in range(n_layer):
         p = f"blocks.{i}."
@@ -71,15 +82,15 @@ def forward_reference(sd: StateDict, n_head: int, idx: torch.Tensor, targets: Op
         h = _layer_norm(x, sd, p + "ln_1")
         qkv = F.linear(h, sd[p + "attn.attn.in_proj_weight"], sd[p + "attn.attn.in_proj_bias"])
         q, k, v = (_split_heads(t, n_head) for t in qkv.chunk(3, dim=-1))
-        y = _attention_core(q, k, v, "add_tril_ones").transpose(1, 2).reshape(B, T, -1)
+        y = _attention_core(q, k, v, "add_tril_ones", masks.get(("attn", i)), pa).transpose(1, 2).reshape(B, T, -1)
         y = F.linear(y, sd[p + "attn.attn.out_proj.weight"], sd[p + "attn.attn.out_proj.bias"])
         y = F.linear(y, sd[p + "attn.c_proj.weight"], sd[p + "attn.c_proj.bias"])
-        x = x + y
+        x = x + _drop(y, masks.get(("resid1", i)), pr)
         # mlp = Linear -> Linear -> GELU(erf) -> Dropout, mingpt/model.py:179-184
         h = _layer_norm(x, sd, p + "ln_2")
         m = F.linear(h, sd[p + "mlp.0.weight"], sd[p + "mlp.0.bias"])
         m = F.linear(m, sd[p + "mlp.1.weight"], sd[p + "mlp.1.bias"])
-        x = x + F.gelu(m)
+        x = x + _drop(F.gelu(m), masks.get(("resid2", i)), pr)
     logits = F.linear(_layer_norm(x, sd, "ln_ff"), sd["head.weight"])
     loss = None
     if targets is not None:
@@ -87,22 +98,26 @@ def forward_reference(sd: StateDict, n_head: int, idx: torch.Tensor, targets: Op
     return logits, loss
 
 
-def forward_mingpt(sd: StateDict, n_head: int, idx: torch.Tensor, targets: Optional[torch.Tensor] = None):
+def forward_mingpt(sd: StateDict, n_head: int, idx: torch.Tensor, targets: Optional[torch.Tensor] = None,
+                   masks: Optional[dict] = None, drop=(0.0, 0.0, 0.0)):
     """The north_star graph: causal attention, c_attn/c_proj, c_fc -> NewGELU(tanh) -> c_proj, lm_head.
-    Keys are upstream minGPT's state_dict names."""
+    Keys are upstream minGPT's state_dict names. Dropout as in forward_reference."""
     B, T = idx.shape
+    masks = masks or {}
+    pe, pr, pa = drop
     x = sd["transformer.wte.weight"][idx] + sd["transformer.wpe.weight"][:T]
+    x = _drop(x, masks.get("embed"), pe)
     n_layer = 1 + max(int(k.split(".")[2]) for k in sd if k.startswith("transformer.h."))
     for i in range(n_layer):
         p = f"transformer.h.{i}."
         h = _layer_norm(x, sd, p + "ln_1")
         qkv = F.linear(h, sd[p + "attn.c_attn.weight"], sd[p + "attn.c_attn.bias"])
         q, k, v = (_split_heads(t, n_head) for t in qkv.chunk(3, dim=-1))
-        y = _attention_core(q, k, v, "causal").transpose(1, 2).reshape(B, T, -1)
-        x = x + F.linear(y, sd[p + "attn.c_proj.weight"], sd[p + "attn.c_proj.bias"])
+        y = _attention_core(q, k, v, "causal", masks.get(("attn", i)), pa).transpose(1, 2).reshape(B, T, -1)
+        x = x + _drop(F.linear(y, sd[p + "attn.c_proj.weight"], sd[p + "attn.c_proj.bias"]), masks.get(("resid1", i)), pr)
         h = _layer_norm(x, sd, p + "ln_2")
         m = F.gelu(F.linear(h, sd[p + "mlp.c_fc.weight"], sd[p + "mlp.c_fc.bias"]), approximate="tanh")
-        x = x + F.linear(m, sd[p + "mlp.c_proj.weight"], sd[p + "mlp.c_proj.bias"])
+        x = x + _drop(F.linear(m, sd[p + "mlp.c_proj.weight"], sd[p + "mlp.c_proj.bias"]), masks.get(("resid2", i)), pr)
     logits = F.linear(_layer_norm(x, sd, "transformer.ln_f"), sd["lm_head.weight"])
     loss = None
     if targets is not None:
@@ -110,10 +125,11 @@ def forward_mingpt(sd: StateDict, n_head: int, idx: torch.Tensor, targets: Optio
     return logits, loss
 
 
-def forward(sd: StateDict, n_head: int, idx, targets=None, variant: Optional[str] = None):
+def forward(sd: StateDict, n_head: int, idx, targets=None, variant: Optional[str] = None, masks=None,
+            drop=(0.0, 0.0, 0.0)):
     variant = variant or ("reference" if "head.weight" in sd else "mingpt")
     fn = forward_reference if variant == "reference" else forward_mingpt
-    return fn(sd, n_head, idx, targets)
+    return fn(sd, n_head, idx, targets, masks, drop)
 
 
 # ----------------------------------------------------------------------------------------------------

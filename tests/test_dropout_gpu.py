@@ -1,0 +1,129 @@
+"""Dropout (the reference trains with p = 0.1 at four sites, mingpt/model.py:49-51,140,150,183,215): the
+counter-based masks have the right statistics, forward and backward use the SAME mask, and a whole training
+forward/backward with dropout equals the oracle run with the exported masks."""
+import math
+
+import pytest
+import torch
+
+import mingpt_distributed_b200 as m
+from conftest import report
+from oracle import gpt_oracle as go
+
+pytestmark = pytest.mark.gpu
+
+
+def _seed(v):
+    return torch.tensor([v], dtype=torch.int64, device="cuda")
+
+
+def test_elementwise_dropout_statistics_and_determinism():
+    from mingpt_distributed_b200 import ops
+    n, p = 1 << 21, 0.1
+    x = (torch.rand(n, device="cuda") + 0.5).bfloat16()
+    res = torch.randn(n, device="cuda").bfloat16()
+    y = torch.empty_like(x)
+    ops.dropout(x, None, y, p, _seed(1234), 7)
+    keep = y != 0
+    rate = keep.float().mean().item()
+    assert abs(rate - (1 - p)) < 4 * math.sqrt(p * (1 - p) / n) + 1e-4, rate
+    assert torch.allclose(y[keep].float(), (x[keep].float() / (1 - p)).bfloat16().float(), rtol=1e-2)
+    y2 = torch.empty_like(x)
+    ops.dropout(x, None, y2, p, _seed(1234), 7)
+    assert torch.equal(y, y2)                                   # same (seed, site) -> same mask
+    ops.dropout(x, None, y2, p, _seed(1235), 7)
+    assert (((y2 != 0) ^ keep).float().mean().item()) > 0.1     # new seed -> new mask
+    ops.dropout(x, None, y2, p, _seed(1234), 8)
+    assert (((y2 != 0) ^ keep).float().mean().item()) > 0.1     # other site -> other mask
+    # fused residual add, and the backward (= the same call on the gradient) sees the same mask
+    ops.dropout(x, res, y2, p, _seed(1234), 7)
+    assert torch.allclose(y2.float(), y.float() + res.float(), rtol=2e-2, atol=2e-2)
+    g = torch.ones_like(x)
+    dg = torch.empty_like(x)
+    ops.dropout(g, None, dg, p, _seed(1234), 7)
+    assert torch.equal(dg != 0, keep)
+    # ragged length
+    ops.dropout(x[:1003], None, y2[:1003], p, _seed(1234), 7)
+    assert torch.equal(y2[:1003], y[:1003])
+    report("dropout_keep_rate", rate=rate)
+
+
+@pytest.mark.parametrize("d", [16, 32, 64])
+@pytest.mark.parametrize("mode", [1, 2])
+def test_attention_dropout_matches_torch_with_the_same_mask(d, mode):
+    from mingpt_distributed_b200 import ops
+    B, T, H, p = 2, 136, 3, 0.2
+    C = H * d
+    g = torch.Generator(device="cuda").manual_seed(5)
+    qkv = torch.randn(B, T, 3 * C, device="cuda", generator=g).bfloat16()
+    dout = torch.randn(B, T, C, device="cuda", generator=g).bfloat16()
+    seed = _seed(99)
+    keep = torch.empty(B, H, T, T, dtype=torch.uint8, device="cuda")
+    ops.attention_dropout_mask(keep, B, T, H, p, seed, 12)
+    rate = keep.float().mean().item()
+    assert abs(rate - (1 - p)) < 0.01
+    out = torch.empty(B, T, C, dtype=torch.bfloat16, device="cuda"); lse = torch.empty(B, H, T, device="cuda")
+    ops.attention_fwd_dropout(qkv, out, lse, B, T, H, d, mode, p, seed, 12)
+    qf = qkv.float().requires_grad_(True)
+    q, k, v = (t.view(B, T, H, d).transpose(1, 2) for t in qf.chunk(3, dim=-1))
+    want = go._attention_core(q, k, v, "causal" if mode == 1 else "add_tril_ones", keep, p).transpose(1, 2).reshape(B, T, C)
+    want.backward(dout.float())
+    err = (out.float() - want).abs().max().item()
+    assert err < 3e-2 * max(1.0, want.abs().max().item()), err
+    dqkv = torch.empty_like(qkv); delta = torch.empty_like(lse); dq = torch.empty(B, T, C, device="cuda")
+    ops.attention_bwd_dropout(qkv, out, dout, lse, delta, dq, dqkv, B, T, H, d, mode, p, seed, 12)
+    torch.cuda.synchronize()
+    gerr = (dqkv.float() - qf.grad).abs()
+    scale = qf.grad.abs().max().item()
+    assert (gerr <= 3e-2 * (qf.grad.abs() + 0.1 * scale)).all(), gerr.max().item()
+    report(f"attn_dropout_d{d}_m{mode}", out_err=err, grad_err=gerr.max().item(), keep_rate=rate)
+
+
+@pytest.mark.parametrize("variant", ["mingpt", "reference"])
+def test_training_step_with_dropout_equals_oracle_with_exported_masks(variant):
+    from mingpt_distributed_b200 import ops
+    L, H, C, V, T, B = 2, 2, 64, 97, 64, 3
+    pe, pr, pa = 0.1, 0.15, 0.2
+    torch.manual_seed(11)
+    cfg = m.GPTConfig(model_type=None, n_layer=L, n_head=H, n_embed=C, vocab_size=V, block_size=T, embed_drop=pe,
+                      resid_drop=pr, attn_drop=pa, variant=variant)
+    model = m.GPT(cfg, verbose=False)
+    sd = {k: v.clone() for k, v in model.state_dict().items()}
+    model = model.cuda().train()
+    x = torch.randint(0, V, (B, T)); y = torch.randint(0, V, (B, T))
+    _, loss = model(x.cuda(), y.cuda())
+    loss.backward()
+    seed = model._rng_seed.clone()
+    # rebuild every mask of that step from (seed, site)
+    ones = torch.ones(B * T * C, device="cuda").bfloat16(); buf = torch.empty_like(ones)
+    def ew_mask(p, site):
+        ops.dropout(ones, None, buf, p, seed, site)
+        return (buf != 0).view(B, T, C).cpu()
+    masks = {"embed": ew_mask(pe, m.GPT.SITE_EMBED)}
+    for l in range(L):
+        keep = torch.empty(B, H, T, T, dtype=torch.uint8, device="cuda")
+        ops.attention_dropout_mask(keep, B, T, H, pa, seed, 4 * l)
+        masks[("attn", l)] = keep.cpu()
+        masks[("resid1", l)] = ew_mask(pr, 4 * l + 1)
+        masks[("resid2", l)] = ew_mask(pr, 4 * l + 2)
+    q = lambda p: 1.0 - round(p * 65536) / 65536       # the kernels quantise the keep probability to 16 bits
+    osd = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    _, oloss = go.forward(osd, H, x, y, variant, masks, (1 - q(pe), 1 - q(pr), 1 - q(pa)))
+    oloss.backward()
+    report(f"dropout_step_{variant}", loss=loss.item(), oracle=oloss.item())
+    assert abs(loss.item() - oloss.item()) < 1e-2 * oloss.item()
+    for n, p in model.named_parameters():
+        ref = osd[n].grad
+        if ref.norm() < 1e-6:
+            continue
+        r = ((p.grad.cpu() - ref).norm() / ref.norm()).item()
+        assert r < 5e-2, f"{n}: {r:.4f}"
+    # eval mode switches dropout off; a second training forward draws a new seed
+    model.eval()
+    with torch.no_grad():
+        _, le = model(x.cuda(), y.cuda())
+    _, oe = go.forward(sd, H, x, y, variant)
+    assert abs(le.item() - oe.item()) < 1e-2 * oe.item()
+    model.train()
+    _, l2 = model(x.cuda(), y.cuda())
+    assert int(model._rng_seed.item()) == int(seed.item()) + 1 and abs(l2.item() - loss.item()) > 0

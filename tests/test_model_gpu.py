@@ -241,15 +241,6 @@ def test_gpttrainer_end_to_end_with_chardataset(tmp_path, monkeypatch):
     assert len(seen) == 5 and all(math.isfinite(v) for v in seen)
 
 
-def test_dropout_in_training_mode_is_refused_loudly():
-    model = m.GPT(m.GPTConfig(model_type="gpt-nano", vocab_size=65, block_size=32), verbose=False).cuda()   # reference default p = 0.1
-    x = torch.zeros(1, 8, dtype=torch.long, device="cuda")
-    with pytest.raises(NotImplementedError):
-        model(x, x)
-    model.eval()
-    model(x, x)
-
-
 def test_gpt2_124m_full_size_properties():
     """BASELINE config 3 shape (vocab 50257, T = 1024, 12 x 12 x 768): initial loss = ln(V), gradient
     linearity in the upstream gradient, finite gradients everywhere, one optimizer step lowers the loss."""
