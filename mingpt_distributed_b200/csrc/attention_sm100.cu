@@ -294,22 +294,30 @@ int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int 
 // =====================================================================================================
 // backward (recompute), head size 64
 // =====================================================================================================
-// One CTA = one block of 128 keys of one (batch, head); it walks over the query blocks that see those keys.
-// Everything is computed TRANSPOSED (rows = keys) so that a thread owns one key row in TMEM and the
-// recomputed P^T / dS^T are directly the A operands of the dV / dK products:
-//   S^T  = K Q^T          tcgen05.mma 128x128x64   TMEM cols [  0,128)
-//   dP^T = V dO^T         tcgen05.mma 128x128x64   TMEM cols [128,256)
-//   P^T  = exp2(S^T*c - lse_q), dS^T = P^T (dP^T - delta_q) * scale      (8 warps, thread = key row, half the queries each)
-//   dV  += P^T dO         A = P^T from TMEM cols [256,320), B = dO tile as MN-major operand; TMEM cols [384,448)
-//   dK  += dS^T Q         A = dS^T from shared memory (K-major view), B = Q tile (MN-major);  TMEM cols [320,384)
-//   dQ_i = dS K           A = the SAME shared-memory dS^T read as an MN-major operand, B = K tile (MN-major);
-//                         TMEM cols [448,512), drained with fp32 vector atomics into dq_accum
-// tcgen05.mma instructions of one thread execute in order, so "S^T of the next query block is done" implies
-// every product of the current block is done: no extra barriers guard the P^T / dS^T / dQ buffers.
-constexpr int kBwdThreads = 320;                  // 8 elementwise warps + TMA warp + MMA warp
+// One CTA = one block of 128 keys of one (batch, head); it walks over the query blocks that see those keys
+// in SUB-BLOCKS of 64 queries. Everything is computed TRANSPOSED (rows = keys) so that a thread owns one key
+// row in TMEM and the recomputed P^T / dS^T are directly the A operands of the dV / dK products:
+//   S^T  = K Q^T          tcgen05.mma 128x64x64    TMEM cols [  0,128): two buffers of 64
+//   dP^T = V dO^T         tcgen05.mma 128x64x64    TMEM cols [128,256): two buffers of 64
+//   P^T  = exp2(S^T*c - lse_q), dS^T = P^T (dP^T - delta_q) * scale     (8 warps, thread = key row, 32 queries each)
+//   dV  += P^T dO         A = P^T from TMEM cols [256,320) (two buffers of 32), B = dO sub-tile, MN-major; cols [384,448)
+//   dK  += dS^T Q         A = dS^T from shared memory (K-major view), B = Q sub-tile, MN-major;        cols [320,384)
+//   dQ_i = dS K           once per PAIR of sub-blocks (128 queries): A = the same shared-memory dS^T read as
+//                         an MN-major operand, B = K tile (MN-major); cols [448,512); four drain warps move it
+//                         TMEM -> registers -> swizzled box -> TMA fp32 reduce-add into dq_accum
+// Pipeline: the MMA thread issues S^T/dP^T of sub-block h+1 BEFORE it waits for the elementwise warps to
+// finish sub-block h, so the tensor pipe works on h+1 (and on dV/dK/dQ of h-1) while the warps do the
+// exponentials of h. tcgen05.mma instructions of one thread execute in order, which is what makes the
+// double buffers safe: "S^T of h+2 is complete" implies dV/dK of h (the readers of P^T[h&1] and of the
+// dS^T atom written four sub-blocks ago) are complete.
+constexpr int kBwdThreads = 448;                  // warps 0-7 elementwise, 8-11 dQ drain, 12 TMA, 13 MMA
+constexpr int SUBQ = 64;
+constexpr int SUB_BYTES = SUBQ * 128;             // 64 rows x 64 bf16
+constexpr int kSlots = 4;                         // Q/dO sub-tiles in flight
 constexpr uint32_t kBwdTmemCols = 512;
 constexpr uint32_t cST = 0, cDPT = 128, cPT = 256, cDK = 320, cDV = 384, cDQ = 448;
-constexpr int BWD_SMEM = 10 * TILE_BYTES + 2 * 128 * 8 + 1024 + 256;   // K, V, 2x(Q,dO), dS^T (2 atoms), dQ staging x2, lse/delta x2
+// K, V | 4 x (Q, dO) sub-tiles | dS^T: 4 atoms of 64 queries | dQ staging: 2 boxes | lse/delta x2 | barriers
+constexpr int BWD_SMEM = 2 * TILE_BYTES + kSlots * 2 * SUB_BYTES + 4 * TILE_BYTES + 2 * TILE_BYTES + 2 * 128 * 8 + 1024 + 256;
 
 __device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_t (&r)[16]) {
     asm volatile(
@@ -320,181 +328,295 @@ __device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_
         : "memory");
 }
 
+
+// Work items (one key block of one (batch, head)) are dealt to a PERSISTENT grid, so TMEM allocation, barrier
+// set-up and the prologue / epilogue bubbles are paid once per SM instead of once per item, and the TMA
+// producer already fetches the next item's Q / dO while the current item drains. The deal is in UNITS of
+// equal work whose items share a (batch, head): causal => the pair (key block p, key block nq-1-p), which
+// together see nq+1 query blocks; otherwise a single key block. Consecutive units are neighbouring key
+// blocks of the same (batch, head), so the CTAs running at any moment share their Q / dO tiles and their
+// dQ accumulator lines in L2.
+struct BwdItem {
+    int b, h, kb, i_begin, nblk;
+};
+struct BwdSched {
+    int H, nq, causal, units_per_bh, nunits, items_per_unit;
+};
+__device__ __forceinline__ BwdSched bwd_sched(int B, int H, int nq, bool causal) {
+    BwdSched sc;
+    sc.H = H; sc.nq = nq; sc.causal = causal;
+    sc.units_per_bh = causal ? (nq + 1) / 2 : nq;
+    sc.nunits = sc.units_per_bh * B * H;
+    sc.items_per_unit = causal ? 2 : 1;
+    return sc;
+}
+// q-th item slot of this CTA: -1 past the end, 0 empty slot (the middle key block of an odd count pairs with
+// itself), 1 valid. Every role walks the same sequence.
+__device__ __forceinline__ int bwd_item(const BwdSched& sc, int q, BwdItem& it) {
+    const int u = (int)blockIdx.x + (q / sc.items_per_unit) * (int)gridDim.x;
+    if (u >= sc.nunits) return -1;
+    const int second = q % sc.items_per_unit;
+    const int bh = u / sc.units_per_bh, p = u - bh * sc.units_per_bh;
+    it.kb = second ? sc.nq - 1 - p : p;
+    if (second && it.kb == p) return 0;
+    it.b = bh / sc.H;
+    it.h = bh - it.b * sc.H;
+    it.i_begin = sc.causal ? it.kb : 0;
+    it.nblk = sc.nq - it.i_begin;
+    return 1;
+}
+
 __global__ void __launch_bounds__(kBwdThreads, 1)
-attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do,
-                   const __grid_constant__ CUtensorMap tmap_dq, const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_accum,
-                   __nv_bfloat16* __restrict__ dqkv, int T, int H, int mask_mode, float scale, float scale_log2) {
+attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_constant__ CUtensorMap tmap_q,
+                   const __grid_constant__ CUtensorMap tmap_do, const __grid_constant__ CUtensorMap tmap_dq,
+                   const float* __restrict__ lse, const float* __restrict__ delta,
+                   __nv_bfloat16* __restrict__ dqkv, int B, int T, int H, int mask_mode, float scale, float scale_log2) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sK = smem;
     uint8_t* sV = smem + TILE_BYTES;
-    uint8_t* sQ = smem + 2 * TILE_BYTES;             // [2] stages: Q at +0, dO at +TILE_BYTES
-    uint8_t* sdS = smem + 6 * TILE_BYTES;            // dS^T: two 64-query atoms of 128 key rows x 128 B
-    uint8_t* sDQ = smem + 8 * TILE_BYTES;            // two boxes (one per warpgroup): 128 query rows x 32 fp32
-    float2* sLD = reinterpret_cast<float2*>(smem + 10 * TILE_BYTES);    // [2][128] (bias - lse*log2e, delta*scale)
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 10 * TILE_BYTES + 2 * 128 * 8);
+    uint8_t* sQ = smem + 2 * TILE_BYTES;                       // slot s: Q at +s*2*SUB_BYTES, dO right behind it
+    uint8_t* sdS = sQ + kSlots * 2 * SUB_BYTES;                // atom a: 128 key rows x 128 B (64 queries)
+    uint8_t* sDQ = sdS + 4 * TILE_BYTES;                       // two boxes: 128 query rows x 32 fp32
+    float2* sLD = reinterpret_cast<float2*>(sDQ + 2 * TILE_BYTES);   // [2][128] (bias - lse*log2e, delta*scale)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sDQ + 2 * TILE_BYTES + 2 * 128 * 8);
     uint64_t* kv_full = bars + 0;
-    uint64_t* qdo_full = bars + 1;     // [2]
-    uint64_t* qdo_empty = bars + 3;    // [2]
-    uint64_t* s_full = bars + 5;
-    uint64_t* p_ready = bars + 6;
-    uint64_t* all_done = bars + 7;
-    uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(bars + 8);
+    uint64_t* qdo_full = bars + 1;     // [4]
+    uint64_t* qdo_empty = bars + 5;    // [4]
+    uint64_t* s_full = bars + 9;       // [2]
+    uint64_t* p_ready = bars + 11;     // [2]
+    uint64_t* dq_full = bars + 13;
+    uint64_t* dq_free = bars + 14;
+    uint64_t* all_done = bars + 15;    // every product of the item has completed: K / V tiles and dK / dV are final
+    uint64_t* acc_free = bars + 16;    // dK / dV accumulators have been read out
+    uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(bars + 17);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int b = blockIdx.y / H, h = blockIdx.y % H;
-    const int kb = blockIdx.x;
-    const int k0 = kb * BKV;
     const int C = H * D;
     const bool causal = mask_mode == MGB_MASK_CAUSAL;
     const bool tril = mask_mode == MGB_MASK_ADD_TRIL_ONES;
     const int nq = (T + BQ - 1) / BQ;
-    const int i_begin = causal ? kb : 0;
-    const int nblk = nq - i_begin;
-    const int row0 = b * T;
+    const BwdSched sched = bwd_sched(B, H, nq, causal);        // key blocks == query blocks (BKV == BQ)
 
-    if (warp == 8 && lane == 0) {
-        tma_prefetch_desc(&tmap_qkv);
+    if (warp == 12 && lane == 0) {
+        tma_prefetch_desc(&tmap_kv);
+        tma_prefetch_desc(&tmap_q);
         tma_prefetch_desc(&tmap_do);
         tma_prefetch_desc(&tmap_dq);
         mbar_init(kv_full, 1);
-        for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
-        mbar_init(s_full, 1); mbar_init(p_ready, 8); mbar_init(all_done, 1);
+        for (int s = 0; s < kSlots; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(&s_full[s], 1); mbar_init(&p_ready[s], 8); }
+        mbar_init(dq_full, 1); mbar_init(dq_free, 4); mbar_init(all_done, 1); mbar_init(acc_free, 8);
         fence_mbar_init();
     }
-    if (warp == 9) tmem_alloc(tmem_base_ptr, kBwdTmemCols);
+    if (warp == 13) tmem_alloc(tmem_base_ptr, kBwdTmemCols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_base_ptr;
 
-    if (warp == 8) {
+    // running counters (identical in every role): g = sub-blocks so far, w = items so far. Every item has an
+    // even number of sub-blocks, so g & 1 is also the sub-block's position inside its 128-query block.
+    if (warp == 12) {
         // ===================== TMA producer =====================
         if (lane == 0) {
-            mbar_arrive_expect_tx(kv_full, 2 * TILE_BYTES);
-            tma_load_2d(sK, &tmap_qkv, kv_full, C + h * D, row0 + k0);
-            tma_load_2d(sV, &tmap_qkv, kv_full, 2 * C + h * D, row0 + k0);
-            for (int n = 0; n < nblk; ++n) {
-                const int st = n & 1;
-                const uint32_t ph = (uint32_t)((n >> 1) & 1);
-                mbar_wait(&qdo_empty[st], ph ^ 1);
-                mbar_arrive_expect_tx(&qdo_full[st], 2 * TILE_BYTES);
-                const int qrow = row0 + (i_begin + n) * BQ;
-                tma_load_2d(sQ + st * 2 * TILE_BYTES, &tmap_qkv, &qdo_full[st], h * D, qrow);
-                tma_load_2d(sQ + st * 2 * TILE_BYTES + TILE_BYTES, &tmap_do, &qdo_full[st], h * D, qrow);
+            uint32_t g = 0, w = 0;
+            for (int q = 0;; ++q) {
+                BwdItem it;
+                const int st = bwd_item(sched, q, it);
+                if (st < 0) break;
+                if (st == 0) continue;
+                const int row0 = it.b * T;
+                // the first 128 queries' Q / dO only need free slots: fetch them while the previous item still runs,
+                // K / V once that item no longer reads them
+                const int nsub = 2 * it.nblk;
+                const int kv_at = (w > 0) ? 2 : 0;
+                for (int n = 0; n <= nsub; ++n) {
+                    if (n == kv_at) {
+                        if (w > 0) mbar_wait(all_done, (w - 1) & 1);
+                        mbar_arrive_expect_tx(kv_full, 2 * TILE_BYTES);
+                        tma_load_2d(sK, &tmap_kv, kv_full, C + it.h * D, row0 + it.kb * BKV);
+                        tma_load_2d(sV, &tmap_kv, kv_full, 2 * C + it.h * D, row0 + it.kb * BKV);
+                    }
+                    if (n == nsub) break;
+                    const uint32_t slot = g & (kSlots - 1);
+                    mbar_wait(&qdo_empty[slot], ((g >> 2) & 1) ^ 1);
+                    mbar_arrive_expect_tx(&qdo_full[slot], 2 * SUB_BYTES);
+                    const int qrow = row0 + it.i_begin * BQ + n * SUBQ;
+                    tma_load_2d(sQ + slot * 2 * SUB_BYTES, &tmap_q, &qdo_full[slot], it.h * D, qrow);
+                    tma_load_2d(sQ + slot * 2 * SUB_BYTES + SUB_BYTES, &tmap_do, &qdo_full[slot], it.h * D, qrow);
+                    ++g;
+                }
+                ++w;
             }
         }
-    } else if (warp == 9) {
+    } else if (warp == 13) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
-            const uint32_t idesc_kk = make_idesc_bf16(128, 128, 0, 0);   // S^T, dP^T
+            const uint32_t idesc_s = make_idesc_bf16(128, SUBQ, 0, 0);   // S^T, dP^T: 128 keys x 64 queries
             const uint32_t idesc_kn = make_idesc_bf16(128, D, 0, 1);     // dV (A in TMEM), dK (A K-major smem)
             const uint32_t idesc_nn = make_idesc_bf16(128, D, 1, 1);     // dQ (A = dS^T read MN-major)
-            const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aS = smem_u32(sdS);
-            mbar_wait(kv_full, 0);
-            for (int n = 0; n < nblk; ++n) {
-                const int st = n & 1;
-                const uint32_t aQ = smem_u32(sQ + st * 2 * TILE_BYTES), aO = aQ + TILE_BYTES;
-                mbar_wait(&qdo_full[st], (uint32_t)((n >> 1) & 1));
+            // descriptor bases; a K step of 16 elements is +32 B (K-major) or +2048 B (MN-major) = +2 / +128 encoded
+            const uint64_t dKk = make_smem_desc_sw128(smem_u32(sK), 0, 1024);
+            const uint64_t dVk = make_smem_desc_sw128(smem_u32(sV), 0, 1024);
+            const uint64_t dKmn = make_smem_desc_sw128(smem_u32(sK), TILE_BYTES, 1024);
+            const uint64_t dQk0 = make_smem_desc_sw128(smem_u32(sQ), 0, 1024);
+            const uint64_t dQmn0 = make_smem_desc_sw128(smem_u32(sQ), TILE_BYTES, 1024);
+            const uint64_t dSk0 = make_smem_desc_sw128(smem_u32(sdS), 0, 1024);
+            const uint64_t dSmn0 = make_smem_desc_sw128(smem_u32(sdS), TILE_BYTES, 1024);
+            constexpr uint64_t kSlotStep = (2 * SUB_BYTES) >> 4, kSubStep = SUB_BYTES >> 4, kAtomStep = TILE_BYTES >> 4;
+
+            auto issue_scores = [&](uint32_t gg) {    // S^T and dP^T of sub-block gg into buffer gg & 1
+                const uint32_t slot = gg & (kSlots - 1);
+                const uint32_t bcol = (gg & 1) * SUBQ;
+                mbar_wait(&qdo_full[slot], (gg >> 2) & 1);
                 tc_fence_after();
+                const uint64_t dq_ = dQk0 + slot * kSlotStep, do_ = dq_ + kSubStep;
 #pragma unroll
                 for (int k = 0; k < D / 16; ++k)
-                    umma_bf16_ss(tmem_base + cST, make_smem_desc_sw128(aK + k * 32, 0, 1024),
-                                 make_smem_desc_sw128(aQ + k * 32, 0, 1024), idesc_kk, k > 0 ? 1u : 0u);
+                    umma_bf16_ss(tmem_base + cST + bcol, dKk + 2 * k, dq_ + 2 * k, idesc_s, k > 0 ? 1u : 0u);
 #pragma unroll
                 for (int k = 0; k < D / 16; ++k)
-                    umma_bf16_ss(tmem_base + cDPT, make_smem_desc_sw128(aV + k * 32, 0, 1024),
-                                 make_smem_desc_sw128(aO + k * 32, 0, 1024), idesc_kk, k > 0 ? 1u : 0u);
-                umma_commit(s_full);
-                mbar_wait(p_ready, (uint32_t)(n & 1));
-                tc_fence_after();
+                    umma_bf16_ss(tmem_base + cDPT + bcol, dVk + 2 * k, do_ + 2 * k, idesc_s, k > 0 ? 1u : 0u);
+                umma_commit(&s_full[gg & 1]);
+            };
+
+            uint32_t g = 0, w = 0;
+            for (int q = 0;; ++q) {
+                BwdItem it;
+                const int st = bwd_item(sched, q, it);
+                if (st < 0) break;
+                if (st == 0) continue;
+                const int nsub = 2 * it.nblk;
+                mbar_wait(kv_full, w & 1);
+                issue_scores(g);
+                for (int n = 0; n < nsub; ++n, ++g) {
+                    if (n + 1 < nsub) issue_scores(g + 1);
+                    mbar_wait(&p_ready[g & 1], (g >> 1) & 1);
+                    if (n == 0 && w > 0) mbar_wait(acc_free, (w - 1) & 1);   // dK / dV of the previous item are out
+                    tc_fence_after();
+                    const uint32_t slot = g & (kSlots - 1);
+                    const uint64_t qmn = dQmn0 + slot * kSlotStep, omn = qmn + kSubStep;
+                    const uint64_t dsk = dSk0 + (uint64_t)(g & 3) * kAtomStep;
 #pragma unroll
-                for (int kk = 0; kk < BQ / 16; ++kk)     // dV += P^T dO   (reduction over the 128 queries)
-                    umma_bf16_ts(tmem_base + cDV, tmem_base + cPT + kk * 8,
-                                 make_smem_desc_sw128(aO + kk * 2048, TILE_BYTES, 1024), idesc_kn,
-                                 (n > 0 || kk > 0) ? 1u : 0u);
+                    for (int kk = 0; kk < SUBQ / 16; ++kk)   // dV += P^T dO   (reduction over the 64 queries)
+                        umma_bf16_ts(tmem_base + cDV, tmem_base + cPT + (g & 1) * 32 + kk * 8, omn + 128 * kk,
+                                     idesc_kn, (n > 0 || kk > 0) ? 1u : 0u);
 #pragma unroll
-                for (int kk = 0; kk < BQ / 16; ++kk)     // dK += dS^T Q
-                    umma_bf16_ss(tmem_base + cDK,
-                                 make_smem_desc_sw128(aS + (kk >> 2) * TILE_BYTES + (kk & 3) * 32, 0, 1024),
-                                 make_smem_desc_sw128(aQ + kk * 2048, TILE_BYTES, 1024), idesc_kn,
-                                 (n > 0 || kk > 0) ? 1u : 0u);
+                    for (int kk = 0; kk < SUBQ / 16; ++kk)   // dK += dS^T Q
+                        umma_bf16_ss(tmem_base + cDK, dsk + 2 * kk, qmn + 128 * kk, idesc_kn, (n > 0 || kk > 0) ? 1u : 0u);
+                    umma_commit(&qdo_empty[slot]);           // last readers of this Q / dO sub-tile
+                    if (g & 1) {
+                        const uint32_t jg = g >> 1;
+                        if (jg > 0) { mbar_wait(dq_free, (jg - 1) & 1); tc_fence_after(); }
+                        const uint64_t dsmn = dSmn0 + (uint64_t)(jg & 1) * 2 * kAtomStep;
 #pragma unroll
-                for (int kk = 0; kk < BKV / 16; ++kk)    // dQ_i = dS K    (reduction over the 128 keys)
-                    umma_bf16_ss(tmem_base + cDQ, make_smem_desc_sw128(aS + kk * 2048, TILE_BYTES, 1024),
-                                 make_smem_desc_sw128(aK + kk * 2048, TILE_BYTES, 1024), idesc_nn, kk > 0 ? 1u : 0u);
-                umma_commit(&qdo_empty[st]);
+                        for (int kk = 0; kk < BKV / 16; ++kk)   // dQ_j = dS K    (reduction over the 128 keys)
+                            umma_bf16_ss(tmem_base + cDQ, dsmn + 128 * kk, dKmn + 128 * kk, idesc_nn, kk > 0 ? 1u : 0u);
+                        umma_commit(dq_full);
+                    }
+                }
+                umma_commit(all_done);
+                ++w;
             }
-            umma_commit(all_done);
         }
+    } else if (warp >= 8) {
+        // ===================== dQ drain warps: thread = query row of the block ==========
+        const int quarter = warp & 3;
+        const int r = quarter * 32 + lane;
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+        const uint32_t swz = (uint32_t)(r & 7);
+        const bool elected = (warp == 8) && (lane == 0);
+        uint32_t jg = 0;
+        for (int q = 0;; ++q) {
+            BwdItem it;
+            const int st = bwd_item(sched, q, it);
+            if (st < 0) break;
+            if (st == 0) continue;
+            for (int j = 0; j < it.nblk; ++j, ++jg) {
+                mbar_wait(dq_full, jg & 1);
+                tc_fence_after();
+                uint32_t lo[32], hi[32];
+                tmem_ld_32x32b_x32(taddr + cDQ, lo);
+                tmem_ld_32x32b_x32(taddr + cDQ + 32, hi);
+                tmem_ld_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(dq_free);          // the next dQ product may overwrite the accumulator
+                if (elected) bulk_wait_read<0>();             // both boxes have been read by the previous reduce
+                named_bar_sync(3, 128);
+                // rows of queries >= T hold exact zeros (their P is zero), so adding them is harmless
+                uint8_t* rowp = sDQ + r * 128;
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    *reinterpret_cast<uint4*>(rowp + (((uint32_t)u ^ swz) << 4)) =
+                        make_uint4(lo[u * 4], lo[u * 4 + 1], lo[u * 4 + 2], lo[u * 4 + 3]);
+                    *reinterpret_cast<uint4*>(rowp + TILE_BYTES + (((uint32_t)u ^ swz) << 4)) =
+                        make_uint4(hi[u * 4], hi[u * 4 + 1], hi[u * 4 + 2], hi[u * 4 + 3]);
+                }
+                fence_proxy_async_smem();
+                named_bar_sync(3, 128);
+                if (elected) {
+                    const int qrow = it.b * T + (it.i_begin + j) * BQ;
+                    tma_reduce_add_2d(&tmap_dq, sDQ, it.h * D, qrow);
+                    tma_reduce_add_2d(&tmap_dq, sDQ + TILE_BYTES, it.h * D + 32, qrow);
+                    bulk_commit();
+                }
+            }
+        }
+        if (elected) bulk_wait<0>();                          // every reduce-add has completed before the CTA exits
     } else {
-        // ===================== elementwise warps: thread = key row, warpgroup = half of the queries ==========
+        // ===================== elementwise warps: thread = key row, warpgroup = 32 of the 64 queries ==========
         const int quarter = warp & 3, wg = warp >> 2;
         const int r = quarter * 32 + lane;               // key row inside the block == TMEM lane
-        const int key = k0 + r;
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
         const uint32_t swz = (uint32_t)(r & 7);
         const int etid = threadIdx.x;                    // 0..255
-
-        uint8_t* dq_box = sDQ + wg * TILE_BYTES;         // this warpgroup's 128 rows x 32 fp32 staging box
-        const bool wg_elected = (quarter == 0) && (lane == 0);
-        auto drain_dq = [&](int iq) {
-            // dQ rows = queries of block iq (TMEM lane = query row); this warpgroup takes 32 of the 64 features.
-            // TMEM -> registers -> swizzled shared-memory box -> ONE TMA fp32 reduce-add per warpgroup (rows of
-            // queries >= T hold exact zeros because their P is zero, so adding them is harmless).
-            uint32_t dv[32];
-            __syncwarp();
-            tmem_ld_32x32b_x32(taddr + cDQ + wg * 32, dv);
-            tmem_ld_wait();
-            if (wg_elected) bulk_wait_read<0>();         // the previous reduce has finished reading the box
-            named_bar_sync(2 + wg, 128);
-            uint8_t* rowp = dq_box + r * 128;
-#pragma unroll
-            for (int u = 0; u < 8; ++u)
-                *reinterpret_cast<uint4*>(rowp + (((uint32_t)u ^ swz) << 4)) =
-                    make_uint4(dv[u * 4], dv[u * 4 + 1], dv[u * 4 + 2], dv[u * 4 + 3]);
-            fence_proxy_async_smem();
-            named_bar_sync(2 + wg, 128);
-            if (wg_elected) {
-                tma_reduce_add_2d(&tmap_dq, dq_box, h * D + wg * 32, row0 + iq * BQ);
-                bulk_commit();
-            }
-        };
-
-        for (int n = 0; n < nblk; ++n) {
-            const int i = i_begin + n;
-            const int buf = n & 1;
-            const bool diag = causal && (i == kb);
-            const bool need_mask = diag || (k0 + BKV > T) || (i * BQ + BQ > T);
-            const float bias_all = (tril && i > kb) ? LOG2E : 0.f;
-            const bool bias_diag = tril && (i == kb);
-            // stage, per query of this block: (bias - lse) in the log2 domain and delta * scale, so the inner
-            // loop is  p = exp2(fma(s, c, a));  ds = p * fma(dp, scale, -b)
+        uint32_t g = 0, w = 0;
+        for (int q = 0;; ++q) {
+            BwdItem it;
+            const int st = bwd_item(sched, q, it);
+            if (st < 0) break;
+            if (st == 0) continue;
+            const int kb = it.kb, k0 = kb * BKV, key = k0 + r;
+            const int64_t bh_off = ((int64_t)it.b * H + it.h) * T;
+            // per query of a 128-query block: (bias - lse) in the log2 domain and delta * scale, so the inner loop
+            // is  p = exp2(fma(s, c, a));  ds = p * fma(dp, scale, -b).   Loaded one block ahead of its use.
+            auto load_ld = [&](int i) {
+                const int tq = i * BQ + etid;
+                float2 v = make_float2(-INFINITY, 0.f);       // queries past the end: p = 0
+                if (tq < T)
+                    v = make_float2(((tril && i > kb) ? LOG2E : 0.f) - lse[bh_off + tq] * LOG2E, delta[bh_off + tq] * scale);
+                return v;
+            };
+            float2 nxt = make_float2(0.f, 0.f);
             if (etid < 128) {
-                const int t = i * BQ + etid;
-                float2 v = make_float2(-INFINITY, 0.f);   // queries past the end: p = 0
-                if (t < T) {
-                    const int64_t idx = ((int64_t)b * H + h) * T + t;
-                    v = make_float2(bias_all - lse[idx] * LOG2E, delta[idx] * scale);
-                }
-                sLD[buf * 128 + etid] = v;
+                sLD[((g >> 1) & 1) * 128 + etid] = load_ld(it.i_begin);   // this buffer was last read two blocks ago
+                if (it.nblk > 1) nxt = load_ld(it.i_begin + 1);
             }
             named_bar_sync(1, 256);
-            mbar_wait(s_full, (uint32_t)(n & 1));
-            tc_fence_after();
-            if (n > 0) drain_dq(i - 1);                  // S^T_n done  =>  dQ of the previous block is complete
-            const float2* ld = sLD + buf * 128 + wg * 64;
-#pragma unroll 1
-            for (int c = 0; c < 2; ++c) {
+
+            for (int n = 0; n < 2 * it.nblk; ++n, ++g) {
+                const int j = n >> 1;
+                const uint32_t half = g & 1, jg = g >> 1;
+                const int i = it.i_begin + j;
+                const bool diag = causal && (i == kb);
+                const bool need_mask = diag || (k0 + BKV > T) || (i * BQ + BQ > T);
+                const bool bias_diag = tril && (i == kb);
+                if (half == 0 && j > 0) named_bar_sync(1, 256);      // sLD[jg & 1] was written at the end of the last sub-block
+                mbar_wait(&s_full[half], jg & 1);
+                tc_fence_after();
+                const int qc0 = (int)half * SUBQ + wg * 32;          // first query column (inside the block) of this thread
+                const float2* ld = sLD + (jg & 1) * 128 + qc0;
                 uint32_t sv[32], dp[32];
-                tmem_ld_32x32b_x32(taddr + cST + wg * 64 + c * 32, sv);
-                tmem_ld_32x32b_x32(taddr + cDPT + wg * 64 + c * 32, dp);
+                tmem_ld_32x32b_x32(taddr + cST + half * SUBQ + wg * 32, sv);
+                tmem_ld_32x32b_x32(taddr + cDPT + half * SUBQ + wg * 32, dp);
                 tmem_ld_wait();
                 uint32_t pk[16], dk[16];
                 if (!need_mask && !bias_diag) {
 #pragma unroll
                     for (int e = 0; e < 16; ++e) {
-                        const float4 l4 = *reinterpret_cast<const float4*>(ld + c * 32 + 2 * e);   // (a0, b0, a1, b1)
+                        const float4 l4 = *reinterpret_cast<const float4*>(ld + 2 * e);   // (a0, b0, a1, b1)
                         const float p0 = exp2f(fmaf(__uint_as_float(sv[2 * e]), scale_log2, l4.x));
                         const float p1 = exp2f(fmaf(__uint_as_float(sv[2 * e + 1]), scale_log2, l4.z));
                         pk[e] = pack_bf16x2(p0, p1);
@@ -507,9 +629,8 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
                         float pv[2], dsv[2];
 #pragma unroll
                         for (int t2 = 0; t2 < 2; ++t2) {
-                            const int cl = c * 32 + 2 * e + t2;         // query column inside this warpgroup's half
-                            const int col = wg * 64 + cl;               // query column inside the block
-                            const float2 ldv = ld[cl];
+                            const int col = qc0 + 2 * e + t2;          // query column inside the block
+                            const float2 ldv = ld[2 * e + t2];
                             float x = fmaf(__uint_as_float(sv[2 * e + t2]), scale_log2, ldv.x);
                             if (bias_diag && r <= col) x += LOG2E;
                             const bool dead = (key >= T) || (diag && r > col);   // queries >= T carry a = -inf
@@ -521,52 +642,59 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
                         dk[e] = pack_bf16x2(dsv[0], dsv[1]);
                     }
                 }
-                tmem_st_32x32b_x16(taddr + cPT + wg * 32 + c * 16, pk);
-                // dS^T row `r`, queries [wg*64 + c*32, +32): four 16-byte units of atom `wg`
-                uint8_t* rowp = sdS + wg * TILE_BYTES + r * 128;
+                tmem_st_32x32b_x16(taddr + cPT + half * 32 + wg * 16, pk);
+                // dS^T row `r` of atom g & 3, queries [wg*32, +32) of the sub-block: four 16-byte units
+                uint8_t* rowp = sdS + (g & 3) * TILE_BYTES + r * 128;
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
-                    const uint32_t jj = (uint32_t)(c * 4 + u);
+                    const uint32_t jj = (uint32_t)(wg * 4 + u);
                     *reinterpret_cast<uint4*>(rowp + ((jj ^ swz) << 4)) =
                         make_uint4(dk[u * 4 + 0], dk[u * 4 + 1], dk[u * 4 + 2], dk[u * 4 + 3]);
                 }
+                tmem_st_wait();
+                tc_fence_before();
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&p_ready[half]);
+                if (half == 1 && j + 1 < it.nblk && etid < 128) {
+                    sLD[((jg + 1) & 1) * 128 + etid] = nxt;          // last read two blocks ago
+                    if (j + 2 < it.nblk) nxt = load_ld(i + 2);
+                }
             }
-            tmem_st_wait();
-            tc_fence_before();
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(p_ready);
-        }
-        // ---- epilogue: last dQ, then dK / dV of this key block ----
-        mbar_wait(all_done, 0);
-        tc_fence_after();
-        drain_dq(i_begin + nblk - 1);
-        const int64_t ld3 = (int64_t)3 * C;
-        __nv_bfloat16* krow = dqkv + ((int64_t)(row0 + key)) * ld3 + C + (int64_t)h * D + wg * 32;
-#pragma unroll 1
-        for (int which = 0; which < 2; ++which) {        // 0: dK, 1: dV
-            uint32_t v[32];
-            __syncwarp();
-            tmem_ld_32x32b_x32(taddr + (which ? cDV : cDK) + wg * 32, v);
+            // ---- item epilogue: dK / dV of this key block ----
+            mbar_wait(all_done, w & 1);
+            tc_fence_after();
+            uint32_t vk[32], vv[32];
+            tmem_ld_32x32b_x32(taddr + cDK + wg * 32, vk);
+            tmem_ld_32x32b_x32(taddr + cDV + wg * 32, vv);
             tmem_ld_wait();
-            if (which == 0 && wg_elected) bulk_wait<0>();   // all dQ reduce-adds have left shared memory
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(acc_free);            // the next item may start accumulating
             if (key < T) {
-                __nv_bfloat16* dst = krow + (int64_t)which * C;
+                __nv_bfloat16* krow = dqkv + ((int64_t)(it.b * T + key)) * (3 * C) + C + (int64_t)it.h * D + wg * 32;
 #pragma unroll
-                for (int u = 0; u < 4; ++u)
-                    stg128(dst + u * 8,
-                           make_uint4(pack_bf16x2(__uint_as_float(v[u * 8 + 0]), __uint_as_float(v[u * 8 + 1])),
-                                      pack_bf16x2(__uint_as_float(v[u * 8 + 2]), __uint_as_float(v[u * 8 + 3])),
-                                      pack_bf16x2(__uint_as_float(v[u * 8 + 4]), __uint_as_float(v[u * 8 + 5])),
-                                      pack_bf16x2(__uint_as_float(v[u * 8 + 6]), __uint_as_float(v[u * 8 + 7]))));
+                for (int u = 0; u < 4; ++u) {
+                    stg128(krow + u * 8,
+                           make_uint4(pack_bf16x2(__uint_as_float(vk[u * 8 + 0]), __uint_as_float(vk[u * 8 + 1])),
+                                      pack_bf16x2(__uint_as_float(vk[u * 8 + 2]), __uint_as_float(vk[u * 8 + 3])),
+                                      pack_bf16x2(__uint_as_float(vk[u * 8 + 4]), __uint_as_float(vk[u * 8 + 5])),
+                                      pack_bf16x2(__uint_as_float(vk[u * 8 + 6]), __uint_as_float(vk[u * 8 + 7]))));
+                    stg128(krow + C + u * 8,
+                           make_uint4(pack_bf16x2(__uint_as_float(vv[u * 8 + 0]), __uint_as_float(vv[u * 8 + 1])),
+                                      pack_bf16x2(__uint_as_float(vv[u * 8 + 2]), __uint_as_float(vv[u * 8 + 3])),
+                                      pack_bf16x2(__uint_as_float(vv[u * 8 + 4]), __uint_as_float(vv[u * 8 + 5])),
+                                      pack_bf16x2(__uint_as_float(vv[u * 8 + 6]), __uint_as_float(vv[u * 8 + 7]))));
+                }
             }
+            ++w;
         }
     }
 
     __syncwarp();
     tc_fence_before();
     __syncthreads();
-    if (warp == 9) {
+    if (warp == 13) {
         tc_fence_after();
         tmem_dealloc(tmem_base, kBwdTmemCols);
     }
@@ -579,16 +707,20 @@ int launch_bwd_main(const void* qkv, const void* dout, const float* lse, const f
     std::call_once(once, [] {
         cudaFuncSetAttribute(attn_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
     });
-    CUtensorMap tq, td, tdq;
+    CUtensorMap tkv, tq, td, tdq;
     const int64_t C = (int64_t)H * D, C3 = 3 * C;
-    int rc = gemm::make_map_2d(&tq, qkv, C3, (int64_t)B * T, C3, 64, 128);
+    int rc = gemm::make_map_2d(&tkv, qkv, C3, (int64_t)B * T, C3, 64, 128);
     if (rc) return rc;
-    rc = gemm::make_map_2d(&td, dout, C, (int64_t)B * T, C, 64, 128);
+    rc = gemm::make_map_2d(&tq, qkv, C3, (int64_t)B * T, C3, 64, SUBQ);
+    if (rc) return rc;
+    rc = gemm::make_map_2d(&td, dout, C, (int64_t)B * T, C, 64, SUBQ);
     if (rc) return rc;
     rc = gemm::make_map_2d(&tdq, dq_accum, C, (int64_t)B * T, C, 32, 128, /*f32=*/true);
     if (rc) return rc;
-    dim3 grid((T + BKV - 1) / BKV, B * H);
-    attn_bwd_tc_kernel<<<grid, kBwdThreads, BWD_SMEM, stream>>>(tq, td, tdq, lse, delta, dq_accum, (__nv_bfloat16*)dqkv, T, H,
+    const int nq = (T + BKV - 1) / BKV;
+    const int nunits = (mask_mode == MGB_MASK_CAUSAL ? (nq + 1) / 2 : nq) * B * H;
+    const int grid = nunits < num_sms() ? nunits : num_sms();
+    attn_bwd_tc_kernel<<<grid, kBwdThreads, BWD_SMEM, stream>>>(tkv, tq, td, tdq, lse, delta, (__nv_bfloat16*)dqkv, B, T, H,
                                                                 mask_mode, scale, scale * LOG2E);
     return kOk;
 }
