@@ -57,7 +57,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
     uint64_t* pv_done = bars + 7;
     uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(bars + 8);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
     const int b = blockIdx.y / H, h = blockIdx.y % H;
     const int qb = gridDim.x - 1 - blockIdx.x;       // heavy (late) causal blocks first
     const int q0 = qb * BQ;
@@ -81,57 +81,68 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
     const uint32_t tmem_base = *tmem_base_ptr;
 
     if (warp == 4) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
+        // ===================== TMA producer (whole warp runs the loop, one lane issues) =====================
+        const bool issuer = elect_one();
+        if (issuer) {
             mbar_arrive_expect_tx(q_full, TILE_BYTES);
             tma_load_2d(sQ, &tmap_qkv, q_full, h * D, row0 + q0);
-            for (int j = 0; j < nkv; ++j) {
-                const uint32_t ph = (uint32_t)(j & 1);
-                mbar_wait(k_empty, ph ^ 1);           // S_{j-1} has consumed the previous K
+        }
+        __syncwarp();
+        for (int j = 0; j < nkv; ++j) {
+            const uint32_t ph = (uint32_t)(j & 1);
+            mbar_wait(k_empty, ph ^ 1);               // S_{j-1} has consumed the previous K
+            if (issuer) {
                 mbar_arrive_expect_tx(k_full, TILE_BYTES);
                 tma_load_2d(sK, &tmap_qkv, k_full, C + h * D, row0 + j * BKV);
-                mbar_wait(v_empty, ph ^ 1);           // P V_{j-1} has consumed the previous V
+            }
+            __syncwarp();
+            mbar_wait(v_empty, ph ^ 1);               // P V_{j-1} has consumed the previous V
+            if (issuer) {
                 mbar_arrive_expect_tx(v_full, TILE_BYTES);
                 tma_load_2d(sV, &tmap_qkv, v_full, 2 * C + h * D, row0 + j * BKV);
             }
+            __syncwarp();
         }
     } else if (warp == 5) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
-            const uint32_t idesc_s = make_idesc_bf16(BQ, BKV, 0, 0);   // S: 128 x 128, both K-major
-            const uint32_t idesc_o = make_idesc_bf16(BQ, D, 0, 1);     // O: 128 x 64, V MN-major
-            const uint32_t aQ = smem_u32(sQ), aK = smem_u32(sK), aV = smem_u32(sV);
-            mbar_wait(q_full, 0);
-            mbar_wait(k_full, 0);
-            tc_fence_after();
+        // ===================== MMA issuer (whole warp runs the loop, one lane issues) =====================
+        const bool issuer = elect_one();
+        const uint32_t idesc_s = make_idesc_bf16(BQ, BKV, 0, 0);   // S: 128 x 128, both K-major
+        const uint32_t idesc_o = make_idesc_bf16(BQ, D, 0, 1);     // O: 128 x 64, V MN-major
+        const uint64_t dQ = make_smem_desc_sw128(smem_u32(sQ), 0, 1024);
+        const uint64_t dK = make_smem_desc_sw128(smem_u32(sK), 0, 1024);
+        const uint64_t dV = make_smem_desc_sw128(smem_u32(sV), TILE_BYTES, 1024);   // MN-major: +2048 B per 16 keys
+        auto issue_s = [&]() {
+            if (issuer) {
 #pragma unroll
-            for (int k = 0; k < D / 16; ++k)
-                umma_bf16_ss(tmem_base + kColS, make_smem_desc_sw128(aQ + k * 32, 0, 1024),
-                             make_smem_desc_sw128(aK + k * 32, 0, 1024), idesc_s, k > 0 ? 1u : 0u);
-            umma_commit(k_empty);
-            umma_commit(s_full);
-            for (int j = 0; j < nkv; ++j) {
-                const uint32_t ph = (uint32_t)(j & 1);
-                mbar_wait(p_ready, ph);               // P_j in TMEM, O rescaled if needed, S consumed
-                mbar_wait(v_full, ph);
-                tc_fence_after();
+                for (int k = 0; k < D / 16; ++k)
+                    umma_bf16_ss(tmem_base + kColS, dQ + 2 * k, dK + 2 * k, idesc_s, k > 0 ? 1u : 0u);
+                umma_commit(k_empty);
+                umma_commit(s_full);
+            }
+            __syncwarp();
+        };
+        mbar_wait(q_full, 0);
+        mbar_wait(k_full, 0);
+        tc_fence_after();
+        issue_s();
+        for (int j = 0; j < nkv; ++j) {
+            const uint32_t ph = (uint32_t)(j & 1);
+            mbar_wait(p_ready, ph);               // P_j in TMEM, O rescaled if needed, S consumed
+            mbar_wait(v_full, ph);
+            tc_fence_after();
+            if (issuer) {
 #pragma unroll
                 for (int kk = 0; kk < BKV / 16; ++kk)   // A = P from TMEM: 16 bf16 = 8 packed columns per step
-                    umma_bf16_ts(tmem_base + kColO, tmem_base + kColP + kk * 8,
-                                 make_smem_desc_sw128(aV + kk * 2048, TILE_BYTES, 1024), idesc_o,
+                    umma_bf16_ts(tmem_base + kColO, tmem_base + kColP + kk * 8, dV + 128 * kk, idesc_o,
                                  (j > 0 || kk > 0) ? 1u : 0u);
                 umma_commit(v_empty);
                 umma_commit(pv_done);
-                if (j + 1 < nkv) {
-                    mbar_wait(k_full, ph ^ 1);
-                    tc_fence_after();
-#pragma unroll
-                    for (int k = 0; k < D / 16; ++k)
-                        umma_bf16_ss(tmem_base + kColS, make_smem_desc_sw128(aQ + k * 32, 0, 1024),
-                                     make_smem_desc_sw128(aK + k * 32, 0, 1024), idesc_s, k > 0 ? 1u : 0u);
-                    umma_commit(k_empty);
-                    umma_commit(s_full);
-                }
+            }
+            __syncwarp();
+            if (j + 1 < nkv) {
+                mbar_wait(k_full, ph ^ 1);
+                tc_fence_after();
+                issue_s();
             }
         }
     } else {
@@ -391,7 +402,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
     uint64_t* acc_free = bars + 16;    // dK / dV accumulators have been read out
     uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(bars + 17);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
     const int C = H * D;
     const bool causal = mask_mode == MGB_MASK_CAUSAL;
     const bool tril = mask_mode == MGB_MASK_ADD_TRIL_ONES;
@@ -418,8 +429,9 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
     // running counters (identical in every role): g = sub-blocks so far, w = items so far. Every item has an
     // even number of sub-blocks, so g & 1 is also the sub-block's position inside its 128-query block.
     if (warp == 12) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
+        // ===================== TMA producer (whole warp runs the loop, one lane issues) =====================
+        {
+            const bool issuer = elect_one();
             uint32_t g = 0, w = 0;
             for (int q = 0;; ++q) {
                 BwdItem it;
@@ -434,25 +446,32 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 for (int n = 0; n <= nsub; ++n) {
                     if (n == kv_at) {
                         if (w > 0) mbar_wait(all_done, (w - 1) & 1);
-                        mbar_arrive_expect_tx(kv_full, 2 * TILE_BYTES);
-                        tma_load_2d(sK, &tmap_kv, kv_full, C + it.h * D, row0 + it.kb * BKV);
-                        tma_load_2d(sV, &tmap_kv, kv_full, 2 * C + it.h * D, row0 + it.kb * BKV);
+                        if (issuer) {
+                            mbar_arrive_expect_tx(kv_full, 2 * TILE_BYTES);
+                            tma_load_2d(sK, &tmap_kv, kv_full, C + it.h * D, row0 + it.kb * BKV);
+                            tma_load_2d(sV, &tmap_kv, kv_full, 2 * C + it.h * D, row0 + it.kb * BKV);
+                        }
+                        __syncwarp();
                     }
                     if (n == nsub) break;
                     const uint32_t slot = g & (kSlots - 1);
                     mbar_wait(&qdo_empty[slot], ((g >> 2) & 1) ^ 1);
-                    mbar_arrive_expect_tx(&qdo_full[slot], 2 * SUB_BYTES);
                     const int qrow = row0 + it.i_begin * BQ + n * SUBQ;
-                    tma_load_2d(sQ + slot * 2 * SUB_BYTES, &tmap_q, &qdo_full[slot], it.h * D, qrow);
-                    tma_load_2d(sQ + slot * 2 * SUB_BYTES + SUB_BYTES, &tmap_do, &qdo_full[slot], it.h * D, qrow);
+                    if (issuer) {
+                        mbar_arrive_expect_tx(&qdo_full[slot], 2 * SUB_BYTES);
+                        tma_load_2d(sQ + slot * 2 * SUB_BYTES, &tmap_q, &qdo_full[slot], it.h * D, qrow);
+                        tma_load_2d(sQ + slot * 2 * SUB_BYTES + SUB_BYTES, &tmap_do, &qdo_full[slot], it.h * D, qrow);
+                    }
+                    __syncwarp();
                     ++g;
                 }
                 ++w;
             }
         }
     } else if (warp == 13) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
+        // ===================== MMA issuer (whole warp runs the loop, one lane issues) =====================
+        {
+            const bool issuer = elect_one();
             const uint32_t idesc_s = make_idesc_bf16(128, SUBQ, 0, 0);   // S^T, dP^T: 128 keys x 64 queries
             const uint32_t idesc_kn = make_idesc_bf16(128, D, 0, 1);     // dV (A in TMEM), dK (A K-major smem)
             const uint32_t idesc_nn = make_idesc_bf16(128, D, 1, 1);     // dQ (A = dS^T read MN-major)
@@ -472,13 +491,16 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 mbar_wait(&qdo_full[slot], (gg >> 2) & 1);
                 tc_fence_after();
                 const uint64_t dq_ = dQk0 + slot * kSlotStep, do_ = dq_ + kSubStep;
+                if (issuer) {
 #pragma unroll
-                for (int k = 0; k < D / 16; ++k)
-                    umma_bf16_ss(tmem_base + cST + bcol, dKk + 2 * k, dq_ + 2 * k, idesc_s, k > 0 ? 1u : 0u);
+                    for (int k = 0; k < D / 16; ++k)
+                        umma_bf16_ss(tmem_base + cST + bcol, dKk + 2 * k, dq_ + 2 * k, idesc_s, k > 0 ? 1u : 0u);
 #pragma unroll
-                for (int k = 0; k < D / 16; ++k)
-                    umma_bf16_ss(tmem_base + cDPT + bcol, dVk + 2 * k, do_ + 2 * k, idesc_s, k > 0 ? 1u : 0u);
-                umma_commit(&s_full[gg & 1]);
+                    for (int k = 0; k < D / 16; ++k)
+                        umma_bf16_ss(tmem_base + cDPT + bcol, dVk + 2 * k, do_ + 2 * k, idesc_s, k > 0 ? 1u : 0u);
+                    umma_commit(&s_full[gg & 1]);
+                }
+                __syncwarp();
             };
 
             uint32_t g = 0, w = 0;
@@ -498,25 +520,32 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                     const uint32_t slot = g & (kSlots - 1);
                     const uint64_t qmn = dQmn0 + slot * kSlotStep, omn = qmn + kSubStep;
                     const uint64_t dsk = dSk0 + (uint64_t)(g & 3) * kAtomStep;
+                    if (issuer) {
 #pragma unroll
-                    for (int kk = 0; kk < SUBQ / 16; ++kk)   // dV += P^T dO   (reduction over the 64 queries)
-                        umma_bf16_ts(tmem_base + cDV, tmem_base + cPT + (g & 1) * 32 + kk * 8, omn + 128 * kk,
-                                     idesc_kn, (n > 0 || kk > 0) ? 1u : 0u);
+                        for (int kk = 0; kk < SUBQ / 16; ++kk)   // dV += P^T dO   (reduction over the 64 queries)
+                            umma_bf16_ts(tmem_base + cDV, tmem_base + cPT + (g & 1) * 32 + kk * 8, omn + 128 * kk,
+                                         idesc_kn, (n > 0 || kk > 0) ? 1u : 0u);
 #pragma unroll
-                    for (int kk = 0; kk < SUBQ / 16; ++kk)   // dK += dS^T Q
-                        umma_bf16_ss(tmem_base + cDK, dsk + 2 * kk, qmn + 128 * kk, idesc_kn, (n > 0 || kk > 0) ? 1u : 0u);
-                    umma_commit(&qdo_empty[slot]);           // last readers of this Q / dO sub-tile
+                        for (int kk = 0; kk < SUBQ / 16; ++kk)   // dK += dS^T Q
+                            umma_bf16_ss(tmem_base + cDK, dsk + 2 * kk, qmn + 128 * kk, idesc_kn, (n > 0 || kk > 0) ? 1u : 0u);
+                        umma_commit(&qdo_empty[slot]);           // last readers of this Q / dO sub-tile
+                    }
+                    __syncwarp();
                     if (g & 1) {
                         const uint32_t jg = g >> 1;
                         if (jg > 0) { mbar_wait(dq_free, (jg - 1) & 1); tc_fence_after(); }
                         const uint64_t dsmn = dSmn0 + (uint64_t)(jg & 1) * 2 * kAtomStep;
+                        if (issuer) {
 #pragma unroll
-                        for (int kk = 0; kk < BKV / 16; ++kk)   // dQ_j = dS K    (reduction over the 128 keys)
-                            umma_bf16_ss(tmem_base + cDQ, dsmn + 128 * kk, dKmn + 128 * kk, idesc_nn, kk > 0 ? 1u : 0u);
-                        umma_commit(dq_full);
+                            for (int kk = 0; kk < BKV / 16; ++kk)   // dQ_j = dS K    (reduction over the 128 keys)
+                                umma_bf16_ss(tmem_base + cDQ, dsmn + 128 * kk, dKmn + 128 * kk, idesc_nn, kk > 0 ? 1u : 0u);
+                            umma_commit(dq_full);
+                        }
+                        __syncwarp();
                     }
                 }
-                umma_commit(all_done);
+                if (issuer) umma_commit(all_done);
+                __syncwarp();
                 ++w;
             }
         }

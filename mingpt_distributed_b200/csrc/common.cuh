@@ -97,6 +97,16 @@ __device__ __forceinline__ float gelu_erf_grad_f(float x) {
 // ----------------------------------------------------------------------------
 // mbarrier
 // ----------------------------------------------------------------------------
+// One lane of a CONVERGED warp. The producer / MMA warps run their loops with all 32 lanes (addresses and
+// descriptors stay warp-uniform, so they live in uniform registers) and predicate only the TMA / tcgen05
+// instructions on this: issuing them from inside an `if (lane == 0)` region makes the compiler wrap every
+// single one in an ELECT / R2UR / BRA.U.ANY loop, ~100 cycles per instruction (tools/micro/mma_rate.cu).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred = 0;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }

@@ -118,7 +118,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     uint64_t* aux_bar = tmem_empty + 2;              // [kNumBoxes]   residual / gate tile landed in box i
     uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(aux_bar + kNumBoxes);
 
-    const int warp = threadIdx.x >> 5;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);   // provably warp-uniform
     const int lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
     const bool leader = rank == 0;
@@ -156,8 +156,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const int units = tiles * p.split_k;
 
     if (warp == 0) {
-        // ===================== TMA producer (both CTAs) =====================
-        if (lane == 0) {
+        // ===================== TMA producer (both CTAs; whole warp runs the loop, one lane issues) ==========
+        {
+            const bool issuer = elect_one();
             uint32_t stage = 0, phase = 0;
             for (int u = cluster_id; u < units; u += num_clusters) {
                 const int split = u / tiles;
@@ -170,30 +171,34 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 const int kb1 = min(kb0 + p.k_blocks_per_split, p.k_blocks_total);
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
-                    if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * stage_bytes);
-                    else mbar_arrive_cluster(&full_bar[stage], 0);
                     uint8_t* sa = smem + stage * stage_bytes;
                     uint8_t* sb = sa + BLOCK_M * BLOCK_K * 2;
                     const int k0 = kb * BLOCK_K;
-                    if (!p.a_mn) {
-                        tma_load_2d_cg2(sa, &tmap_a, &full_bar[stage], k0, m0);
-                    } else {
-                        tma_load_2d_cg2(sa, &tmap_a, &full_bar[stage], m0, k0);
-                        tma_load_2d_cg2(sa + ATOM_BYTES, &tmap_a, &full_bar[stage], m0 + 64, k0);
+                    if (issuer) {
+                        if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * stage_bytes);
+                        else mbar_arrive_cluster(&full_bar[stage], 0);
+                        if (!p.a_mn) {
+                            tma_load_2d_cg2(sa, &tmap_a, &full_bar[stage], k0, m0);
+                        } else {
+                            tma_load_2d_cg2(sa, &tmap_a, &full_bar[stage], m0, k0);
+                            tma_load_2d_cg2(sa + ATOM_BYTES, &tmap_a, &full_bar[stage], m0 + 64, k0);
+                        }
+                        if (!p.b_mn) {
+                            tma_load_2d_cg2(sb, &tmap_b, &full_bar[stage], k0, n0);
+                        } else {
+                            for (int a = 0; a < nb / 64; ++a)
+                                tma_load_2d_cg2(sb + a * ATOM_BYTES, &tmap_b, &full_bar[stage], n0 + a * 64, k0);
+                        }
                     }
-                    if (!p.b_mn) {
-                        tma_load_2d_cg2(sb, &tmap_b, &full_bar[stage], k0, n0);
-                    } else {
-                        for (int a = 0; a < nb / 64; ++a)
-                            tma_load_2d_cg2(sb + a * ATOM_BYTES, &tmap_b, &full_bar[stage], n0 + a * 64, k0);
-                    }
+                    __syncwarp();
                     if (++stage == (uint32_t)p.num_stages) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer (leader CTA only) =====================
-        if (leader && lane == 0) {
+        // ===================== MMA issuer (leader CTA only; whole warp runs the loop, one lane issues) ======
+        if (leader) {
+            const bool issuer = elect_one();
             const uint32_t idesc = make_idesc_bf16(2 * BLOCK_M, block_n, p.a_mn, p.b_mn);
             const uint32_t a_lbo = p.a_mn ? ATOM_BYTES : 0, b_lbo = p.b_mn ? ATOM_BYTES : 0;
             const uint32_t a_kstep = p.a_mn ? UMMA_K * 128 : UMMA_K * 2;
@@ -212,16 +217,20 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     tc_fence_after();
                     const uint32_t sa = smem_u32(smem + stage * stage_bytes);
                     const uint32_t sb = sa + BLOCK_M * BLOCK_K * 2;
+                    if (issuer) {
 #pragma unroll
-                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-                        const uint64_t da = make_smem_desc_sw128(sa + k * a_kstep, a_lbo, 1024);
-                        const uint64_t db = make_smem_desc_sw128(sb + k * b_kstep, b_lbo, 1024);
-                        umma_bf16_ss_cg2(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                            const uint64_t da = make_smem_desc_sw128(sa + k * a_kstep, a_lbo, 1024);
+                            const uint64_t db = make_smem_desc_sw128(sb + k * b_kstep, b_lbo, 1024);
+                            umma_bf16_ss_cg2(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        }
+                        umma_commit_cg2_mc(&empty_bar[stage], 0x3);   // frees this stage in both CTAs
                     }
-                    umma_commit_cg2_mc(&empty_bar[stage], 0x3);   // frees this stage in both CTAs
+                    __syncwarp();
                     if (++stage == (uint32_t)p.num_stages) { stage = 0; phase ^= 1; }
                 }
-                umma_commit_cg2_mc(&tmem_full[acc], 0x3);         // accumulators ready in both CTAs
+                if (issuer) umma_commit_cg2_mc(&tmem_full[acc], 0x3);   // accumulators ready in both CTAs
+                __syncwarp();
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }
@@ -230,7 +239,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int ew = warp - 4;
         const int quarter = warp & 3;
         const int half = ew >> 2;
-        const bool elected = (quarter == 0) && (lane == 0);
+        // one lane of warp quarter 0 owns this half's TMA traffic (elect.sync picks the same lane every time, so the
+        // bulk async-groups it commits are the ones it later waits on)
+        const bool elected = (quarter == 0) && elect_one();
         const int r_local = quarter * 32 + lane;
         const uint32_t swz = (uint32_t)(r_local & 7);
         const bool vec_ok = ((p.ldd & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.d) & 15) == 0) &&

@@ -45,7 +45,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     uint64_t* tmem_empty = tmem_full + 2;       // [2]
     uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
-    const int warp = threadIdx.x >> 5;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);   // provably warp-uniform
     const int lane = threadIdx.x & 31;
 
     if (warp == 0 && lane == 0) {
@@ -75,8 +75,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     const uint32_t stage_tx = A_STAGE_BYTES + (uint32_t)block_n * BLOCK_K * 2;
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
+        // ===================== TMA producer (whole warp runs the loop, one lane issues) =====================
+        {
+            const bool issuer = elect_one();
             uint32_t stage = 0, phase = 0;
             for (int u = blockIdx.x; u < units; u += gridDim.x) {
                 const int split = u / tiles;
@@ -87,29 +88,33 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
                 const int kb1 = min(kb0 + p.k_blocks_per_split, p.k_blocks_total);
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
-                    mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
                     uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
                     uint8_t* sb = smem_b + stage * B_STAGE_BYTES;
                     const int k0 = kb * BLOCK_K;
-                    if (!p.a_mn) {
-                        tma_load_2d(sa, &tmap_a, &full_bar[stage], k0, m0);
-                    } else {
-                        tma_load_2d(sa, &tmap_a, &full_bar[stage], m0, k0);
-                        tma_load_2d(sa + ATOM_BYTES, &tmap_a, &full_bar[stage], m0 + 64, k0);
+                    if (issuer) {
+                        mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
+                        if (!p.a_mn) {
+                            tma_load_2d(sa, &tmap_a, &full_bar[stage], k0, m0);
+                        } else {
+                            tma_load_2d(sa, &tmap_a, &full_bar[stage], m0, k0);
+                            tma_load_2d(sa + ATOM_BYTES, &tmap_a, &full_bar[stage], m0 + 64, k0);
+                        }
+                        if (!p.b_mn) {
+                            tma_load_2d(sb, &tmap_b, &full_bar[stage], k0, n0);
+                        } else {
+                            for (int a = 0; a < block_n / 64; ++a)
+                                tma_load_2d(sb + a * ATOM_BYTES, &tmap_b, &full_bar[stage], n0 + a * 64, k0);
+                        }
                     }
-                    if (!p.b_mn) {
-                        tma_load_2d(sb, &tmap_b, &full_bar[stage], k0, n0);
-                    } else {
-                        for (int a = 0; a < block_n / 64; ++a)
-                            tma_load_2d(sb + a * ATOM_BYTES, &tmap_b, &full_bar[stage], n0 + a * 64, k0);
-                    }
+                    __syncwarp();
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
+        // ===================== MMA issuer (whole warp runs the loop, one lane issues) =====================
+        {
+            const bool issuer = elect_one();
             const uint32_t idesc = make_idesc_bf16(BLOCK_M, block_n, p.a_mn, p.b_mn);
             // K-major: 8-row groups are 1024 B apart (SBO), LBO unused; advance 32 B per UMMA_K.
             // MN-major: 8 k-rows of 128 B per group (SBO = 1024), 64-wide atoms BLOCK_K*128 B apart (LBO);
@@ -131,16 +136,20 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
                     tc_fence_after();
                     const uint32_t sa = smem_u32(smem_a + stage * A_STAGE_BYTES);
                     const uint32_t sb = smem_u32(smem_b + stage * B_STAGE_BYTES);
+                    if (issuer) {
 #pragma unroll
-                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-                        const uint64_t da = make_smem_desc_sw128(sa + k * a_kstep, a_lbo, 1024);
-                        const uint64_t db = make_smem_desc_sw128(sb + k * b_kstep, b_lbo, 1024);
-                        umma_bf16_ss(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                            const uint64_t da = make_smem_desc_sw128(sa + k * a_kstep, a_lbo, 1024);
+                            const uint64_t db = make_smem_desc_sw128(sb + k * b_kstep, b_lbo, 1024);
+                            umma_bf16_ss(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        }
+                        umma_commit(&empty_bar[stage]);   // frees the smem slot when these MMAs retire
                     }
-                    umma_commit(&empty_bar[stage]);   // frees the smem slot when these MMAs retire
+                    __syncwarp();
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(&tmem_full[acc]);         // accumulator ready for the epilogue
+                if (issuer) umma_commit(&tmem_full[acc]);   // accumulator ready for the epilogue
+                __syncwarp();
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }
