@@ -310,26 +310,57 @@ int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int 
 // row in TMEM and the recomputed P^T / dS^T are directly the A operands of the dV / dK products:
 //   S^T  = K Q^T          tcgen05.mma 128x64x64    TMEM cols [  0,128): two buffers of 64
 //   dP^T = V dO^T         tcgen05.mma 128x64x64    TMEM cols [128,256): two buffers of 64
-//   P^T  = exp2(S^T*c - lse_q), dS^T = P^T (dP^T - delta_q) * scale     (8 warps, thread = key row, 32 queries each)
-//   dV  += P^T dO         A = P^T from TMEM cols [256,320) (two buffers of 32), B = dO sub-tile, MN-major; cols [384,448)
-//   dK  += dS^T Q         A = dS^T from shared memory (K-major view), B = Q sub-tile, MN-major;        cols [320,384)
-//   dQ_i = dS K           once per PAIR of sub-blocks (128 queries): A = the same shared-memory dS^T read as
+//                         K and V are this item's CONSTANT A operands: the elementwise warps copy them once per
+//                         item into TMEM (bf16, cols [256,288) and [288,320)), so these products read only the
+//                         64x64 Q / dO sub-tile from shared memory (an A operand in TMEM costs 42 cycles per
+//                         128x64x16 instruction, one in shared memory 75: tools/micro/mma_rate.cu)
+//   P^T  = exp2(S^T*c - lse_q), dS^T = P^T (dP^T - delta_q) * scale     (16 warps, thread = key row, 16 queries each)
+//                         written back IN PLACE as bf16 pairs over the thread's own fp32 S^T / dP^T columns
+//   dV  += P^T dO         A = P^T from TMEM, B = dO sub-tile, MN-major;                                cols [384,448)
+//   dK  += dS^T Q         A = dS^T from TMEM, B = Q sub-tile, MN-major;                                cols [320,384)
+//   dQ_i = dS K           once per PAIR of sub-blocks (128 queries): A = a shared-memory copy of dS^T read as
 //                         an MN-major operand, B = K tile (MN-major); cols [448,512); four drain warps move it
 //                         TMEM -> registers -> swizzled box -> TMA fp32 reduce-add into dq_accum
 // Pipeline: the MMA thread issues S^T/dP^T of sub-block h+1 BEFORE it waits for the elementwise warps to
 // finish sub-block h, so the tensor pipe works on h+1 (and on dV/dK/dQ of h-1) while the warps do the
 // exponentials of h. tcgen05.mma instructions of one thread execute in order, which is what makes the
-// double buffers safe: "S^T of h+2 is complete" implies dV/dK of h (the readers of P^T[h&1] and of the
-// dS^T atom written four sub-blocks ago) are complete.
-constexpr int kBwdThreads = 448;                  // warps 0-7 elementwise, 8-11 dQ drain, 12 TMA, 13 MMA
+// double buffers safe: S^T / dP^T of h+2 are issued after dV / dK of h, the readers of the bf16 P^T / dS^T that
+// live in the same columns, and "S^T of h+4 is complete" implies dQ of the block that read the shared-memory
+// dS^T atom written four sub-blocks ago is complete.
 constexpr int SUBQ = 64;
+constexpr int kEwWarps = 16;                      // elementwise warps: 4 per TMEM lane quarter
+constexpr int kEwGroups = kEwWarps / 4;           // warpgroups; each takes SUBQ / kEwGroups query columns
+constexpr int CPT = SUBQ / kEwGroups;             // columns per elementwise thread (16)
+static_assert(CPT == 16, "the K/V copy and the in-place bf16 write-back assume 16 columns per thread");
+constexpr int kDrainWarp = kEwWarps, kTmaWarp = kEwWarps + 4, kMmaWarp = kEwWarps + 5;
+constexpr int kBwdThreads = (kEwWarps + 6) * 32;  // elementwise | 4 dQ drain | TMA | MMA
 constexpr int SUB_BYTES = SUBQ * 128;             // 64 rows x 64 bf16
 constexpr int kSlots = 4;                         // Q/dO sub-tiles in flight
 constexpr uint32_t kBwdTmemCols = 512;
-constexpr uint32_t cST = 0, cDPT = 128, cPT = 256, cDK = 320, cDV = 384, cDQ = 448;
+constexpr uint32_t cST = 0, cDPT = 128, cKT = 256, cVT = 288, cDK = 320, cDV = 384, cDQ = 448;
 // K, V | 4 x (Q, dO) sub-tiles | dS^T: 4 atoms of 64 queries | dQ staging: 2 boxes | lse/delta x2 | barriers
 constexpr int BWD_SMEM = 2 * TILE_BYTES + kSlots * 2 * SUB_BYTES + 4 * TILE_BYTES + 2 * TILE_BYTES + 2 * 128 * 8 + 1024 + 256;
 
+__device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_32x32b_x8(uint32_t taddr, const uint32_t (&r)[8]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_cols(uint32_t taddr, uint32_t (&r)[32]) { tmem_ld_32x32b_x32(taddr, r); }
+__device__ __forceinline__ void tmem_ld_cols(uint32_t taddr, uint32_t (&r)[16]) { tmem_ld_32x32b_x16(taddr, r); }
+__device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_t (&r)[16]);
+__device__ __forceinline__ void tmem_st_cols(uint32_t taddr, const uint32_t (&r)[16]) { tmem_st_32x32b_x16(taddr, r); }
+__device__ __forceinline__ void tmem_st_cols(uint32_t taddr, const uint32_t (&r)[8]) { tmem_st_32x32b_x8(taddr, r); }
 __device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_t (&r)[16]) {
     asm volatile(
         "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
@@ -400,7 +431,8 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
     uint64_t* dq_free = bars + 14;
     uint64_t* all_done = bars + 15;    // every product of the item has completed: K / V tiles and dK / dV are final
     uint64_t* acc_free = bars + 16;    // dK / dV accumulators have been read out
-    uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(bars + 17);
+    uint64_t* kv_ready = bars + 17;    // K / V copied into TMEM
+    uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(bars + 18);
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
     const int C = H * D;
@@ -409,18 +441,18 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
     const int nq = (T + BQ - 1) / BQ;
     const BwdSched sched = bwd_sched(B, H, nq, causal);        // key blocks == query blocks (BKV == BQ)
 
-    if (warp == 12 && lane == 0) {
+    if (warp == kTmaWarp && lane == 0) {
         tma_prefetch_desc(&tmap_kv);
         tma_prefetch_desc(&tmap_q);
         tma_prefetch_desc(&tmap_do);
         tma_prefetch_desc(&tmap_dq);
         mbar_init(kv_full, 1);
         for (int s = 0; s < kSlots; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(&s_full[s], 1); mbar_init(&p_ready[s], 8); }
-        mbar_init(dq_full, 1); mbar_init(dq_free, 4); mbar_init(all_done, 1); mbar_init(acc_free, 8);
+        for (int s = 0; s < 2; ++s) { mbar_init(&s_full[s], 1); mbar_init(&p_ready[s], kEwWarps); }
+        mbar_init(dq_full, 1); mbar_init(dq_free, 4); mbar_init(all_done, 1); mbar_init(acc_free, kEwWarps); mbar_init(kv_ready, kEwWarps);
         fence_mbar_init();
     }
-    if (warp == 13) tmem_alloc(tmem_base_ptr, kBwdTmemCols);
+    if (warp == kMmaWarp) tmem_alloc(tmem_base_ptr, kBwdTmemCols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -428,7 +460,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
 
     // running counters (identical in every role): g = sub-blocks so far, w = items so far. Every item has an
     // even number of sub-blocks, so g & 1 is also the sub-block's position inside its 128-query block.
-    if (warp == 12) {
+    if (warp == kTmaWarp) {
         // ===================== TMA producer (whole warp runs the loop, one lane issues) =====================
         {
             const bool issuer = elect_one();
@@ -468,7 +500,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 ++w;
             }
         }
-    } else if (warp == 13) {
+    } else if (warp == kMmaWarp) {
         // ===================== MMA issuer (whole warp runs the loop, one lane issues) =====================
         {
             const bool issuer = elect_one();
@@ -476,12 +508,9 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
             const uint32_t idesc_kn = make_idesc_bf16(128, D, 0, 1);     // dV (A in TMEM), dK (A K-major smem)
             const uint32_t idesc_nn = make_idesc_bf16(128, D, 1, 1);     // dQ (A = dS^T read MN-major)
             // descriptor bases; a K step of 16 elements is +32 B (K-major) or +2048 B (MN-major) = +2 / +128 encoded
-            const uint64_t dKk = make_smem_desc_sw128(smem_u32(sK), 0, 1024);
-            const uint64_t dVk = make_smem_desc_sw128(smem_u32(sV), 0, 1024);
             const uint64_t dKmn = make_smem_desc_sw128(smem_u32(sK), TILE_BYTES, 1024);
             const uint64_t dQk0 = make_smem_desc_sw128(smem_u32(sQ), 0, 1024);
             const uint64_t dQmn0 = make_smem_desc_sw128(smem_u32(sQ), TILE_BYTES, 1024);
-            const uint64_t dSk0 = make_smem_desc_sw128(smem_u32(sdS), 0, 1024);
             const uint64_t dSmn0 = make_smem_desc_sw128(smem_u32(sdS), TILE_BYTES, 1024);
             constexpr uint64_t kSlotStep = (2 * SUB_BYTES) >> 4, kSubStep = SUB_BYTES >> 4, kAtomStep = TILE_BYTES >> 4;
 
@@ -494,10 +523,10 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 if (issuer) {
 #pragma unroll
                     for (int k = 0; k < D / 16; ++k)
-                        umma_bf16_ss(tmem_base + cST + bcol, dKk + 2 * k, dq_ + 2 * k, idesc_s, k > 0 ? 1u : 0u);
+                        umma_bf16_ts(tmem_base + cST + bcol, tmem_base + cKT + k * 8, dq_ + 2 * k, idesc_s, k > 0 ? 1u : 0u);
 #pragma unroll
                     for (int k = 0; k < D / 16; ++k)
-                        umma_bf16_ss(tmem_base + cDPT + bcol, dVk + 2 * k, do_ + 2 * k, idesc_s, k > 0 ? 1u : 0u);
+                        umma_bf16_ts(tmem_base + cDPT + bcol, tmem_base + cVT + k * 8, do_ + 2 * k, idesc_s, k > 0 ? 1u : 0u);
                     umma_commit(&s_full[gg & 1]);
                 }
                 __syncwarp();
@@ -510,7 +539,8 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 if (st < 0) break;
                 if (st == 0) continue;
                 const int nsub = 2 * it.nblk;
-                mbar_wait(kv_full, w & 1);
+                mbar_wait(kv_ready, w & 1);              // K / V are in TMEM (and the K tile in shared memory)
+                tc_fence_after();
                 issue_scores(g);
                 for (int n = 0; n < nsub; ++n, ++g) {
                     if (n + 1 < nsub) issue_scores(g + 1);
@@ -519,15 +549,16 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                     tc_fence_after();
                     const uint32_t slot = g & (kSlots - 1);
                     const uint64_t qmn = dQmn0 + slot * kSlotStep, omn = qmn + kSubStep;
-                    const uint64_t dsk = dSk0 + (uint64_t)(g & 3) * kAtomStep;
+                    const uint32_t bcol = (g & 1) * SUBQ;    // 16 queries = one warpgroup's 8 packed columns, CPT apart
                     if (issuer) {
 #pragma unroll
                         for (int kk = 0; kk < SUBQ / 16; ++kk)   // dV += P^T dO   (reduction over the 64 queries)
-                            umma_bf16_ts(tmem_base + cDV, tmem_base + cPT + (g & 1) * 32 + kk * 8, omn + 128 * kk,
+                            umma_bf16_ts(tmem_base + cDV, tmem_base + cST + bcol + kk * CPT, omn + 128 * kk,
                                          idesc_kn, (n > 0 || kk > 0) ? 1u : 0u);
 #pragma unroll
                         for (int kk = 0; kk < SUBQ / 16; ++kk)   // dK += dS^T Q
-                            umma_bf16_ss(tmem_base + cDK, dsk + 2 * kk, qmn + 128 * kk, idesc_kn, (n > 0 || kk > 0) ? 1u : 0u);
+                            umma_bf16_ts(tmem_base + cDK, tmem_base + cDPT + bcol + kk * CPT, qmn + 128 * kk,
+                                         idesc_kn, (n > 0 || kk > 0) ? 1u : 0u);
                         umma_commit(&qdo_empty[slot]);           // last readers of this Q / dO sub-tile
                     }
                     __syncwarp();
@@ -549,13 +580,13 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 ++w;
             }
         }
-    } else if (warp >= 8) {
+    } else if (warp >= kDrainWarp) {
         // ===================== dQ drain warps: thread = query row of the block ==========
         const int quarter = warp & 3;
         const int r = quarter * 32 + lane;
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
         const uint32_t swz = (uint32_t)(r & 7);
-        const bool elected = (warp == 8) && (lane == 0);
+        const bool elected = (warp == kDrainWarp) && (lane == 0);
         uint32_t jg = 0;
         for (int q = 0;; ++q) {
             BwdItem it;
@@ -587,20 +618,22 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 named_bar_sync(3, 128);
                 if (elected) {
                     const int qrow = it.b * T + (it.i_begin + j) * BQ;
+#ifndef MGB_ATTN_NO_DQ_REDUCE
                     tma_reduce_add_2d(&tmap_dq, sDQ, it.h * D, qrow);
                     tma_reduce_add_2d(&tmap_dq, sDQ + TILE_BYTES, it.h * D + 32, qrow);
+#endif
                     bulk_commit();
                 }
             }
         }
         if (elected) bulk_wait<0>();                          // every reduce-add has completed before the CTA exits
     } else {
-        // ===================== elementwise warps: thread = key row, warpgroup = 32 of the 64 queries ==========
+        // ===================== elementwise warps: thread = key row, warpgroup = CPT of the 64 queries ==========
         const int quarter = warp & 3, wg = warp >> 2;
         const int r = quarter * 32 + lane;               // key row inside the block == TMEM lane
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
         const uint32_t swz = (uint32_t)(r & 7);
-        const int etid = threadIdx.x;                    // 0..255
+        const int etid = threadIdx.x;                    // 0 .. 32 * kEwWarps - 1
         uint32_t g = 0, w = 0;
         for (int q = 0;; ++q) {
             BwdItem it;
@@ -618,12 +651,31 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                     v = make_float2(((tril && i > kb) ? LOG2E : 0.f) - lse[bh_off + tq] * LOG2E, delta[bh_off + tq] * scale);
                 return v;
             };
+            {   // this item's K and V rows -> TMEM (bf16): 16 features of row r per thread. The previous item's products
+                // are complete (all_done was waited for in its epilogue).
+                mbar_wait(kv_full, w & 1);
+                uint32_t kreg[8], vreg[8];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    const uint32_t off = (uint32_t)r * 128 + ((((uint32_t)(wg * 2 + u)) ^ swz) << 4);
+                    const uint4 k4 = *reinterpret_cast<const uint4*>(sK + off);
+                    const uint4 v4 = *reinterpret_cast<const uint4*>(sV + off);
+                    kreg[u * 4 + 0] = k4.x; kreg[u * 4 + 1] = k4.y; kreg[u * 4 + 2] = k4.z; kreg[u * 4 + 3] = k4.w;
+                    vreg[u * 4 + 0] = v4.x; vreg[u * 4 + 1] = v4.y; vreg[u * 4 + 2] = v4.z; vreg[u * 4 + 3] = v4.w;
+                }
+                tmem_st_32x32b_x8(taddr + cKT + wg * 8, kreg);
+                tmem_st_32x32b_x8(taddr + cVT + wg * 8, vreg);
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(kv_ready);
+            }
             float2 nxt = make_float2(0.f, 0.f);
             if (etid < 128) {
                 sLD[((g >> 1) & 1) * 128 + etid] = load_ld(it.i_begin);   // this buffer was last read two blocks ago
                 if (it.nblk > 1) nxt = load_ld(it.i_begin + 1);
             }
-            named_bar_sync(1, 256);
+            named_bar_sync(1, 32 * kEwWarps);
 
             for (int n = 0; n < 2 * it.nblk; ++n, ++g) {
                 const int j = n >> 1;
@@ -632,19 +684,19 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 const bool diag = causal && (i == kb);
                 const bool need_mask = diag || (k0 + BKV > T) || (i * BQ + BQ > T);
                 const bool bias_diag = tril && (i == kb);
-                if (half == 0 && j > 0) named_bar_sync(1, 256);      // sLD[jg & 1] was written at the end of the last sub-block
+                if (half == 0 && j > 0) named_bar_sync(1, 32 * kEwWarps);      // sLD[jg & 1] was written at the end of the last sub-block
                 mbar_wait(&s_full[half], jg & 1);
                 tc_fence_after();
-                const int qc0 = (int)half * SUBQ + wg * 32;          // first query column (inside the block) of this thread
+                const int qc0 = (int)half * SUBQ + wg * CPT;         // first query column (inside the block) of this thread
                 const float2* ld = sLD + (jg & 1) * 128 + qc0;
-                uint32_t sv[32], dp[32];
-                tmem_ld_32x32b_x32(taddr + cST + half * SUBQ + wg * 32, sv);
-                tmem_ld_32x32b_x32(taddr + cDPT + half * SUBQ + wg * 32, dp);
+                uint32_t sv[CPT], dp[CPT];
+                tmem_ld_cols(taddr + cST + half * SUBQ + wg * CPT, sv);
+                tmem_ld_cols(taddr + cDPT + half * SUBQ + wg * CPT, dp);
                 tmem_ld_wait();
-                uint32_t pk[16], dk[16];
+                uint32_t pk[CPT / 2], dk[CPT / 2];
                 if (!need_mask && !bias_diag) {
 #pragma unroll
-                    for (int e = 0; e < 16; ++e) {
+                    for (int e = 0; e < CPT / 2; ++e) {
                         const float4 l4 = *reinterpret_cast<const float4*>(ld + 2 * e);   // (a0, b0, a1, b1)
                         const float p0 = exp2f(fmaf(__uint_as_float(sv[2 * e]), scale_log2, l4.x));
                         const float p1 = exp2f(fmaf(__uint_as_float(sv[2 * e + 1]), scale_log2, l4.z));
@@ -654,7 +706,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                     }
                 } else {
 #pragma unroll
-                    for (int e = 0; e < 16; ++e) {
+                    for (int e = 0; e < CPT / 2; ++e) {
                         float pv[2], dsv[2];
 #pragma unroll
                         for (int t2 = 0; t2 < 2; ++t2) {
@@ -671,12 +723,14 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                         dk[e] = pack_bf16x2(dsv[0], dsv[1]);
                     }
                 }
-                tmem_st_32x32b_x16(taddr + cPT + half * 32 + wg * 16, pk);
-                // dS^T row `r` of atom g & 3, queries [wg*32, +32) of the sub-block: four 16-byte units
+                // bf16 pairs over the first half of this thread's own fp32 columns (both were just read)
+                tmem_st_cols(taddr + cST + half * SUBQ + wg * CPT, pk);
+                tmem_st_cols(taddr + cDPT + half * SUBQ + wg * CPT, dk);
+                // and dS^T once more in shared memory for dQ: row `r` of atom g & 3, queries [wg*CPT, +CPT): CPT/8 units
                 uint8_t* rowp = sdS + (g & 3) * TILE_BYTES + r * 128;
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const uint32_t jj = (uint32_t)(wg * 4 + u);
+                for (int u = 0; u < CPT / 8; ++u) {
+                    const uint32_t jj = (uint32_t)(wg * (CPT / 8) + u);
                     *reinterpret_cast<uint4*>(rowp + ((jj ^ swz) << 4)) =
                         make_uint4(dk[u * 4 + 0], dk[u * 4 + 1], dk[u * 4 + 2], dk[u * 4 + 3]);
                 }
@@ -693,17 +747,17 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
             // ---- item epilogue: dK / dV of this key block ----
             mbar_wait(all_done, w & 1);
             tc_fence_after();
-            uint32_t vk[32], vv[32];
-            tmem_ld_32x32b_x32(taddr + cDK + wg * 32, vk);
-            tmem_ld_32x32b_x32(taddr + cDV + wg * 32, vv);
+            uint32_t vk[CPT], vv[CPT];
+            tmem_ld_cols(taddr + cDK + wg * CPT, vk);
+            tmem_ld_cols(taddr + cDV + wg * CPT, vv);
             tmem_ld_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_free);            // the next item may start accumulating
             if (key < T) {
-                __nv_bfloat16* krow = dqkv + ((int64_t)(it.b * T + key)) * (3 * C) + C + (int64_t)it.h * D + wg * 32;
+                __nv_bfloat16* krow = dqkv + ((int64_t)(it.b * T + key)) * (3 * C) + C + (int64_t)it.h * D + wg * CPT;
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
+                for (int u = 0; u < CPT / 8; ++u) {
                     stg128(krow + u * 8,
                            make_uint4(pack_bf16x2(__uint_as_float(vk[u * 8 + 0]), __uint_as_float(vk[u * 8 + 1])),
                                       pack_bf16x2(__uint_as_float(vk[u * 8 + 2]), __uint_as_float(vk[u * 8 + 3])),
@@ -723,7 +777,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
     __syncwarp();
     tc_fence_before();
     __syncthreads();
-    if (warp == 13) {
+    if (warp == kMmaWarp) {
         tc_fence_after();
         tmem_dealloc(tmem_base, kBwdTmemCols);
     }
