@@ -609,10 +609,9 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 uint8_t* rowp = sDQ + r * 128;
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
-                    *reinterpret_cast<uint4*>(rowp + (((uint32_t)u ^ swz) << 4)) =
-                        make_uint4(lo[u * 4], lo[u * 4 + 1], lo[u * 4 + 2], lo[u * 4 + 3]);
-                    *reinterpret_cast<uint4*>(rowp + TILE_BYTES + (((uint32_t)u ^ swz) << 4)) =
-                        make_uint4(hi[u * 4], hi[u * 4 + 1], hi[u * 4 + 2], hi[u * 4 + 3]);
+                    sts128(rowp + (((uint32_t)u ^ swz) << 4), make_uint4(lo[u * 4], lo[u * 4 + 1], lo[u * 4 + 2], lo[u * 4 + 3]));
+                    sts128(rowp + TILE_BYTES + (((uint32_t)u ^ swz) << 4),
+                           make_uint4(hi[u * 4], hi[u * 4 + 1], hi[u * 4 + 2], hi[u * 4 + 3]));
                 }
                 fence_proxy_async_smem();
                 named_bar_sync(3, 128);
@@ -658,8 +657,8 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
 #pragma unroll
                 for (int u = 0; u < 2; ++u) {
                     const uint32_t off = (uint32_t)r * 128 + ((((uint32_t)(wg * 2 + u)) ^ swz) << 4);
-                    const uint4 k4 = *reinterpret_cast<const uint4*>(sK + off);
-                    const uint4 v4 = *reinterpret_cast<const uint4*>(sV + off);
+                    const uint4 k4 = lds128(sK + off);
+                    const uint4 v4 = lds128(sV + off);
                     kreg[u * 4 + 0] = k4.x; kreg[u * 4 + 1] = k4.y; kreg[u * 4 + 2] = k4.z; kreg[u * 4 + 3] = k4.w;
                     vreg[u * 4 + 0] = v4.x; vreg[u * 4 + 1] = v4.y; vreg[u * 4 + 2] = v4.z; vreg[u * 4 + 3] = v4.w;
                 }
@@ -697,7 +696,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 if (!need_mask && !bias_diag) {
 #pragma unroll
                     for (int e = 0; e < CPT / 2; ++e) {
-                        const float4 l4 = *reinterpret_cast<const float4*>(ld + 2 * e);   // (a0, b0, a1, b1)
+                        const float4 l4 = lds128f(ld + 2 * e);   // (a0, b0, a1, b1)
                         const float p0 = exp2f(fmaf(__uint_as_float(sv[2 * e]), scale_log2, l4.x));
                         const float p1 = exp2f(fmaf(__uint_as_float(sv[2 * e + 1]), scale_log2, l4.z));
                         pk[e] = pack_bf16x2(p0, p1);
@@ -708,10 +707,11 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
 #pragma unroll
                     for (int e = 0; e < CPT / 2; ++e) {
                         float pv[2], dsv[2];
+                        const float4 l4 = lds128f(ld + 2 * e);
 #pragma unroll
                         for (int t2 = 0; t2 < 2; ++t2) {
                             const int col = qc0 + 2 * e + t2;          // query column inside the block
-                            const float2 ldv = ld[2 * e + t2];
+                            const float2 ldv = t2 ? make_float2(l4.z, l4.w) : make_float2(l4.x, l4.y);
                             float x = fmaf(__uint_as_float(sv[2 * e + t2]), scale_log2, ldv.x);
                             if (bias_diag && r <= col) x += LOG2E;
                             const bool dead = (key >= T) || (diag && r > col);   // queries >= T carry a = -inf
@@ -731,8 +731,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
 #pragma unroll
                 for (int u = 0; u < CPT / 8; ++u) {
                     const uint32_t jj = (uint32_t)(wg * (CPT / 8) + u);
-                    *reinterpret_cast<uint4*>(rowp + ((jj ^ swz) << 4)) =
-                        make_uint4(dk[u * 4 + 0], dk[u * 4 + 1], dk[u * 4 + 2], dk[u * 4 + 3]);
+                    sts128(rowp + ((jj ^ swz) << 4), make_uint4(dk[u * 4 + 0], dk[u * 4 + 1], dk[u * 4 + 2], dk[u * 4 + 3]));
                 }
                 tmem_st_wait();
                 tc_fence_before();

@@ -335,9 +335,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
                             const uint32_t j = (uint32_t)(ch * 4 + q);
-                            *reinterpret_cast<uint4*>(rowp2 + ((j ^ swz) << 4)) =
-                                make_uint4(pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
-                                           pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]));
+                            sts128(rowp2 + ((j ^ swz) << 4),
+                                   make_uint4(pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
+                                              pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7])));
                         }
                     }
                     if (p.act) act_inplace(v, p.act);
@@ -347,7 +347,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
                             const uint32_t j = (uint32_t)(ch * 4 + q);
-                            const uint4 xi = *reinterpret_cast<const uint4*>(rowp + ((j ^ swz) << 4));
+                            const uint4 xi = lds128(rowp + ((j ^ swz) << 4));
                             xw[q * 4 + 0] = xi.x; xw[q * 4 + 1] = xi.y; xw[q * 4 + 2] = xi.z; xw[q * 4 + 3] = xi.w;
                         }
                         if (aux == 2) gate_inplace(v, xw, p.gate_kind);
@@ -378,15 +378,14 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     if (p.d_f32) {
 #pragma unroll
                         for (int q = 0; q < 8; ++q)
-                            *reinterpret_cast<float4*>(rowp + (((uint32_t)q ^ swz) << 4)) =
-                                make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+                            sts128f(rowp + (((uint32_t)q ^ swz) << 4), make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]));
                     } else {
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
                             const uint32_t j = (uint32_t)(ch * 4 + q);
-                            *reinterpret_cast<uint4*>(rowp + ((j ^ swz) << 4)) =
-                                make_uint4(pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
-                                           pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]));
+                            sts128(rowp + ((j ^ swz) << 4),
+                                   make_uint4(pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
+                                              pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7])));
                         }
                     }
                 }
