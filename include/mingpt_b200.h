@@ -38,7 +38,9 @@ enum {
     MGB_ERR_TOO_LARGE = -7
 };
 
-enum { MGB_ACT_NONE = 0, MGB_ACT_GELU_TANH = 1, MGB_ACT_GELU_ERF = 2 };
+enum { MGB_ACT_NONE = 0, MGB_ACT_GELU_TANH = 1, MGB_ACT_GELU_ERF = 2,
+       MGB_GATE_MUL = 3,            /* gate_kind only: the gate tensor holds the factor itself */
+       MGB_ACT_STORE_GRAD = 256 };  /* OR-ed into act: preact receives act'(v) instead of v */
 enum { MGB_GEMM_ENGINE_SINGLE = 1024, MGB_GEMM_ENGINE_PAIR = 2048 };
 
 /* attention mask modes.
@@ -66,8 +68,10 @@ int mgb_set_option(const char* key, int value);
  * (mingpt/trainer.py:127).
  *   a_mn_major = 0: A stored [m][k] (k contiguous, lda between rows of m)
  *   a_mn_major = 1: A stored [k][m] (m contiguous, lda between rows of k)       -- same for B with n
- * epilogue, in this order:  v = alpha*acc;  v += bias[n];  preact[m,n] = bf16(v) (if preact);
- *   v = act(v);  v *= act'(gate[m,n]) (if gate; gate_kind selects the derivative);  v += residual[m,n];
+ * epilogue, in this order:  v = alpha*acc;  v += bias[n];  preact[m,n] = bf16(v) (if preact; bf16(act'(v))
+ *   when act carries MGB_ACT_STORE_GRAD: the forward GEMM then leaves exactly what the backward needs and
+ *   its tanh / erf is evaluated once);  v = act(v);  v *= act'(gate[m,n]) (if gate; gate_kind selects the
+ *   derivative, MGB_GATE_MUL multiplies by gate[m,n] itself);  v += residual[m,n];
  *   D = v  (bf16 or fp32)   or   D += v (fp32, atomic; required for split_k > 1)
  * D rows are written in 16-byte units: when n is not a multiple of 8 (bf16) / 4 (fp32) AND ldd leaves room
  * after column n, the rest of the last unit (at most 7 / 3 elements) is overwritten too (with the epilogue of

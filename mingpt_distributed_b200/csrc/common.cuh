@@ -77,21 +77,34 @@ __device__ __forceinline__ float gelu_tanh_f(float x) {
     float u = k0 * (x + k1 * x * x * x);
     return 0.5f * x * (1.0f + tanhf(u));
 }
-__device__ __forceinline__ float gelu_tanh_grad_f(float x) {
+// with h = (1 + tanh u) / 2:  gelu = x h,  gelu' = h (1 + 2 x (1 - h) u'),  u' = k0 (1 + 3 k1 x^2)
+__device__ __forceinline__ void gelu_tanh_both_f(float x, float& y, float& g) {
     const float k0 = 0.7978845608028654f, k1 = 0.044715f;
-    float x2 = x * x;
-    float u = k0 * (x + k1 * x * x2);
-    float t = tanhf(u);
-    float du = k0 * (1.0f + 3.0f * k1 * x2);
-    return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * du;
+    const float x2 = x * x;
+    const float u = x * fmaf(k0 * k1, x2, k0);
+    const float h = fmaf(tanhf(u), 0.5f, 0.5f);
+    const float q = x * fmaf(6.0f * k0 * k1, x2, 2.0f * k0);      // 2 x u'
+    y = x * h;
+    g = fmaf(h, fmaf(-h, q, q), h);
+}
+__device__ __forceinline__ float gelu_tanh_grad_f(float x) {
+    float y, g;
+    gelu_tanh_both_f(x, y, g);
+    return g;
 }
 __device__ __forceinline__ float gelu_erf_f(float x) {
     return 0.5f * x * (1.0f + erff(x * 0.7071067811865476f));
 }
-__device__ __forceinline__ float gelu_erf_grad_f(float x) {
+__device__ __forceinline__ void gelu_erf_both_f(float x, float& y, float& g) {
     const float inv_sqrt_2pi = 0.3989422804014327f;
-    float cdf = 0.5f * (1.0f + erff(x * 0.7071067811865476f));
-    return cdf + x * inv_sqrt_2pi * __expf(-0.5f * x * x);
+    const float cdf = 0.5f * (1.0f + erff(x * 0.7071067811865476f));
+    y = x * cdf;
+    g = cdf + x * inv_sqrt_2pi * __expf(-0.5f * x * x);
+}
+__device__ __forceinline__ float gelu_erf_grad_f(float x) {
+    float y, g;
+    gelu_erf_both_f(x, y, g);
+    return g;
 }
 
 // ----------------------------------------------------------------------------

@@ -29,14 +29,15 @@ __device__ __forceinline__ void epilogue_direct(const Params& p, float (&v)[32],
                                                 bool vec_ok) {
     const bool full = (col0 + 32 <= p.N) && vec_ok;
     if (full) {
+        bool acted = false;
         if (p.preact) {
             __nv_bfloat16* dst = p.preact + row * p.ldp + col0;
+            uint32_t pw[16];
+            acted = preact_words(v, pw, p.act, p.act_grad);
 #pragma unroll
-            for (int q = 0; q < 4; ++q)
-                stg128(dst + q * 8, make_uint4(pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
-                                               pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7])));
+            for (int q = 0; q < 4; ++q) stg128(dst + q * 8, make_uint4(pw[q * 4], pw[q * 4 + 1], pw[q * 4 + 2], pw[q * 4 + 3]));
         }
-        if (p.act) act_inplace(v, p.act);
+        if (p.act && !acted) act_inplace(v, p.act);
         if (p.gate) {
             const __nv_bfloat16* g = p.gate + row * p.ldg + col0;
             uint32_t gw[16];
@@ -82,11 +83,11 @@ __device__ __forceinline__ void epilogue_direct(const Params& p, float (&v)[32],
             const int64_t col = col0 + j;
             if (col >= p.N) continue;
             float x = v[j];
-            if (p.preact) p.preact[row * p.ldp + col] = __float2bfloat16(x);
+            if (p.preact) p.preact[row * p.ldp + col] = __float2bfloat16(p.act_grad ? apply_act_grad(x, p.act) : x);
             if (p.act) x = tanh_kind ? gelu_tanh_f(x) : gelu_erf_f(x);
             if (p.gate) {
                 const float g = __bfloat162float(p.gate[row * p.ldg + col]);
-                x *= gate_tanh ? gelu_tanh_grad_f(g) : gelu_erf_grad_f(g);
+                x *= apply_gate(g, p.gate_kind);
             }
             if (p.residual) x += __bfloat162float(p.residual[row * p.ldr + col]);
             if (p.d_f32) {
@@ -330,17 +331,18 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         continue;
                     }
                     // ---- staged path: everything below touches shared memory only ----
+                    bool acted = false;
                     if (two_out) {
                         uint8_t* rowp2 = box2 + r_local * 128;
+                        uint32_t pw[16];
+                        acted = preact_words(v, pw, p.act, p.act_grad);
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
                             const uint32_t j = (uint32_t)(ch * 4 + q);
-                            sts128(rowp2 + ((j ^ swz) << 4),
-                                   make_uint4(pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
-                                              pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7])));
+                            sts128(rowp2 + ((j ^ swz) << 4), make_uint4(pw[q * 4], pw[q * 4 + 1], pw[q * 4 + 2], pw[q * 4 + 3]));
                         }
                     }
-                    if (p.act) act_inplace(v, p.act);
+                    if (p.act && !acted) act_inplace(v, p.act);
                     if (aux) {
                         // this thread's 64 bytes of the TMA-loaded residual / gate tile (swizzled like the output)
                         uint32_t xw[16];

@@ -42,6 +42,7 @@ struct Params {
     const __nv_bfloat16* residual;
     int64_t ldr;
     int32_t act;
+    int32_t act_grad;        // preact receives act'(v) instead of v (MGB_ACT_STORE_GRAD)
     __nv_bfloat16* preact;
     int64_t ldp;
     const __nv_bfloat16* gate;
@@ -56,7 +57,11 @@ __device__ __forceinline__ float apply_act(float v, int act) {
     return v;
 }
 __device__ __forceinline__ float apply_gate(float g, int kind) {
+    if (kind == MGB_GATE_MUL) return g;
     return kind == MGB_ACT_GELU_TANH ? gelu_tanh_grad_f(g) : gelu_erf_grad_f(g);
+}
+__device__ __forceinline__ float apply_act_grad(float v, int act) {
+    return act == MGB_ACT_GELU_TANH ? gelu_tanh_grad_f(v) : gelu_erf_grad_f(v);
 }
 
 // The activation kind is uniform over the launch: branch ONCE around a fully unrolled loop. (Selecting per
@@ -70,9 +75,44 @@ __device__ __forceinline__ void act_inplace(float (&v)[32], int act) {
         for (int j = 0; j < 32; ++j) v[j] = gelu_erf_f(v[j]);
     }
 }
-// v[j] *= act'(g[j]) with g given as 16 packed bf16x2 words
+// The 16 packed bf16x2 words a `preact` output receives for these 32 columns: the pre-activation itself, or
+// (act_grad) the activation's derivative -- in which case the activation is applied to v on the way (the two
+// share the tanh / erf) and true is returned.
+__device__ __forceinline__ bool preact_words(float (&v)[32], uint32_t (&w)[16], int act, int act_grad) {
+    if (!act_grad) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) w[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+        return false;
+    }
+    if (act == MGB_ACT_GELU_TANH) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            float g0, g1;
+            gelu_tanh_both_f(v[2 * j], v[2 * j], g0);
+            gelu_tanh_both_f(v[2 * j + 1], v[2 * j + 1], g1);
+            w[j] = pack_bf16x2(g0, g1);
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            float g0, g1;
+            gelu_erf_both_f(v[2 * j], v[2 * j], g0);
+            gelu_erf_both_f(v[2 * j + 1], v[2 * j + 1], g1);
+            w[j] = pack_bf16x2(g0, g1);
+        }
+    }
+    return true;
+}
+// v[j] *= act'(g[j]) (or v[j] *= g[j] for MGB_GATE_MUL) with g given as 16 packed bf16x2 words
 __device__ __forceinline__ void gate_inplace(float (&v)[32], const uint32_t (&g)[16], int kind) {
-    if (kind == MGB_ACT_GELU_TANH) {
+    if (kind == MGB_GATE_MUL) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const float2 f = unpack_bf16x2(g[j]);
+            v[2 * j] *= f.x;
+            v[2 * j + 1] *= f.y;
+        }
+    } else if (kind == MGB_ACT_GELU_TANH) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
             const float2 f = unpack_bf16x2(g[j]);

@@ -204,19 +204,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
                     }
                 }
                 if (full) {
+                    bool acted = false;
                     if (p.preact) {
                         __nv_bfloat16* dst = p.preact + row * p.ldp + col0;
+                        uint32_t pw[16];
+                        acted = preact_words(v, pw, p.act, p.act_grad);
 #pragma unroll
-                        for (int q = 0; q < 4; ++q) {
-                            uint4 o;
-                            o.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]);
-                            o.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
-                            o.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]);
-                            o.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
-                            stg128(dst + q * 8, o);
-                        }
+                        for (int q = 0; q < 4; ++q)
+                            stg128(dst + q * 8, make_uint4(pw[q * 4], pw[q * 4 + 1], pw[q * 4 + 2], pw[q * 4 + 3]));
                     }
-                    if (p.act) act_inplace(v, p.act);
+                    if (p.act && !acted) act_inplace(v, p.act);
                     if (p.gate) {
                         const __nv_bfloat16* g = p.gate + row * p.ldg + col0;
                         uint32_t gw[16];
@@ -268,7 +265,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
                         const int64_t col = col0 + j;
                         if (col >= p.N) continue;
                         float x = v[j];
-                        if (p.preact) p.preact[row * p.ldp + col] = __float2bfloat16(x);
+                        if (p.preact) p.preact[row * p.ldp + col] = __float2bfloat16(p.act_grad ? apply_act_grad(x, p.act) : x);
                         if (p.act) x = apply_act(x, p.act);
                         if (p.gate) x *= apply_gate(__bfloat162float(p.gate[row * p.ldg + col]), p.gate_kind);
                         if (p.residual) x += __bfloat162float(p.residual[row * p.ldr + col]);
@@ -340,6 +337,18 @@ extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
     }
     if (a->accumulate && !a->d_f32) { set_last_error("gemm: accumulate requires fp32 D"); return kErrBadDtype; }
     if (a->split_k > 1 && !a->accumulate) { set_last_error("gemm: split_k > 1 requires accumulate"); return kErrUnsupported; }
+    {
+        const int act_kind = a->act & ~MGB_ACT_STORE_GRAD;
+        if (act_kind != MGB_ACT_NONE && act_kind != MGB_ACT_GELU_TANH && act_kind != MGB_ACT_GELU_ERF) {
+            set_last_error("gemm: unknown activation"); return kErrUnsupported;
+        }
+        if ((a->act & MGB_ACT_STORE_GRAD) && (act_kind == MGB_ACT_NONE || !a->preact)) {
+            set_last_error("gemm: MGB_ACT_STORE_GRAD needs an activation and a preact output"); return kErrUnsupported;
+        }
+        if (a->gate && a->gate_kind != MGB_ACT_GELU_TANH && a->gate_kind != MGB_ACT_GELU_ERF && a->gate_kind != MGB_GATE_MUL) {
+            set_last_error("gemm: unknown gate_kind"); return kErrUnsupported;
+        }
+    }
 
     std::call_once(g_attr_once, [] {
         int dev = 0;
@@ -356,8 +365,9 @@ extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
     p.d = a->d; p.ldd = a->ldd; p.d_f32 = a->d_f32; p.accumulate = a->accumulate;
     p.bias = a->bias;
     p.residual = reinterpret_cast<const __nv_bfloat16*>(a->residual); p.ldr = a->ldr;
-    p.act = a->act;
+    p.act = a->act & ~MGB_ACT_STORE_GRAD;
     p.preact = reinterpret_cast<__nv_bfloat16*>(a->preact); p.ldp = a->ldp;
+    p.act_grad = (a->act & MGB_ACT_STORE_GRAD) ? 1 : 0;
     p.gate = reinterpret_cast<const __nv_bfloat16*>(a->gate); p.ldg = a->ldg; p.gate_kind = a->gate_kind;
     p.alpha = a->alpha == 0.0f ? 1.0f : a->alpha;
 

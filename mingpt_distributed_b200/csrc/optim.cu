@@ -257,8 +257,11 @@ act_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __rest
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
             const float2 fa = unpack_bf16x2(wa[e]), fb = unpack_bf16x2(wb[e]);
-            const float g0 = act == MGB_ACT_GELU_TANH ? gelu_tanh_grad_f(fb.x) : (act == MGB_ACT_GELU_ERF ? gelu_erf_grad_f(fb.x) : 1.f);
-            const float g1 = act == MGB_ACT_GELU_TANH ? gelu_tanh_grad_f(fb.y) : (act == MGB_ACT_GELU_ERF ? gelu_erf_grad_f(fb.y) : 1.f);
+            float g0, g1;
+            if (act == MGB_GATE_MUL) { g0 = fb.x; g1 = fb.y; }          // z already holds the derivative
+            else if (act == MGB_ACT_GELU_TANH) { g0 = gelu_tanh_grad_f(fb.x); g1 = gelu_tanh_grad_f(fb.y); }
+            else if (act == MGB_ACT_GELU_ERF) { g0 = gelu_erf_grad_f(fb.x); g1 = gelu_erf_grad_f(fb.y); }
+            else { g0 = 1.f; g1 = 1.f; }
             o[e] = pack_bf16x2(fa.x * g0, fa.y * g1);
         }
         stg128(dz + i * 8, make_uint4(o[0], o[1], o[2], o[3]));
@@ -266,7 +269,7 @@ act_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __rest
     if (blockIdx.x == 0)
         for (int64_t i = (n8 << 3) + threadIdx.x; i < n; i += blockDim.x) {
             const float zz = __bfloat162float(z[i]);
-            const float g = act == MGB_ACT_GELU_TANH ? gelu_tanh_grad_f(zz) : (act == MGB_ACT_GELU_ERF ? gelu_erf_grad_f(zz) : 1.f);
+            const float g = act == MGB_GATE_MUL ? zz : act == MGB_ACT_GELU_TANH ? gelu_tanh_grad_f(zz) : (act == MGB_ACT_GELU_ERF ? gelu_erf_grad_f(zz) : 1.f);
             dz[i] = __float2bfloat16(__bfloat162float(dy[i]) * g);
         }
 }

@@ -556,15 +556,16 @@ class GPT(nn.Module):
             if ref:  # Linear -> Linear -> GELU(erf) -> Dropout (model.py:179-184)
                 ops.linear_fwd(ws.ln2[l], W(f"{l}.fc_w"), ws.fc_pre[l], bias=P(f"{l}.fc_b"))
                 if pr > 0:
-                    ops.linear_fwd(ws.fc_pre[l], W(f"{l}.fc2_w"), ws.tmp, bias=P(f"{l}.fc2_b"), act=ops.ACT_GELU_ERF,
-                                   preact=ws.z[l])
+                    ops.linear_fwd(ws.fc_pre[l], W(f"{l}.fc2_w"), ws.tmp, bias=P(f"{l}.fc2_b"),
+                                   act=ops.ACT_GELU_ERF | ops.ACT_STORE_GRAD, preact=ws.z[l])
                     ops.dropout(ws.tmp, ws.xmid[l], ws.x[l + 1], pr, seed, 4 * l + 2)
                 else:
                     ops.linear_fwd(ws.fc_pre[l], W(f"{l}.fc2_w"), ws.x[l + 1], bias=P(f"{l}.fc2_b"),
-                                   act=ops.ACT_GELU_ERF, preact=ws.z[l], residual=ws.xmid[l])
+                                   act=ops.ACT_GELU_ERF | ops.ACT_STORE_GRAD, preact=ws.z[l], residual=ws.xmid[l])
             else:    # c_fc + NewGELU epilogue, then c_proj (+ dropout) + residual
-                ops.linear_fwd(ws.ln2[l], W(f"{l}.fc_w"), ws.fc_act[l], bias=P(f"{l}.fc_b"), act=ops.ACT_GELU_TANH,
-                               preact=ws.fc_pre[l])
+                # the "pre-activation" buffers (fc_pre here, z above) receive GELU'(pre-activation): all backward needs
+                ops.linear_fwd(ws.ln2[l], W(f"{l}.fc_w"), ws.fc_act[l], bias=P(f"{l}.fc_b"),
+                               act=ops.ACT_GELU_TANH | ops.ACT_STORE_GRAD, preact=ws.fc_pre[l])
                 if pr > 0:
                     ops.linear_fwd(ws.fc_act[l], W(f"{l}.fc2_w"), ws.tmp, bias=P(f"{l}.fc2_b"))
                     ops.dropout(ws.tmp, ws.xmid[l], ws.x[l + 1], pr, seed, 4 * l + 2)
@@ -701,14 +702,14 @@ class GPT(nn.Module):
                 ops.dropout(dx, None, ws.dtmp, pr, seed, 4 * l + 2)
                 dmlp = ws.dtmp
             if ref:
-                ops.act_bwd(dmlp, ws.z[l], ws.dz, ops.ACT_GELU_ERF)
+                ops.act_bwd(dmlp, ws.z[l], ws.dz, ops.GATE_MUL)
                 ops.colsum(ws.dz, G(f"{l}.fc2_b"))
                 ops.linear_wgrad(ws.dz, ws.fc_pre[l], G(f"{l}.fc2_w"))
                 ops.linear_dgrad(ws.dz, W(f"{l}.fc2_w"), ws.dfc)
             else:
                 ops.colsum(dmlp, G(f"{l}.fc2_b"))
                 ops.linear_wgrad(dmlp, ws.fc_act[l], G(f"{l}.fc2_w"))
-                ops.linear_dgrad(dmlp, W(f"{l}.fc2_w"), ws.dfc, gate=ws.fc_pre[l], gate_kind=ops.ACT_GELU_TANH)
+                ops.linear_dgrad(dmlp, W(f"{l}.fc2_w"), ws.dfc, gate=ws.fc_pre[l], gate_kind=ops.GATE_MUL)
             ops.colsum(ws.dfc, G(f"{l}.fc_b"))
             ops.linear_wgrad(ws.dfc, ws.ln2[l], G(f"{l}.fc_w"))
             ops.linear_dgrad(ws.dfc, W(f"{l}.fc_w"), ws.dln)

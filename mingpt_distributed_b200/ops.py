@@ -18,6 +18,8 @@ from . import _lib
 from ._lib import AdamWChunk, GemmArgs, check
 
 ACT_NONE, ACT_GELU_TANH, ACT_GELU_ERF = 0, 1, 2
+GATE_MUL = 3            # gate_kind / act_bwd kind: the tensor holds the derivative itself
+ACT_STORE_GRAD = 256    # OR-ed into act: the preact output receives act'(v) instead of v
 MASK_NONE, MASK_CAUSAL, MASK_ADD_TRIL_ONES = 0, 1, 2
 ACT_BY_NAME = {None: 0, "none": 0, "gelu_tanh": 1, "gelu_erf": 2}
 MASK_BY_NAME = {None: 0, "none": 0, "causal": 1, "add_tril_ones": 2}

@@ -88,6 +88,38 @@ def test_gemm_forward_epilogues(act, N):
     _check(f"gemm_epi_out_act{act}_N{N}", out, y + res.float(), 2e-2)
 
 
+@pytest.mark.parametrize("engine", [1024, 2048])
+@pytest.mark.parametrize("act", [1, 2])
+@pytest.mark.parametrize("N", [768, 65])
+def test_gemm_forward_stores_activation_derivative(engine, act, N):
+    """MGB_ACT_STORE_GRAD: the preact output receives GELU'(z); MGB_GATE_MUL then multiplies by it -- together the
+    same forward/backward as saving z and evaluating GELU' in the backward GEMM."""
+    from mingpt_distributed_b200 import ops
+    M, K = 384, 256
+    a, b, acc = _mk(M, N, K, False, False, seed=5)
+    bias = torch.randn(N, device="cuda")
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    dact = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    ops.gemm(a, b, out, bias=bias, act=act | ops.ACT_STORE_GRAD, preact=dact, block_n=engine)
+    z = (acc + bias).requires_grad_(True)
+    y = torch.nn.functional.gelu(z, approximate="tanh" if act == 1 else "none")
+    y.sum().backward()
+    _check(f"gemm_storegrad_out_act{act}_N{N}_e{engine}", out, y.detach(), 2e-2)
+    _check(f"gemm_storegrad_dact_act{act}_N{N}_e{engine}", dact, z.grad, 2e-2)
+    if N % 8 == 0:      # gate operands feed TMA: 16-byte row pitch
+        g = torch.Generator(device="cuda").manual_seed(6)
+        dy = (torch.randn(M, 128, device="cuda", generator=g) * 0.5).bfloat16()
+        w = (torch.randn(128, N, device="cuda", generator=g) * 0.1).bfloat16()
+        dx = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+        ops.linear_dgrad(dy, w, dx, gate=dact, gate_kind=ops.GATE_MUL, block_n=engine)
+        torch.cuda.synchronize()
+        _check(f"gemm_gatemul_act{act}_e{engine}", dx, (dy.float() @ w.float()) * dact.float(), 2e-2)
+    with pytest.raises(RuntimeError):       # needs both an activation and somewhere to store its derivative
+        ops.gemm(a, b, out, bias=bias, act=ops.ACT_STORE_GRAD, preact=dact)
+    with pytest.raises(RuntimeError):
+        ops.gemm(a, b, out, bias=bias, act=act | ops.ACT_STORE_GRAD)
+
+
 @pytest.mark.parametrize("kind", [1, 2])
 def test_gemm_dgrad_gate_epilogue(kind):
     """dX = (dY W) * gelu'(pre): the fused backward of c_fc's activation"""
