@@ -128,6 +128,12 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
         for (int j = 0; j < nkv; ++j) {
             const uint32_t ph = (uint32_t)(j & 1);
             mbar_wait(p_ready, ph);               // P_j in TMEM, O rescaled if needed, S consumed
+            tc_fence_after();
+            if (j + 1 < nkv) {                    // S_{j+1} first: the softmax warps start on it while P V_j runs
+                mbar_wait(k_full, ph ^ 1);
+                tc_fence_after();
+                issue_s();
+            }
             mbar_wait(v_full, ph);
             tc_fence_after();
             if (issuer) {
@@ -139,11 +145,6 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
                 umma_commit(pv_done);
             }
             __syncwarp();
-            if (j + 1 < nkv) {
-                mbar_wait(k_full, ph ^ 1);
-                tc_fence_after();
-                issue_s();
-            }
         }
     } else {
         // ===================== softmax: one thread per query row =====================
