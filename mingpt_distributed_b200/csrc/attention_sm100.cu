@@ -26,6 +26,7 @@ constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 constexpr float kRescaleThreshold = 8.0f;         // log2 units: P stays below 2^8 between rescales
 
+__device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_t (&r)[16]);
 __device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t (&r)[32]) {
     asm volatile(
         "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
@@ -160,31 +161,56 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
             const float bias_all = (tril && j < qb) ? LOG2E : 0.f;
             const bool bias_diag = tril && diag;
             const bool fast = !need_mask && !bias_diag;
+            // causal diagonal block with every key present (and no additive bias): handled per 32-column group
+            const bool diag_groups = causal && diag && (kvalid == BKV) && !bias_diag;
             mbar_wait(s_full, ph);
             tc_fence_after();
-            // ---- pass 1: row maximum of this block (log2 domain); 64 columns per TMEM round trip ----
             float mx = -INFINITY;
+            if (diag_groups) {
+                // causal diagonal block, all keys present: this warp's rows are 32w..32w+31, so 32-column groups left
+                // of the diagonal group need no mask, the diagonal group a per-element one, and the groups right of
+                // it are entirely masked (no TMEM read, no exponentials). All of it warp-uniform.
+                float mx_raw = -INFINITY;
 #pragma unroll 1
-            for (int c = 0; c < 2; ++c) {
-                uint32_t s0[32], s1[32];
-                tmem_ld_32x32b_x32(taddr + kColS + c * 64, s0);
-                tmem_ld_32x32b_x32(taddr + kColS + c * 64 + 32, s1);
-                tmem_ld_wait();
-                if (fast) {
+                for (int g = 0; g <= warp; ++g) {
+                    uint32_t sv[32];
+                    tmem_ld_32x32b_x32(taddr + kColS + g * 32, sv);
+                    tmem_ld_wait();
+                    if (g < warp) {
 #pragma unroll
-                    for (int e = 0; e < 32; ++e) mx = fmaxf(mx, fmaxf(__uint_as_float(s0[e]), __uint_as_float(s1[e])));
-                } else {
+                        for (int e = 0; e < 32; e += 2)
+                            mx_raw = fmaxf(mx_raw, fmaxf(__uint_as_float(sv[e]), __uint_as_float(sv[e + 1])));
+                    } else {
 #pragma unroll
-                    for (int e = 0; e < 64; ++e) {
-                        const int col = c * 64 + e;
-                        float x = fmaf(__uint_as_float(e < 32 ? s0[e & 31] : s1[e & 31]), scale_log2, bias_all);
-                        if (bias_diag && col <= r) x += LOG2E;
-                        if (col >= kvalid || (causal && diag && col > r)) x = -INFINITY;
-                        mx = fmaxf(mx, x);
+                        for (int e = 0; e < 32; ++e)
+                            if (e <= lane) mx_raw = fmaxf(mx_raw, __uint_as_float(sv[e]));
                     }
                 }
+                mx = mx_raw * scale_log2;
+            } else {
+                // ---- pass 1: row maximum of this block (log2 domain); 64 columns per TMEM round trip ----
+#pragma unroll 1
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t s0[32], s1[32];
+                    tmem_ld_32x32b_x32(taddr + kColS + c * 64, s0);
+                    tmem_ld_32x32b_x32(taddr + kColS + c * 64 + 32, s1);
+                    tmem_ld_wait();
+                    if (fast) {
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) mx = fmaxf(mx, fmaxf(__uint_as_float(s0[e]), __uint_as_float(s1[e])));
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 64; ++e) {
+                            const int col = c * 64 + e;
+                            float x = fmaf(__uint_as_float(e < 32 ? s0[e & 31] : s1[e & 31]), scale_log2, bias_all);
+                            if (bias_diag && col <= r) x += LOG2E;
+                            if (col >= kvalid || (causal && diag && col > r)) x = -INFINITY;
+                            mx = fmaxf(mx, x);
+                        }
+                    }
+                }
+                if (fast) mx = fmaf(mx, scale_log2, bias_all);
             }
-            if (fast) mx = fmaf(mx, scale_log2, bias_all);
             // ---- running max with lazy rescale ----
             float factor = 1.0f;
             const bool grow = mx > m_run + kRescaleThreshold;    // also true on the first block (m_run = -inf)
@@ -211,42 +237,69 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
             // ---- pass 2: P = exp2(x - m_run), row sum, bf16 pairs back into TMEM ----
             const float off = bias_all - m_run;
             float rs = 0.f;
+            if (diag_groups) {
 #pragma unroll 1
-            for (int c = 0; c < 2; ++c) {
-                uint32_t s0[32], s1[32];
-                tmem_ld_32x32b_x32(taddr + kColS + c * 64, s0);
-                tmem_ld_32x32b_x32(taddr + kColS + c * 64 + 32, s1);
-                tmem_ld_wait();
-                uint32_t pk[32];
-                if (fast) {
+                for (int g = 0; g < 4; ++g) {
+                    uint32_t pk[16];
+                    if (g > warp) {
 #pragma unroll
-                    for (int e = 0; e < 16; ++e) {
-                        const float a0 = exp2f(fmaf(__uint_as_float(s0[2 * e]), scale_log2, off));
-                        const float a1 = exp2f(fmaf(__uint_as_float(s0[2 * e + 1]), scale_log2, off));
-                        const float b0 = exp2f(fmaf(__uint_as_float(s1[2 * e]), scale_log2, off));
-                        const float b1 = exp2f(fmaf(__uint_as_float(s1[2 * e + 1]), scale_log2, off));
-                        rs += (a0 + a1) + (b0 + b1);
-                        pk[e] = pack_bf16x2(a0, a1);
-                        pk[16 + e] = pack_bf16x2(b0, b1);
-                    }
-                } else {
+                        for (int e = 0; e < 16; ++e) pk[e] = 0u;
+                    } else {
+                        uint32_t sv[32];
+                        tmem_ld_32x32b_x32(taddr + kColS + g * 32, sv);
+                        tmem_ld_wait();
 #pragma unroll
-                    for (int e = 0; e < 32; ++e) {
-                        float pv[2];
-#pragma unroll
-                        for (int t2 = 0; t2 < 2; ++t2) {
-                            const int idx = 2 * e + t2;                       // 0..63 inside this 64-column group
-                            const int col = c * 64 + idx;
-                            float x = fmaf(__uint_as_float(idx < 32 ? s0[idx & 31] : s1[idx & 31]), scale_log2, off);
-                            if (bias_diag && col <= r) x += LOG2E;
-                            const bool dead = col >= kvalid || (causal && diag && col > r);
-                            pv[t2] = dead ? 0.f : exp2f(x);
+                        for (int e = 0; e < 16; ++e) {
+                            float a0 = exp2f(fmaf(__uint_as_float(sv[2 * e]), scale_log2, off));
+                            float a1 = exp2f(fmaf(__uint_as_float(sv[2 * e + 1]), scale_log2, off));
+                            if (g == warp) {
+                                if (2 * e > lane) a0 = 0.f;
+                                if (2 * e + 1 > lane) a1 = 0.f;
+                            }
+                            rs += a0 + a1;
+                            pk[e] = pack_bf16x2(a0, a1);
                         }
-                        rs += pv[0] + pv[1];
-                        pk[e] = pack_bf16x2(pv[0], pv[1]);
                     }
+                    tmem_st_32x32b_x16(taddr + kColP + g * 16, pk);
                 }
-                tmem_st_32x32b_x32(taddr + kColP + c * 32, pk);
+            } else {
+#pragma unroll 1
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t s0[32], s1[32];
+                    tmem_ld_32x32b_x32(taddr + kColS + c * 64, s0);
+                    tmem_ld_32x32b_x32(taddr + kColS + c * 64 + 32, s1);
+                    tmem_ld_wait();
+                    uint32_t pk[32];
+                    if (fast) {
+#pragma unroll
+                        for (int e = 0; e < 16; ++e) {
+                            const float a0 = exp2f(fmaf(__uint_as_float(s0[2 * e]), scale_log2, off));
+                            const float a1 = exp2f(fmaf(__uint_as_float(s0[2 * e + 1]), scale_log2, off));
+                            const float b0 = exp2f(fmaf(__uint_as_float(s1[2 * e]), scale_log2, off));
+                            const float b1 = exp2f(fmaf(__uint_as_float(s1[2 * e + 1]), scale_log2, off));
+                            rs += (a0 + a1) + (b0 + b1);
+                            pk[e] = pack_bf16x2(a0, a1);
+                            pk[16 + e] = pack_bf16x2(b0, b1);
+                        }
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) {
+                            float pv[2];
+#pragma unroll
+                            for (int t2 = 0; t2 < 2; ++t2) {
+                                const int idx = 2 * e + t2;                       // 0..63 inside this 64-column group
+                                const int col = c * 64 + idx;
+                                float x = fmaf(__uint_as_float(idx < 32 ? s0[idx & 31] : s1[idx & 31]), scale_log2, off);
+                                if (bias_diag && col <= r) x += LOG2E;
+                                const bool dead = col >= kvalid || (causal && diag && col > r);
+                                pv[t2] = dead ? 0.f : exp2f(x);
+                            }
+                            rs += pv[0] + pv[1];
+                            pk[e] = pack_bf16x2(pv[0], pv[1]);
+                        }
+                    }
+                    tmem_st_32x32b_x32(taddr + kColP + c * 32, pk);
+                }
             }
             l_run += rs;
             tmem_st_wait();
