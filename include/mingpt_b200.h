@@ -57,7 +57,9 @@ int mgb_version(void);
 int64_t mgb_launch_count(void);
 /* Tuning / test knobs (process-wide). Keys: "gemm_single" (1 = always use the single-CTA tile engine),
  * "gemm_direct_store" (1 = CTA-pair engine writes D from registers instead of through TMA), "attn_mma"
- * (1 = head size 64 also uses the mma.sync attention kernels instead of the tcgen05 ones). Returns the
+ * (1 = head size 64 also uses the mma.sync attention kernels instead of the tcgen05 ones), "ln_unstaged"
+ * (1 = LayerNorm backward loads its rows straight into registers instead of staging them through shared
+ * memory with bulk copies). Returns the
  * previous value, or -1 for an unknown key. Every alternative computes the same result. */
 int mgb_set_option(const char* key, int value);
 

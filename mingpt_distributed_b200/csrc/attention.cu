@@ -239,19 +239,19 @@ attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict
 // backward
 // =====================================================================================
 // delta[b,h,t] = sum_e dO[b,t,h,e] * O[b,t,h,e]
+// D/8 consecutive threads share one (b,t,h) row: every load instruction of a warp covers contiguous 16-byte pieces.
 template <int D>
 __global__ void __launch_bounds__(256)
 attn_bwd_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ dout,
                       float* __restrict__ delta, int64_t B, int64_t T, int H) {
-    const int64_t total = B * T * H;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int h = (int)(i % H);
-        const int64_t bt = i / H;
-        const int64_t b = bt / T, t = bt - b * T;
+    constexpr int TPR = D / 8;                      // threads per row: 2, 4 or 8
+    const int64_t total = B * T * H * TPR;          // a multiple of TPR, so the shuffle groups below are always whole
+    // the loop condition is on the warp's first element, so whole warps stay in it for the shuffles
+    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31); i0 < total; i0 += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = i0 + (threadIdx.x & 31);
         float s = 0.f;
-#pragma unroll
-        for (int c = 0; c < D / 8; ++c) {
-            const uint4 a = ldg128(o + i * D + c * 8), d = ldg128(dout + i * D + c * 8);
+        if (i < total) {
+            const uint4 a = ldg128(o + i * 8), d = ldg128(dout + i * 8);
             const uint32_t wa[4] = {a.x, a.y, a.z, a.w}, wd[4] = {d.x, d.y, d.z, d.w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
@@ -259,7 +259,15 @@ attn_bwd_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* 
                 s += fa.x * fd.x + fa.y * fd.y;
             }
         }
-        delta[(b * H + h) * T + t] = s;
+#pragma unroll
+        for (int off = TPR / 2; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+        if (i < total && (i & (TPR - 1)) == 0) {
+            const int64_t row = i / TPR;
+            const int h = (int)(row % H);
+            const int64_t bt = row / H;
+            const int64_t b = bt / T, t = bt - b * T;
+            delta[(b * H + h) * T + t] = s;
+        }
     }
 }
 
@@ -497,7 +505,7 @@ static int launch_bwd(const void* qkv, const void* out, const void* dout, const 
                       float p_drop = 0.f, const uint64_t* seed_dev = nullptr, uint32_t site = 0) {
     const uint32_t thresh = p_drop > 0.f ? dropout_thresh16(p_drop) : 0u;
     const float inv_keep = thresh ? 65536.0f / (65536.0f - (float)thresh) : 1.0f;
-    const int64_t rows = (int64_t)B * T * H;
+    const int64_t rows = (int64_t)B * T * H * (D / 8);
     int g = (int)((rows + 255) / 256);
     if (g > num_sms() * 16) g = num_sms() * 16;
     attn_bwd_delta_kernel<D><<<g, 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, B, T, H);

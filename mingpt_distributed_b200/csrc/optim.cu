@@ -301,12 +301,14 @@ namespace mgb {
 std::atomic<int> g_opt_gemm_single{0};
 std::atomic<int> g_opt_gemm_direct_store{0};
 std::atomic<int> g_opt_attn_mma{0};
+std::atomic<int> g_opt_ln_unstaged{0};
 }
 extern "C" int mgb_set_option(const char* key, int value) {
     if (!key) return -1;
     if (!std::strcmp(key, "gemm_single")) return mgb::g_opt_gemm_single.exchange(value);
     if (!std::strcmp(key, "gemm_direct_store")) return mgb::g_opt_gemm_direct_store.exchange(value);
     if (!std::strcmp(key, "attn_mma")) return mgb::g_opt_attn_mma.exchange(value);
+    if (!std::strcmp(key, "ln_unstaged")) return mgb::g_opt_ln_unstaged.exchange(value);
     return -1;
 }
 

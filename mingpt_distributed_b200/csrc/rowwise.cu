@@ -1,10 +1,15 @@
 // HBM-bound row-wise kernels of the training step: LayerNorm fwd/bwd, embedding fwd/bwd,
 // cross-entropy (in place on a logits chunk). Single pass over the data, 16-byte vector accesses,
 // fp32 statistics.
+#include <atomic>
+#include <mutex>
+
 #include "common.cuh"
 #include "mingpt_b200.h"
 
 namespace mgb {
+
+extern std::atomic<int> g_opt_ln_unstaged;   // optim.cu: 1 = LayerNorm backward keeps its rows in registers
 
 // =====================================================================================
 // LayerNorm  (nn.LayerNorm: mingpt/model.py:176,178,248)
@@ -199,6 +204,146 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
     for (int c = threadIdx.x; c < cols; c += blockDim.x) {
         atomicAdd(dgamma + c, ln_smem[c]);
         atomicAdd(dbeta + c, ln_smem[cols + c]);
+    }
+}
+
+// Same computation with the three input rows STAGED THROUGH SHARED MEMORY by 1-D bulk copies (the TMA engine's
+// non-tensor mode): each warp owns a contiguous range of rows and a ring of LNB_STAGES row slots, lane 0 keeps
+// the next rows in flight while the warp works on the current one, so the loads no longer occupy registers and
+// the number of bytes in flight per SM is set by shared memory (2 CTAs x 8 warps x 2 rows x 4.5 KiB at C = 768),
+// not by occupancy. The row is read back from shared memory in both passes (conflict-free 16-byte accesses).
+constexpr int LNB_STAGES = 2;
+template <int MAXCH>
+__global__ void __launch_bounds__(LN_WARPS * 32, MAXCH <= 3 ? 2 : 1)
+ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                     const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd,
+                     const __nv_bfloat16* dres, __nv_bfloat16* dx, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                     int64_t rows, int cols, int64_t rows_per_warp) {
+    extern __shared__ __align__(128) uint8_t lnb_smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nch = cols >> 3;
+    const uint32_t rowbytes = (uint32_t)cols * 2;
+    const float inv_cols = 1.0f / (float)cols;
+    float* acc = reinterpret_cast<float*>(lnb_smem);                        // [2][cols] CTA-level dgamma / dbeta
+    uint8_t* ring = lnb_smem + (size_t)2 * cols * sizeof(float) + (size_t)warp * LNB_STAGES * 3 * rowbytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(lnb_smem + (size_t)2 * cols * sizeof(float) +
+                                                 (size_t)LN_WARPS * LNB_STAGES * 3 * rowbytes) + warp * LNB_STAGES;
+    for (int c = threadIdx.x; c < 2 * cols; c += blockDim.x) acc[c] = 0.f;
+    if (lane == 0) {
+        for (int s = 0; s < LNB_STAGES; ++s) mbar_init(&bars[s], 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+
+    const int64_t gw = (int64_t)blockIdx.x * LN_WARPS + warp;
+    const int64_t row0 = gw * rows_per_warp;
+    const int64_t row1 = row0 + rows_per_warp < rows ? row0 + rows_per_warp : rows;
+    const uint32_t tx = (dres ? 3u : 2u) * rowbytes;
+    auto issue = [&](int64_t row, int s) {       // lane 0 only
+        uint8_t* slot = ring + (size_t)s * 3 * rowbytes;
+        mbar_arrive_expect_tx(&bars[s], tx);
+        bulk_load_1d(slot, x + row * cols, rowbytes, &bars[s]);
+        bulk_load_1d(slot + rowbytes, dy + row * cols, rowbytes, &bars[s]);
+        if (dres) bulk_load_1d(slot + 2 * rowbytes, dres + row * cols, rowbytes, &bars[s]);
+    };
+    if (lane == 0)
+        for (int s = 0; s < LNB_STAGES; ++s)
+            if (row0 + s < row1) issue(row0 + s, s);
+
+    float gam[MAXCH][8], dg[MAXCH][8], db[MAXCH][8];
+#pragma unroll
+    for (int i = 0; i < MAXCH; ++i) {
+        const int ch = lane + 32 * i;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            gam[i][e] = (ch < nch) ? gamma[ch * 8 + e] : 0.f;
+            dg[i][e] = 0.f;
+            db[i][e] = 0.f;
+        }
+    }
+    float mu_n = 0.f, rs_n = 0.f;
+    if (row0 < row1) { mu_n = mean[row0]; rs_n = rstd[row0]; }
+    int s = 0;
+    uint32_t ph = 0;
+    for (int64_t row = row0; row < row1; ++row) {
+        const float mu = mu_n, rs = rs_n;
+        if (row + 1 < row1) { mu_n = mean[row + 1]; rs_n = rstd[row + 1]; }
+        const uint8_t* xs = ring + (size_t)s * 3 * rowbytes;
+        const uint8_t* ds = xs + rowbytes;
+        const uint8_t* rsd = xs + 2 * rowbytes;
+        mbar_wait(&bars[s], ph);
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < MAXCH; ++i) {
+            const int ch = lane + 32 * i;
+            if (ch < nch) {
+                const uint4 px = lds128(xs + ch * 16), pd = lds128(ds + ch * 16);
+                const uint32_t wx[4] = {px.x, px.y, px.z, px.w};
+                const uint32_t wd[4] = {pd.x, pd.y, pd.z, pd.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float2 fx = unpack_bf16x2(wx[e]);
+                    const float2 fd = unpack_bf16x2(wd[e]);
+                    const float h0 = (fx.x - mu) * rs, h1 = (fx.y - mu) * rs;
+                    dg[i][2 * e] += fd.x * h0; dg[i][2 * e + 1] += fd.y * h1;
+                    db[i][2 * e] += fd.x;      db[i][2 * e + 1] += fd.y;
+                    const float g0 = fd.x * gam[i][2 * e], g1 = fd.y * gam[i][2 * e + 1];
+                    s1 += g0 + g1;
+                    s2 += g0 * h0 + g1 * h1;
+                }
+            }
+        }
+        const float m1 = warp_sum(s1) * inv_cols;
+        const float m2 = warp_sum(s2) * inv_cols;
+#pragma unroll
+        for (int i = 0; i < MAXCH; ++i) {
+            const int ch = lane + 32 * i;
+            if (ch < nch) {
+                const uint4 px = lds128(xs + ch * 16), pd = lds128(ds + ch * 16);
+                const uint32_t wx[4] = {px.x, px.y, px.z, px.w};
+                const uint32_t wd[4] = {pd.x, pd.y, pd.z, pd.w};
+                float r[8];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float2 fx = unpack_bf16x2(wx[e]);
+                    const float2 fd = unpack_bf16x2(wd[e]);
+                    const float h0 = (fx.x - mu) * rs, h1 = (fx.y - mu) * rs;
+                    r[2 * e] = rs * (fd.x * gam[i][2 * e] - m1 - h0 * m2);
+                    r[2 * e + 1] = rs * (fd.y * gam[i][2 * e + 1] - m1 - h1 * m2);
+                }
+                if (dres) {
+                    const uint4 pr = lds128(rsd + ch * 16);
+                    const uint32_t wr[4] = {pr.x, pr.y, pr.z, pr.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float2 f = unpack_bf16x2(wr[e]);
+                        r[2 * e] += f.x; r[2 * e + 1] += f.y;
+                    }
+                }
+                stg128(dx + row * cols + ch * 8,
+                       make_uint4(pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]),
+                                  pack_bf16x2(r[6], r[7])));
+            }
+        }
+        __syncwarp();                                            // every lane is done with this slot
+        if (lane == 0 && row + LNB_STAGES < row1) issue(row + LNB_STAGES, s);
+        if (++s == LNB_STAGES) { s = 0; ph ^= 1; }
+    }
+#pragma unroll
+    for (int i = 0; i < MAXCH; ++i) {
+        const int ch = lane + 32 * i;
+        if (ch < nch) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                atomicAdd(&acc[ch * 8 + e], dg[i][e]);
+                atomicAdd(&acc[cols + ch * 8 + e], db[i][e]);
+            }
+        }
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < cols; c += blockDim.x) {
+        atomicAdd(dgamma + c, acc[c]);
+        atomicAdd(dbeta + c, acc[cols + c]);
     }
 }
 
@@ -469,6 +614,35 @@ extern "C" int mgb_layernorm_bwd(const void* dy, const void* x, const float* gam
     const bool vec = (cols % 8 == 0) && cols <= 2048 && ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0) &&
                      ((uintptr_t)dx % 16 == 0) && (!dres || (uintptr_t)dres % 16 == 0);
     // persistent: each CTA owns register accumulators for dgamma/dbeta, flushed once
+    const size_t stage_smem = (size_t)2 * cols * sizeof(float) + (size_t)LN_WARPS * LNB_STAGES * 3 * cols * 2 +
+                              LN_WARPS * LNB_STAGES * sizeof(uint64_t);
+    if (vec && stage_smem <= 227 * 1024 && !g_opt_ln_unstaged.load(std::memory_order_relaxed)) {
+        // rows staged through shared memory by bulk copies; every warp owns a contiguous range of rows
+        const int per_sm = (cols <= 768 && 2 * stage_smem <= 227 * 1024) ? 2 : 1;
+        int grid = num_sms() * per_sm;
+        const int64_t warps_wanted = (rows + 3) / 4;                 // at least ~4 rows per warp
+        if ((int64_t)grid * LN_WARPS > warps_wanted) grid = (int)((warps_wanted + LN_WARPS - 1) / LN_WARPS);
+        const int64_t rpw = (rows + (int64_t)grid * LN_WARPS - 1) / ((int64_t)grid * LN_WARPS);
+#define MGB_LNB_STAGED(N)                                                                                          \
+    do {                                                                                                           \
+        static std::once_flag once;                                                                                \
+        std::call_once(once, [] {                                                                                  \
+            cudaFuncSetAttribute(ln_bwd_staged_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); \
+        });                                                                                                        \
+        ln_bwd_staged_kernel<N><<<grid, LN_WARPS * 32, stage_smem, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma,  \
+                                                                        dbeta, rows, cols, rpw);                    \
+    } while (0)
+        if (cols <= 256) MGB_LNB_STAGED(1);
+        else if (cols <= 512) MGB_LNB_STAGED(2);
+        else if (cols <= 768) MGB_LNB_STAGED(3);
+        else if (cols <= 1024) MGB_LNB_STAGED(4);
+        else if (cols <= 1536) MGB_LNB_STAGED(6);
+        else MGB_LNB_STAGED(8);
+#undef MGB_LNB_STAGED
+        count_launch(1);
+        MGB_CHECK_LAUNCH();
+        return kOk;
+    }
     const int grid = grid_for(rows, LN_WARPS * 4, num_sms() * (cols <= 768 ? 4 : 2));
     const size_t smem = (size_t)2 * cols * sizeof(float);
     if (!vec) ln_bwd_generic_kernel<<<grid, LN_WARPS * 32, 0, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, dbeta, rows, cols);
