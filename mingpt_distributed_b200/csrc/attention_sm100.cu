@@ -393,7 +393,9 @@ constexpr int kSlots = 4;                         // Q/dO sub-tiles in flight
 constexpr uint32_t kBwdTmemCols = 512;
 constexpr uint32_t cST = 0, cDPT = 128, cKT = 256, cVT = 288, cDK = 320, cDV = 384, cDQ = 448;
 // K, V | 4 x (Q, dO) sub-tiles | dS^T: 4 atoms of 64 queries | dQ staging: 2 boxes | lse/delta x2 | barriers
-constexpr int BWD_SMEM = 2 * TILE_BYTES + kSlots * 2 * SUB_BYTES + 4 * TILE_BYTES + 2 * TILE_BYTES + 2 * 128 * 8 + 1024 + 256;
+// 2 x (K, V) | 4 x (Q, dO) sub-tiles | dS^T: 4 atoms | dQ staging: 2 boxes | lse/delta x2 | barriers. No alignment slack:
+// the kernel has no static shared memory, so the dynamic window starts 1024-aligned (checked at kernel entry).
+constexpr int BWD_SMEM = 4 * TILE_BYTES + kSlots * 2 * SUB_BYTES + 4 * TILE_BYTES + 2 * TILE_BYTES + 2 * 128 * 8 + 256;
 
 __device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&r)[16]) {
     asm volatile(
@@ -467,16 +469,15 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                    const __grid_constant__ CUtensorMap tmap_do, const __grid_constant__ CUtensorMap tmap_dq,
                    const float* __restrict__ lse, const float* __restrict__ delta,
                    __nv_bfloat16* __restrict__ dqkv, int B, int T, int H, int mask_mode, float scale, float scale_log2) {
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t* sK = smem;
-    uint8_t* sV = smem + TILE_BYTES;
-    uint8_t* sQ = smem + 2 * TILE_BYTES;                       // slot s: Q at +s*2*SUB_BYTES, dO right behind it
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = smem_raw;
+    if (smem_u32(smem) & 1023u) __trap();                      // SWIZZLE_128B tiles need 1024-byte alignment
+    uint8_t* sKV = smem;                                       // item w: K at (w&1)*2 tiles, V one tile behind it
+    uint8_t* sQ = smem + 4 * TILE_BYTES;                       // slot s: Q at +s*2*SUB_BYTES, dO right behind it
     uint8_t* sdS = sQ + kSlots * 2 * SUB_BYTES;                // atom a: 128 key rows x 128 B (64 queries)
     uint8_t* sDQ = sdS + 4 * TILE_BYTES;                       // two boxes: 128 query rows x 32 fp32
     float2* sLD = reinterpret_cast<float2*>(sDQ + 2 * TILE_BYTES);   // [2][128] (bias - lse*log2e, delta*scale)
     uint64_t* bars = reinterpret_cast<uint64_t*>(sDQ + 2 * TILE_BYTES + 2 * 128 * 8);
-    uint64_t* kv_full = bars + 0;
     uint64_t* qdo_full = bars + 1;     // [4]
     uint64_t* qdo_empty = bars + 5;    // [4]
     uint64_t* s_full = bars + 9;       // [2]
@@ -486,7 +487,8 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
     uint64_t* all_done = bars + 15;    // every product of the item has completed: K / V tiles and dK / dV are final
     uint64_t* acc_free = bars + 16;    // dK / dV accumulators have been read out
     uint64_t* kv_ready = bars + 17;    // K / V copied into TMEM
-    uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(bars + 18);
+    uint64_t* kv_full = bars + 18;     // [2] K / V tiles of item w landed in slot w & 1
+    uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(bars + 20);
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
     const int C = H * D;
@@ -500,7 +502,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
         tma_prefetch_desc(&tmap_q);
         tma_prefetch_desc(&tmap_do);
         tma_prefetch_desc(&tmap_dq);
-        mbar_init(kv_full, 1);
+        mbar_init(&kv_full[0], 1); mbar_init(&kv_full[1], 1);
         for (int s = 0; s < kSlots; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
         for (int s = 0; s < 2; ++s) { mbar_init(&s_full[s], 1); mbar_init(&p_ready[s], kEwWarps); }
         mbar_init(dq_full, 1); mbar_init(dq_free, 4); mbar_init(all_done, 1); mbar_init(acc_free, kEwWarps); mbar_init(kv_ready, kEwWarps);
@@ -519,25 +521,39 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
         {
             const bool issuer = elect_one();
             uint32_t g = 0, w = 0;
-            for (int q = 0;; ++q) {
-                BwdItem it;
-                const int st = bwd_item(sched, q, it);
-                if (st < 0) break;
-                if (st == 0) continue;
+            auto next_item = [&](int& q, BwdItem& it) {       // advance q to the next non-empty slot; false at the end
+                for (;; ++q) {
+                    const int st = bwd_item(sched, q, it);
+                    if (st < 0) return false;
+                    if (st > 0) return true;
+                }
+            };
+            auto load_kv = [&](const BwdItem& it, uint32_t slot) {
+                if (issuer) {
+                    uint8_t* k = sKV + slot * 2 * TILE_BYTES;
+                    mbar_arrive_expect_tx(&kv_full[slot], 2 * TILE_BYTES);
+                    tma_load_2d(k, &tmap_kv, &kv_full[slot], C + it.h * D, it.b * T + it.kb * BKV);
+                    tma_load_2d(k + TILE_BYTES, &tmap_kv, &kv_full[slot], 2 * C + it.h * D, it.b * T + it.kb * BKV);
+                }
+                __syncwarp();
+            };
+            int q = 0;
+            BwdItem it;
+            bool have = next_item(q, it);
+            if (have) load_kv(it, 0);
+            while (have) {
+                // K / V are double-buffered: the NEXT item's tiles are fetched while this item runs, as soon as the
+                // item before this one (the slot's last reader) is finished.
+                int q2 = q + 1;
+                BwdItem it2;
+                const bool have2 = next_item(q2, it2);
                 const int row0 = it.b * T;
-                // the first 128 queries' Q / dO only need free slots: fetch them while the previous item still runs,
-                // K / V once that item no longer reads them
                 const int nsub = 2 * it.nblk;
                 const int kv_at = (w > 0) ? 2 : 0;
                 for (int n = 0; n <= nsub; ++n) {
-                    if (n == kv_at) {
+                    if (n == kv_at && have2) {
                         if (w > 0) mbar_wait(all_done, (w - 1) & 1);
-                        if (issuer) {
-                            mbar_arrive_expect_tx(kv_full, 2 * TILE_BYTES);
-                            tma_load_2d(sK, &tmap_kv, kv_full, C + it.h * D, row0 + it.kb * BKV);
-                            tma_load_2d(sV, &tmap_kv, kv_full, 2 * C + it.h * D, row0 + it.kb * BKV);
-                        }
-                        __syncwarp();
+                        load_kv(it2, (w + 1) & 1);
                     }
                     if (n == nsub) break;
                     const uint32_t slot = g & (kSlots - 1);
@@ -552,6 +568,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                     ++g;
                 }
                 ++w;
+                q = q2; it = it2; have = have2;
             }
         }
     } else if (warp == kMmaWarp) {
@@ -562,7 +579,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
             const uint32_t idesc_kn = make_idesc_bf16(128, D, 0, 1);     // dV (A in TMEM), dK (A K-major smem)
             const uint32_t idesc_nn = make_idesc_bf16(128, D, 1, 1);     // dQ (A = dS^T read MN-major)
             // descriptor bases; a K step of 16 elements is +32 B (K-major) or +2048 B (MN-major) = +2 / +128 encoded
-            const uint64_t dKmn = make_smem_desc_sw128(smem_u32(sK), TILE_BYTES, 1024);
+            const uint64_t dKmn0 = make_smem_desc_sw128(smem_u32(sKV), TILE_BYTES, 1024);
             const uint64_t dQk0 = make_smem_desc_sw128(smem_u32(sQ), 0, 1024);
             const uint64_t dQmn0 = make_smem_desc_sw128(smem_u32(sQ), TILE_BYTES, 1024);
             const uint64_t dSmn0 = make_smem_desc_sw128(smem_u32(sdS), TILE_BYTES, 1024);
@@ -593,6 +610,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 if (st < 0) break;
                 if (st == 0) continue;
                 const int nsub = 2 * it.nblk;
+                const uint64_t dKmn = dKmn0 + (uint64_t)(w & 1) * 2 * kAtomStep;   // this item's K tile
                 mbar_wait(kv_ready, w & 1);              // K / V are in TMEM (and the K tile in shared memory)
                 tc_fence_after();
                 issue_scores(g);
@@ -706,7 +724,9 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
             };
             {   // this item's K and V rows -> TMEM (bf16): 16 features of row r per thread. The previous item's products
                 // are complete (all_done was waited for in its epilogue).
-                mbar_wait(kv_full, w & 1);
+                mbar_wait(&kv_full[w & 1], (w >> 1) & 1);
+                const uint8_t* sK = sKV + (w & 1) * 2 * TILE_BYTES;
+                const uint8_t* sV = sK + TILE_BYTES;
                 uint32_t kreg[8], vreg[8];
 #pragma unroll
                 for (int u = 0; u < 2; ++u) {

@@ -20,9 +20,9 @@ hw = bf(V, C); lg = torch.empty(Mc, 50304, device=dev, dtype=torch.bfloat16); hd
 cases = [
     ("fwd qkv + bias", lambda: ops.linear_fwd(x, w_qkv, o3, bias=b3), (M, 3 * C, C), 2 * (M * C + 3 * C * C + M * 3 * C)),
     ("fwd proj + bias + residual", lambda: ops.linear_fwd(x, w_proj, o1, bias=b1, residual=x), (M, C, C), 2 * (M * C + C * C + 2 * M * C)),
-    ("fwd fc + bias + gelu + preact", lambda: ops.linear_fwd(x, w_fc, o4, bias=b4, act=1, preact=p4), (M, 4 * C, C), 2 * (M * C + 4 * C * C + 2 * M * 4 * C)),
+    ("fwd fc + bias + gelu + stored gelu'", lambda: ops.linear_fwd(x, w_fc, o4, bias=b4, act=1 | ops.ACT_STORE_GRAD, preact=p4), (M, 4 * C, C), 2 * (M * C + 4 * C * C + 2 * M * 4 * C)),
     ("fwd fc2 + bias + residual", lambda: ops.linear_fwd(x4, w_fc2, o1, bias=b1, residual=x), (M, C, 4 * C), 2 * (M * 4 * C + 4 * C * C + 2 * M * C)),
-    ("dgrad fc2 + gelu gate", lambda: ops.linear_dgrad(x, w_fc2, o4, gate=p4, gate_kind=1), (M, 4 * C, C), 2 * (M * C + 4 * C * C + 2 * M * 4 * C)),
+    ("dgrad fc2 * stored gelu'", lambda: ops.linear_dgrad(x, w_fc2, o4, gate=p4, gate_kind=ops.GATE_MUL), (M, 4 * C, C), 2 * (M * C + 4 * C * C + 2 * M * 4 * C)),
     ("dgrad fc", lambda: ops.linear_dgrad(x4, w_fc, o1), (M, C, 4 * C), 2 * (M * 4 * C + 4 * C * C + M * C)),
     ("dgrad proj", lambda: ops.linear_dgrad(x, w_proj, o1), (M, C, C), 2 * (M * C + C * C + M * C)),
     ("dgrad qkv", lambda: ops.linear_dgrad(x3, w_qkv, o1), (M, C, 3 * C), 2 * (M * 3 * C + 3 * C * C + M * C)),
