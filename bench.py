@@ -307,7 +307,9 @@ def main():
                     config=dict(workload=f"gpt2-124M train step (L12 H12 C768 V50257 T{T}), variant={args.variant}, "
                                          "fp32 master weights + AdamW state, bf16 GEMM/attention operands",
                                 global_batch=world * B, seq_len=T, parallelism=f"dp{world}", dropout=args.dropout,
-                                launch="CUDA graph replay of the whole step" if stepper.use_graph else "eager (one Python call per kernel)",
+                                launch=("eager (one Python call per kernel)" if not stepper.use_graph else
+                                        "CUDA graph replay of the whole step" if dp is None else
+                                        "CUDA graph segments cut at gradient-bucket boundaries, NCCL all-reduces launched between them"),
                                 l2="per-step working set (>10 GB of activations + 2 GB of parameters/state) is far larger than the 126 MB L2"),
                     mfu=dict(flops_per_token=f_tok, of_nominal_2p25pf=value * f_tok / (world * NOMINAL_BF16),
                              of_measured_sustained=value * f_tok / (world * peaks["bf16_sustained"] * 1e12)),

@@ -13,6 +13,7 @@ from __future__ import annotations
 
 import os
 import time
+import warnings
 from collections import defaultdict
 from dataclasses import asdict, dataclass
 from typing import Any, Dict, Optional
@@ -85,23 +86,31 @@ class GraphedTrainStep:
 
     The step launches ~320 kernels of 20-600 us each; issued one by one from Python their launch overhead
     shows up as ~15 % of idle GPU time on a B200. After `warmup` eager steps the whole step -- forward,
-    backward, (bucketed all-reduce), norm, clip + AdamW -- is captured once per (batch, seq) shape and replayed.
-    Inputs are copied into static device buffers; the returned loss is a static device scalar (read it
-    before the next call). With use_graph=False the same body runs eagerly."""
+    backward, norm, clip + AdamW -- is captured once per (batch, seq) shape and replayed. Inputs are copied
+    into static device buffers; the returned loss is a static device scalar (read it before the next call).
+    With use_graph=False the same body runs eagerly.
+
+    Data parallel: NCCL stays OUT of the graphs. The step is captured as a chain of graph SEGMENTS cut where a
+    gradient bucket completes; on replay each bucket's all-reduce is launched eagerly on the side stream
+    between two segments, so it overlaps the rest of the backward exactly like the eager path, and the last
+    segment (norm, clip, AdamW) starts after the side stream has drained."""
 
     def __init__(self, model, optimizer, grad_norm_clip: Optional[float] = None, dp: Optional[DataParallel] = None,
                  use_graph: bool = True, warmup: int = 2):
         if not isinstance(optimizer, FusedAdamW):
             raise TypeError("GraphedTrainStep needs the FusedAdamW returned by create_optimizer")
         self.model, self.opt, self.clip, self.dp = model, optimizer, grad_norm_clip, dp
-        # With data parallelism the step stays eager: capturing the side-stream NCCL all-reduces together with
-        # the compute hung in testing on 2 x B200 (torch 2.11 / NCCL 2.28), and the all-reduce must overlap the
-        # backward, so it cannot simply be left outside the graph.
-        self.use_graph, self.warmup = (use_graph and dp is None), warmup
+        self.use_graph, self.warmup = use_graph, warmup
         self._states = {}
 
+    def _optimizer_part(self, scale: float, graph_step: bool):
+        clip = self.clip is not None and self.clip > 0
+        norm_sq = self.opt.grad_norm_sq() if clip else None
+        self.opt.step(grad_scale=scale, gradnorm_sq=norm_sq, max_norm=float(self.clip) if clip else 0.0,
+                      graph_step=graph_step)
+
     def _body(self, st, graph_step: bool):
-        model, opt = self.model, self.opt
+        model = self.model
         for p in model.parameters():          # optimizer.zero_grad(set_to_none=True), mingpt/trainer.py:125
             p.grad = None
         if self.dp is not None:
@@ -111,10 +120,76 @@ class GraphedTrainStep:
         if self.dp is not None:
             self.dp.finish_backward()
             scale = self.dp.grad_scale
-        clip = self.clip is not None and self.clip > 0
-        norm_sq = opt.grad_norm_sq() if clip else None
-        opt.step(grad_scale=scale, gradnorm_sq=norm_sq, max_norm=float(self.clip) if clip else 0.0, graph_step=graph_step)
+        self._optimizer_part(scale, graph_step)
         return loss
+
+    # ---- data parallel: a chain of graph segments with the all-reduces in between ----
+    def _capture_segments(self, st):
+        model, dp = self.model, self.dp
+        dp._ensure()
+        buckets = dp.buckets
+        segs = []
+        pool = torch.cuda.graph_pool_handle()
+        cur = {"g": None}
+
+        def begin():
+            g = torch.cuda.CUDAGraph()
+            # thread_local: NCCL's watchdog thread polls CUDA events; in the default (global) mode that invalidates
+            # a capture in progress on this thread
+            g.capture_begin(pool=pool, capture_error_mode="thread_local")
+            cur["g"] = g
+
+        def end():
+            with warnings.catch_warnings():       # a cut right after another cut leaves an (harmless) empty graph
+                warnings.simplefilter("ignore")
+                cur["g"].capture_end()
+            segs.append(("graph", cur["g"]))
+            cur["g"] = None
+
+        def hook(group: int):
+            span = buckets._by_trigger.get(group)
+            if span is None or not buckets.enabled or buckets.world == 1:
+                return
+            end()
+            segs.append(("allreduce", span))
+            begin()
+
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        saved = model._layer_done_hook
+        with torch.cuda.stream(side):
+            begin()
+            try:
+                model._layer_done_hook = hook
+                for p in model.parameters():
+                    p.grad = None
+                st["loss"] = model.forward_backward(st["x"], st["y"])
+                end()
+                segs.append(("drain", None))
+                begin()
+                self._optimizer_part(dp.grad_scale, True)
+                end()
+            finally:
+                model._layer_done_hook = saved
+        torch.cuda.current_stream().wait_stream(side)
+        return segs
+
+    def _replay_segments(self, segs):
+        buckets = self.dp.buckets
+        cur = torch.cuda.current_stream()
+        for kind, obj in segs:
+            if kind == "graph":
+                obj.replay()
+            elif kind == "allreduce":
+                s, e = obj
+                ev = torch.cuda.Event()
+                ev.record(cur)
+                buckets.stream.wait_event(ev)
+                with torch.cuda.stream(buckets.stream):
+                    dist.all_reduce(buckets.flat[s:e], op=dist.ReduceOp.SUM, group=buckets.group)
+                buckets.launched += 1
+            else:
+                cur.wait_stream(buckets.stream)
 
     def __call__(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         key = tuple(x.shape)
@@ -134,12 +209,18 @@ class GraphedTrainStep:
                 self.opt.begin_graph_mode()
                 from . import _lib
                 n0 = _lib.launch_count()
-                g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g):
-                    st["loss"] = self._body(st, graph_step=True)
-                st["graph"] = g
+                if self.dp is not None:
+                    st["graph"] = self._capture_segments(st)
+                else:
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g):
+                        st["loss"] = self._body(st, graph_step=True)
+                    st["graph"] = g
                 st["launches"] = _lib.launch_count() - n0      # kernels of ours inside one replay
-            st["graph"].replay()
+            if self.dp is not None:
+                self._replay_segments(st["graph"])
+            else:
+                st["graph"].replay()
             self.opt.note_replay()
         st["calls"] += 1
         return st["loss"]

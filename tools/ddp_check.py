@@ -34,6 +34,32 @@ torch.cuda.synchronize()
 ref = model._flat.clone(); dist.broadcast(ref, src=0)
 same = bool(torch.equal(ref, model._flat))
 flags = torch.tensor([rel, float(same)], device="cuda"); dist.all_reduce(flags, op=dist.ReduceOp.MAX if False else dist.ReduceOp.MIN)
+
+# (4) the segmented CUDA-graph step (graphs cut at bucket boundaries, all-reduces launched between them) follows
+#     the eager data-parallel step
+def run(use_graph, steps=6):
+    torch.manual_seed(0)
+    mdl = m.GPT(cfg, verbose=False).cuda()
+    op = m.create_optimizer(mdl, m.OptimizerConfig(learning_rate=1e-3))
+    d = m.DataParallel(mdl, bucket_cap_mb=1.0)
+    stepper = m.GraphedTrainStep(mdl, op, 1.0, d, use_graph=use_graph, warmup=2)
+    losses = []
+    for s_ in range(steps):
+        gg = torch.Generator().manual_seed(100 + s_)
+        tk = torch.randint(0, 1000, (4 * world, 129), generator=gg)[4 * rank:4 * rank + 4]
+        losses.append(float(stepper(tk[:, :-1].contiguous().pin_memory(), tk[:, 1:].contiguous().pin_memory())))
+    torch.cuda.synchronize()
+    return losses, mdl._flat.clone(), stepper
+le, pe, _ = run(False)
+lg, pg, stp = run(True)
+graph_rel = ((pg - pe).norm() / pe.norm()).item()
+loss_dev = max(abs(a - b) / abs(b) for a, b in zip(lg, le))
+refp = pg.clone(); dist.broadcast(refp, src=0)
+graph_same = bool(torch.equal(refp, pg))
+nseg = len([k for k, _ in stp._states[(4, 128)]["graph"] if k == "graph"])
+if rank == 0:
+    print(json.dumps(dict(world=world, graph_segments=nseg, graph_vs_eager_param_rel=graph_rel, graph_vs_eager_loss_dev=loss_dev,
+                          graph_params_identical_across_ranks=graph_same)))
 if rank == 0:
     print(json.dumps(dict(world=world, grad_rel_err_vs_global_batch=rel, params_identical_after_step=same,
                           buckets=len(dp.buckets.buckets), allreduces_launched=dp.buckets.launched)))
