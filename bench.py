@@ -273,9 +273,9 @@ def main():
         finally:
             ops.gemm = orig
         # DRAM traffic per launch from the committed ncu --set full capture of every GEMM shape of the step
-        # (tools/gemm_ncu.py -> profiles/r1_gemm_shapes_ncu.json), weighted by how often each shape runs
+        # (tools/gemm_ncu.py -> profiles/r1_e_gemm_shapes_ncu.json), weighted by how often each shape runs
         traffic, traffic_alg = None, None
-        tpath = os.path.join(ROOT, "profiles", "r1_gemm_shapes_ncu.json")
+        tpath = os.path.join(ROOT, "profiles", "r1_e_gemm_shapes_ncu.json")
         if os.path.exists(tpath) and B == 32 and T == 1024 and args.variant == "mingpt":
             shapes = json.load(open(tpath))
             weights = [2 if s["name"].startswith("head") else GPT2["n_layer"] for s in shapes]
@@ -289,7 +289,7 @@ def main():
                     achieved=achieved, peak=peaks["bf16_sustained"], unit="TFLOP/s", frac=achieved / peaks["bf16_sustained"],
                     peak_source=peaks["source"] + " bf16_tflops_sustained (kernel timed inside a long step)",
                     frac_of_nominal=achieved * 1e12 / NOMINAL_BF16, traffic=traffic, traffic_algorithmic=traffic_alg,
-                    traffic_source="profiles/r1_gemm_shapes_ncu.json (ncu --set full, dram read+write, mean per launch)",
+                    traffic_source="profiles/r1_e_gemm_shapes_ncu.json (ncu --set full, dram read+write, mean per launch)",
                     share_of_step=gemm_ms / step_ms_instr, flops_per_launch_avg=flops / max(len(records), 1),
                     ms_per_launch_avg=gemm_ms / max(len(records), 1))
 

@@ -59,7 +59,8 @@ int64_t mgb_launch_count(void);
  * "gemm_direct_store" (1 = CTA-pair engine writes D from registers instead of through TMA), "attn_mma"
  * (1 = head size 64 also uses the mma.sync attention kernels instead of the tcgen05 ones), "ln_unstaged"
  * (1 = LayerNorm backward loads its rows straight into registers instead of staging them through shared
- * memory with bulk copies). Returns the
+ * memory with bulk copies), "ce_unstaged" (1 = cross-entropy streams its rows from global memory, two
+ * exponentials per logit, instead of staging them in shared memory). Returns the
  * previous value, or -1 for an unknown key. Every alternative computes the same result. */
 int mgb_set_option(const char* key, int value);
 

@@ -302,6 +302,7 @@ std::atomic<int> g_opt_gemm_single{0};
 std::atomic<int> g_opt_gemm_direct_store{0};
 std::atomic<int> g_opt_attn_mma{0};
 std::atomic<int> g_opt_ln_unstaged{0};
+std::atomic<int> g_opt_ce_unstaged{0};
 }
 extern "C" int mgb_set_option(const char* key, int value) {
     if (!key) return -1;
@@ -309,6 +310,7 @@ extern "C" int mgb_set_option(const char* key, int value) {
     if (!std::strcmp(key, "gemm_direct_store")) return mgb::g_opt_gemm_direct_store.exchange(value);
     if (!std::strcmp(key, "attn_mma")) return mgb::g_opt_attn_mma.exchange(value);
     if (!std::strcmp(key, "ln_unstaged")) return mgb::g_opt_ln_unstaged.exchange(value);
+    if (!std::strcmp(key, "ce_unstaged")) return mgb::g_opt_ce_unstaged.exchange(value);
     return -1;
 }
 

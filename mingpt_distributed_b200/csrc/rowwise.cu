@@ -10,6 +10,7 @@
 namespace mgb {
 
 extern std::atomic<int> g_opt_ln_unstaged;   // optim.cu: 1 = LayerNorm backward keeps its rows in registers
+extern std::atomic<int> g_opt_ce_unstaged;   // optim.cu: 1 = cross-entropy streams its rows from global memory
 
 // =====================================================================================
 // LayerNorm  (nn.LayerNorm: mingpt/model.py:176,178,248)
@@ -546,6 +547,148 @@ cross_entropy_kernel(__nv_bfloat16* logits, int64_t ld, const int64_t* __restric
     }
 }
 
+// The same loss / gradient with the logits row STAGED IN SHARED MEMORY: a persistent CTA per SM, two row buffers,
+// a producer warp that bulk-copies rows in (cp.async.bulk, one 100 KB transfer per row) and the finished
+// gradient rows out, 16 compute warps that make three passes over the on-chip row: maximum (packed bf16x2);
+// e = exp(x - max) summed in fp32 and written back as bf16; (e / sum - onehot) * scale. One exponential per
+// element instead of two, DRAM sees each row exactly once in each direction, and the loads / stores run ahead
+// of the arithmetic.
+constexpr int CES_WARPS = 16;                       // compute warps; warp CES_WARPS is the producer
+__global__ void __launch_bounds__((CES_WARPS + 1) * 32, 1)
+cross_entropy_staged_kernel(__nv_bfloat16* logits, int64_t ld, const int64_t* __restrict__ targets,
+                            float* __restrict__ row_loss, const int32_t* __restrict__ n_valid, int64_t rows,
+                            int64_t vocab, float grad_scale, int32_t* err_flag) {
+    extern __shared__ __align__(128) uint8_t ces_smem[];
+    const uint32_t rowbytes = (uint32_t)ld * 2;
+    __nv_bfloat16* bufs[2] = {reinterpret_cast<__nv_bfloat16*>(ces_smem),
+                              reinterpret_cast<__nv_bfloat16*>(ces_smem + rowbytes)};
+    uint64_t* full = reinterpret_cast<uint64_t*>(ces_smem + 2 * (size_t)rowbytes);   // [2] row landed
+    uint64_t* done = full + 2;                                                       // [2] gradient row complete
+    float* sh = reinterpret_cast<float*>(done + 2);                                  // [32] block reductions
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int b = 0; b < 2; ++b) { mbar_init(&full[b], 1); mbar_init(&done[b], 1); }
+        fence_mbar_init();
+    }
+    __syncthreads();
+    const int64_t nmine = (rows - blockIdx.x + gridDim.x - 1) / gridDim.x;           // rows of this CTA
+
+    if (warp == CES_WARPS) {
+        // ===================== producer: rows in, gradient rows out =====================
+        if (lane == 0) {
+            for (int64_t k = 0; k < nmine && k < 2; ++k) {
+                mbar_arrive_expect_tx(&full[k], rowbytes);
+                bulk_load_1d(bufs[k], logits + (blockIdx.x + k * gridDim.x) * ld, rowbytes, &full[k]);
+            }
+            for (int64_t k = 0; k < nmine; ++k) {
+                const int b = (int)(k & 1);
+                mbar_wait(&done[b], (uint32_t)((k >> 1) & 1));
+                bulk_store_1d(logits + (blockIdx.x + k * gridDim.x) * ld, bufs[b], rowbytes);
+                bulk_commit();
+                if (k + 2 < nmine) {
+                    bulk_wait_read<0>();                                  // the store has left the buffer
+                    mbar_arrive_expect_tx(&full[b], rowbytes);
+                    bulk_load_1d(bufs[b], logits + (blockIdx.x + (k + 2) * gridDim.x) * ld, rowbytes, &full[b]);
+                }
+            }
+            bulk_wait<0>();
+        }
+        return;
+    }
+
+    // ===================== compute warps =====================
+    const int tid = threadIdx.x;                       // 0 .. 511
+    constexpr int NT = CES_WARPS * 32;
+    constexpr float LOG2E_F = 1.4426950408889634f;
+    const int64_t vmain = vocab & ~int64_t(7);
+    const int nv = max(*n_valid, 1);
+    const float sc = grad_scale / (float)nv;
+    auto reduce = [&](float v, bool is_max) {          // over the 512 compute threads (named barrier 1)
+        v = is_max ? warp_max(v) : warp_sum(v);
+        if (lane == 0) sh[warp] = v;
+        named_bar_sync(1, NT);
+        float r = (lane < CES_WARPS) ? sh[lane] : (is_max ? -INFINITY : 0.f);
+        r = is_max ? warp_max(r) : warp_sum(r);
+        named_bar_sync(1, NT);
+        return r;
+    };
+    for (int64_t k = 0; k < nmine; ++k) {
+        const int b = (int)(k & 1);
+        const int64_t row = blockIdx.x + k * gridDim.x;
+        __nv_bfloat16* lr = bufs[b];
+        int64_t tgt = targets[row];
+        bool ignored = (tgt == -1);
+        if (!ignored && (tgt < 0 || tgt >= vocab)) {
+            if (err_flag && tid == 0) atomicExch(err_flag, 2);
+            ignored = true;
+        }
+        mbar_wait(&full[b], (uint32_t)((k >> 1) & 1));
+        if (ignored) {
+            if (tid == 0) row_loss[row] = 0.f;
+            for (int64_t c = (int64_t)tid * 8; c < ld; c += NT * 8) sts128(lr + c, make_uint4(0, 0, 0, 0));
+        } else {
+            const float tgt_logit = __bfloat162float(lr[tgt]);
+            // pass A: maximum (packed bf16x2: the maximum of bf16 values is exact in bf16)
+            __nv_bfloat162 m2 = __float2bfloat162_rn(-INFINITY);
+            for (int64_t c = (int64_t)tid * 8; c < vmain; c += NT * 8) {
+                const uint4 v = lds128(lr + c);
+                const __nv_bfloat162 a = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&v.x), *reinterpret_cast<const __nv_bfloat162*>(&v.y));
+                const __nv_bfloat162 b2 = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&v.z), *reinterpret_cast<const __nv_bfloat162*>(&v.w));
+                m2 = __hmax2(m2, __hmax2(a, b2));
+            }
+            float m = fmaxf(__low2float(m2), __high2float(m2));
+            for (int64_t c = vmain + tid; c < vocab; c += NT) m = fmaxf(m, __bfloat162float(lr[c]));
+            const float gm = reduce(m, true);          // (its barriers also order the tgt_logit read before pass B)
+            // pass B: e = exp(x - max) = exp2(x * log2e - max * log2e): fp32 sum, bf16 copy in place
+            const float gml = -gm * LOG2E_F;
+            float ssum = 0.f;
+            for (int64_t c = (int64_t)tid * 8; c < vmain; c += NT * 8) {
+                const uint4 v = lds128(lr + c);
+                const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+                uint32_t o[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float2 t = unpack_bf16x2(w[e]);
+                    const float e0 = exp2f(fmaf(t.x, LOG2E_F, gml)), e1 = exp2f(fmaf(t.y, LOG2E_F, gml));
+                    ssum += e0 + e1;
+                    o[e] = pack_bf16x2(e0, e1);
+                }
+                sts128(lr + c, make_uint4(o[0], o[1], o[2], o[3]));
+            }
+            for (int64_t c = vmain + tid; c < ld; c += NT) {
+                float e0 = 0.f;
+                if (c < vocab) { e0 = exp2f(fmaf(__bfloat162float(lr[c]), LOG2E_F, gml)); ssum += e0; }
+                lr[c] = __float2bfloat16(e0);
+            }
+            const float gs = reduce(ssum, false);
+            if (tid == 0) row_loss[row] = gm + logf(gs) - tgt_logit;
+            // pass C: gradient. Each thread revisits exactly the elements it wrote in pass B.
+            const float inv = sc / gs;
+            for (int64_t c = (int64_t)tid * 8; c < vmain; c += NT * 8) {
+                const uint4 v = lds128(lr + c);
+                const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+                float f[8];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) { const float2 t = unpack_bf16x2(w[e]); f[2 * e] = t.x * inv; f[2 * e + 1] = t.y * inv; }
+                if (tgt >= c && tgt < c + 8) {
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) if (c + e == tgt) f[e] -= sc;
+                }
+                sts128(lr + c, make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
+                                          pack_bf16x2(f[6], f[7])));
+            }
+            for (int64_t c = vmain + tid; c < ld; c += NT) {
+                float g = 0.f;
+                if (c < vocab) g = __bfloat162float(lr[c]) * inv - (c == tgt ? sc : 0.f);
+                lr[c] = __float2bfloat16(g);
+            }
+        }
+        fence_proxy_async_smem();                      // the row goes out through the async proxy
+        named_bar_sync(1, NT);
+        if (tid == 0) mbar_arrive(&done[b]);
+    }
+}
+
 __global__ void __launch_bounds__(256)
 count_valid_kernel(const int64_t* __restrict__ targets, int64_t n, int32_t* out) {
     __shared__ int sh[8];
@@ -697,8 +840,19 @@ extern "C" int mgb_cross_entropy_fwd_bwd(void* logits, int64_t ld, const int64_t
     if (rows < 0 || vocab <= 0 || ld < vocab) { set_last_error("cross_entropy: bad shape"); return kErrBadShape; }
     if (rows > INT32_MAX) { set_last_error("cross_entropy: too many rows"); return kErrTooLarge; }
     if (rows == 0) return kOk;
-    cross_entropy_kernel<<<(int)rows, CE_THREADS, 0, s>>>((__nv_bfloat16*)logits, ld, targets, row_loss, n_valid, vocab,
-                                                         grad_scale, write_grad, err_flag);
+    const size_t stage_smem = (size_t)4 * ld + 4 * sizeof(uint64_t) + 32 * sizeof(float);
+    if (write_grad && (ld % 8 == 0) && ((uintptr_t)logits % 16 == 0) && stage_smem <= 227 * 1024 && rows >= 2 * num_sms() &&
+        !g_opt_ce_unstaged.load(std::memory_order_relaxed)) {
+        static std::once_flag once;
+        std::call_once(once, [] {
+            cudaFuncSetAttribute(cross_entropy_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        });
+        cross_entropy_staged_kernel<<<num_sms(), (CES_WARPS + 1) * 32, stage_smem, s>>>(
+            (__nv_bfloat16*)logits, ld, targets, row_loss, n_valid, rows, vocab, grad_scale, err_flag);
+    } else {
+        cross_entropy_kernel<<<(int)rows, CE_THREADS, 0, s>>>((__nv_bfloat16*)logits, ld, targets, row_loss, n_valid, vocab,
+                                                             grad_scale, write_grad, err_flag);
+    }
     count_launch(1);
     MGB_CHECK_LAUNCH();
     return kOk;

@@ -156,7 +156,9 @@ def test_attention_gpt2_shape_property():
 
 
 # ------------------------------------------------------------------ cross entropy
-@pytest.mark.parametrize("rows,V,ld", [(64, 65, 72), (33, 50257, 50304), (128, 1000, 1000), (7, 130, 131)])
+# the last three shapes have enough rows for the shared-memory-staged kernel (one persistent CTA per SM)
+@pytest.mark.parametrize("rows,V,ld", [(64, 65, 72), (33, 50257, 50304), (128, 1000, 1000), (7, 130, 131),
+                                       (1200, 1000, 1000), (515, 50257, 50304), (700, 2003, 2008)])
 def test_cross_entropy_in_place(rows, V, ld):
     from mingpt_distributed_b200 import ops
     g = torch.Generator(device="cuda").manual_seed(3)
@@ -181,6 +183,28 @@ def test_cross_entropy_in_place(rows, V, ld):
     _close(f"ce_dlogits_{rows}x{V}", logits[:, :V], lf.grad, 2e-2)
     assert (logits[:, V:] == 0).all() and (logits[::5] == 0).all()
     report(f"ce_loss_{rows}x{V}", got=loss.item(), want=want.item())
+
+
+def test_cross_entropy_staged_matches_streaming():
+    """the two kernels (mgb_set_option "ce_unstaged") agree to bf16 rounding of the stored exponentials"""
+    from mingpt_distributed_b200 import ops, _lib
+    g = torch.Generator(device="cuda").manual_seed(13)
+    rows, V, ld = 600, 50257, 50304
+    base = torch.zeros(rows, ld, device="cuda").bfloat16()
+    base[:, :V] = (torch.randn(rows, V, device="cuda", generator=g) * 2).bfloat16()
+    tg = torch.randint(0, V, (rows,), device="cuda", generator=g); tg[::7] = -1
+    nv = torch.zeros(1, dtype=torch.int32, device="cuda"); ops.count_valid_targets(tg, nv)
+    outs = []
+    for unstaged in (0, 1):
+        prev = _lib.set_option("ce_unstaged", unstaged)
+        lg = base.clone(); rl = torch.empty(rows, device="cuda")
+        ops.cross_entropy_fwd_bwd(lg, tg, rl, nv, V, grad_scale=1.0, write_grad=True)
+        torch.cuda.synchronize()
+        _lib.set_option("ce_unstaged", prev)
+        outs.append((lg.float(), rl))
+    assert torch.allclose(outs[0][1], outs[1][1], rtol=1e-5, atol=1e-5)
+    scale = outs[1][0].abs().max().item()
+    assert (outs[0][0] - outs[1][0]).abs().max().item() <= 1e-2 * scale
 
 
 def test_cross_entropy_all_ignored_and_bad_target():

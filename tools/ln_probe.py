@@ -37,3 +37,11 @@ out = torch.empty(B, T, C, dtype=torch.bfloat16, device=dev); lse = torch.empty(
 dqkv = torch.empty_like(qkv); delta = torch.empty_like(lse); dq = torch.empty(B, T, C, device=dev)
 ops.attention_fwd(qkv, out, lse, B, T, H, d, 1)
 print(f"attention bwd total   [cold L2] {bench(lambda: ops.attention_bwd(qkv, out, dout, lse, delta, dq, dqkv, B, T, H, d, 1)):7.1f} us")
+rows, V, ld = 16384, 50257, 50304
+lg = torch.randn(rows, ld, device=dev).bfloat16(); tg = torch.randint(0, V, (rows,), device=dev)
+rl = torch.empty(rows, device=dev); nv = torch.full((1,), rows, dtype=torch.int32, device=dev)
+for opt in (0, 1):
+    _lib.set_option("ce_unstaged", opt)
+    t = bench(lambda: ops.cross_entropy_fwd_bwd(lg, tg, rl, nv, V), iters=6)
+    print(f"cross entropy {'streaming' if opt else 'staged   '} [16384 x 50257] {t:7.1f} us   {2 * rows * ld * 2 / t / 1e6:6.2f} TB/s")
+_lib.set_option("ce_unstaged", 0)
