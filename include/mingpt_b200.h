@@ -109,6 +109,13 @@ int mgb_layernorm_fwd(const void* x, const float* gamma, const float* beta, void
 int mgb_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
                       const void* dres, void* dx, float* dgamma, float* dbeta, int64_t rows, int32_t cols,
                       mgb_stream_t stream);
+/* Same, and additionally dres_colsum[c] += sum over rows of dres[row, c] (fp32, atomic): dres is the gradient of
+ * the residual stream, i.e. also the output gradient of the linear layer that wrote into it (c_proj of the
+ * attention or of the MLP, mingpt/model.py:138,181), so this is that layer's bias gradient, taken from the read
+ * this kernel makes anyway instead of a separate pass over dres. dres must not be NULL. */
+int mgb_layernorm_bwd_colsum(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
+                             const void* dres, void* dx, float* dgamma, float* dbeta, float* dres_colsum,
+                             int64_t rows, int32_t cols, mgb_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------------
  * Embedding (GPTEmbedding.forward, mingpt/model.py:222-231 as repaired: wte[idx] + wpe[:, :T]).

@@ -214,22 +214,25 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
 // the number of bytes in flight per SM is set by shared memory (2 CTAs x 8 warps x 2 rows x 4.5 KiB at C = 768),
 // not by occupancy. The row is read back from shared memory in both passes (conflict-free 16-byte accesses).
 constexpr int LNB_STAGES = 2;
-template <int MAXCH>
+// COLSUM: additionally dres_colsum[c] += sum over rows of dres[row, c] -- the bias gradient of the linear layer whose
+// output gradient `dres` is (it is being read anyway).
+template <int MAXCH, bool COLSUM>
 __global__ void __launch_bounds__(LN_WARPS * 32, MAXCH <= 3 ? 2 : 1)
 ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                      const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd,
                      const __nv_bfloat16* dres, __nv_bfloat16* dx, float* __restrict__ dgamma, float* __restrict__ dbeta,
-                     int64_t rows, int cols, int64_t rows_per_warp) {
+                     float* __restrict__ dres_colsum, int64_t rows, int cols, int64_t rows_per_warp) {
     extern __shared__ __align__(128) uint8_t lnb_smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nch = cols >> 3;
     const uint32_t rowbytes = (uint32_t)cols * 2;
     const float inv_cols = 1.0f / (float)cols;
-    float* acc = reinterpret_cast<float*>(lnb_smem);                        // [2][cols] CTA-level dgamma / dbeta
-    uint8_t* ring = lnb_smem + (size_t)2 * cols * sizeof(float) + (size_t)warp * LNB_STAGES * 3 * rowbytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(lnb_smem + (size_t)2 * cols * sizeof(float) +
+    constexpr int NACC = COLSUM ? 3 : 2;
+    float* acc = reinterpret_cast<float*>(lnb_smem);                        // [NACC][cols] CTA-level dgamma / dbeta (/ colsum)
+    uint8_t* ring = lnb_smem + (size_t)NACC * cols * sizeof(float) + (size_t)warp * LNB_STAGES * 3 * rowbytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(lnb_smem + (size_t)NACC * cols * sizeof(float) +
                                                  (size_t)LN_WARPS * LNB_STAGES * 3 * rowbytes) + warp * LNB_STAGES;
-    for (int c = threadIdx.x; c < 2 * cols; c += blockDim.x) acc[c] = 0.f;
+    for (int c = threadIdx.x; c < NACC * cols; c += blockDim.x) acc[c] = 0.f;
     if (lane == 0) {
         for (int s = 0; s < LNB_STAGES; ++s) mbar_init(&bars[s], 1);
         fence_mbar_init();
@@ -251,7 +254,7 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
         for (int s = 0; s < LNB_STAGES; ++s)
             if (row0 + s < row1) issue(row0 + s, s);
 
-    float gam[MAXCH][8], dg[MAXCH][8], db[MAXCH][8];
+    float gam[MAXCH][8], dg[MAXCH][8], db[MAXCH][8], dr[COLSUM ? MAXCH : 1][8];
 #pragma unroll
     for (int i = 0; i < MAXCH; ++i) {
         const int ch = lane + 32 * i;
@@ -260,6 +263,7 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
             gam[i][e] = (ch < nch) ? gamma[ch * 8 + e] : 0.f;
             dg[i][e] = 0.f;
             db[i][e] = 0.f;
+            if (COLSUM) dr[i][e] = 0.f;
         }
     }
     float mu_n = 0.f, rs_n = 0.f;
@@ -319,6 +323,7 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                     for (int e = 0; e < 4; ++e) {
                         const float2 f = unpack_bf16x2(wr[e]);
                         r[2 * e] += f.x; r[2 * e + 1] += f.y;
+                        if (COLSUM) { dr[i][2 * e] += f.x; dr[i][2 * e + 1] += f.y; }
                     }
                 }
                 stg128(dx + row * cols + ch * 8,
@@ -338,6 +343,7 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
             for (int e = 0; e < 8; ++e) {
                 atomicAdd(&acc[ch * 8 + e], dg[i][e]);
                 atomicAdd(&acc[cols + ch * 8 + e], db[i][e]);
+                if (COLSUM) atomicAdd(&acc[2 * cols + ch * 8 + e], dr[i][e]);
             }
         }
     }
@@ -345,6 +351,7 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     for (int c = threadIdx.x; c < cols; c += blockDim.x) {
         atomicAdd(dgamma + c, acc[c]);
         atomicAdd(dbeta + c, acc[cols + c]);
+        if (COLSUM) atomicAdd(dres_colsum + c, acc[2 * cols + c]);
     }
 }
 
@@ -746,10 +753,11 @@ extern "C" int mgb_layernorm_fwd(const void* x, const float* gamma, const float*
     return kOk;
 }
 
-extern "C" int mgb_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean,
-                                 const float* rstd, const void* dres, void* dx, float* dgamma, float* dbeta,
-                                 int64_t rows, int32_t cols, mgb_stream_t s_) {
-    cudaStream_t s = (cudaStream_t)s_;
+extern "C" int mgb_colsum_bf16(const void* x, int64_t ld, int64_t rows, int64_t cols, float* out, mgb_stream_t s);
+
+static int layernorm_bwd_impl(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
+                              const void* dres, void* dx, float* dgamma, float* dbeta, float* dres_colsum, int64_t rows,
+                              int32_t cols, cudaStream_t s) {
     if (rows < 0 || cols <= 0) { set_last_error("layernorm_bwd: bad shape"); return kErrBadShape; }
     if (rows == 0) return kOk;
     auto DY = (const __nv_bfloat16*)dy; auto X = (const __nv_bfloat16*)x;
@@ -759,9 +767,12 @@ extern "C" int mgb_layernorm_bwd(const void* dy, const void* x, const float* gam
     // persistent: each CTA owns register accumulators for dgamma/dbeta, flushed once
     const size_t stage_smem = (size_t)2 * cols * sizeof(float) + (size_t)LN_WARPS * LNB_STAGES * 3 * cols * 2 +
                               LN_WARPS * LNB_STAGES * sizeof(uint64_t);
-    if (vec && stage_smem <= 227 * 1024 && !g_opt_ln_unstaged.load(std::memory_order_relaxed)) {
+    if (dres_colsum && !dres) { set_last_error("layernorm_bwd: dres_colsum needs dres"); return kErrBadShape; }
+    if (vec && stage_smem + (size_t)cols * sizeof(float) <= 227 * 1024 && !g_opt_ln_unstaged.load(std::memory_order_relaxed)) {
         // rows staged through shared memory by bulk copies; every warp owns a contiguous range of rows
-        const int per_sm = (cols <= 768 && 2 * stage_smem <= 227 * 1024) ? 2 : 1;
+        const bool colsum = dres_colsum != nullptr;
+        const size_t smem_used = stage_smem + (colsum ? (size_t)cols * sizeof(float) : 0);
+        const int per_sm = (cols <= 768 && 2 * smem_used <= 227 * 1024) ? 2 : 1;
         int grid = num_sms() * per_sm;
         const int64_t warps_wanted = (rows + 3) / 4;                 // at least ~4 rows per warp
         if ((int64_t)grid * LN_WARPS > warps_wanted) grid = (int)((warps_wanted + LN_WARPS - 1) / LN_WARPS);
@@ -770,10 +781,15 @@ extern "C" int mgb_layernorm_bwd(const void* dy, const void* x, const float* gam
     do {                                                                                                           \
         static std::once_flag once;                                                                                \
         std::call_once(once, [] {                                                                                  \
-            cudaFuncSetAttribute(ln_bwd_staged_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); \
+            cudaFuncSetAttribute(ln_bwd_staged_kernel<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); \
+            cudaFuncSetAttribute(ln_bwd_staged_kernel<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);  \
         });                                                                                                        \
-        ln_bwd_staged_kernel<N><<<grid, LN_WARPS * 32, stage_smem, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma,  \
-                                                                        dbeta, rows, cols, rpw);                    \
+        if (colsum)                                                                                                \
+            ln_bwd_staged_kernel<N, true><<<grid, LN_WARPS * 32, smem_used, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, \
+                                                                                 dbeta, dres_colsum, rows, cols, rpw);     \
+        else                                                                                                       \
+            ln_bwd_staged_kernel<N, false><<<grid, LN_WARPS * 32, smem_used, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, \
+                                                                                  dbeta, nullptr, rows, cols, rpw);         \
     } while (0)
         if (cols <= 256) MGB_LNB_STAGED(1);
         else if (cols <= 512) MGB_LNB_STAGED(2);
@@ -797,8 +813,21 @@ extern "C" int mgb_layernorm_bwd(const void* dy, const void* x, const float* gam
     else ln_bwd_kernel<8><<<grid, LN_WARPS * 32, smem, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, dbeta, rows, cols);
     count_launch(1);
     MGB_CHECK_LAUNCH();
+    if (dres_colsum) return mgb_colsum_bf16(dres, cols, rows, cols, dres_colsum, (mgb_stream_t)s);   // unfused fallback
     return kOk;
 }
+
+extern "C" int mgb_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean,
+                                 const float* rstd, const void* dres, void* dx, float* dgamma, float* dbeta,
+                                 int64_t rows, int32_t cols, mgb_stream_t s_) {
+    return layernorm_bwd_impl(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, nullptr, rows, cols, (cudaStream_t)s_);
+}
+extern "C" int mgb_layernorm_bwd_colsum(const void* dy, const void* x, const float* gamma, const float* mean,
+                                        const float* rstd, const void* dres, void* dx, float* dgamma, float* dbeta,
+                                        float* dres_colsum, int64_t rows, int32_t cols, mgb_stream_t s_) {
+    return layernorm_bwd_impl(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, dres_colsum, rows, cols, (cudaStream_t)s_);
+}
+
 
 extern "C" int mgb_embedding_fwd(const int64_t* idx, const void* wte, const void* wpe, void* out, int64_t B,
                                  int64_t T, int32_t C, int64_t vocab, int32_t* err_flag, mgb_stream_t s_) {

@@ -707,20 +707,23 @@ class GPT(nn.Module):
                 ops.linear_wgrad(ws.dz, ws.fc_pre[l], G(f"{l}.fc2_w"))
                 ops.linear_dgrad(ws.dz, W(f"{l}.fc2_w"), ws.dfc)
             else:
-                ops.colsum(dmlp, G(f"{l}.fc2_b"))
+                if pr > 0:     # (without dropout the bias gradient comes out of the LayerNorm backward below, which reads dx anyway)
+                    ops.colsum(dmlp, G(f"{l}.fc2_b"))
                 ops.linear_wgrad(dmlp, ws.fc_act[l], G(f"{l}.fc2_w"))
                 ops.linear_dgrad(dmlp, W(f"{l}.fc2_w"), ws.dfc, gate=ws.fc_pre[l], gate_kind=ops.GATE_MUL)
             ops.colsum(ws.dfc, G(f"{l}.fc_b"))
             ops.linear_wgrad(ws.dfc, ws.ln2[l], G(f"{l}.fc_w"))
             ops.linear_dgrad(ws.dfc, W(f"{l}.fc_w"), ws.dln)
-            ops.layernorm_bwd(ws.dln, ws.xmid[l], P(f"{l}.ln2_w"), s[2], s[3], ws.dx_b, G(f"{l}.ln2_w"), G(f"{l}.ln2_b"), dres=dx)
+            ops.layernorm_bwd(ws.dln, ws.xmid[l], P(f"{l}.ln2_w"), s[2], s[3], ws.dx_b, G(f"{l}.ln2_w"), G(f"{l}.ln2_b"), dres=dx,
+                              dres_colsum=G(f"{l}.fc2_b") if (pr == 0 and not ref) else None)
             dxm = ws.dx_b
             a_in = ws.att_o[l] if ref else ws.att[l]
             dproj = dxm
             if pr > 0:
                 ops.dropout(dxm, None, ws.dtmp, pr, seed, 4 * l + 1)
                 dproj = ws.dtmp
-            ops.colsum(dproj, G(f"{l}.proj_b"))
+            if pr > 0:         # (else: fused into the ln_1 backward below, whose dres is this tensor)
+                ops.colsum(dproj, G(f"{l}.proj_b"))
             ops.linear_wgrad(dproj, a_in, G(f"{l}.proj_w"))
             ops.linear_dgrad(dproj, W(f"{l}.proj_w"), ws.datt)
             datt = ws.datt
@@ -737,7 +740,8 @@ class GPT(nn.Module):
             ops.colsum(ws.dqkv, G(f"{l}.qkv_b"))
             ops.linear_wgrad(ws.dqkv, ws.ln1[l], G(f"{l}.qkv_w"))
             ops.linear_dgrad(ws.dqkv, W(f"{l}.qkv_w"), ws.dln)
-            ops.layernorm_bwd(ws.dln, ws.x[l], P(f"{l}.ln1_w"), s[0], s[1], ws.dx_a, G(f"{l}.ln1_w"), G(f"{l}.ln1_b"), dres=dxm)
+            ops.layernorm_bwd(ws.dln, ws.x[l], P(f"{l}.ln1_w"), s[0], s[1], ws.dx_a, G(f"{l}.ln1_w"), G(f"{l}.ln1_b"), dres=dxm,
+                              dres_colsum=G(f"{l}.proj_b") if pr == 0 else None)
             dx = ws.dx_a
             if self._layer_done_hook is not None:
                 self._layer_done_hook(l + 1)

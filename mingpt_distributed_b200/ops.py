@@ -112,10 +112,16 @@ def layernorm_fwd(x, gamma, beta, y, mean, rstd, eps=1e-5):
     return y
 
 
-def layernorm_bwd(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, dres=None):
-    _chk_cuda(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, dres)
+def layernorm_bwd(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, dres=None, dres_colsum=None):
+    """dres_colsum (fp32 [cols], accumulated): column sums of dres, i.e. the bias gradient of the linear layer whose
+    output gradient dres is, taken from the read this kernel makes anyway."""
+    _chk_cuda(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, dres, dres_colsum)
     rows, cols = x.shape
-    check(_lib.lib().mgb_layernorm_bwd(_p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), _p(dres), _p(dx), _p(dgamma), _p(dbeta), rows, cols, _stream()), "layernorm_bwd")
+    if dres_colsum is not None:
+        check(_lib.lib().mgb_layernorm_bwd_colsum(_p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), _p(dres), _p(dx), _p(dgamma),
+                                                  _p(dbeta), _p(dres_colsum), rows, cols, _stream()), "layernorm_bwd_colsum")
+    else:
+        check(_lib.lib().mgb_layernorm_bwd(_p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), _p(dres), _p(dx), _p(dgamma), _p(dbeta), rows, cols, _stream()), "layernorm_bwd")
     return dx
 
 

@@ -52,6 +52,16 @@ def test_layernorm_fwd_bwd(rows, cols):
     torch.cuda.synchronize()
     _close(f"ln_dgamma_acc_{rows}x{cols}", dg, 2 * gf.grad, 1e-3)
     _close(f"ln_dx_alias_{rows}x{cols}", dres, dx, 1e-6)
+    # fused column sum of dres (the bias gradient of the layer above): accumulates, leaves everything else unchanged
+    dres2 = torch.randn(rows, cols, device="cuda", generator=g).bfloat16()
+    dx2 = torch.empty_like(x); dx3 = torch.empty_like(x)
+    dg2 = torch.zeros(cols, device="cuda"); db2 = torch.zeros(cols, device="cuda"); cs = torch.ones(cols, device="cuda")
+    ops.layernorm_bwd(dy, x, gamma, mean, rstd, dx2, dg2, db2, dres=dres2, dres_colsum=cs)
+    ops.layernorm_bwd(dy, x, gamma, mean, rstd, dx3, torch.zeros_like(dg2), torch.zeros_like(db2), dres=dres2)
+    torch.cuda.synchronize()
+    _close(f"ln_dres_colsum_{rows}x{cols}", cs, 1 + dres2.float().sum(0), 1e-3)
+    assert torch.equal(dx2, dx3)
+    _close(f"ln_dgamma_colsum_{rows}x{cols}", dg2, gf.grad, 1e-3)
 
 
 def test_layernorm_custom_op_autograd():

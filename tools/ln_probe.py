@@ -31,6 +31,9 @@ for cold in (True, False):
         t = bench(lambda: ops.layernorm_bwd(dy, x, g, mean, rstd, y, dg, db, dres=dres), cold=cold)
         print(f"ln bwd {'registers' if opt else 'staged   '}      [{tag}] {t:7.1f} us   {4 * M * C * 2 / t / 1e6:6.2f} TB/s")
     _lib.set_option("ln_unstaged", 0)
+    cs = torch.zeros(C, device=dev)
+    t = bench(lambda: ops.layernorm_bwd(dy, x, g, mean, rstd, y, dg, db, dres=dres, dres_colsum=cs), cold=cold)
+    print(f"ln bwd staged + colsum [{tag}] {t:7.1f} us   (separate colsum [32768x768]: {bench(lambda: ops.colsum(dres, cs), cold=cold):5.1f} us)")
 B, T, H, d = 32, 1024, 12, 64
 qkv = bf(B, T, 3 * C); dout = bf(B, T, C)
 out = torch.empty(B, T, C, dtype=torch.bfloat16, device=dev); lse = torch.empty(B, H, T, device=dev)
