@@ -95,6 +95,8 @@ typedef struct mgb_gemm_args {
                           MGB_GEMM_ENGINE_SINGLE (128-row tiles, one CTA) or MGB_GEMM_ENGINE_PAIR (256-row tiles,
                           two CTAs, tcgen05 cta_group::2). Both engines compute the same result. */
     float alpha;       /* 0 is read as 1 */
+    float* colsum;     /* optional, bf16 D only: colsum[n] += sum_m D[m,n] (fp32, atomic) -- the bias gradient of the
+                          layer below when D is an output gradient; taken from the accumulators before rounding */
 } mgb_gemm_args;
 int mgb_gemm_bf16(const mgb_gemm_args* args, mgb_stream_t stream);
 

@@ -34,6 +34,7 @@ class GemmArgs(C.Structure):
         ("split_k", C.c_int32),
         ("block_n", C.c_int32),
         ("alpha", C.c_float),
+        ("colsum", C.c_void_p),
     ]
 
 

@@ -101,6 +101,11 @@ __device__ __forceinline__ void epilogue_direct(const Params& p, float (&v)[32],
     }
 }
 
+// COLSUM: the epilogue also reduces every output tile over its rows (a 31-shuffle transpose-reduce per 32x32 chunk,
+// shared-memory atomics per CTA, one global atomic per column and tile) into p.colsum: the bias gradient that
+// goes with an output-gradient GEMM, without another pass over D. A separate instantiation, so the register
+// allocation of the plain kernel is untouched.
+template <bool COLSUM>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_d, const __grid_constant__ CUtensorMap tmap_p,
@@ -118,6 +123,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     uint64_t* tmem_empty = tmem_full + 2;            // [2]           (leader's copy is the live one)
     uint64_t* aux_bar = tmem_empty + 2;              // [kNumBoxes]   residual / gate tile landed in box i
     uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(aux_bar + kNumBoxes);
+    float* cs_smem = reinterpret_cast<float*>(boxes + kNumBoxes * kBoxBytes + 512);   // [256] (COLSUM only)
+    if (COLSUM) {
+        for (int c = threadIdx.x; c < 256; c += blockDim.x) cs_smem[c] = 0.f;
+    }
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);   // provably warp-uniform
     const int lane = threadIdx.x & 31;
@@ -377,6 +386,27 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         }
                         add_bf16_inplace(v, rw);
                     }
+                    if (COLSUM) {
+                        // lane l ends up with the sum over this warp's 32 rows of column ccol + l
+                        float t16[16], t8[8], t4[4], t2[2];
+                        const bool b16 = lane & 16, b8 = lane & 8, b4 = lane & 4, b2 = lane & 2, b1 = lane & 1;
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const float lo = row_ok ? v[i] : 0.f, hi = row_ok ? v[i + 16] : 0.f;
+                            t16[i] = (b16 ? hi : lo) + __shfl_xor_sync(0xffffffffu, b16 ? lo : hi, 16);
+                        }
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            t8[i] = (b8 ? t16[i + 8] : t16[i]) + __shfl_xor_sync(0xffffffffu, b8 ? t16[i] : t16[i + 8], 8);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            t4[i] = (b4 ? t8[i + 4] : t8[i]) + __shfl_xor_sync(0xffffffffu, b4 ? t8[i] : t8[i + 4], 4);
+#pragma unroll
+                        for (int i = 0; i < 2; ++i)
+                            t2[i] = (b2 ? t4[i + 2] : t4[i]) + __shfl_xor_sync(0xffffffffu, b2 ? t4[i] : t4[i + 2], 2);
+                        const float tot = (b1 ? t2[1] : t2[0]) + __shfl_xor_sync(0xffffffffu, b1 ? t2[0] : t2[1], 1);
+                        atomicAdd(&cs_smem[ccol + lane], tot);
+                    }
                     if (p.d_f32) {
 #pragma unroll
                         for (int q = 0; q < 8; ++q)
@@ -410,6 +440,14 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive_cluster(&tmem_empty[acc], 0);
+            }
+            if (COLSUM) {      // all eight epilogue warps have added their rows: one global atomic per column of the tile
+                named_bar_sync(3, kEpiWarps * 32);
+                const int c = (int)threadIdx.x - 128;
+                const float tot = cs_smem[c];
+                cs_smem[c] = 0.f;
+                if (c < block_n && n0 + c < p.N) atomicAdd(p.colsum + n0 + c, tot);
+                named_bar_sync(3, kEpiWarps * 32);
             }
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
@@ -457,7 +495,8 @@ static bool tma_ok(const void* base, int64_t ld, int elem_bytes) {
 int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t stream) {
     static std::once_flag once;
     std::call_once(once, [] {
-        cudaFuncSetAttribute(gemm_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+        cudaFuncSetAttribute(gemm_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+        cudaFuncSetAttribute(gemm_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     });
     const int num_clusters = num_sms / 2;
     int bn = a->block_n;
@@ -505,7 +544,10 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
 
     const int nb = bn / 2;
     const uint32_t stage_bytes = BLOCK_M * BLOCK_K * 2 + (uint32_t)nb * BLOCK_K * 2;
-    const int fixed = kNumBoxes * kBoxBytes + 1024 + 512;
+    // column sums ride along only on the staged bf16 path; otherwise mgb_gemm_bf16 adds them with a separate pass
+    const bool fused_colsum = a->colsum && p.tma_store && !a->d_f32;
+    p.colsum = fused_colsum ? a->colsum : nullptr;
+    const int fixed = kNumBoxes * kBoxBytes + 1024 + 512 + (fused_colsum ? 1024 : 0);
     int stages = (kSmemLimit - fixed) / (int)stage_bytes;
     if (stages > kMaxStages) stages = kMaxStages;
     p.num_stages = stages;
@@ -535,10 +577,11 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
     }
     const int64_t units = (int64_t)tiles * p.split_k;
     const int clusters = (int)(units < num_clusters ? units : num_clusters);
-    gemm_pair_kernel<<<2 * clusters, kThreads, smem_bytes, stream>>>(ta, tb, td, tp, tx, p);
+    if (fused_colsum) gemm_pair_kernel<true><<<2 * clusters, kThreads, smem_bytes, stream>>>(ta, tb, td, tp, tx, p);
+    else gemm_pair_kernel<false><<<2 * clusters, kThreads, smem_bytes, stream>>>(ta, tb, td, tp, tx, p);
     count_launch(1);
     MGB_CHECK_LAUNCH();
-    return kOk;
+    return fused_colsum ? kFusedColsum : kOk;
 }
 
 }  // namespace gemm

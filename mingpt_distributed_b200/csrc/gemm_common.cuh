@@ -49,6 +49,7 @@ struct Params {
     int64_t ldg;
     int32_t gate_kind;
     float alpha;
+    float* colsum;           // CTA-pair kernel, COLSUM instantiation: column sums of D (fp32, atomic)
 };
 
 __device__ __forceinline__ float apply_act(float v, int act) {
@@ -175,6 +176,7 @@ inline int make_map_2d(CUtensorMap* out, const void* base, int64_t inner, int64_
 }
 
 // CTA-pair kernel launcher (gemm2_sm100.cu). Fills the remaining Params fields itself.
+constexpr int kFusedColsum = 1;   // launch_gemm_pair: launched, and the column sums were part of the kernel
 int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t stream);
 
 }  // namespace gemm

@@ -323,6 +323,8 @@ static int pick_block_n(int64_t M, int64_t N, int b_mn, int num_sms) {
 using namespace mgb;
 using namespace mgb::gemm;
 
+extern "C" int mgb_colsum_bf16(const void* x, int64_t ld, int64_t rows, int64_t cols, float* out, mgb_stream_t s);
+
 extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
     if (!a || !a->a || !a->b || !a->d) { set_last_error("gemm: null pointer"); return kErrBadShape; }
@@ -379,7 +381,13 @@ extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
     a_local.block_n = a->block_n & ~(MGB_GEMM_ENGINE_SINGLE | MGB_GEMM_ENGINE_PAIR);
     const bool want_pair = engine == MGB_GEMM_ENGINE_PAIR ||
                            (engine == 0 && a->m > BLOCK_M && !g_opt_gemm_single.load(std::memory_order_relaxed));
-    if (want_pair) return launch_gemm_pair(&a_local, p, num_sms, stream);
+    if (a->colsum && a->d_f32) { set_last_error("gemm: colsum needs a bf16 D"); return kErrUnsupported; }
+    if (want_pair) {
+        const int rc = launch_gemm_pair(&a_local, p, num_sms, stream);
+        if (rc == kFusedColsum) return kOk;
+        if (rc == kOk && a->colsum) return mgb_colsum_bf16(a->d, a->ldd, a->m, a->n, a->colsum, stream_);
+        return rc;
+    }
 
     int bn = a_local.block_n;
     if (bn == 0) bn = (a->accumulate && a->n > 128) ? 256 : pick_block_n(a->m, a->n, p.b_mn, num_sms);
@@ -423,5 +431,6 @@ extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
     gemm_kernel<<<grid, kThreads, SMEM_BYTES, stream>>>(ta, tb, p);
     count_launch(1);
     MGB_CHECK_LAUNCH();
+    if (a->colsum) return mgb_colsum_bf16(a->d, a->ldd, a->m, a->n, a->colsum, stream_);   // no fused variant on this engine
     return kOk;
 }

@@ -710,8 +710,10 @@ class GPT(nn.Module):
                 if pr > 0:     # (without dropout the bias gradient comes out of the LayerNorm backward below, which reads dx anyway)
                     ops.colsum(dmlp, G(f"{l}.fc2_b"))
                 ops.linear_wgrad(dmlp, ws.fc_act[l], G(f"{l}.fc2_w"))
-                ops.linear_dgrad(dmlp, W(f"{l}.fc2_w"), ws.dfc, gate=ws.fc_pre[l], gate_kind=ops.GATE_MUL)
-            ops.colsum(ws.dfc, G(f"{l}.fc_b"))
+                # d(c_fc output) and, in the same epilogue, its column sums = the c_fc bias gradient
+                ops.linear_dgrad(dmlp, W(f"{l}.fc2_w"), ws.dfc, gate=ws.fc_pre[l], gate_kind=ops.GATE_MUL, colsum=G(f"{l}.fc_b"))
+            if ref:
+                ops.colsum(ws.dfc, G(f"{l}.fc_b"))
             ops.linear_wgrad(ws.dfc, ws.ln2[l], G(f"{l}.fc_w"))
             ops.linear_dgrad(ws.dfc, W(f"{l}.fc_w"), ws.dln)
             ops.layernorm_bwd(ws.dln, ws.xmid[l], P(f"{l}.ln2_w"), s[2], s[3], ws.dx_b, G(f"{l}.ln2_w"), G(f"{l}.ln2_b"), dres=dx,

@@ -52,9 +52,10 @@ def _chk2d(t: torch.Tensor, dtype, name: str):
 def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
          bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None, act: int = 0,
          preact: Optional[torch.Tensor] = None, gate: Optional[torch.Tensor] = None, gate_kind: int = 0,
-         accumulate: bool = False, split_k: int = 0, block_n: int = 0, alpha: float = 1.0) -> torch.Tensor:
+         accumulate: bool = False, split_k: int = 0, block_n: int = 0, alpha: float = 1.0,
+         colsum: Optional[torch.Tensor] = None) -> torch.Tensor:
     """out[M,N] = epilogue(alpha * A B^T).  a is [M,K] (or [K,M] if a_mn), b is [N,K] (or [K,N] if b_mn)."""
-    _chk_cuda(a, b, out, bias, residual, preact, gate)
+    _chk_cuda(a, b, out, bias, residual, preact, gate, colsum)
     _chk2d(a, torch.bfloat16, "gemm a")
     _chk2d(b, torch.bfloat16, "gemm b")
     if out.dim() != 2 or out.stride(1) != 1 or out.dtype not in (torch.bfloat16, torch.float32):
@@ -83,6 +84,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = Fa
         _chk2d(gate, torch.bfloat16, "gemm gate")
         args.gate, args.ldg, args.gate_kind = gate.data_ptr(), gate.stride(0), gate_kind
     args.split_k, args.block_n, args.alpha = split_k, block_n, alpha
+    if colsum is not None:
+        if colsum.dtype != torch.float32 or colsum.numel() != N or not colsum.is_contiguous():
+            raise RuntimeError("gemm colsum: expected contiguous fp32 [N]")
+        args.colsum = colsum.data_ptr()
     check(_lib.lib().mgb_gemm_bf16(C.byref(args), _stream()), "gemm")
     return out
 
@@ -92,7 +97,7 @@ def linear_fwd(x, w, out, bias=None, act=0, residual=None, preact=None, **kw):
     return gemm(x, w, out, bias=bias, act=act, residual=residual, preact=preact, **kw)
 
 
-def linear_dgrad(dy, w, out, gate=None, gate_kind=0, residual=None, **kw):
+def linear_dgrad(dy, w, out, gate=None, gate_kind=0, residual=None, **kw):   # kw: colsum=fp32 [K] += column sums of out
     """dX = dY W: dY [M,N], W [N,K] read as the MN-major B operand"""
     return gemm(dy, w, out, b_mn=True, gate=gate, gate_kind=gate_kind, residual=residual, **kw)
 

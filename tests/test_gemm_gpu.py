@@ -120,6 +120,28 @@ def test_gemm_forward_stores_activation_derivative(engine, act, N):
         ops.gemm(a, b, out, bias=bias, act=act | ops.ACT_STORE_GRAD)
 
 
+@pytest.mark.parametrize("engine", [0, 1024, 2048])
+@pytest.mark.parametrize("N", [768, 200, 65])
+def test_gemm_column_sums_of_the_output(engine, N):
+    """colsum[n] += sum_m D[m,n]: the bias gradient that goes with an output-gradient GEMM (fused into the CTA-pair
+    kernel's epilogue when D leaves through TMA, a separate pass otherwise)"""
+    from mingpt_distributed_b200 import ops
+    M, K = 1000, 256          # ragged last row tile
+    a, b, acc = _mk(M, N, K, False, False, seed=8)
+    gate = torch.randn(M, N, device="cuda").bfloat16()
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    cs = torch.ones(N, device="cuda")
+    ops.gemm(a, b, out, gate=gate, gate_kind=ops.GATE_MUL, colsum=cs, block_n=engine)
+    ops.gemm(a, b, out, gate=gate, gate_kind=ops.GATE_MUL, colsum=cs, block_n=engine)      # accumulates
+    torch.cuda.synchronize()
+    want = acc * gate.float()
+    _check(f"gemm_colsum_out_N{N}_e{engine}", out, want, 2e-2)
+    got, ref = cs - 1, 2 * want.sum(0)
+    assert (got - ref).abs().max().item() <= 2e-2 * ref.abs().max().item() + 1e-3, (got - ref).abs().max().item()
+    with pytest.raises(RuntimeError):
+        ops.gemm(a, b, torch.empty(M, N, device="cuda"), colsum=cs)          # fp32 D
+
+
 @pytest.mark.parametrize("kind", [1, 2])
 def test_gemm_dgrad_gate_epilogue(kind):
     """dX = (dY W) * gelu'(pre): the fused backward of c_fc's activation"""
