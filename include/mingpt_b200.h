@@ -144,6 +144,12 @@ int mgb_attention_fwd(const void* qkv, void* out, float* lse, int32_t B, int32_t
 int mgb_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
                       float* dq_accum, void* dqkv, int32_t B, int32_t T, int32_t H, int32_t d, int32_t mask_mode,
                       float scale, mgb_stream_t stream);
+/* Same, and additionally dqkv_colsum[0 .. 3*H*d) += column sums of dqkv (fp32, atomic) = the bias gradient of the
+ * qkv projection (torch/nn/functional.py:6478 in_proj_bias), produced where the values are already in registers
+ * (head size 64: the main kernel's per-key-block epilogue and the dQ conversion) instead of by a pass over dqkv. */
+int mgb_attention_bwd_colsum(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                             float* dq_accum, void* dqkv, float* dqkv_colsum, int32_t B, int32_t T, int32_t H,
+                             int32_t d, int32_t mask_mode, float scale, mgb_stream_t stream);
 
 /* Dropout (the reference trains with p = 0.1 at four sites and never calls eval(): mingpt/model.py:49-51,140,
  * 150,183,215). Masks are counter based (Philox4x32-10 over (seed, site, element)) and never stored: the

@@ -22,7 +22,7 @@ extern std::atomic<int> g_opt_attn_mma;
 namespace attn_tc {   // tcgen05 / TMEM kernels for head size 64 (attention_sm100.cu)
 int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream);
 int launch_bwd_main(const void* qkv, const void* dout, const float* lse, const float* delta, float* dq_accum,
-                    void* dqkv, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream);
+                    void* dqkv, float* dqkv_colsum, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream);
 }
 namespace attn {
 
@@ -487,6 +487,34 @@ attn_dq_convert_kernel(const float* __restrict__ dq_accum, __nv_bfloat16* __rest
                make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(c.x, c.y), pack_bf16x2(c.z, c.w)));
     }
 }
+// Same, and colsum[0 .. HD) += column sums of dQ (the Q third of the qkv bias gradient). The block is
+// (HD/8) x rows_per_block threads: a thread keeps its 8 columns for the whole grid-stride loop, so the sums
+// stay in registers until one shared-memory and one global atomic per column and block.
+__global__ void __launch_bounds__(256)
+attn_dq_convert_colsum_kernel(const float* __restrict__ dq_accum, __nv_bfloat16* __restrict__ dqkv, int64_t BT, int HD,
+                              float* __restrict__ colsum) {
+    extern __shared__ float cvt_smem[];              // [HD]
+    const int nch = HD >> 3;
+    const int rpb = blockDim.x / nch;                // rows per block iteration
+    const int ch = threadIdx.x % nch, r = threadIdx.x / nch;
+    for (int c = threadIdx.x; c < HD; c += blockDim.x) cvt_smem[c] = 0.f;
+    __syncthreads();
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (r < rpb) {
+        for (int64_t row = (int64_t)blockIdx.x * rpb + r; row < BT; row += (int64_t)gridDim.x * rpb) {
+            const float4 a = *reinterpret_cast<const float4*>(dq_accum + row * HD + ch * 8);
+            const float4 c = *reinterpret_cast<const float4*>(dq_accum + row * HD + ch * 8 + 4);
+            acc[0] += a.x; acc[1] += a.y; acc[2] += a.z; acc[3] += a.w;
+            acc[4] += c.x; acc[5] += c.y; acc[6] += c.z; acc[7] += c.w;
+            stg128(dqkv + row * 3 * HD + ch * 8,
+                   make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(c.x, c.y), pack_bf16x2(c.z, c.w)));
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) atomicAdd(&cvt_smem[ch * 8 + e], acc[e]);
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < HD; c += blockDim.x) atomicAdd(colsum + c, cvt_smem[c]);
+}
 
 template <int D>
 static int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int mask_mode, float scale,
@@ -502,7 +530,7 @@ static int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int 
 template <int D>
 static int launch_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
                       float* dq_accum, void* dqkv, int B, int T, int H, int mask_mode, float scale, cudaStream_t s,
-                      float p_drop = 0.f, const uint64_t* seed_dev = nullptr, uint32_t site = 0) {
+                      float p_drop = 0.f, const uint64_t* seed_dev = nullptr, uint32_t site = 0, float* dqkv_colsum = nullptr) {
     const uint32_t thresh = p_drop > 0.f ? dropout_thresh16(p_drop) : 0u;
     const float inv_keep = thresh ? 65536.0f / (65536.0f - (float)thresh) : 1.0f;
     const int64_t rows = (int64_t)B * T * H * (D / 8);
@@ -515,8 +543,13 @@ static int launch_bwd(const void* qkv, const void* out, const void* dout, const 
         cudaFuncSetAttribute(attn_bwd_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         attr_set = true;
     }
+    // column sums of dqkv (the qkv bias gradient): fused on the tcgen05 path (K / V thirds in the main kernel's item
+    // epilogue, Q third in the convert kernel), a separate pass otherwise
+    bool fused_colsum = false;
     if (D == 64 && !thresh && !g_opt_attn_mma.load(std::memory_order_relaxed)) {
-        const int rc = attn_tc::launch_bwd_main(qkv, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
+        fused_colsum = dqkv_colsum != nullptr && (H * D / 8) <= 256;
+        const int rc = attn_tc::launch_bwd_main(qkv, dout, lse, delta, dq_accum, dqkv, fused_colsum ? dqkv_colsum : nullptr, B, T,
+                                                H, mask_mode, scale, s);
         if (rc) return rc;
     } else {
         dim3 grid((T + BN - 1) / BN, B * H);
@@ -524,11 +557,21 @@ static int launch_bwd(const void* qkv, const void* out, const void* dout, const 
                                                        dq_accum, (__nv_bfloat16*)dqkv, T, H, mask_mode, scale, scale * LOG2E,
                                                        thresh, inv_keep, seed_dev, site);
     }
+    if (fused_colsum) {
+        const int nch = H * D / 8;
+        const int threads = (256 / nch) * nch;
+        const int64_t rows = (int64_t)B * T;
+        int64_t g2 = (rows + (threads / nch) - 1) / (threads / nch);
+        if (g2 > num_sms() * 8) g2 = num_sms() * 8;
+        attn_dq_convert_colsum_kernel<<<(int)g2, threads, H * D * sizeof(float), s>>>(dq_accum, (__nv_bfloat16*)dqkv, rows,
+                                                                                  H * D, dqkv_colsum);
+        return 0;
+    }
     const int64_t chunks = (int64_t)B * T * (H * D / 8);
     int g2 = (int)((chunks + 255) / 256);
     if (g2 > num_sms() * 16) g2 = num_sms() * 16;
     attn_dq_convert_kernel<<<g2, 256, 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, (int64_t)B * T, (int64_t)H * D);
-    return 0;
+    return dqkv_colsum ? 1 : 0;      // 1: the caller still owes the column sums
 }
 
 }  // namespace attn
@@ -563,9 +606,11 @@ extern "C" int mgb_attention_fwd(const void* qkv, void* out, float* lse, int32_t
     return kOk;
 }
 
-extern "C" int mgb_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
-                                 float* dq_accum, void* dqkv, int32_t B, int32_t T, int32_t H, int32_t d,
-                                 int32_t mask_mode, float scale, mgb_stream_t s_) {
+extern "C" int mgb_colsum_bf16(const void* x, int64_t ld, int64_t rows, int64_t cols, float* out, mgb_stream_t s);
+
+static int attention_bwd_impl(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                              float* dq_accum, void* dqkv, float* dqkv_colsum, int32_t B, int32_t T, int32_t H, int32_t d,
+                              int32_t mask_mode, float scale, mgb_stream_t s_) {
     cudaStream_t s = (cudaStream_t)s_;
     int rc = check_attn_shape("bwd", B, T, H, d, mask_mode);
     if (rc) return rc;
@@ -574,12 +619,27 @@ extern "C" int mgb_attention_bwd(const void* qkv, const void* out, const void* d
         set_last_error("attention: pointers must be 16-byte aligned"); return kErrBadAlign;
     }
     cudaMemsetAsync(dq_accum, 0, (size_t)B * T * H * d * sizeof(float), s);
-    if (d == 64) attn::launch_bwd<64>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
-    else if (d == 32) attn::launch_bwd<32>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
-    else attn::launch_bwd<16>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
+    int owed;
+    if (d == 64) owed = attn::launch_bwd<64>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s, 0.f, nullptr, 0, dqkv_colsum);
+    else if (d == 32) owed = attn::launch_bwd<32>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s, 0.f, nullptr, 0, dqkv_colsum);
+    else owed = attn::launch_bwd<16>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s, 0.f, nullptr, 0, dqkv_colsum);
+    if (owed < 0) return owed;
     count_launch(3);
     MGB_CHECK_LAUNCH();
+    if (owed == 1) return mgb_colsum_bf16(dqkv, (int64_t)3 * H * d, (int64_t)B * T, (int64_t)3 * H * d, dqkv_colsum, s_);
     return kOk;
+}
+
+extern "C" int mgb_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                                 float* dq_accum, void* dqkv, int32_t B, int32_t T, int32_t H, int32_t d,
+                                 int32_t mask_mode, float scale, mgb_stream_t s_) {
+    return attention_bwd_impl(qkv, out, dout, lse, delta, dq_accum, dqkv, nullptr, B, T, H, d, mask_mode, scale, s_);
+}
+extern "C" int mgb_attention_bwd_colsum(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                                        float* dq_accum, void* dqkv, float* dqkv_colsum, int32_t B, int32_t T, int32_t H,
+                                        int32_t d, int32_t mask_mode, float scale, mgb_stream_t s_) {
+    if (!dqkv_colsum) { set_last_error("attention_bwd_colsum: null colsum"); return kErrBadShape; }
+    return attention_bwd_impl(qkv, out, dout, lse, delta, dq_accum, dqkv, dqkv_colsum, B, T, H, d, mask_mode, scale, s_);
 }
 
 // =====================================================================================

@@ -468,7 +468,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_constant__ CUtensorMap tmap_q,
                    const __grid_constant__ CUtensorMap tmap_do, const __grid_constant__ CUtensorMap tmap_dq,
                    const float* __restrict__ lse, const float* __restrict__ delta,
-                   __nv_bfloat16* __restrict__ dqkv, int B, int T, int H, int mask_mode, float scale, float scale_log2) {
+                   __nv_bfloat16* __restrict__ dqkv, float* __restrict__ kv_colsum, int B, int T, int H, int mask_mode,
+                   float scale, float scale_log2) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = smem_raw;
     if (smem_u32(smem) & 1023u) __trap();                      // SWIZZLE_128B tiles need 1024-byte alignment
@@ -827,6 +828,38 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_free);            // the next item may start accumulating
+            if (kv_colsum) {
+                // bias gradient of the qkv projection, K and V thirds: column sums over this warp's 32 key rows by a
+                // transpose-reduce (rows of keys >= T hold exact zeros), one atomic per column and warp
+                float tk[8], tv[8];
+                const bool b16 = lane & 16, b8 = lane & 8, b4 = lane & 4, b2 = lane & 2;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float klo = __uint_as_float(vk[i]), khi = __uint_as_float(vk[i + 8]);
+                    const float vlo = __uint_as_float(vv[i]), vhi = __uint_as_float(vv[i + 8]);
+                    tk[i] = (b16 ? khi : klo) + __shfl_xor_sync(0xffffffffu, b16 ? klo : khi, 16);
+                    tv[i] = (b16 ? vhi : vlo) + __shfl_xor_sync(0xffffffffu, b16 ? vlo : vhi, 16);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    tk[i] = (b8 ? tk[i + 4] : tk[i]) + __shfl_xor_sync(0xffffffffu, b8 ? tk[i] : tk[i + 4], 8);
+                    tv[i] = (b8 ? tv[i + 4] : tv[i]) + __shfl_xor_sync(0xffffffffu, b8 ? tv[i] : tv[i + 4], 8);
+                }
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    tk[i] = (b4 ? tk[i + 2] : tk[i]) + __shfl_xor_sync(0xffffffffu, b4 ? tk[i] : tk[i + 2], 4);
+                    tv[i] = (b4 ? tv[i + 2] : tv[i]) + __shfl_xor_sync(0xffffffffu, b4 ? tv[i] : tv[i + 2], 4);
+                }
+                float sk = (b2 ? tk[1] : tk[0]) + __shfl_xor_sync(0xffffffffu, b2 ? tk[0] : tk[1], 2);
+                float sv = (b2 ? tv[1] : tv[0]) + __shfl_xor_sync(0xffffffffu, b2 ? tv[0] : tv[1], 2);
+                sk += __shfl_xor_sync(0xffffffffu, sk, 1);       // lanes l and l^1 hold the two halves of the rows
+                sv += __shfl_xor_sync(0xffffffffu, sv, 1);
+                if ((lane & 1) == 0) {
+                    const int col = it.h * D + wg * CPT + (lane >> 1);      // bits 4..1 of the lane picked the column
+                    atomicAdd(kv_colsum + C + col, sk);
+                    atomicAdd(kv_colsum + 2 * C + col, sv);
+                }
+            }
             if (key < T) {
                 __nv_bfloat16* krow = dqkv + ((int64_t)(it.b * T + key)) * (3 * C) + C + (int64_t)it.h * D + wg * CPT;
 #pragma unroll
@@ -858,7 +891,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
 
 // main backward kernel only: delta must be precomputed and dq_accum zeroed by the caller (attention.cu)
 int launch_bwd_main(const void* qkv, const void* dout, const float* lse, const float* delta, float* dq_accum,
-                    void* dqkv, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream) {
+                    void* dqkv, float* dqkv_colsum, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream) {
     static std::once_flag once;
     std::call_once(once, [] {
         cudaFuncSetAttribute(attn_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
@@ -876,7 +909,7 @@ int launch_bwd_main(const void* qkv, const void* dout, const float* lse, const f
     const int nq = (T + BKV - 1) / BKV;
     const int nunits = (mask_mode == MGB_MASK_CAUSAL ? (nq + 1) / 2 : nq) * B * H;
     const int grid = nunits < num_sms() ? nunits : num_sms();
-    attn_bwd_tc_kernel<<<grid, kBwdThreads, BWD_SMEM, stream>>>(tkv, tq, td, tdq, lse, delta, (__nv_bfloat16*)dqkv, B, T, H,
+    attn_bwd_tc_kernel<<<grid, kBwdThreads, BWD_SMEM, stream>>>(tkv, tq, td, tdq, lse, delta, (__nv_bfloat16*)dqkv, dqkv_colsum, B, T, H,
                                                                 mask_mode, scale, scale * LOG2E);
     return kOk;
 }

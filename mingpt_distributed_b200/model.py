@@ -737,9 +737,10 @@ class GPT(nn.Module):
             if pa > 0:
                 ops.attention_bwd_dropout(ws.qkv[l], ws.att[l], datt, ws.lse[l], ws.delta, ws.dq_acc, ws.dqkv, B, T, H, d,
                                           mask, pa, seed, 4 * l)
-            else:
-                ops.attention_bwd(ws.qkv[l], ws.att[l], datt, ws.lse[l], ws.delta, ws.dq_acc, ws.dqkv, B, T, H, d, mask)
-            ops.colsum(ws.dqkv, G(f"{l}.qkv_b"))
+                ops.colsum(ws.dqkv, G(f"{l}.qkv_b"))
+            else:      # the qkv bias gradient (column sums of dqkv) comes out of the attention backward itself
+                ops.attention_bwd(ws.qkv[l], ws.att[l], datt, ws.lse[l], ws.delta, ws.dq_acc, ws.dqkv, B, T, H, d, mask,
+                                  dqkv_colsum=G(f"{l}.qkv_b"))
             ops.linear_wgrad(ws.dqkv, ws.ln1[l], G(f"{l}.qkv_w"))
             ops.linear_dgrad(ws.dqkv, W(f"{l}.qkv_w"), ws.dln)
             ops.layernorm_bwd(ws.dln, ws.x[l], P(f"{l}.ln1_w"), s[0], s[1], ws.dx_a, G(f"{l}.ln1_w"), G(f"{l}.ln1_b"), dres=dxm,

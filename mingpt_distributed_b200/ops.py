@@ -152,10 +152,15 @@ def attention_fwd(qkv, out, lse, B, T, H, d, mask_mode, scale=None):
     return out
 
 
-def attention_bwd(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, d, mask_mode, scale=None):
-    _chk_cuda(qkv, out, dout, lse, delta, dq_accum, dqkv)
+def attention_bwd(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, d, mask_mode, scale=None, dqkv_colsum=None):
+    """dqkv_colsum (fp32 [3*H*d], accumulated): column sums of dqkv, i.e. the qkv projection's bias gradient."""
+    _chk_cuda(qkv, out, dout, lse, delta, dq_accum, dqkv, dqkv_colsum)
     scale = 1.0 / math.sqrt(d) if scale is None else scale
-    check(_lib.lib().mgb_attention_bwd(_p(qkv), _p(out), _p(dout), _p(lse), _p(delta), _p(dq_accum), _p(dqkv), B, T, H, d, mask_mode, scale, _stream()), "attention_bwd")
+    if dqkv_colsum is not None:
+        check(_lib.lib().mgb_attention_bwd_colsum(_p(qkv), _p(out), _p(dout), _p(lse), _p(delta), _p(dq_accum), _p(dqkv),
+                                                  _p(dqkv_colsum), B, T, H, d, mask_mode, scale, _stream()), "attention_bwd_colsum")
+    else:
+        check(_lib.lib().mgb_attention_bwd(_p(qkv), _p(out), _p(dout), _p(lse), _p(delta), _p(dq_accum), _p(dqkv), B, T, H, d, mask_mode, scale, _stream()), "attention_bwd")
     return dqkv
 
 

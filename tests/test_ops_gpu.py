@@ -146,6 +146,13 @@ def test_attention_fwd_bwd(d, mode, B, T, H):
     torch.cuda.synchronize()
     assert torch.isfinite(dqkv.float()).all()
     _close("attn_dqkv_" + tag, dqkv, qf.grad, 3e-2)
+    # the same call with the qkv bias gradient (column sums of dqkv) produced on the way: accumulates, dqkv unchanged
+    dqkv2 = torch.full_like(qkv, float("nan")); cs = torch.ones(3 * C, device="cuda")
+    ops.attention_bwd(qkv, out, dout, lse, delta, dq_acc, dqkv2, B, T, H, d, mode, dqkv_colsum=cs)
+    torch.cuda.synchronize()
+    assert torch.equal(dqkv2, dqkv)
+    want_cs = qf.grad.reshape(B * T, 3 * C).sum(0)
+    assert (cs - 1 - want_cs).abs().max().item() <= 2e-2 * want_cs.abs().max().item() + 2e-2, tag
 
 
 def test_attention_gpt2_shape_property():
