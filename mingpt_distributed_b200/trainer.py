@@ -148,7 +148,7 @@ class GraphedTrainStep:
 
         def hook(group: int):
             span = buckets._by_trigger.get(group)
-            if span is None or not buckets.enabled or buckets.world == 1:
+            if span is None or not buckets.enabled:      # (world size 1 still cuts: its all-reduces are no-ops)
                 return
             end()
             segs.append(("allreduce", span))

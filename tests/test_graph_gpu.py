@@ -51,3 +51,25 @@ def test_forward_backward_equals_autograd_path():
     assert abs(l2.item() - loss.item()) < 1e-5
     for n, p in model.named_parameters():
         assert torch.allclose(p.grad, want[n], rtol=1e-2, atol=1e-6 * (1 + want[n].abs().max().item())), n
+
+
+def test_data_parallel_step_as_graph_segments_single_rank(tmp_path):
+    """GraphedTrainStep with a DataParallel model: CUDA-graph segments cut at the gradient buckets with the NCCL
+    all-reduces launched between them. One rank is enough to drive every part of it (the all-reduces are no-ops);
+    tools/ddp_check.py is the same check the 2- and 8-GPU runs use. Own process: it owns a process group."""
+    import json, os, socket, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    env = dict(os.environ, RANK="0", LOCAL_RANK="0", WORLD_SIZE="1", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "ddp_check.py")], env=env, capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    seg = next(l for l in lines if "graph_segments" in l)
+    chk = next(l for l in lines if "grad_rel_err_vs_global_batch" in l)
+    report("dp_graph_segments", **seg)
+    assert seg["graph_segments"] >= 3 and seg["graph_vs_eager_loss_dev"] < 2e-3 and seg["graph_vs_eager_param_rel"] < 1e-2
+    assert seg["graph_params_identical_across_ranks"] and chk["params_identical_after_step"]
+    assert chk["grad_rel_err_vs_global_batch"] < 1e-5
