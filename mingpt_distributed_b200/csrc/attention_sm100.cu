@@ -477,7 +477,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
     uint8_t* sQ = smem + 4 * TILE_BYTES;                       // slot s: Q at +s*2*SUB_BYTES, dO right behind it
     uint8_t* sdS = sQ + kSlots * 2 * SUB_BYTES;                // atom a: 128 key rows x 128 B (64 queries)
     uint8_t* sDQ = sdS + 4 * TILE_BYTES;                       // two boxes: 128 query rows x 32 fp32
-    float2* sLD = reinterpret_cast<float2*>(sDQ + 2 * TILE_BYTES);   // [2][128] (bias - lse*log2e, delta*scale)
+    float2* sLD = reinterpret_cast<float2*>(sDQ + 2 * TILE_BYTES);   // [16 warps][16] (bias - lse*log2e, delta*scale)
     uint64_t* bars = reinterpret_cast<uint64_t*>(sDQ + 2 * TILE_BYTES + 2 * 128 * 8);
     uint64_t* qdo_full = bars + 1;     // [4]
     uint64_t* qdo_empty = bars + 5;    // [4]
@@ -705,7 +705,6 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
         const int r = quarter * 32 + lane;               // key row inside the block == TMEM lane
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
         const uint32_t swz = (uint32_t)(r & 7);
-        const int etid = threadIdx.x;                    // 0 .. 32 * kEwWarps - 1
         uint32_t g = 0, w = 0;
         for (int q = 0;; ++q) {
             BwdItem it;
@@ -714,15 +713,19 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
             if (st == 0) continue;
             const int kb = it.kb, k0 = kb * BKV, key = k0 + r;
             const int64_t bh_off = ((int64_t)it.b * H + it.h) * T;
-            // per query of a 128-query block: (bias - lse) in the log2 domain and delta * scale, so the inner loop
-            // is  p = exp2(fma(s, c, a));  ds = p * fma(dp, scale, -b).   Loaded one block ahead of its use.
-            auto load_ld = [&](int i) {
-                const int tq = i * BQ + etid;
-                float2 v = make_float2(-INFINITY, 0.f);       // queries past the end: p = 0
-                if (tq < T)
-                    v = make_float2(((tril && i > kb) ? LOG2E : 0.f) - lse[bh_off + tq] * LOG2E, delta[bh_off + tq] * scale);
+            // per query: (bias - lse) in the log2 domain and delta * scale, so the inner loop is
+            //   p = exp2(fma(s, c, a));  ds = p * fma(dp, scale, -b).
+            // Each warp keeps its OWN 16 pairs of the current sub-block in a private 128-byte shared-memory slot: lanes
+            // 0-15 fetch them one sub-block ahead into a register and publish them after a __syncwarp -- no CTA-wide
+            // rendezvous, the warps drift apart freely.
+            // (the fetch returns the RAW values: touching them here would stall on the load it has just issued)
+            auto fetch_ld = [&](int n_local) {
+                float2 v = make_float2(INFINITY, 0.f);        // queries past the end (and lanes 16-31): lse = +inf -> p = 0
+                const int tq = (it.i_begin + (n_local >> 1)) * BQ + (n_local & 1) * SUBQ + wg * CPT + (lane & 15);
+                if (lane < 16 && n_local < 2 * it.nblk && tq < T) v = make_float2(lse[bh_off + tq], delta[bh_off + tq]);
                 return v;
             };
+            float2 nxt = fetch_ld(0);
             {   // this item's K and V rows -> TMEM (bf16): 16 features of row r per thread. The previous item's products
                 // are complete (all_done was waited for in its epilogue).
                 mbar_wait(&kv_full[w & 1], (w >> 1) & 1);
@@ -744,12 +747,6 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 __syncwarp();
                 if (lane == 0) mbar_arrive(kv_ready);
             }
-            float2 nxt = make_float2(0.f, 0.f);
-            if (etid < 128) {
-                sLD[((g >> 1) & 1) * 128 + etid] = load_ld(it.i_begin);   // this buffer was last read two blocks ago
-                if (it.nblk > 1) nxt = load_ld(it.i_begin + 1);
-            }
-            named_bar_sync(1, 32 * kEwWarps);
 
             for (int n = 0; n < 2 * it.nblk; ++n, ++g) {
                 const int j = n >> 1;
@@ -758,11 +755,13 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 const bool diag = causal && (i == kb);
                 const bool need_mask = diag || (k0 + BKV > T) || (i * BQ + BQ > T);
                 const bool bias_diag = tril && (i == kb);
-                if (half == 0 && j > 0) named_bar_sync(1, 32 * kEwWarps);      // sLD[jg & 1] was written at the end of the last sub-block
+                float2* ld = sLD + warp * CPT;                       // this warp's slot; its last readers passed the __syncwarp below
+                if (lane < CPT) ld[lane] = make_float2(((tril && i > kb) ? LOG2E : 0.f) - nxt.x * LOG2E, nxt.y * scale);
+                nxt = fetch_ld(n + 1);
+                __syncwarp();
                 mbar_wait(&s_full[half], jg & 1);
                 tc_fence_after();
                 const int qc0 = (int)half * SUBQ + wg * CPT;         // first query column (inside the block) of this thread
-                const float2* ld = sLD + (jg & 1) * 128 + qc0;
                 uint32_t sv[CPT], dp[CPT];
                 tmem_ld_cols(taddr + cST + half * SUBQ + wg * CPT, sv);
                 tmem_ld_cols(taddr + cDPT + half * SUBQ + wg * CPT, dp);
@@ -810,13 +809,11 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 }
                 tmem_st_wait();
                 tc_fence_before();
-                fence_proxy_async_smem();
+                // the shared-memory dS^T is read (by dQ) only after the block's second sub-block: this thread's fence
+                // there also covers what it wrote in the first
+                if (half == 1) fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&p_ready[half]);
-                if (half == 1 && j + 1 < it.nblk && etid < 128) {
-                    sLD[((jg + 1) & 1) * 128 + etid] = nxt;          // last read two blocks ago
-                    if (j + 2 < it.nblk) nxt = load_ld(i + 2);
-                }
             }
             // ---- item epilogue: dK / dV of this key block ----
             mbar_wait(all_done, w & 1);
