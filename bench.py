@@ -161,6 +161,11 @@ def main():
 
     import torch.distributed as dist
     import mingpt_distributed_b200 as m
+    for key in ("pdl",):                           # experiment knobs: MGB_OPT_PDL=0 python bench.py ...
+        val = os.environ.get("MGB_OPT_" + key.upper())
+        if val is not None:
+            from mingpt_distributed_b200 import _lib as _l
+            _l.set_option(key, int(val))
     from mingpt_distributed_b200 import _lib, ops
     from oracle import gpt_oracle as go
 

@@ -246,6 +246,8 @@ attn_bwd_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* 
                       float* __restrict__ delta, int64_t B, int64_t T, int H) {
     constexpr int TPR = D / 8;                      // threads per row: 2, 4 or 8
     const int64_t total = B * T * H * TPR;          // a multiple of TPR, so the shuffle groups below are always whole
+    grid_dep_launch();
+    grid_dep_wait();                                // dout is the previous kernel's output (programmatic dependent launch)
     // the loop condition is on the warp's first element, so whole warps stay in it for the shuffles
     for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31); i0 < total; i0 += (int64_t)gridDim.x * blockDim.x) {
         const int64_t i = i0 + (threadIdx.x & 31);
@@ -477,6 +479,8 @@ attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __re
 // dqkv[b,t,0,h,:] = bf16(dq_accum[b,t,h,:])
 __global__ void __launch_bounds__(256)
 attn_dq_convert_kernel(const float* __restrict__ dq_accum, __nv_bfloat16* __restrict__ dqkv, int64_t BT, int64_t HD) {
+    grid_dep_launch();
+    grid_dep_wait();
     const int64_t nch = HD >> 3;
     const int64_t total = BT * nch;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -499,6 +503,8 @@ attn_dq_convert_colsum_kernel(const float* __restrict__ dq_accum, __nv_bfloat16*
     const int ch = threadIdx.x % nch, r = threadIdx.x / nch;
     for (int c = threadIdx.x; c < HD; c += blockDim.x) cvt_smem[c] = 0.f;
     __syncthreads();
+    grid_dep_launch();
+    grid_dep_wait();                                 // dq_accum is complete once the main backward kernel has finished
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (r < rpb) {
         for (int64_t row = (int64_t)blockIdx.x * rpb + r; row < BT; row += (int64_t)gridDim.x * rpb) {
@@ -536,7 +542,8 @@ static int launch_bwd(const void* qkv, const void* out, const void* dout, const 
     const int64_t rows = (int64_t)B * T * H * (D / 8);
     int g = (int)((rows + 255) / 256);
     if (g > num_sms() * 16) g = num_sms() * 16;
-    attn_bwd_delta_kernel<D><<<g, 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, B, T, H);
+    launch_pdl(attn_bwd_delta_kernel<D>, dim3(g), dim3(256), 0, s, (const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta,
+               (int64_t)B, (int64_t)T, H);
     constexpr int smem = 4 * 64 * (D + 8) * 2 + 64 * (64 + 8) * 2 + 2 * 64 * 4;
     static bool attr_set = false;
     if (!attr_set && smem > 48 * 1024) {
@@ -563,14 +570,14 @@ static int launch_bwd(const void* qkv, const void* out, const void* dout, const 
         const int64_t rows = (int64_t)B * T;
         int64_t g2 = (rows + (threads / nch) - 1) / (threads / nch);
         if (g2 > num_sms() * 8) g2 = num_sms() * 8;
-        attn_dq_convert_colsum_kernel<<<(int)g2, threads, H * D * sizeof(float), s>>>(dq_accum, (__nv_bfloat16*)dqkv, rows,
-                                                                                  H * D, dqkv_colsum);
+        launch_pdl(attn_dq_convert_colsum_kernel, dim3((int)g2), dim3(threads), H * D * sizeof(float), s, dq_accum,
+                   (__nv_bfloat16*)dqkv, rows, H * D, dqkv_colsum);
         return 0;
     }
     const int64_t chunks = (int64_t)B * T * (H * D / 8);
     int g2 = (int)((chunks + 255) / 256);
     if (g2 > num_sms() * 16) g2 = num_sms() * 16;
-    attn_dq_convert_kernel<<<g2, 256, 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, (int64_t)B * T, (int64_t)H * D);
+    launch_pdl(attn_dq_convert_kernel, dim3(g2), dim3(256), 0, s, dq_accum, (__nv_bfloat16*)dqkv, (int64_t)B * T, (int64_t)H * D);
     return dqkv_colsum ? 1 : 0;      // 1: the caller still owes the column sums
 }
 

@@ -80,6 +80,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_base_ptr;
+    grid_dep_launch();
+    grid_dep_wait();                                 // qkv is the previous kernel's output (programmatic dependent launch)
 
     if (warp == 4) {
         // ===================== TMA producer (whole warp runs the loop, one lane issues) =====================
@@ -351,8 +353,8 @@ int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int 
     int rc = gemm::make_map_2d(&tm, qkv, C3, (int64_t)B * T, C3, 64, 128);
     if (rc) return rc;
     dim3 grid((T + BQ - 1) / BQ, B * H);
-    attn_fwd_tc_kernel<<<grid, kThreads, SMEM_BYTES, stream>>>(tm, (__nv_bfloat16*)out, lse, T, H, mask_mode,
-                                                               scale * LOG2E);
+    launch_pdl(attn_fwd_tc_kernel, grid, dim3(kThreads), (size_t)SMEM_BYTES, stream, tm, (__nv_bfloat16*)out, lse, T, H, mask_mode,
+               scale * LOG2E);
     return kOk;
 }
 
@@ -514,6 +516,8 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_base_ptr;
+    grid_dep_launch();
+    grid_dep_wait();                                 // inputs come from the previous kernels (programmatic dependent launch)
 
     // running counters (identical in every role): g = sub-blocks so far, w = items so far. Every item has an
     // even number of sub-blocks, so g & 1 is also the sub-block's position inside its 128-query block.
@@ -906,8 +910,8 @@ int launch_bwd_main(const void* qkv, const void* dout, const float* lse, const f
     const int nq = (T + BKV - 1) / BKV;
     const int nunits = (mask_mode == MGB_MASK_CAUSAL ? (nq + 1) / 2 : nq) * B * H;
     const int grid = nunits < num_sms() ? nunits : num_sms();
-    attn_bwd_tc_kernel<<<grid, kBwdThreads, BWD_SMEM, stream>>>(tkv, tq, td, tdq, lse, delta, (__nv_bfloat16*)dqkv, dqkv_colsum, B, T, H,
-                                                                mask_mode, scale, scale * LOG2E);
+    launch_pdl(attn_bwd_tc_kernel, dim3(grid), dim3(kBwdThreads), (size_t)BWD_SMEM, stream, tkv, tq, td, tdq, lse, delta,
+               (__nv_bfloat16*)dqkv, dqkv_colsum, B, T, H, mask_mode, scale, scale * LOG2E);
     return kOk;
 }
 

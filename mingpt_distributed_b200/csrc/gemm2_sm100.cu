@@ -161,6 +161,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_base_ptr;
+    // Everything above touched only this CTA's shared memory / TMEM: under a programmatic dependent launch it ran
+    // while the previous kernel of the stream was still draining. From here on its results are read.
+    grid_dep_launch();
+    grid_dep_wait();
 
     const int tiles = p.num_m_tiles * p.num_n_tiles;
     const int units = tiles * p.split_k;
@@ -577,8 +581,12 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
     }
     const int64_t units = (int64_t)tiles * p.split_k;
     const int clusters = (int)(units < num_clusters ? units : num_clusters);
-    if (fused_colsum) gemm_pair_kernel<true><<<2 * clusters, kThreads, smem_bytes, stream>>>(ta, tb, td, tp, tx, p);
-    else gemm_pair_kernel<false><<<2 * clusters, kThreads, smem_bytes, stream>>>(ta, tb, td, tp, tx, p);
+    {
+        const cudaError_t e = fused_colsum
+            ? launch_pdl(gemm_pair_kernel<true>, dim3(2 * clusters), dim3(kThreads), (size_t)smem_bytes, stream, ta, tb, td, tp, tx, p)
+            : launch_pdl(gemm_pair_kernel<false>, dim3(2 * clusters), dim3(kThreads), (size_t)smem_bytes, stream, ta, tb, td, tp, tx, p);
+        if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); return kErrLaunch; }
+    }
     count_launch(1);
     MGB_CHECK_LAUNCH();
     return fused_colsum ? kFusedColsum : kOk;

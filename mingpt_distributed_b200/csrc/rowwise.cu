@@ -26,6 +26,8 @@ ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gam
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nch = cols >> 3;
     const float inv_cols = 1.0f / (float)cols;
+    grid_dep_launch();
+    grid_dep_wait();                                 // x is the previous kernel's output (programmatic dependent launch)
     for (int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp; row < rows; row += (int64_t)gridDim.x * LN_WARPS) {
         const __nv_bfloat16* xr = x + row * cols;
         uint4 buf[MAXCH];
@@ -238,6 +240,8 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
         fence_mbar_init();
     }
     __syncthreads();
+    grid_dep_launch();
+    grid_dep_wait();                                 // inputs come from the previous kernels (programmatic dependent launch)
 
     const int64_t gw = (int64_t)blockIdx.x * LN_WARPS + warp;
     const int64_t row0 = gw * rows_per_warp;
@@ -744,10 +748,10 @@ extern "C" int mgb_layernorm_fwd(const void* x, const float* gamma, const float*
     const bool vec = (cols % 8 == 0) && cols <= 2048 && ((uintptr_t)x % 16 == 0) && ((uintptr_t)y % 16 == 0) &&
                      ((uintptr_t)gamma % 16 == 0) && ((uintptr_t)beta % 16 == 0);
     if (!vec) ln_fwd_generic_kernel<<<grid, LN_WARPS * 32, 0, s>>>(X, gamma, beta, Y, mean, rstd, rows, cols, eps);
-    else if (cols <= 256) ln_fwd_kernel<1><<<grid, LN_WARPS * 32, 0, s>>>(X, gamma, beta, Y, mean, rstd, rows, cols, eps);
-    else if (cols <= 512) ln_fwd_kernel<2><<<grid, LN_WARPS * 32, 0, s>>>(X, gamma, beta, Y, mean, rstd, rows, cols, eps);
-    else if (cols <= 1024) ln_fwd_kernel<4><<<grid, LN_WARPS * 32, 0, s>>>(X, gamma, beta, Y, mean, rstd, rows, cols, eps);
-    else ln_fwd_kernel<8><<<grid, LN_WARPS * 32, 0, s>>>(X, gamma, beta, Y, mean, rstd, rows, cols, eps);
+    else if (cols <= 256) launch_pdl(ln_fwd_kernel<1>, dim3(grid), dim3(LN_WARPS * 32), 0, s, X, gamma, beta, Y, mean, rstd, rows, cols, eps);
+    else if (cols <= 512) launch_pdl(ln_fwd_kernel<2>, dim3(grid), dim3(LN_WARPS * 32), 0, s, X, gamma, beta, Y, mean, rstd, rows, cols, eps);
+    else if (cols <= 1024) launch_pdl(ln_fwd_kernel<4>, dim3(grid), dim3(LN_WARPS * 32), 0, s, X, gamma, beta, Y, mean, rstd, rows, cols, eps);
+    else launch_pdl(ln_fwd_kernel<8>, dim3(grid), dim3(LN_WARPS * 32), 0, s, X, gamma, beta, Y, mean, rstd, rows, cols, eps);
     count_launch(1);
     MGB_CHECK_LAUNCH();
     return kOk;
@@ -785,11 +789,11 @@ static int layernorm_bwd_impl(const void* dy, const void* x, const float* gamma,
             cudaFuncSetAttribute(ln_bwd_staged_kernel<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);  \
         });                                                                                                        \
         if (colsum)                                                                                                \
-            ln_bwd_staged_kernel<N, true><<<grid, LN_WARPS * 32, smem_used, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, \
-                                                                                 dbeta, dres_colsum, rows, cols, rpw);     \
+            launch_pdl(ln_bwd_staged_kernel<N, true>, dim3(grid), dim3(LN_WARPS * 32), smem_used, s, DY, X, gamma, mean, rstd, DR, \
+                       DX, dgamma, dbeta, dres_colsum, rows, cols, rpw);                                           \
         else                                                                                                       \
-            ln_bwd_staged_kernel<N, false><<<grid, LN_WARPS * 32, smem_used, s>>>(DY, X, gamma, mean, rstd, DR, DX, dgamma, \
-                                                                                  dbeta, nullptr, rows, cols, rpw);         \
+            launch_pdl(ln_bwd_staged_kernel<N, false>, dim3(grid), dim3(LN_WARPS * 32), smem_used, s, DY, X, gamma, mean, rstd, DR, \
+                       DX, dgamma, dbeta, (float*)nullptr, rows, cols, rpw);                                       \
     } while (0)
         if (cols <= 256) MGB_LNB_STAGED(1);
         else if (cols <= 512) MGB_LNB_STAGED(2);
