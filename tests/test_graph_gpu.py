@@ -38,6 +38,23 @@ def test_graph_replay_matches_eager_steps():
     assert stepper.launches_per_replay((4, 64)) > 50
 
 
+def test_programmatic_dependent_launch_option_same_results():
+    """mgb_set_option("pdl", 1): GEMM / LayerNorm / attention kernels start under programmatic stream serialization
+    and wait on griddepcontrol before their first global read -- same losses and weights, eager and graph"""
+    from mingpt_distributed_b200 import _lib
+    base_l, base_p, _, _ = _run(True)
+    prev = _lib.set_option("pdl", 1)
+    try:
+        for use_graph in (False, True):
+            l, p, _, _ = _run(use_graph)
+            dev = max(abs(a - b) / abs(b) for a, b in zip(l, base_l))
+            worst = max(((p[n] - base_p[n]).norm() / (base_p[n].norm() + 1e-12)).item() for n in p if p[n].dim() == 2)
+            report(f"pdl_vs_plain_graph{int(use_graph)}", max_rel_dev=dev, worst_param_rel=worst)
+            assert dev < 2e-3 and worst < 5e-3, (use_graph, dev, worst)
+    finally:
+        _lib.set_option("pdl", prev)
+
+
 def test_forward_backward_equals_autograd_path():
     torch.manual_seed(1)
     cfg = m.GPTConfig(model_type="gpt-nano", vocab_size=65, block_size=64, embed_drop=0, resid_drop=0, attn_drop=0)
