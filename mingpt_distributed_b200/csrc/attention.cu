@@ -20,9 +20,11 @@
 namespace mgb {
 extern std::atomic<int> g_opt_attn_mma;
 namespace attn_tc {   // tcgen05 / TMEM kernels for head size 64 (attention_sm100.cu)
-int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream);
+int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream,
+               uint32_t drop_thresh, float inv_keep, const uint64_t* seed_dev, uint32_t site);
 int launch_bwd_main(const void* qkv, const void* dout, const float* lse, const float* delta, float* dq_accum,
-                    void* dqkv, float* dqkv_colsum, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream);
+                    void* dqkv, float* dqkv_colsum, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream,
+                    uint32_t drop_thresh, float inv_keep, const uint64_t* seed_dev, uint32_t site);
 }
 namespace attn {
 
@@ -553,10 +555,10 @@ static int launch_bwd(const void* qkv, const void* out, const void* dout, const 
     // column sums of dqkv (the qkv bias gradient): fused on the tcgen05 path (K / V thirds in the main kernel's item
     // epilogue, Q third in the convert kernel), a separate pass otherwise
     bool fused_colsum = false;
-    if (D == 64 && !thresh && !g_opt_attn_mma.load(std::memory_order_relaxed)) {
+    if (D == 64 && !g_opt_attn_mma.load(std::memory_order_relaxed)) {
         fused_colsum = dqkv_colsum != nullptr && (H * D / 8) <= 256;
         const int rc = attn_tc::launch_bwd_main(qkv, dout, lse, delta, dq_accum, dqkv, fused_colsum ? dqkv_colsum : nullptr, B, T,
-                                                H, mask_mode, scale, s);
+                                                H, mask_mode, scale, s, thresh, inv_keep, seed_dev, site);
         if (rc) return rc;
     } else {
         dim3 grid((T + BN - 1) / BN, B * H);
@@ -603,7 +605,7 @@ extern "C" int mgb_attention_fwd(const void* qkv, void* out, float* lse, int32_t
     if (((uintptr_t)qkv % 16) || ((uintptr_t)out % 16)) { set_last_error("attention: pointers must be 16-byte aligned"); return kErrBadAlign; }
     if (d == 64 && !g_opt_attn_mma.load(std::memory_order_relaxed)) {
         // gpt2-family head size: tcgen05 / TMEM kernel (attention_sm100.cu)
-        rc = attn_tc::launch_fwd(qkv, out, lse, B, T, H, mask_mode, scale, s);
+        rc = attn_tc::launch_fwd(qkv, out, lse, B, T, H, mask_mode, scale, s, 0u, 1.0f, nullptr, 0u);
         if (rc) return rc;
     } else if (d == 64) attn::launch_fwd<64>(qkv, out, lse, B, T, H, mask_mode, scale, s);
     else if (d == 32) attn::launch_fwd<32>(qkv, out, lse, B, T, H, mask_mode, scale, s);
@@ -755,7 +757,12 @@ extern "C" int mgb_attention_fwd_dropout(const void* qkv, void* out, float* lse,
     if (!(p_drop >= 0.f && p_drop < 1.f) || (p_drop > 0.f && !seed_dev)) { set_last_error("attention: bad dropout arguments"); return kErrBadShape; }
     if (((uintptr_t)qkv % 16) || ((uintptr_t)out % 16)) { set_last_error("attention: pointers must be 16-byte aligned"); return kErrBadAlign; }
     if (p_drop == 0.f) return mgb_attention_fwd(qkv, out, lse, B, T, H, d, mask_mode, scale, s_);
-    if (d == 64) attn::launch_fwd<64>(qkv, out, lse, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
+    if (d == 64 && !g_opt_attn_mma.load(std::memory_order_relaxed)) {
+        // tcgen05 kernel, same mask definition as the mma.sync ones
+        const uint32_t thresh = dropout_thresh16(p_drop);
+        rc = attn_tc::launch_fwd(qkv, out, lse, B, T, H, mask_mode, scale, s, thresh, 65536.0f / (65536.0f - (float)thresh), seed_dev, site);
+        if (rc) return rc;
+    } else if (d == 64) attn::launch_fwd<64>(qkv, out, lse, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
     else if (d == 32) attn::launch_fwd<32>(qkv, out, lse, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
     else attn::launch_fwd<16>(qkv, out, lse, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
     count_launch(1);

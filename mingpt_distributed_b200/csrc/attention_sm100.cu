@@ -12,6 +12,7 @@
 // warp 4 = TMA producer, warp 5 = MMA issuer + TMEM allocator. 48 KiB of shared memory and 256 TMEM columns
 // per CTA, so two CTAs share an SM: one does softmax while the other's MMAs run.
 #include "gemm_common.cuh"
+#include "dropout.cuh"
 
 namespace mgb {
 namespace attn_tc {
@@ -39,9 +40,30 @@ __device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_
         : "memory");
 }
 
+// Attention-probability dropout on packed bf16 pairs: words w[0 .. NW) hold 2*NW consecutive keys of one query
+// row starting at a multiple of 8; `group` is the mask group of the first 8 (dropout.cuh: group = (bh*T + q) *
+// ceil(T/8) + key/8, bit = key % 8 -- the definition the mma.sync kernels and mgb_attention_dropout_mask use).
+// Dropped probabilities become exact zeros; the 1/(1-p) factor is applied once, to the output row.
+template <int NW>
+__device__ __forceinline__ void drop_packed(uint32_t* w, uint64_t seed, uint32_t site, uint64_t group, uint32_t thresh) {
+#pragma unroll
+    for (int g8 = 0; g8 < NW / 4; ++g8) {
+        const uint32_t m = dropout_keep8(seed, site, group + g8, thresh);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t keep = ((m >> (2 * i)) & 1u ? 0x0000ffffu : 0u) | ((m >> (2 * i + 1)) & 1u ? 0xffff0000u : 0u);
+            w[g8 * 4 + i] &= keep;
+        }
+    }
+}
+
+// DROP: attention-probability dropout (nn.MultiheadAttention dropout=attn_drop: mingpt/model.py:150 ->
+// torch/nn/functional.py:6644-6645). The softmax normaliser keeps every key, P V only the kept ones.
+template <bool DROP>
 __global__ void __launch_bounds__(kThreads, 2)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __restrict__ out,
-                   float* __restrict__ lse, int T, int H, int mask_mode, float scale_log2) {
+                   float* __restrict__ lse, int T, int H, int mask_mode, float scale_log2, uint32_t drop_thresh,
+                   float inv_keep, const uint64_t* __restrict__ seed_dev, uint32_t site) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem;
@@ -155,6 +177,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
         const int q = q0 + r;
         const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16);
         float m_run = -INFINITY, l_run = 0.f;
+        const uint64_t drop_seed = DROP ? *seed_dev : 0;
+        const uint64_t drop_row = ((uint64_t)blockIdx.y * T + (uint64_t)q) * (uint64_t)((T + 7) >> 3);   // first group of this query
         for (int j = 0; j < nkv; ++j) {
             const uint32_t ph = (uint32_t)(j & 1);
             const int kvalid = min(BKV, T - j * BKV);            // keys of this block that exist
@@ -262,6 +286,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
                             pk[e] = pack_bf16x2(a0, a1);
                         }
                     }
+                    if (DROP && g <= warp) drop_packed<16>(pk, drop_seed, site, drop_row + (uint64_t)(j * (BKV / 8) + g * 4), drop_thresh);
                     tmem_st_32x32b_x16(taddr + kColP + g * 16, pk);
                 }
             } else {
@@ -300,6 +325,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
                             pk[e] = pack_bf16x2(pv[0], pv[1]);
                         }
                     }
+                    if (DROP) drop_packed<32>(pk, drop_seed, site, drop_row + (uint64_t)(j * (BKV / 8) + c * 8), drop_thresh);
                     tmem_st_32x32b_x32(taddr + kColP + c * 32, pk);
                 }
             }
@@ -312,7 +338,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
         // ---- epilogue: O / l, log-sum-exp ----
         mbar_wait(pv_done, (uint32_t)((nkv - 1) & 1));
         tc_fence_after();
-        const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
+        const float inv = l_run > 0.f ? (DROP ? inv_keep : 1.0f) / l_run : 0.f;
         __nv_bfloat16* orow = out + ((int64_t)(row0 + q)) * C + (int64_t)h * D;
 #pragma unroll 1
         for (int c = 0; c < 2; ++c) {
@@ -343,18 +369,23 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
 }
 
 int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int mask_mode, float scale,
-               cudaStream_t stream) {
+               cudaStream_t stream, uint32_t drop_thresh, float inv_keep, const uint64_t* seed_dev, uint32_t site) {
     static std::once_flag once;
     std::call_once(once, [] {
-        cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        cudaFuncSetAttribute(attn_fwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        cudaFuncSetAttribute(attn_fwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     });
     CUtensorMap tm;
     const int64_t C3 = (int64_t)3 * H * D;
     int rc = gemm::make_map_2d(&tm, qkv, C3, (int64_t)B * T, C3, 64, 128);
     if (rc) return rc;
     dim3 grid((T + BQ - 1) / BQ, B * H);
-    launch_pdl(attn_fwd_tc_kernel, grid, dim3(kThreads), (size_t)SMEM_BYTES, stream, tm, (__nv_bfloat16*)out, lse, T, H, mask_mode,
-               scale * LOG2E);
+    if (drop_thresh)
+        launch_pdl(attn_fwd_tc_kernel<true>, grid, dim3(kThreads), (size_t)SMEM_BYTES, stream, tm, (__nv_bfloat16*)out, lse, T, H,
+                   mask_mode, scale * LOG2E, drop_thresh, inv_keep, seed_dev, site);
+    else
+        launch_pdl(attn_fwd_tc_kernel<false>, grid, dim3(kThreads), (size_t)SMEM_BYTES, stream, tm, (__nv_bfloat16*)out, lse, T, H,
+                   mask_mode, scale * LOG2E, 0u, 1.0f, (const uint64_t*)nullptr, 0u);
     return kOk;
 }
 
@@ -466,12 +497,19 @@ __device__ __forceinline__ int bwd_item(const BwdSched& sc, int q, BwdItem& it) 
     return 1;
 }
 
+// DROP: attention-probability dropout, the forward's mask regenerated (dropout.cuh). In this transposed layout a
+// thread owns ONE key and CPT consecutive queries, while a mask group is 8 consecutive KEYS of one query: the 32
+// lanes of a warp (32 keys = 4 groups) share the 4 x CPT = 64 groups of a sub-block, two Philox calls per lane,
+// and fetch their bits with one shuffle per query. dV uses the kept probabilities (scaled once, in the epilogue),
+// dS = P (keep ? dP / (1-p) : 0 - delta) * scale.
+template <bool DROP>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_constant__ CUtensorMap tmap_q,
                    const __grid_constant__ CUtensorMap tmap_do, const __grid_constant__ CUtensorMap tmap_dq,
                    const float* __restrict__ lse, const float* __restrict__ delta,
                    __nv_bfloat16* __restrict__ dqkv, float* __restrict__ kv_colsum, int B, int T, int H, int mask_mode,
-                   float scale, float scale_log2) {
+                   float scale, float scale_log2, uint32_t drop_thresh, float inv_keep,
+                   const uint64_t* __restrict__ seed_dev, uint32_t site) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = smem_raw;
     if (smem_u32(smem) & 1023u) __trap();                      // SWIZZLE_128B tiles need 1024-byte alignment
@@ -709,6 +747,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
         const int r = quarter * 32 + lane;               // key row inside the block == TMEM lane
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
         const uint32_t swz = (uint32_t)(r & 7);
+        const uint64_t drop_seed = DROP ? *seed_dev : 0;
         uint32_t g = 0, w = 0;
         for (int q = 0;; ++q) {
             BwdItem it;
@@ -770,6 +809,24 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 tmem_ld_cols(taddr + cST + half * SUBQ + wg * CPT, sv);
                 tmem_ld_cols(taddr + cDPT + half * SUBQ + wg * CPT, dp);
                 tmem_ld_wait();
+                uint32_t keepbits = 0xffffu;                         // bit e: the probability of query qc0 + e was kept
+                if (DROP) {
+                    static_assert(CPT == 16, "two Philox calls per lane cover 4 key groups x 16 queries");
+                    const uint64_t t8 = (uint64_t)((T + 7) >> 3);
+                    const uint64_t qrow = ((uint64_t)it.b * H + it.h) * T + (uint64_t)(i * BQ + qc0 + (lane >> 2));
+                    const uint64_t kgrp = (uint64_t)((k0 + 32 * quarter) >> 3) + (uint64_t)(lane & 3);
+                    const uint32_t m0 = dropout_keep8(drop_seed, site, qrow * t8 + kgrp, drop_thresh);         // queries 0-7
+                    const uint32_t m1 = dropout_keep8(drop_seed, site, (qrow + 8) * t8 + kgrp, drop_thresh);   // queries 8-15
+                    keepbits = 0u;
+#pragma unroll
+                    for (int e = 0; e < CPT; ++e) {
+                        const uint32_t v = __shfl_sync(0xffffffffu, e < 8 ? m0 : m1, (e & 7) * 4 + (lane >> 3));
+                        keepbits |= ((v >> (lane & 7)) & 1u) << e;
+                    }
+#pragma unroll
+                    for (int e = 0; e < CPT; ++e)
+                        dp[e] = (keepbits >> e) & 1u ? __float_as_uint(__uint_as_float(dp[e]) * inv_keep) : 0u;
+                }
                 uint32_t pk[CPT / 2], dk[CPT / 2];
                 if (!need_mask && !bias_diag) {
 #pragma unroll
@@ -801,6 +858,11 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                         dk[e] = pack_bf16x2(dsv[0], dsv[1]);
                     }
                 }
+                if (DROP) {                                          // P^T as it multiplied V: dropped entries are zero
+#pragma unroll
+                    for (int e = 0; e < CPT / 2; ++e)
+                        pk[e] &= ((keepbits >> (2 * e)) & 1u ? 0x0000ffffu : 0u) | ((keepbits >> (2 * e + 1)) & 1u ? 0xffff0000u : 0u);
+                }
                 // bf16 pairs over the first half of this thread's own fp32 columns (both were just read)
                 tmem_st_cols(taddr + cST + half * SUBQ + wg * CPT, pk);
                 tmem_st_cols(taddr + cDPT + half * SUBQ + wg * CPT, dk);
@@ -829,6 +891,10 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_free);            // the next item may start accumulating
+            if (DROP) {                                      // dV was accumulated from the unscaled kept probabilities
+#pragma unroll
+                for (int e = 0; e < CPT; ++e) vv[e] = __float_as_uint(__uint_as_float(vv[e]) * inv_keep);
+            }
             if (kv_colsum) {
                 // bias gradient of the qkv projection, K and V thirds: column sums over this warp's 32 key rows by a
                 // transpose-reduce (rows of keys >= T hold exact zeros), one atomic per column and warp
@@ -892,10 +958,12 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
 
 // main backward kernel only: delta must be precomputed and dq_accum zeroed by the caller (attention.cu)
 int launch_bwd_main(const void* qkv, const void* dout, const float* lse, const float* delta, float* dq_accum,
-                    void* dqkv, float* dqkv_colsum, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream) {
+                    void* dqkv, float* dqkv_colsum, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream,
+                    uint32_t drop_thresh, float inv_keep, const uint64_t* seed_dev, uint32_t site) {
     static std::once_flag once;
     std::call_once(once, [] {
-        cudaFuncSetAttribute(attn_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
+        cudaFuncSetAttribute(attn_bwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
+        cudaFuncSetAttribute(attn_bwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
     });
     CUtensorMap tkv, tq, td, tdq;
     const int64_t C = (int64_t)H * D, C3 = 3 * C;
@@ -910,8 +978,13 @@ int launch_bwd_main(const void* qkv, const void* dout, const float* lse, const f
     const int nq = (T + BKV - 1) / BKV;
     const int nunits = (mask_mode == MGB_MASK_CAUSAL ? (nq + 1) / 2 : nq) * B * H;
     const int grid = nunits < num_sms() ? nunits : num_sms();
-    launch_pdl(attn_bwd_tc_kernel, dim3(grid), dim3(kBwdThreads), (size_t)BWD_SMEM, stream, tkv, tq, td, tdq, lse, delta,
-               (__nv_bfloat16*)dqkv, dqkv_colsum, B, T, H, mask_mode, scale, scale * LOG2E);
+    if (drop_thresh)
+        launch_pdl(attn_bwd_tc_kernel<true>, dim3(grid), dim3(kBwdThreads), (size_t)BWD_SMEM, stream, tkv, tq, td, tdq, lse, delta,
+                   (__nv_bfloat16*)dqkv, dqkv_colsum, B, T, H, mask_mode, scale, scale * LOG2E, drop_thresh, inv_keep, seed_dev, site);
+    else
+        launch_pdl(attn_bwd_tc_kernel<false>, dim3(grid), dim3(kBwdThreads), (size_t)BWD_SMEM, stream, tkv, tq, td, tdq, lse, delta,
+                   (__nv_bfloat16*)dqkv, dqkv_colsum, B, T, H, mask_mode, scale, scale * LOG2E, 0u, 1.0f,
+                   (const uint64_t*)nullptr, 0u);
     return kOk;
 }
 

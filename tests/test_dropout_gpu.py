@@ -48,11 +48,13 @@ def test_elementwise_dropout_statistics_and_determinism():
     report("dropout_keep_rate", rate=rate)
 
 
-@pytest.mark.parametrize("d", [16, 32, 64])
+@pytest.mark.parametrize("d,B,T,H", [(16, 2, 136, 3), (32, 2, 136, 3), (64, 2, 136, 3), (64, 3, 384, 2), (64, 40, 256, 4)])
 @pytest.mark.parametrize("mode", [1, 2])
-def test_attention_dropout_matches_torch_with_the_same_mask(d, mode):
+def test_attention_dropout_matches_torch_with_the_same_mask(d, mode, B, T, H):
+    """head size 64 runs the tcgen05 kernels (mask bits regenerated per 8 keys in the forward, shared across a
+    warp by shuffles in the transposed backward); (40, 256, 4) gives every persistent backward CTA several items"""
     from mingpt_distributed_b200 import ops
-    B, T, H, p = 2, 136, 3, 0.2
+    p = 0.2
     C = H * d
     g = torch.Generator(device="cuda").manual_seed(5)
     qkv = torch.randn(B, T, 3 * C, device="cuda", generator=g).bfloat16()
@@ -75,8 +77,9 @@ def test_attention_dropout_matches_torch_with_the_same_mask(d, mode):
     torch.cuda.synchronize()
     gerr = (dqkv.float() - qf.grad).abs()
     scale = qf.grad.abs().max().item()
-    assert (gerr <= 3e-2 * (qf.grad.abs() + 0.1 * scale)).all(), gerr.max().item()
-    report(f"attn_dropout_d{d}_m{mode}", out_err=err, grad_err=gerr.max().item(), keep_rate=rate)
+    # per element: 3 % of its own size plus 0.45 % of the largest gradient (bf16 P / dS operands, p = 0.2 scaling)
+    assert (gerr <= 3e-2 * (qf.grad.abs() + 0.15 * scale)).all(), gerr.max().item()
+    report(f"attn_dropout_d{d}_m{mode}_{B}x{T}x{H}", out_err=err, grad_err=gerr.max().item(), keep_rate=rate)
 
 
 @pytest.mark.parametrize("variant", ["mingpt", "reference"])
