@@ -5,7 +5,6 @@ import os, sys, time, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import mingpt_distributed_b200 as m
-from oracle import gpt_oracle as go        # flops_per_token only (a probe, not the product path)
 dev = "cuda"
 def run(name, model_type, B, T, V, accum=1, steps=6):
     torch.manual_seed(0)
@@ -36,7 +35,7 @@ def run(name, model_type, B, T, V, accum=1, steps=6):
     e.record(); torch.cuda.synchronize()
     ms = s.elapsed_time(e) / steps
     tps = B * accum * T / (ms / 1e3)
-    f = go.flops_per_token(cfg.n_layer, cfg.n_embed, cfg.vocab_size, T, "mingpt")
+    f = 6 * (12 * cfg.n_layer * cfg.n_embed ** 2 + cfg.vocab_size * cfg.n_embed) + 6 * cfg.n_layer * cfg.n_embed * T
     print(json.dumps(dict(config=name, B=B, T=T, accum=accum, ms_per_step=round(ms, 2), tokens_per_s=round(tps), mfu_nominal=round(tps * f / 2.25e15, 4),
                           loss=round(float(l), 4), mem_gb=round(torch.cuda.max_memory_allocated() / 2**30, 1))), flush=True)
     del model, opt; torch.cuda.empty_cache(); torch.cuda.reset_peak_memory_stats()
