@@ -63,7 +63,10 @@ int64_t mgb_launch_count(void);
  * exponentials per logit, instead of staging them in shared memory), "pdl" (default 0; 1 = launch the GEMM,
  * LayerNorm and attention kernels with programmatic stream serialization, so that a kernel's prologue --
  * barrier set-up, TMEM allocation -- overlaps the tail of the kernel before it; every such kernel waits on
- * griddepcontrol before it reads global memory). Returns the
+ * griddepcontrol before it reads global memory), "reserved_sms" (default 0; n = size the persistent grids -- GEMM,
+ * attention backward, cross-entropy, LayerNorm backward -- for n fewer SMs than the device has, leaving them to a
+ * concurrent communication kernel: the data-parallel trainer sets it while gradient all-reduces are in flight, so no
+ * CTA pair of a persistent GEMM waits a whole tile wave for SMs that NCCL occupies). Returns the
  * previous value, or -1 for an unknown key. Every alternative computes the same result. */
 int mgb_set_option(const char* key, int value);
 
@@ -79,6 +82,10 @@ int mgb_set_option(const char* key, int value);
  *   its tanh / erf is evaluated once);  v = act(v);  v *= act'(gate[m,n]) (if gate; gate_kind selects the
  *   derivative, MGB_GATE_MUL multiplies by gate[m,n] itself);  v += residual[m,n];
  *   D = v  (bf16 or fp32)   or   D += v (fp32, atomic; required for split_k > 1)
+ * The epilogue is applied exactly once per output element: with `accumulate` the reduction is split over K only
+ * when there is NO epilogue term (bias, act, gate, residual, preact, colsum all absent -- the weight-gradient
+ * case); with any of them present an automatic split (split_k = 0) is forced to 1 and an explicit split_k > 1 is
+ * rejected (MGB_ERR_UNSUPPORTED), because every split unit would otherwise run the epilogue on its partial sum.
  * D rows are written in 16-byte units: when n is not a multiple of 8 (bf16) / 4 (fp32) AND ldd leaves room
  * after column n, the rest of the last unit (at most 7 / 3 elements) is overwritten too (with the epilogue of
  * a zero accumulator). With ldd == n (a dense D) nothing outside the matrix is ever touched.

@@ -15,8 +15,9 @@ from .optim import FusedAdamW, clip_grad_norm_
 from .parallel import DataParallel, GradBuckets, plan_buckets
 from .trainer import GPTTrainer, GPTTrainerConfig, GraphedTrainStep, ModelSnapshot, Trainer, train_step
 from .config import load_config
+from .flops import flops_per_token, mfu, model_flops_per_token
 
 __all__ = ["GPT", "CfgNode", "GPTConfig", "LazyLogits", "OptimizerConfig", "create_optimizer", "param_groups",
            "print_model_size", "CharDataset", "DataConfig", "FusedAdamW", "clip_grad_norm_", "DataParallel",
            "GradBuckets", "plan_buckets", "GPTTrainer", "GraphedTrainStep", "GPTTrainerConfig", "ModelSnapshot", "Trainer",
-           "train_step", "load_config"]
+           "train_step", "load_config", "flops_per_token", "model_flops_per_token", "mfu"]

@@ -6,7 +6,9 @@ library is missing and cannot be built, importing any op raises.
 from __future__ import annotations
 
 import ctypes as C
+import hashlib
 import os
+import shutil
 import subprocess
 import threading
 
@@ -81,24 +83,47 @@ SIGNATURES = {
 INTROSPECTION = {"mgb_last_error": C.c_char_p, "mgb_version": C.c_int, "mgb_launch_count": C.c_int64}
 
 
+STAMP_PATH = LIB_PATH + ".srchash"
+
+
+def source_hash() -> str:
+    """sha256 over the CUDA sources, the public header and the build script: what LIB_PATH must be built from"""
+    src_dir = os.path.join(_HERE, "csrc")
+    inc = os.path.join(os.path.dirname(_HERE), "include", "mingpt_b200.h")
+    files = sorted(os.path.join(src_dir, f) for f in os.listdir(src_dir) if f.endswith((".cu", ".cuh", ".sh"))) + [inc]
+    h = hashlib.sha256()       # == `cat <files> | sha256sum`, which is how csrc/build.sh writes the stamp
+    for f in files:
+        with open(f, "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()
+
+
 def build(verbose: bool = False) -> str:
-    """Compile the CUDA sources for sm_100a into LIB_PATH (nvcc cross-compiles without a GPU)."""
-    res = subprocess.run(["bash", BUILD_SCRIPT], capture_output=True, text=True)
-    if res.returncode != 0:
-        raise RuntimeError(f"building {LIB_PATH} failed:\n{res.stdout}\n{res.stderr}")
+    """Compile the CUDA sources for sm_100a into LIB_PATH (nvcc cross-compiles without a GPU) and record the
+    hash of the sources it was built from next to it."""
+    import fcntl
+    with open(LIB_PATH + ".lock", "w") as lock:       # several ranks may reach this at once
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        if os.path.exists(LIB_PATH) and not _lib_is_stale():
+            return LIB_PATH                           # another process built it while we waited
+        res = subprocess.run(["bash", BUILD_SCRIPT], capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError(f"building {LIB_PATH} failed:\n{res.stdout}\n{res.stderr}")
     if verbose:
         print(res.stdout.strip())
     return LIB_PATH
 
 
-def _sources_newer_than_lib() -> bool:
+def _lib_is_stale() -> bool:
+    """True when LIB_PATH was built from different sources than the ones on disk (content hash, not mtimes:
+    a snapshot copy does not preserve modification times)."""
     if not os.path.exists(LIB_PATH):
         return True
-    t = os.path.getmtime(LIB_PATH)
-    src_dir = os.path.join(_HERE, "csrc")
-    inc = os.path.join(os.path.dirname(_HERE), "include", "mingpt_b200.h")
-    files = [os.path.join(src_dir, f) for f in os.listdir(src_dir) if f.endswith((".cu", ".cuh"))] + [inc]
-    return any(os.path.exists(f) and os.path.getmtime(f) > t for f in files)
+    try:
+        with open(STAMP_PATH) as f:
+            return f.read().strip() != source_hash()
+    except OSError:
+        return True
 
 
 def lib() -> C.CDLL:
@@ -109,7 +134,11 @@ def lib() -> C.CDLL:
     with _lock:
         if _lib is not None:
             return _lib
-        if not os.path.exists(LIB_PATH):
+        if _lib_is_stale():
+            # an edited .cu / .cuh / header must never silently run the old binary: rebuild, or refuse to load
+            if shutil.which(os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")) is None:
+                raise RuntimeError(f"{LIB_PATH} is missing or was built from other sources than the ones on disk, "
+                                   "and nvcc is not available to rebuild it")
             build()
         handle = C.CDLL(LIB_PATH)
         for name, argtypes in SIGNATURES.items():

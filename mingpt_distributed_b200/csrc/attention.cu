@@ -547,10 +547,9 @@ static int launch_bwd(const void* qkv, const void* out, const void* dout, const 
     launch_pdl(attn_bwd_delta_kernel<D>, dim3(g), dim3(256), 0, s, (const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta,
                (int64_t)B, (int64_t)T, H);
     constexpr int smem = 4 * 64 * (D + 8) * 2 + 64 * (64 + 8) * 2 + 2 * 64 * 4;
-    static bool attr_set = false;
-    if (!attr_set && smem > 48 * 1024) {
-        cudaFuncSetAttribute(attn_bwd_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        attr_set = true;
+    if (smem > 48 * 1024) {
+        static PerDeviceOnce once;
+        once.run([] { cudaFuncSetAttribute(attn_bwd_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); });
     }
     // column sums of dqkv (the qkv bias gradient): fused on the tcgen05 path (K / V thirds in the main kernel's item
     // epilogue, Q third in the convert kernel), a separate pass otherwise
@@ -718,9 +717,11 @@ extern "C" int mgb_attention_bwd_noalloc(const void* qkv, const void* out, const
     float* delta = scratch + attn::kNoAllocMaxElems;            // [B,H,T];   fully overwritten
     // the array still holds the previous call's partial sums: clear the part this call accumulates into
     cudaMemsetAsync(dq_accum, 0, (size_t)elems * sizeof(float), s);
-    if (d == 64) attn::launch_bwd<64>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
-    else if (d == 32) attn::launch_bwd<32>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
-    else attn::launch_bwd<16>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
+    int owed;
+    if (d == 64) owed = attn::launch_bwd<64>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
+    else if (d == 32) owed = attn::launch_bwd<32>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
+    else owed = attn::launch_bwd<16>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s);
+    if (owed < 0) return owed;       // e.g. a tensor-map encode failed: the main kernel was never launched
     count_launch(3);
     MGB_CHECK_LAUNCH();
     return kOk;
@@ -784,9 +785,11 @@ extern "C" int mgb_attention_bwd_dropout(const void* qkv, const void* out, const
         set_last_error("attention: pointers must be 16-byte aligned"); return kErrBadAlign;
     }
     cudaMemsetAsync(dq_accum, 0, (size_t)B * T * H * d * sizeof(float), s);
-    if (d == 64) attn::launch_bwd<64>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
-    else if (d == 32) attn::launch_bwd<32>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
-    else attn::launch_bwd<16>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
+    int owed;
+    if (d == 64) owed = attn::launch_bwd<64>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
+    else if (d == 32) owed = attn::launch_bwd<32>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
+    else owed = attn::launch_bwd<16>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s, p_drop, seed_dev, site);
+    if (owed < 0) return owed;
     count_launch(3);
     MGB_CHECK_LAUNCH();
     return kOk;

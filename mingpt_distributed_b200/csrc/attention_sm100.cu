@@ -370,8 +370,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
 
 int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int mask_mode, float scale,
                cudaStream_t stream, uint32_t drop_thresh, float inv_keep, const uint64_t* seed_dev, uint32_t site) {
-    static std::once_flag once;
-    std::call_once(once, [] {
+    static PerDeviceOnce once;
+    once.run([] {
         cudaFuncSetAttribute(attn_fwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
         cudaFuncSetAttribute(attn_fwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     });
@@ -960,8 +960,8 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
 int launch_bwd_main(const void* qkv, const void* dout, const float* lse, const float* delta, float* dq_accum,
                     void* dqkv, float* dqkv_colsum, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream,
                     uint32_t drop_thresh, float inv_keep, const uint64_t* seed_dev, uint32_t site) {
-    static std::once_flag once;
-    std::call_once(once, [] {
+    static PerDeviceOnce once;
+    once.run([] {
         cudaFuncSetAttribute(attn_bwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
         cudaFuncSetAttribute(attn_bwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
     });

@@ -19,4 +19,6 @@ for f in gemm_sm100 gemm2_sm100 rowwise optim attention attention_sm100 dropout;
 done
 for p in "${pids[@]}"; do wait "$p"; done
 "$NVCC" -shared -o "$OUT" "${OBJS[@]}" -lcudart
+# stamp: hash of the sources this binary was built from (_lib.py refuses to load a binary whose stamp differs)
+(cd "$HERE" && LC_ALL=C ls *.cu *.cuh *.sh | LC_ALL=C sort | xargs cat; cat "$ROOT/include/mingpt_b200.h") | sha256sum | cut -d' ' -f1 > "$OUT.srchash"
 echo "built $OUT"

@@ -9,6 +9,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+#include <mutex>
+
 namespace mgb {
 
 // ----------------------------------------------------------------------------
@@ -36,7 +39,28 @@ enum : int {
 
 void set_last_error(const char* msg);
 void count_launch(int n);   // bumps mgb_launch_count()
-int num_sms();
+int num_sms();              // SMs of the CURRENT device minus mgb_set_option("reserved_sms"): what persistent grids are sized to
+int num_sms_total();        // SMs of the current device
+
+// One-time set-up that is PER DEVICE (cudaFuncSetAttribute opt-ins, attribute queries): run(f) calls f() the first
+// time it is reached with each device ordinal current, so a process that drives several GPUs gets the opt-in on
+// every one of them (a process-wide std::once_flag would leave all but the first device without it).
+struct PerDeviceOnce {
+    std::atomic<uint64_t> done[2] = {{0}, {0}};   // ordinals 0..127
+    std::mutex mu;
+    template <typename F>
+    void run(F&& f) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev > 127) dev = 0;
+        const uint64_t bit = 1ull << (dev & 63);
+        std::atomic<uint64_t>& word = done[dev >> 6];
+        if (word.load(std::memory_order_acquire) & bit) return;
+        std::lock_guard<std::mutex> lock(mu);
+        if (word.load(std::memory_order_relaxed) & bit) return;
+        f();
+        word.fetch_or(bit, std::memory_order_release);
+    }
+};
 bool pdl_enabled();   // optim.cu: mgb_set_option("pdl", ...)
 
 // Launch with programmatic stream serialization when enabled (the kernel MUST call grid_dep_wait() before it reads

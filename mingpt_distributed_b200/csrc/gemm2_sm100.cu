@@ -497,8 +497,8 @@ static bool tma_ok(const void* base, int64_t ld, int elem_bytes) {
 }
 
 int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t stream) {
-    static std::once_flag once;
-    std::call_once(once, [] {
+    static PerDeviceOnce once;
+    once.run([] {
         cudaFuncSetAttribute(gemm_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
         cudaFuncSetAttribute(gemm_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     });

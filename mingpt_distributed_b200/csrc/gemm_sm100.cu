@@ -295,8 +295,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
 // ----------------------------------------------------------------------------
 // host side
 // ----------------------------------------------------------------------------
-static int g_num_sms = 0;
-static std::once_flag g_attr_once;
+static PerDeviceOnce g_attr_once;
 
 static int pick_block_n(int64_t M, int64_t N, int b_mn, int num_sms) {
     // minimise (waves * block_n): quantisation-aware choice among the legal UMMA N sizes
@@ -352,13 +351,17 @@ extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
         }
     }
 
-    std::call_once(g_attr_once, [] {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaFuncSetAttribute(gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-    });
-    const int num_sms = g_num_sms > 0 ? g_num_sms : 148;
+    g_attr_once.run([] { cudaFuncSetAttribute(gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES); });
+    const int num_sms = mgb::num_sms();
+    // The epilogue (bias, activation, gate, residual, saved pre-activation, column sums) is applied ONCE per output
+    // element. Split-K units each run the whole epilogue on their partial sum, so accumulate + an epilogue term
+    // never splits: an automatic split is forced to 1, an explicit one is an error.
+    const bool has_epilogue = a->bias || a->residual || a->gate || a->preact || a->colsum ||
+                              (a->act & ~MGB_ACT_STORE_GRAD) != MGB_ACT_NONE;
+    if (has_epilogue && a->split_k > 1) {
+        set_last_error("gemm: split_k > 1 cannot be combined with bias / act / gate / residual / preact / colsum");
+        return kErrUnsupported;
+    }
 
     Params p{};
     p.M = a->m; p.N = a->n; p.K = a->k;
@@ -379,6 +382,7 @@ extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
     const int engine = a->block_n & (MGB_GEMM_ENGINE_SINGLE | MGB_GEMM_ENGINE_PAIR);
     mgb_gemm_args a_local = *a;
     a_local.block_n = a->block_n & ~(MGB_GEMM_ENGINE_SINGLE | MGB_GEMM_ENGINE_PAIR);
+    if (has_epilogue && a->accumulate) a_local.split_k = 1;
     const bool want_pair = engine == MGB_GEMM_ENGINE_PAIR ||
                            (engine == 0 && a->m > BLOCK_M && !g_opt_gemm_single.load(std::memory_order_relaxed));
     if (a->colsum && a->d_f32) { set_last_error("gemm: colsum needs a bf16 D"); return kErrUnsupported; }
@@ -396,7 +400,7 @@ extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
     p.num_m_tiles = (int)ceil_div64(a->m, BLOCK_M);
     p.num_n_tiles = (int)ceil_div64(a->n, bn);
     p.k_blocks_total = (int)ceil_div64(a->k, BLOCK_K);
-    int split = a->split_k;
+    int split = a_local.split_k;
     const int tiles = p.num_m_tiles * p.num_n_tiles;
     if (split <= 0) {
         split = 1;

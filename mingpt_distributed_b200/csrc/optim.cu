@@ -20,16 +20,24 @@ void set_last_error(const char* msg) {
 }
 static std::atomic<int64_t> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
-int num_sms() {
-    static int n = 0;
-    static std::once_flag once;
-    std::call_once(once, [] {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess ||
-            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-            n = 148;
-    });
+std::atomic<int> g_opt_reserved_sms{0};
+int num_sms_total() {
+    static std::atomic<int> cache[128];          // per device ordinal; 0 = not queried yet
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev > 127) dev = 0;
+    int n = cache[dev].load(std::memory_order_relaxed);
+    if (n == 0) {
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cache[dev].store(n, std::memory_order_relaxed);
+    }
     return n;
+}
+int num_sms() {
+    const int total = num_sms_total();
+    int r = g_opt_reserved_sms.load(std::memory_order_relaxed);
+    if (r < 0) r = 0;
+    r &= ~1;                                      // CTA pairs: keep the usable count even
+    return total - r >= 16 ? total - r : total;
 }
 
 // ---------------------------------------------------------------------------
@@ -314,6 +322,7 @@ extern "C" int mgb_set_option(const char* key, int value) {
     if (!std::strcmp(key, "attn_mma")) return mgb::g_opt_attn_mma.exchange(value);
     if (!std::strcmp(key, "ln_unstaged")) return mgb::g_opt_ln_unstaged.exchange(value);
     if (!std::strcmp(key, "ce_unstaged")) return mgb::g_opt_ce_unstaged.exchange(value);
+    if (!std::strcmp(key, "reserved_sms")) return mgb::g_opt_reserved_sms.exchange(value);
     return -1;
 }
 

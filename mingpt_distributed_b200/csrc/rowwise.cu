@@ -783,8 +783,8 @@ static int layernorm_bwd_impl(const void* dy, const void* x, const float* gamma,
         const int64_t rpw = (rows + (int64_t)grid * LN_WARPS - 1) / ((int64_t)grid * LN_WARPS);
 #define MGB_LNB_STAGED(N)                                                                                          \
     do {                                                                                                           \
-        static std::once_flag once;                                                                                \
-        std::call_once(once, [] {                                                                                  \
+        static PerDeviceOnce once;                                                                                 \
+        once.run([] {                                                                                              \
             cudaFuncSetAttribute(ln_bwd_staged_kernel<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); \
             cudaFuncSetAttribute(ln_bwd_staged_kernel<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);  \
         });                                                                                                        \
@@ -876,8 +876,8 @@ extern "C" int mgb_cross_entropy_fwd_bwd(void* logits, int64_t ld, const int64_t
     const size_t stage_smem = (size_t)4 * ld + 4 * sizeof(uint64_t) + 32 * sizeof(float);
     if (write_grad && (ld % 8 == 0) && ((uintptr_t)logits % 16 == 0) && stage_smem <= 227 * 1024 && rows >= 2 * num_sms() &&
         !g_opt_ce_unstaged.load(std::memory_order_relaxed)) {
-        static std::once_flag once;
-        std::call_once(once, [] {
+        static PerDeviceOnce once;
+        once.run([] {
             cudaFuncSetAttribute(cross_entropy_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         });
         cross_entropy_staged_kernel<<<num_sms(), (CES_WARPS + 1) * 32, stage_smem, s>>>(

@@ -189,6 +189,7 @@ class LazyLogits:
     def materialize(self) -> torch.Tensor:
         if self._ws.generation != self._gen:
             raise RuntimeError("LazyLogits is stale: the model ran another forward since it was returned")
+        self._model.check_device_errors()
         return self._model._head_logits(self._ws)
 
     def view(self, *shape):
@@ -254,6 +255,7 @@ class _Workspace:
         self.idx = None
         self.has_head_grads = False
         self.drop = (0.0, 0.0, 0.0)      # dropout probabilities used by the forward that filled this workspace
+        self.seed = torch.zeros(1, dtype=torch.int64, device=dev)   # dropout seed of that forward (backward regenerates its masks)
         self.tmp = self.dtmp = None
         self._mc = (M, C, dev)
 
@@ -280,6 +282,39 @@ class _LossFn(torch.autograd.Function):
             raise RuntimeError("backward() after another forward reused the activation workspace")
         ctx.model._backward(ctx.ws, grad_loss.contiguous().float())
         return None, None, None
+
+
+class _LossFnParams(torch.autograd.Function):
+    """The same, with every parameter as an autograd INPUT: backward returns the parameter gradients instead of
+    publishing them itself, so they reach p.grad through autograd's AccumulateGrad nodes -- which is where
+    torch.nn.parallel.DistributedDataParallel hangs its reducer hooks (mingpt/trainer.py:71). Used when the model
+    finds itself wrapped in torch's DDP (or when GPT.autograd_param_grads is set): DDP then buckets, all-reduces
+    and averages the gradients exactly as it does for the reference. The returned tensors are views of the flat
+    gradient buffer, so AccumulateGrad normally adopts them without a copy."""
+
+    @staticmethod
+    def forward(ctx, anchor, model, ws, *params):
+        ctx.model, ctx.ws, ctx.gen = model, ws, ws.generation
+        return ws.loss.clone()
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        if ctx.ws.generation != ctx.gen:
+            raise RuntimeError("backward() after another forward reused the activation workspace")
+        grads = ctx.model._backward_returning_grads(ctx.ws, grad_loss.contiguous().float())
+        return (None, None, None) + tuple(grads)
+
+
+def _called_from_torch_ddp() -> bool:
+    import sys
+    f = sys._getframe(2)
+    for _ in range(16):
+        if f is None:
+            return False
+        if f.f_code.co_filename.endswith("torch/nn/parallel/distributed.py"):
+            return True
+        f = f.f_back
+    return False
 
 
 class GPT(nn.Module):
@@ -339,6 +374,9 @@ class GPT(nn.Module):
         self._anchor = None
         self._layer_done_hook: Optional[Callable[[int], None]] = None
         self._rng_seed: Optional[torch.Tensor] = None   # device int64: dropout seed, advanced once per training forward
+        self.autograd_param_grads = False     # True: gradients reach p.grad through autograd (torch DDP's hooks fire)
+        self._grad_target: Optional[torch.Tensor] = None
+        self._warned_ddp = False
         self.loss_scale_hint = 1.0
         self._flatten()
 
@@ -486,7 +524,8 @@ class GPT(nn.Module):
     def _g(self, role: str) -> torch.Tensor:
         name = self._roles[role]
         o, n = self._spans[name]
-        return self._flat_grad[o:o + n].view(self._shape_of[name])
+        buf = self._flat_grad if self._grad_target is None else self._grad_target
+        return buf[o:o + n].view(self._shape_of[name])
 
     @property
     def _shape_of(self):
@@ -495,6 +534,19 @@ class GPT(nn.Module):
             cache = {n: p.shape for n, p in self.named_parameters()}
             self.__dict__["_shape_cache"] = cache
         return cache
+
+    def check_device_errors(self):
+        """Raise if a kernel flagged an out-of-range token id (embedding) or target (cross entropy) since the last
+        check -- the device assert torch's nn.Embedding / F.cross_entropy would have hit (mingpt/model.py:226,316).
+        The kernels themselves only set a flag (and produce zeros / ignore the row) so the step never syncs with
+        the host; this reads the flags back, so call it where the host syncs anyway (the trainer does, whenever
+        it prints the loss)."""
+        for ws in self._workspaces.values():
+            flag = int(ws.err_flag.item())
+            if flag:
+                ws.err_flag.zero_()
+                what = {1: "token id outside [0, vocab_size)", 2: "target outside [0, vocab_size) and != -1"}.get(flag, f"flag {flag}")
+                raise IndexError(f"GPT.forward: {what} (batch {ws.B} x {ws.T})")
 
     def _ws(self, B: int, T: int) -> _Workspace:
         ws = self._workspaces.get((B, T))
@@ -517,6 +569,9 @@ class GPT(nn.Module):
             # follows torch.manual_seed(): drawn from the default CPU generator once, then advanced on the device
             self._rng_seed = torch.randint(0, 2 ** 62, (1,), dtype=torch.int64).to(self._flat.device)
         self._rng_seed += 1
+        # the seed travels with the workspace: a training forward of ANOTHER shape between this forward and its
+        # backward advances the model-wide seed, and backward must still regenerate THIS forward's masks
+        ws.seed.copy_(self._rng_seed)
         ws.ensure_dropout_buffers()
         ws.drop = self.drop_p
         return ws.drop
@@ -531,7 +586,7 @@ class GPT(nn.Module):
         P = lambda r: self._w(r)
         wpe = W("wpe").view(-1, C)
         pe, pr, pa = self._dropout_now(ws)
-        seed = self._rng_seed
+        seed = ws.seed
         ops.embedding_fwd(idx, W("wte"), wpe, ws.x[0], ws.err_flag)
         if pe > 0:   # nn.Dropout(embed_drop), mingpt/model.py:215,231
             ops.dropout(ws.x[0], None, ws.x[0], pe, seed, self.SITE_EMBED)
@@ -633,7 +688,21 @@ class GPT(nn.Module):
         need_grad = torch.is_grad_enabled()
         self._head_loss(ws, tg, need_grad)
         logits = LazyLogits(self, ws, ws.generation)
-        if need_grad:
+        if need_grad and not self.autograd_param_grads and _called_from_torch_ddp():
+            # torch's DistributedDataParallel wraps this model (mingpt/trainer.py:71): its reducer only sees
+            # gradients that arrive through autograd, so switch to that path (DataParallel is the fast one)
+            self.autograd_param_grads = True
+            self.mark_params_dirty()           # DDP's construction-time broadcast wrote the parameters in place
+            self._ensure_device_state()
+            if not self._warned_ddp:
+                import warnings
+                warnings.warn("GPT is wrapped in torch.nn.parallel.DistributedDataParallel: gradients now go through "
+                              "autograd so DDP's hooks fire. mingpt_distributed_b200.DataParallel (what GPTTrainer "
+                              "uses) overlaps the all-reduce without the extra copies.")
+                self._warned_ddp = True
+        if need_grad and self.autograd_param_grads:
+            loss = _LossFnParams.apply(self._anchor, self, ws, *self.parameters())
+        elif need_grad:
             loss = _LossFn.apply(self._anchor, self, ws)
         else:
             loss = ws.loss.clone()
@@ -675,7 +744,23 @@ class GPT(nn.Module):
                 o, k = self._spans[n]
                 p.grad = self._flat_grad[o:o + k].view(p.shape)
 
-    def _backward(self, ws: _Workspace, grad_loss: torch.Tensor):
+    def _backward_returning_grads(self, ws: _Workspace, grad_loss: torch.Tensor) -> List[torch.Tensor]:
+        """backward for the autograd-visible path: computes THIS backward's gradients (not accumulated onto
+        p.grad -- autograd's AccumulateGrad does that) and returns one tensor per parameter."""
+        params = list(self.named_parameters())
+        fresh = all(p.grad is None for _, p in params)
+        # gradients already live in the flat buffer (accumulation, e.g. DDP.no_sync): write this pass elsewhere
+        target = self._flat_grad if fresh else torch.zeros_like(self._flat_grad)
+        if fresh:
+            target.zero_()
+        self._grad_target = target
+        try:
+            self._backward(ws, grad_loss, publish=False)
+        finally:
+            self._grad_target = None
+        return [target[o:o + k].view(p.shape) for (o, k), p in ((self._spans[n], p) for n, p in params)]
+
+    def _backward(self, ws: _Workspace, grad_loss: torch.Tensor, publish: bool = True):
         if not ws.has_head_grads:
             raise RuntimeError("backward() needs a forward that ran with gradients enabled")
         B, T, M = ws.B, ws.T, ws.M
@@ -685,7 +770,8 @@ class GPT(nn.Module):
         W = lambda r: self._w(r, bf16=True)
         P = lambda r: self._w(r)
         G = self._g
-        self._prepare_grads()
+        if publish:
+            self._prepare_grads()
         # upstream gradient of the scalar loss, applied on the device (no host sync)
         ops.scale_bf16_dev(ws.dlnf, grad_loss)
         ops.axpy(G("head_w"), ws.head_dw, grad_loss)
@@ -694,7 +780,7 @@ class GPT(nn.Module):
             self._layer_done_hook(L + 1)
         dx = ws.dx_a
         pe, pr, pa = ws.drop
-        seed = self._rng_seed
+        seed = ws.seed
         for l in range(L - 1, -1, -1):
             s = ws.stats[l]
             dmlp = dx          # gradient of the MLP branch output: through its dropout mask when there is one

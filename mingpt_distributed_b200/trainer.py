@@ -23,6 +23,7 @@ import torch.distributed as dist
 from torch.utils.data import DataLoader, Dataset
 from torch.utils.data.distributed import DistributedSampler
 
+from .flops import mfu, model_flops_per_token
 from .model import CfgNode
 from .optim import FusedAdamW, clip_grad_norm_
 from .parallel import DataParallel
@@ -93,15 +94,24 @@ class GraphedTrainStep:
     Data parallel: NCCL stays OUT of the graphs. The step is captured as a chain of graph SEGMENTS cut where a
     gradient bucket completes; on replay each bucket's all-reduce is launched eagerly on the side stream
     between two segments, so it overlaps the rest of the backward exactly like the eager path, and the last
-    segment (norm, clip, AdamW) starts after the side stream has drained."""
+    segment (norm, clip, AdamW) starts after the side stream has drained.
+
+    Gradient accumulation (`accum` = k > 1, BASELINE config 5): a call takes k micro-batches stacked along dim 0
+    ((k*B, T) tokens), runs k forward/backward passes that add into the same flat gradient buffer and ONE
+    optimizer step; the 1/k of the mean is folded into the AdamW kernel's gradient scale (no extra pass), and under
+    data parallelism only the LAST micro-step exchanges gradients (DDP.no_sync for the others). The returned loss
+    is the mean over the k micro-batches."""
 
     def __init__(self, model, optimizer, grad_norm_clip: Optional[float] = None, dp: Optional[DataParallel] = None,
-                 use_graph: bool = True, warmup: int = 2):
+                 use_graph: bool = True, warmup: int = 2, accum: int = 1):
         if not isinstance(optimizer, FusedAdamW):
             raise TypeError("GraphedTrainStep needs the FusedAdamW returned by create_optimizer")
+        if accum < 1:
+            raise ValueError("accum must be >= 1")
         self.model, self.opt, self.clip, self.dp = model, optimizer, grad_norm_clip, dp
-        self.use_graph, self.warmup = use_graph, warmup
+        self.use_graph, self.warmup, self.accum = use_graph, warmup, accum
         self._states = {}
+        self.replays = 0          # graph replays so far (the trainers' tests assert the fast path really ran)
 
     def _optimizer_part(self, scale: float, graph_step: bool):
         clip = self.clip is not None and self.clip > 0
@@ -109,17 +119,33 @@ class GraphedTrainStep:
         self.opt.step(grad_scale=scale, gradnorm_sq=norm_sq, max_norm=float(self.clip) if clip else 0.0,
                       graph_step=graph_step)
 
-    def _body(self, st, graph_step: bool):
-        model = self.model
+    def _micro_steps(self, st, last_hook=None):
+        """the k forward/backward passes of one step; `last_hook` (data parallel) is installed for the last one only"""
+        model, k = self.model, self.accum
         for p in model.parameters():          # optimizer.zero_grad(set_to_none=True), mingpt/trainer.py:125
             p.grad = None
+        if k == 1:
+            if last_hook is not None:
+                model._layer_done_hook = last_hook
+            return model.forward_backward(st["x"], st["y"])
+        B = st["x"].shape[0] // k
+        st["loss_acc"].zero_()
+        saved = model._layer_done_hook
+        for i in range(k):
+            model._layer_done_hook = (last_hook if last_hook is not None else saved) if i == k - 1 else None
+            loss = model.forward_backward(st["x"][i * B:(i + 1) * B], st["y"][i * B:(i + 1) * B])
+            st["loss_acc"].add_(loss, alpha=1.0 / k)
+        model._layer_done_hook = saved
+        return st["loss_acc"]
+
+    def _body(self, st, graph_step: bool):
         if self.dp is not None:
             self.dp._ensure()
-        loss = model.forward_backward(st["x"], st["y"])
-        scale = 1.0
+        loss = self._micro_steps(st)
+        scale = 1.0 / self.accum
         if self.dp is not None:
             self.dp.finish_backward()
-            scale = self.dp.grad_scale
+            scale *= self.dp.grad_scale
         self._optimizer_part(scale, graph_step)
         return loss
 
@@ -160,14 +186,11 @@ class GraphedTrainStep:
         with torch.cuda.stream(side):
             begin()
             try:
-                model._layer_done_hook = hook
-                for p in model.parameters():
-                    p.grad = None
-                st["loss"] = model.forward_backward(st["x"], st["y"])
+                st["loss"] = self._micro_steps(st, last_hook=hook)
                 end()
                 segs.append(("drain", None))
                 begin()
-                self._optimizer_part(dp.grad_scale, True)
+                self._optimizer_part(dp.grad_scale / self.accum, True)
                 end()
             finally:
                 model._layer_done_hook = saved
@@ -195,9 +218,12 @@ class GraphedTrainStep:
         key = tuple(x.shape)
         st = self._states.get(key)
         if st is None:
+            if key[0] % self.accum:
+                raise ValueError(f"batch dimension {key[0]} is not a multiple of accum={self.accum}")
             dev = self.model._flat.device
             st = dict(x=torch.empty(key, dtype=torch.int64, device=dev), y=torch.empty(key, dtype=torch.int64, device=dev),
-                      calls=0, graph=None, loss=None, launches=0)
+                      calls=0, graph=None, loss=None, launches=0,
+                      loss_acc=torch.zeros((), dtype=torch.float32, device=dev))
             self._states[key] = st
         st["x"].copy_(x, non_blocking=True)
         st["y"].copy_(y, non_blocking=True)
@@ -222,6 +248,7 @@ class GraphedTrainStep:
             else:
                 st["graph"].replay()
             self.opt.note_replay()
+            self.replays += 1
         st["calls"] += 1
         return st["loss"]
 
@@ -258,6 +285,17 @@ class GPTTrainer:
             self.dp = DataParallel(self.model, device_ids=[self.local_rank])
             self.model = self.dp
         self.tokens_seen = 0
+        # the fast path: the whole step (forward, backward, clip + AdamW) replayed as a CUDA graph (graph segments with
+        # the all-reduces between them under data parallelism). Needs the fused optimizer and a static batch shape;
+        # anything else (a foreign optimizer, the ragged last batch of an epoch) runs the same kernels eagerly.
+        self._stepper = None
+        if isinstance(optimizer, FusedAdamW) and os.environ.get("MGB_EAGER_STEP", "0") != "1":
+            self._stepper = GraphedTrainStep(self.raw_model, optimizer, config.grad_norm_clip, self.dp)
+        self._f_tok = None
+
+    @property
+    def graph_replays(self) -> int:
+        return self._stepper.replays if self._stepper is not None else 0
 
     def _prepare_dataloader(self, dataset: Dataset):
         if dist.is_initialized():
@@ -306,21 +344,32 @@ class GPTTrainer:
             with torch.no_grad():
                 _, loss = self.model(inputs, labels)
             return loss
+        if self._stepper is not None and inputs.shape[0] == self.config.batch_size:
+            return self._stepper(inputs, labels)       # static device scalar: read it before the next step
         return train_step(self.raw_model, self.optimizer, inputs, labels, self.config.grad_norm_clip, self.dp,
                           zero_grad=True)
 
     def _run_epoch(self, epoch: int, dataloader: DataLoader, train: bool = True) -> None:
         t0, tok0 = time.time(), self.tokens_seen
         for idx, (x, y) in enumerate(dataloader):
-            inputs = x.to(self.device, non_blocking=True)
-            labels = y.to(self.device, non_blocking=True)
+            if train and self._stepper is not None and x.shape[0] == self.config.batch_size:
+                inputs, labels = x, y      # pinned host batch: the graphed step copies it straight into its static buffers
+            else:
+                inputs = x.to(self.device, non_blocking=True)
+                labels = y.to(self.device, non_blocking=True)
             loss = self._run_batch(inputs, labels, train)
             self.tokens_seen += inputs.numel()
             if idx % 100 == 0:
                 lv = float(loss)   # the only device->host sync
+                self.raw_model.check_device_errors()    # out-of-range token ids / targets flagged by the kernels
                 dt = max(time.time() - t0, 1e-9)
+                tps = (self.tokens_seen - tok0) / dt
+                if self._f_tok is None:
+                    self._f_tok = model_flops_per_token(self.raw_model, inputs.shape[1])
+                # forward only = a third of the training flops
+                util = mfu(tps, self._f_tok if train else self._f_tok / 3.0)
                 print(f"[GPU{self.local_rank}] Epoch {epoch},{'Training' if train else 'Test'} loss {lv} "
-                      f"| {(self.tokens_seen - tok0) / dt:.0f} tok/s/rank")
+                      f"| {tps:.0f} tok/s/rank | MFU {100.0 * util:.1f}% of 2.25 PFLOP/s bf16")
 
     def train(self) -> None:
         for epoch in range(self.last_epoch, self.config.max_epochs):
@@ -354,6 +403,7 @@ class Trainer:
         print("running on device", self.device)
         self.iter_num, self.iter_time, self.iter_dt = 0, 0.0, 0.0
         self.loss = None
+        self.graph_replays = 0
 
     def add_callback(self, onevent: str, callback):
         self.callbacks[onevent].append(callback)
@@ -373,6 +423,9 @@ class Trainer:
         loader = DataLoader(self.train_dataset, sampler=sampler, shuffle=False, pin_memory=True,
                             batch_size=config.batch_size, num_workers=config.num_workers)
         model.train()
+        stepper = None
+        if isinstance(self.optimizer, FusedAdamW) and os.environ.get("MGB_EAGER_STEP", "0") != "1":
+            stepper = GraphedTrainStep(model, self.optimizer, config.grad_norm_clip, dp)
         self.iter_num, self.iter_time = 0, time.time()
         it = iter(loader)
         while True:
@@ -381,8 +434,13 @@ class Trainer:
             except StopIteration:
                 it = iter(loader)
                 batch = next(it)
-            x, y = [t.to(self.device, non_blocking=True) for t in batch]
-            self.loss = train_step(model, self.optimizer, x, y, config.grad_norm_clip, dp, zero_grad=True)
+            x, y = batch
+            if stepper is not None and x.shape[0] == config.batch_size:
+                self.loss = stepper(x, y)          # copies the pinned host batch into its static device buffers
+                self.graph_replays = stepper.replays
+            else:
+                x, y = x.to(self.device, non_blocking=True), y.to(self.device, non_blocking=True)
+                self.loss = train_step(model, self.optimizer, x, y, config.grad_norm_clip, dp, zero_grad=True)
             self.trigger_callbacks("on_batch_end")
             self.iter_num += 1
             tnow = time.time()

@@ -120,7 +120,7 @@ def test_training_step_with_dropout_equals_oracle_with_exported_masks(variant):
         if ref.norm() < 1e-6:
             continue
         r = ((p.grad.cpu() - ref).norm() / ref.norm()).item()
-        assert r < 5e-2, f"{n}: {r:.4f}"
+        assert r < 2e-2, f"{n}: {r:.4f}"
     # eval mode switches dropout off; a second training forward draws a new seed
     model.eval()
     with torch.no_grad():

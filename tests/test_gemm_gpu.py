@@ -174,6 +174,28 @@ def test_gemm_wgrad_split_k_accumulates(split_k):
     _check(f"gemm_wgrad_split{split_k}", dw, 2 * (dy.float().t() @ x.float()), 1e-3)
 
 
+@pytest.mark.parametrize("engine", [1024, 2048])          # MGB_GEMM_ENGINE_SINGLE / _PAIR
+def test_gemm_accumulate_with_epilogue_applies_it_once(engine):
+    """D += bias + residual + A B^T at K = 4096: with `accumulate` the automatic split over K must not run the
+    epilogue once per split (it is forced to 1 when an epilogue term is present); an explicit split is refused"""
+    from mingpt_distributed_b200 import ops
+    M, N, K = 256, 256, 4096
+    a, b, acc = _mk(M, N, K, False, False, seed=9)
+    bias = torch.randn(N, device="cuda") * 5
+    res = (torch.randn(M, N, device="cuda") * 5).bfloat16()
+    d0 = torch.randn(M, N, device="cuda")
+    out = d0.clone()
+    ops.gemm(a, b, out, bias=bias, residual=res, accumulate=True, block_n=engine)
+    torch.cuda.synchronize()
+    _check(f"gemm_accumulate_bias_residual_e{engine}", out, d0 + acc + bias + res.float(), 1e-3)
+    out = d0.clone()
+    ops.gemm(a, b, out, accumulate=True, block_n=engine)        # no epilogue: split-K is free to kick in
+    torch.cuda.synchronize()
+    _check(f"gemm_accumulate_plain_e{engine}", out, d0 + acc, 1e-3)
+    with pytest.raises(RuntimeError, match="split_k"):
+        ops.gemm(a, b, out, bias=bias, accumulate=True, split_k=4, block_n=engine)
+
+
 def test_gemm_strided_views_and_padded_vocab():
     """the head: logits chunk written into a wider (padded) buffer, then used as a K-major A operand whose
     reduction length (the vocabulary) is not a multiple of anything"""

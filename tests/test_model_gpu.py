@@ -48,7 +48,7 @@ def test_reference_fixture_loss_logits_grads(name):
             assert p.grad.float().norm().item() < 1e-3, n
             continue
         worst = max(worst, r)
-        assert r < 5e-2, f"{n}: relative gradient error {r:.4f}"
+        assert r < 2e-2, f"{n}: relative gradient error {r:.4f}"
     report(f"{name}_worst_grad_rel", value=worst)
 
 
@@ -87,7 +87,7 @@ def test_forward_backward_vs_oracle(variant, shape):
             continue
         r = _rel(p.grad, ref)
         worst = max(worst, r)
-        assert r < 5e-2, f"{n}: relative gradient error {r:.4f}"
+        assert r < 2e-2, f"{n}: relative gradient error {r:.4f}"
     report(tag + "_worst_grad_rel", value=worst)
     # inference path: full fp32 logits, no loss
     lg2, none = model(x.cuda())
@@ -157,10 +157,7 @@ def test_loss_trajectory_200_steps_and_greedy_generate(variant):
         idx = torch.cat([idx, lg[:, -1].argmax(-1, keepdim=True)], 1)
     got = model.generate(prompt.cuda(), 24).cpu()
     report(f"generate_{variant}", match=float((got == idx).float().mean()))
-    if variant == "mingpt":
-        assert torch.equal(got, idx)
-    else:   # the as-written model sees the future during training, so its continuation is not peaked
-        assert got.shape == idx.shape
+    assert torch.equal(got, idx), f"greedy tokens differ from the oracle's ({variant})"
 
 
 def test_fixture_trajectory_and_generate_reference_variant():
@@ -199,6 +196,26 @@ def test_fixture_trajectory_and_generate_reference_variant():
     report("fixture_params_after10", worst_rel=worst)
     out = model.generate(fx["prompt"].cuda(), 12)
     assert out.shape == fx["generated"].shape and torch.equal(out[:, :8].cpu(), fx["prompt"])
+    # The reference's own generate() output (fx["generated"], from ITS weights after the 10 steps). Ten steps on
+    # random tokens leave the logits nearly flat (top-2 margins down to 1e-4), so a free-running comparison would
+    # only measure rounding luck. Teacher-forced instead: load the reference's weights, feed the reference's own
+    # prefix, and demand the same greedy token wherever the fp32 top-2 margin exceeds the bf16 error of a logit.
+    ref_model = _model_from(fx["state_dict_after"], cfg, "reference")
+    sd_after = {k: v for k, v in fx["state_dict_after"].items()}
+    gen = fx["generated"]
+    decided = agree = 0
+    for t in range(8, gen.shape[1]):
+        prefix = gen[:, :t]
+        ol, _ = go.forward(sd_after, cfg["n_head"], prefix, None, "reference")
+        top2 = ol[:, -1].topk(2, dim=-1).values
+        margin = top2[:, 0] - top2[:, 1]
+        assert torch.equal(ol[:, -1].argmax(-1), gen[:, t]), "the oracle itself must reproduce the reference's generate()"
+        ours = ref_model.generate(prefix.cuda(), 1)[:, -1].cpu()
+        tol = 2e-2 * max(1.0, ol[:, -1].abs().max().item())
+        sure = margin > tol
+        decided += int(sure.sum()); agree += int((ours[sure] == gen[:, t][sure]).sum())
+        assert torch.equal(ours[sure], gen[:, t][sure]), f"step {t}: greedy token differs from the reference's generate()"
+    report("fixture_generate_teacher_forced", decided=decided, agree=agree, total=int(gen[:, 8:].numel()))
 
 
 def test_gpttrainer_end_to_end_with_chardataset(tmp_path, monkeypatch):
@@ -220,6 +237,9 @@ def test_gpttrainer_end_to_end_with_chardataset(tmp_path, monkeypatch):
     with torch.no_grad():
         _, l0 = tr.model(x0[None].cuda(), y0[None].cuda())
     tr.train()
+    # the reference-API trainer runs the benchmarked path: every full batch after the 2 warm-up steps is a graph replay
+    n_full = len(ds) // 64
+    assert tr.graph_replays >= n_full - 2 > 10, (tr.graph_replays, n_full)
     with torch.no_grad():
         _, l1 = tr.model(x0[None].cuda(), y0[None].cuda())
     report("gpttrainer", loss_before=l0.item(), loss_after=l1.item())
@@ -239,6 +259,7 @@ def test_gpttrainer_end_to_end_with_chardataset(tmp_path, monkeypatch):
     t3.set_callback("on_batch_end", lambda t: seen.append(float(t.loss)))
     t3.run()
     assert len(seen) == 5 and all(math.isfinite(v) for v in seen)
+    assert t3.graph_replays == 3             # 2 eager warm-up steps, then the captured graph
 
 
 def test_gpt2_124m_full_size_properties():

@@ -5,7 +5,8 @@ mkdir -p gpurun_out
 rm -f gpurun_out/parity_report.jsonl
 nvidia-smi --query-gpu=name,driver_version,clocks.sm,clocks.max.sm --format=csv > gpurun_out/gpu.txt 2>&1
 rc=0
-for f in tests/test_gemm_gpu.py tests/test_ops_gpu.py tests/test_model_gpu.py tests/test_graph_gpu.py tests/test_shapes_gpu.py tests/test_dropout_gpu.py tests/test_zz_no_alloc.py; do
+FILES=${GPU_TEST_FILES:-$(ls tests/test_*_gpu.py tests/test_zz_no_alloc.py)}
+for f in $FILES; do
   n=$(basename "$f" .py)
   timeout 900 python -m pytest "$f" -q -m gpu -p no:cacheprovider "$@" > "gpurun_out/$n.log" 2>&1
   r=$?
