@@ -136,6 +136,14 @@ int mgb_layernorm_bwd_colsum(const void* dy, const void* x, const float* gamma, 
  * ------------------------------------------------------------------------------------------------- */
 int mgb_embedding_fwd(const int64_t* idx, const void* wte, const void* wpe, void* out, int64_t B, int64_t T,
                       int32_t C, int64_t vocab, int32_t* err_flag, mgb_stream_t stream);
+/* Input pipeline: cuts a batch of training windows out of a byte-coded corpus that already lives on the device --
+ * CharDataset.__getitem__ (mingpt/char_dataset.py:35-47) for B window starts at once, instead of the reference's
+ * per-item Python list comprehension + DataLoader collation + two blocking H2D copies (mingpt/trainer.py:141-142).
+ * codes: uint8 [n_codes] (vocabulary index of every corpus byte); starts: int64 [B];
+ * x[b,t] = codes[starts[b] + t], y[b,t] = codes[starts[b] + t + 1], both int64 [B,T] (the dtype GPT.forward takes).
+ * A window that does not fit (start < 0 or start + T + 1 > n_codes) sets *err_flag = 3 (may be NULL) and is skipped. */
+int mgb_token_windows(const void* codes, int64_t n_codes, const int64_t* starts, int64_t B, int32_t T,
+                      int64_t* x, int64_t* y, int32_t* err_flag, mgb_stream_t stream);
 /* dwte[idx[b,t], :] += dx[b,t,:] (fp32 atomics);  dwpe[t,:] += sum_b dx[b,t,:] */
 int mgb_embedding_bwd(const int64_t* idx, const void* dx, float* dwte, float* dwpe, int64_t B, int64_t T,
                       int32_t C, int64_t vocab, mgb_stream_t stream);

@@ -10,7 +10,7 @@ and building models / optimizers / datasets works anywhere.
 """
 from .model import (GPT, CfgNode, GPTConfig, LazyLogits, OptimizerConfig, create_optimizer, param_groups,
                     print_model_size)
-from .char_dataset import CharDataset, DataConfig
+from .char_dataset import CharDataset, DataConfig, DeviceWindowLoader
 from .optim import FusedAdamW, clip_grad_norm_
 from .parallel import DataParallel, GradBuckets, plan_buckets
 from .trainer import GPTTrainer, GPTTrainerConfig, GraphedTrainStep, ModelSnapshot, Trainer, train_step
@@ -18,6 +18,6 @@ from .config import load_config
 from .flops import flops_per_token, mfu, model_flops_per_token
 
 __all__ = ["GPT", "CfgNode", "GPTConfig", "LazyLogits", "OptimizerConfig", "create_optimizer", "param_groups",
-           "print_model_size", "CharDataset", "DataConfig", "FusedAdamW", "clip_grad_norm_", "DataParallel",
+           "print_model_size", "CharDataset", "DataConfig", "DeviceWindowLoader", "FusedAdamW", "clip_grad_norm_", "DataParallel",
            "GradBuckets", "plan_buckets", "GPTTrainer", "GraphedTrainStep", "GPTTrainerConfig", "ModelSnapshot", "Trainer",
            "train_step", "load_config", "flops_per_token", "model_flops_per_token", "mfu"]

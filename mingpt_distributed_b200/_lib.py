@@ -56,6 +56,7 @@ SIGNATURES = {
     "mgb_layernorm_bwd_colsum": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I32, _P],
     "mgb_embedding_fwd": [_P, _P, _P, _P, _I64, _I64, _I32, _I64, _P, _P],
     "mgb_embedding_bwd": [_P, _P, _P, _P, _I64, _I64, _I32, _I64, _P],
+    "mgb_token_windows": [_P, _I64, _P, _I64, _I32, _P, _P, _P, _P],
     "mgb_attention_fwd": [_P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _P],
     "mgb_attention_bwd": [_P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _P],
     "mgb_attention_bwd_colsum": [_P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _P],

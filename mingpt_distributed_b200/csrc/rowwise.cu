@@ -833,6 +833,57 @@ extern "C" int mgb_layernorm_bwd_colsum(const void* dy, const void* x, const flo
 }
 
 
+// =====================================================================================
+// Input pipeline: (x, y) training windows cut out of a device-resident byte corpus
+// (CharDataset.__getitem__, mingpt/char_dataset.py:35-47, for a whole batch of window starts at once)
+// =====================================================================================
+// One thread per 8 consecutive positions of one window: 9 code bytes in, 2 x 8 int64 out (two 64-byte stores, and
+// the warp's stores are contiguous). The int64 outputs are what dominates: 16 B written per token.
+__global__ void __launch_bounds__(256)
+token_windows_kernel(const uint8_t* __restrict__ codes, int64_t n_codes, const int64_t* __restrict__ starts, int64_t B,
+                     int T, int64_t* __restrict__ x, int64_t* __restrict__ y, int32_t* err_flag) {
+    const int per_row = (T + 7) >> 3;
+    const int64_t total = B * per_row;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t b = i / per_row;
+        const int t0 = (int)(i - b * per_row) * 8;
+        const int64_t s = starts[b];
+        if (s < 0 || s + T + 1 > n_codes) {       // the window (T inputs + 1 shifted target) must lie inside the corpus
+            if (err_flag && t0 == 0) atomicExch(err_flag, 3);
+            continue;
+        }
+        const uint8_t* src = codes + s + t0;
+        const int n = min(8, T - t0);
+        int64_t v[9];
+#pragma unroll
+        for (int e = 0; e < 9; ++e) v[e] = e <= n ? (int64_t)src[e] : 0;
+        int64_t* xo = x + b * T + t0;
+        int64_t* yo = y + b * T + t0;
+        if (n == 8 && ((T & 1) == 0)) {           // rows stay 16-byte aligned: vector stores
+#pragma unroll
+            for (int e = 0; e < 8; e += 2) {
+                *reinterpret_cast<longlong2*>(xo + e) = make_longlong2(v[e], v[e + 1]);
+                *reinterpret_cast<longlong2*>(yo + e) = make_longlong2(v[e + 1], v[e + 2]);
+            }
+        } else {
+            for (int e = 0; e < n; ++e) { xo[e] = v[e]; yo[e] = v[e + 1]; }
+        }
+    }
+}
+
+extern "C" int mgb_token_windows(const void* codes, int64_t n_codes, const int64_t* starts, int64_t B, int32_t T,
+                                 int64_t* x, int64_t* y, int32_t* err_flag, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    if (B < 0 || T <= 0 || n_codes < 0) { set_last_error("token_windows: bad shape"); return kErrBadShape; }
+    if (((uintptr_t)x % 16) || ((uintptr_t)y % 16)) { set_last_error("token_windows: x / y must be 16-byte aligned"); return kErrBadAlign; }
+    if (B == 0) return kOk;
+    const int grid = grid_for(B * ((T + 7) / 8), 256, num_sms() * 8);
+    token_windows_kernel<<<grid, 256, 0, s>>>((const uint8_t*)codes, n_codes, starts, B, T, x, y, err_flag);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
 extern "C" int mgb_embedding_fwd(const int64_t* idx, const void* wte, const void* wpe, void* out, int64_t B,
                                  int64_t T, int32_t C, int64_t vocab, int32_t* err_flag, mgb_stream_t s_) {
     cudaStream_t s = (cudaStream_t)s_;

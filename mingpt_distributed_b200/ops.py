@@ -145,6 +145,18 @@ def embedding_bwd(idx, dx, dwte, dwpe):
     check(_lib.lib().mgb_embedding_bwd(_p(idx), _p(dx), _p(dwte), _p(dwpe), B, T, Cdim, vocab, _stream()), "embedding_bwd")
 
 
+def token_windows(codes, starts, T, x, y, err_flag=None):
+    """x[b] = codes[starts[b] : +T], y[b] = codes[starts[b]+1 : +T] (int64) from a device-resident uint8 corpus"""
+    _chk_cuda(codes, starts, x, y, err_flag)
+    if codes.dtype != torch.uint8 or starts.dtype != torch.int64 or x.dtype != torch.int64 or y.dtype != torch.int64:
+        raise RuntimeError("token_windows: codes uint8, starts / x / y int64")
+    B = starts.numel()
+    if tuple(x.shape) != (B, T) or tuple(y.shape) != (B, T) or not x.is_contiguous() or not y.is_contiguous():
+        raise RuntimeError("token_windows: x and y must be contiguous [len(starts), T]")
+    check(_lib.lib().mgb_token_windows(_p(codes), codes.numel(), _p(starts), B, T, _p(x), _p(y), _p(err_flag), _stream()), "token_windows")
+    return x, y
+
+
 def attention_fwd(qkv, out, lse, B, T, H, d, mask_mode, scale=None):
     _chk_cuda(qkv, out, lse)
     scale = 1.0 / math.sqrt(d) if scale is None else scale

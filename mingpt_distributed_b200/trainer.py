@@ -23,6 +23,7 @@ import torch.distributed as dist
 from torch.utils.data import DataLoader, Dataset
 from torch.utils.data.distributed import DistributedSampler
 
+from .char_dataset import DeviceWindowLoader, _unwrap_subset
 from .flops import mfu, model_flops_per_token
 from .model import CfgNode
 from .optim import FusedAdamW, clip_grad_norm_
@@ -39,6 +40,11 @@ class GPTTrainerConfig:
     dl_num_workers: Optional[int] = None
     snapshot_path: Optional[str] = None
     save_every: Optional[int] = None
+    # additions (defaults keep the reference's behaviour):
+    shuffle_each_epoch: bool = False       # True: call sampler.set_epoch(epoch); the reference never does, so every
+                                           # epoch replays the same order (mingpt/trainer.py:80,135-147,174)
+    device_loader: Optional[bool] = None   # None/True: CharDataset batches are cut on the GPU from a device-resident
+                                           # corpus (DeviceWindowLoader); False: torch DataLoader as in the reference
 
 
 @dataclass
@@ -268,10 +274,10 @@ class GPTTrainer:
         self.config = config
         self.train_dataset = train_dataset
         self.test_dataset = test_dataset
-        self.train_loader = self._prepare_dataloader(train_dataset)
-        self.test_loader = self._prepare_dataloader(test_dataset) if test_dataset else None
         self.device = torch.device("cuda", self.local_rank)
         torch.cuda.set_device(self.device)
+        self.train_loader = self._prepare_dataloader(train_dataset)
+        self.test_loader = self._prepare_dataloader(test_dataset) if test_dataset else None
         self.model = model.to(self.device)
         self.optimizer = optimizer
         self.save_every = config.save_every if config.save_every else 1
@@ -302,6 +308,8 @@ class GPTTrainer:
             sampler = DistributedSampler(dataset)
         else:
             sampler = DistributedSampler(dataset, num_replicas=1, rank=0)
+        if self.config.device_loader is not False and _unwrap_subset(dataset)[0] is not None:
+            return DeviceWindowLoader(dataset, self.config.batch_size, self.device, sampler)
         workers = self.config.dl_num_workers or 0
         return DataLoader(dataset, batch_size=self.config.batch_size, pin_memory=True, shuffle=False,
                           num_workers=workers, sampler=sampler)
@@ -373,6 +381,10 @@ class GPTTrainer:
 
     def train(self) -> None:
         for epoch in range(self.last_epoch, self.config.max_epochs):
+            if self.config.shuffle_each_epoch:      # the DistributedSampler.set_epoch call the reference lacks
+                for loader in (self.train_loader, self.test_loader):
+                    if loader is not None and hasattr(loader.sampler, "set_epoch"):
+                        loader.sampler.set_epoch(epoch)
             self._run_epoch(epoch, self.train_loader, True)
             if self.local_rank == 0 and epoch % self.save_every == 0:
                 self._save_snapshot(epoch)

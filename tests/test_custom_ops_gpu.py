@@ -111,7 +111,7 @@ def test_cross_entropy_op_fwd_bwd(rows, V):
 def test_ops_chain_like_a_block():
     """the ops compose under autograd the way a transformer block chains them: LN -> linear(qkv) -> attention ->
     linear(+residual) -> LN -> linear(gelu) -> linear(+residual) -> cross entropy"""
-    B, T, H, d, V = 2, 128, 2, 64, 150
+    B, T, H, d, V = 2, 128, 2, 64, 152       # (the linear op's backward reads dY through TMA: N must be a multiple of 8)
     C = H * d
     g = torch.Generator(device="cuda").manual_seed(80)
     mk = lambda *s, sc=0.05: (torch.randn(*s, device="cuda", generator=g) * sc)

@@ -32,9 +32,10 @@ def test_gpt2_124m_T1024_loss_and_every_gradient_vs_oracle(variant):
     sd = {k: v.clone() for k, v in model.state_dict().items()}
     model = model.cuda()
     g = torch.Generator().manual_seed(1234)
-    tok = torch.randint(0, GPT2["vocab_size"], (1, 1025), generator=g)
+    B = 4      # (gradient sums over B*T rows: their bf16 rounding noise falls as 1/sqrt(rows); the bench uses B = 32)
+    tok = torch.randint(0, GPT2["vocab_size"], (B, 1025), generator=g)
     x, y = tok[:, :-1].contiguous(), tok[:, 1:].clone()
-    y[torch.rand(1, 1024, generator=g) < 0.1] = -1
+    y[torch.rand(B, 1024, generator=g) < 0.1] = -1
     osd = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
     _, oloss = go.forward(osd, GPT2["n_head"], x, y, variant)
     oloss.backward()
@@ -43,16 +44,17 @@ def test_gpt2_124m_T1024_loss_and_every_gradient_vs_oracle(variant):
     torch.cuda.synchronize()
     report(f"gpt2_T1024_{variant}_loss", got=loss.item(), want=oloss.item())
     assert abs(loss.item() - oloss.item()) < 1e-2 * oloss.item()
-    worst, worst_name = 0.0, ""
+    errs = {}
     for n, p in model.named_parameters():
         ref = osd[n].grad
         if ref.norm() < 1e-7:      # the key bias: analytically zero gradient
             continue
-        r = ((p.grad.cpu() - ref).norm() / ref.norm()).item()
-        if r > worst:
-            worst, worst_name = r, n
-        assert r < 2e-2, f"{variant} {n}: relative gradient error {r:.4f}"
-    report(f"gpt2_T1024_{variant}_worst_grad_rel", value=worst, name=worst_name)
+        errs[n] = ((p.grad.cpu() - ref).norm() / ref.norm()).item()
+    worst_name = max(errs, key=errs.get)
+    report(f"gpt2_T1024_{variant}_worst_grad_rel", value=errs[worst_name], tensor=worst_name,
+           above_1e_2=sum(v > 1e-2 for v in errs.values()), tensors=len(errs))
+    bad = {n: round(v, 4) for n, v in errs.items() if v >= 2e-2}
+    assert not bad, f"{variant}: relative gradient error >= 2e-2 for {bad}"
 
 
 def _attn_ref(qkv, H, mode, keep=None, p=0.0):

@@ -154,3 +154,33 @@ def test_cabi_library_exports_every_declared_symbol():
     assert declared == set(_lib.SIGNATURES) | set(_lib.INTROSPECTION)
     assert handle.mgb_version() == 100
     assert ctypes.sizeof(_lib.GemmArgs) == 184 and ctypes.sizeof(_lib.AdamWChunk) == 16
+
+
+def test_device_window_loader_follows_the_distributed_sampler_order():
+    """DeviceWindowLoader (host side only here): window starts == the indices torch's DistributedSampler hands the
+    reference's DataLoader (mingpt/trainer.py:73-81), per rank, through random_split Subsets (mingpt/train.py:20-22),
+    same order every epoch unless set_epoch is called (the reference never calls it)"""
+    from torch.utils.data import random_split
+    from torch.utils.data.distributed import DistributedSampler
+    data = bytes((97 + (i * 7 + i // 5) % 26) for i in range(3000))
+    ds = m.CharDataset(m.DataConfig(path=None, block_size=16, train_split=0.9, truncate=1.0), data=data)
+    for rank in (0, 1, 2):
+        sampler = DistributedSampler(ds, num_replicas=3, rank=rank)
+        loader = m.DeviceWindowLoader(ds, 64, "cpu", sampler)
+        starts = loader.window_starts()
+        assert starts.tolist() == list(iter(DistributedSampler(ds, num_replicas=3, rank=rank)))
+        assert len(loader) == (len(sampler) + 63) // 64
+        again = loader.window_starts()
+        assert torch.equal(starts, again)                       # no set_epoch -> same order (reference behaviour)
+        sampler.set_epoch(1)
+        assert not torch.equal(loader.window_starts(), starts)  # the fix behind GPTTrainerConfig.shuffle_each_epoch
+    train, test = random_split(ds, [2000, len(ds) - 2000], generator=torch.Generator().manual_seed(3))
+    sampler = DistributedSampler(test, num_replicas=1, rank=0, shuffle=False)
+    loader = m.DeviceWindowLoader(test, 32, "cpu", sampler)
+    starts = loader.window_starts()
+    assert starts.tolist() == [test.indices[i] for i in range(len(test))]
+    x0, y0 = test[5]
+    s = int(starts[5])
+    assert torch.equal(ds.codes[s:s + 16], x0) and torch.equal(ds.codes[s + 1:s + 17], y0)
+    with pytest.raises(TypeError):
+        m.DeviceWindowLoader(torch.utils.data.TensorDataset(torch.zeros(4)), 2, "cpu", None)

@@ -150,7 +150,8 @@ def test_attention_fwd_bwd(d, mode, B, T, H):
     dqkv2 = torch.full_like(qkv, float("nan")); cs = torch.ones(3 * C, device="cuda")
     ops.attention_bwd(qkv, out, dout, lse, delta, dq_acc, dqkv2, B, T, H, d, mode, dqkv_colsum=cs)
     torch.cuda.synchronize()
-    assert torch.equal(dqkv2, dqkv)
+    # (not bit-equal: dQ is summed with fp32 atomics, whose order -- and so the last bf16 bit -- changes run to run)
+    assert torch.allclose(dqkv2.float(), dqkv.float(), rtol=1.6e-2, atol=1e-3 * dqkv.float().abs().max().item())
     want_cs = qf.grad.reshape(B * T, 3 * C).sum(0)
     assert (cs - 1 - want_cs).abs().max().item() <= 2e-2 * want_cs.abs().max().item() + 2e-2, tag
 
