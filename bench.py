@@ -5,6 +5,8 @@ tokens, data parallel over N GPUs (weak scaling: per-GPU batch fixed).
 
     python bench.py --gpus N --steps K --warmup W            # our arm  (N > 1: launched by torchrun)
     python bench.py --impl reference --steps K --warmup W    # the reference's arithmetic on the host cores
+    python bench.py --model gpt2-medium | gpt2-xl --accum 4 | gpt-mini | gpt-nano   # the other BASELINE.json configs
+                                                             # (default --model gpt2 = config 3, the headline)
 
 One "step" = forward, backward (gradient all-reduce overlapped when N > 1), global-norm clip + AdamW:
 exactly GPTTrainer._run_batch (mingpt/trainer.py:118-133).  Prints ONE JSON line (rank 0).
@@ -28,6 +30,14 @@ import torch
 
 GPT2 = dict(n_layer=12, n_head=12, n_embed=768, vocab_size=50257, block_size=1024)
 NOMINAL_BF16 = 2.25e15
+# BASELINE.json configs (SURVEY.md 8, table of shapes): per-GPU batch, sequence length, vocabulary, accumulation
+MODELS = {
+    "gpt-nano": dict(dims=dict(n_layer=3, n_head=3, n_embed=48), batch=64, seq=128, vocab=65, accum=1, char=True, cfg=1),
+    "gpt-mini": dict(dims=dict(n_layer=6, n_head=6, n_embed=192), batch=64, seq=256, vocab=65, accum=1, char=True, cfg=2),
+    "gpt2": dict(dims=dict(n_layer=12, n_head=12, n_embed=768), batch=32, seq=1024, vocab=50257, accum=1, char=False, cfg=3),
+    "gpt2-medium": dict(dims=dict(n_layer=24, n_head=16, n_embed=1024), batch=32, seq=1024, vocab=50257, accum=1, char=False, cfg=4),
+    "gpt2-xl": dict(dims=dict(n_layer=48, n_head=25, n_embed=1600), batch=8, seq=1024, vocab=50257, accum=4, char=False, cfg=5),
+}
 
 
 def measured_peaks():
@@ -85,22 +95,30 @@ def make_tokens(B, T, V, seed):
     return tok[:, :-1].contiguous(), tok[:, 1:].contiguous()
 
 
+def make_corpus(n_bytes, vocab, seed):
+    """seeded synthetic byte corpus over a `vocab`-symbol alphabet (configs 1-2 are char-LMs "via CharDataset")"""
+    g = torch.Generator().manual_seed(seed)
+    alphabet = torch.arange(33, 33 + vocab, dtype=torch.uint8)
+    return bytes(alphabet[torch.randint(0, vocab, (n_bytes,), generator=g)].tolist())
+
+
 # ----------------------------------------------------------------------------------------------------
 # reference arm / cpu baseline: the oracle (a port of the reference's arithmetic) on the host cores
 # ----------------------------------------------------------------------------------------------------
-def cpu_oracle_tokens_per_s(variant: str, steps: int, warmup: int, budget_s: float, B: int = 1, T: int = 1024):
+def cpu_oracle_tokens_per_s(variant: str, steps: int, warmup: int, budget_s: float, B: int = 1, T: int = 1024, dims=None):
     from oracle import gpt_oracle as go
     import mingpt_distributed_b200 as m
+    dims = dims or GPT2
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     torch.manual_seed(0)
-    model = m.GPT(m.GPTConfig(model_type=None, embed_drop=0.0, resid_drop=0.0, attn_drop=0.0, variant=variant, **GPT2), verbose=False)
-    tr = go.OracleTrainer(model.state_dict(), GPT2["n_head"], variant)
+    model = m.GPT(m.GPTConfig(model_type=None, embed_drop=0.0, resid_drop=0.0, attn_drop=0.0, variant=variant, **dims), verbose=False)
+    tr = go.OracleTrainer(model.state_dict(), dims["n_head"], variant)
     del model
     times = []
     t_start = time.time()
     for i in range(warmup + steps):
-        x, y = make_tokens(B, T, GPT2["vocab_size"], 1234 + i)
+        x, y = make_tokens(B, T, dims["vocab_size"], 1234 + i)
         t0 = time.time()
         tr.run_batch(x, y)
         dt = time.time() - t0
@@ -117,11 +135,15 @@ def run_reference_arm(args):
     if rank != 0:
         return
     budget = 150.0
-    val, ms, cores, n, sample = cpu_oracle_tokens_per_s("reference", args.steps, min(args.warmup, 1), budget)
+    spec = MODELS[args.model]
+    dims = dict(vocab_size=spec["vocab"], block_size=spec["seq"], **spec["dims"])
+    Bc = spec["batch"] if spec["char"] else 1         # the small char-LM configs fit the host at their full batch
+    val, ms, cores, n, sample = cpu_oracle_tokens_per_s("reference", args.steps, min(args.warmup, 1), budget, B=Bc, T=spec["seq"], dims=dims)
     line = dict(impl="reference", metric="train_tokens_per_s", value=val, unit="tokens/s", n_gpus=args.gpus, steps=n,
                 warmup=min(args.warmup, 1), ms_per_step=ms, higher_is_better=True, scaling="weak", vs_baseline=None,
                 dtype="f32", data="synthetic",
-                config=dict(workload="gpt2-124M train step (L12 H12 C768 V50257 T1024)", global_batch=1, seq_len=1024,
+                config=dict(workload=f"{args.model} train step (L{dims['n_layer']} H{dims['n_head']} C{dims['n_embed']} V{dims['vocab_size']} T{dims['block_size']})",
+                            global_batch=Bc, seq_len=spec["seq"],
                             parallelism="cpu", note="the reference's as-written graph (oracle port of mingpt/model.py + trainer.py:118-133; "
                                                     "the reference itself is CUDA+NCCL-only and absent from this box)"),
                 cpu_baseline=dict(value=val, unit="tokens/s", cores=cores, kind="port", sample=sample),
@@ -138,8 +160,10 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--batch", type=int, default=32, help="sequences per GPU per step")
-    ap.add_argument("--seq", type=int, default=1024)
+    ap.add_argument("--model", default="gpt2", choices=list(MODELS), help="BASELINE.json config; gpt2 (config 3) is the headline")
+    ap.add_argument("--batch", type=int, default=0, help="sequences per GPU per micro-step (0 = the config's)")
+    ap.add_argument("--seq", type=int, default=0)
+    ap.add_argument("--accum", type=int, default=0, help="gradient-accumulation micro-steps per optimizer step (0 = the config's)")
     ap.add_argument("--variant", default="mingpt")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=25.0)
@@ -147,6 +171,7 @@ def main():
     ap.add_argument("--quick", action="store_true", help="timed loop only (for runs under ncu): no e2e, roofline or cpu legs")
     ap.add_argument("--dropout", type=float, default=0.0, help="embed/resid/attn dropout (reference default 0.1); headline is 0")
     ap.add_argument("--no-graph", action="store_true", help="issue every kernel from Python instead of replaying a CUDA graph")
+    ap.add_argument("--opt", action="append", default=[], help="library option key=value (mgb_set_option), repeatable")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -161,14 +186,16 @@ def main():
 
     import torch.distributed as dist
     import mingpt_distributed_b200 as m
+    from mingpt_distributed_b200 import _lib, ops
+    opts = dict(kv.split("=") for kv in args.opt)
     for key in ("pdl",):                           # experiment knobs: MGB_OPT_PDL=0 python bench.py ...
         val = os.environ.get("MGB_OPT_" + key.upper())
         if val is not None:
-            from mingpt_distributed_b200 import _lib as _l
-            _l.set_option(key, int(val))
-    from mingpt_distributed_b200 import _lib, ops
-    from oracle import gpt_oracle as go
+            opts.setdefault(key, val)
+    for key, val in opts.items():
+        _lib.set_option(key, int(val))
 
+    spec = MODELS[args.model]
     rank = int(os.environ.get("RANK", 0))
     local = int(os.environ.get("LOCAL_RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -176,34 +203,66 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    B, T, V = args.batch, args.seq, GPT2["vocab_size"]
+    B = args.batch or spec["batch"]
+    T = args.seq or spec["seq"]
+    K = args.accum or spec["accum"]
+    V = spec["vocab"]
+    dims = dict(vocab_size=V, block_size=T, **spec["dims"])
+    headline = args.model == "gpt2" and B == 32 and T == 1024 and K == 1 and args.variant == "mingpt"
 
     torch.manual_seed(0)
     cfg = m.GPTConfig(model_type=None, embed_drop=args.dropout, resid_drop=args.dropout, attn_drop=args.dropout,
-                      variant=args.variant, **GPT2)
+                      variant=args.variant, **dims)
     model = m.GPT(cfg, verbose=False)
     opt = m.create_optimizer(model, m.OptimizerConfig())
     model = model.to(dev)
     dp = m.DataParallel(model) if world > 1 else None
 
     nbatches = 4
-    host = [make_tokens(B, T, V, 1234 + rank + 100 * i) for i in range(nbatches)]
-    pinned = [(x.pin_memory(), y.pin_memory()) for x, y in host]
-    resident = [(x.to(dev), y.to(dev)) for x, y in host]
+    loader = None
+    if spec["char"]:
+        # configs 1-2 are char-LMs "via CharDataset": a seeded synthetic byte corpus, encoded once, resident on the
+        # device; a batch is cut out of it by the window-gather kernel from host-chosen window starts
+        ds = m.CharDataset(m.DataConfig(path=None, block_size=T, train_split=0.9, truncate=1.0), data=make_corpus(1 << 20, V, 7 + rank))
+        codes = ds.device_codes(dev)
+        g = torch.Generator().manual_seed(1234 + rank)
+        starts_host = [torch.randint(0, len(ds), (K * B,), generator=g).pin_memory() for _ in range(nbatches)]
+        err = torch.zeros(1, dtype=torch.int32, device=dev)
 
-    stepper = m.GraphedTrainStep(model, opt, 1.0, dp, use_graph=not args.no_graph)
+        def cut(starts_dev):
+            x = torch.empty(K * B, T, dtype=torch.int64, device=dev); y = torch.empty_like(x)
+            ops.token_windows(codes, starts_dev, T, x, y, err)
+            return x, y
+        resident = [cut(s.to(dev)) for s in starts_host]
+        h2d_bytes = K * B * 8
+    else:
+        host = [make_tokens(K * B, T, V, 1234 + rank + 100 * i) for i in range(nbatches)]
+        pinned = [(x.pin_memory(), y.pin_memory()) for x, y in host]
+        resident = [(x.to(dev), y.to(dev)) for x, y in host]
+        h2d_bytes = 2 * K * B * T * 8
+
+    stepper = m.GraphedTrainStep(model, opt, 1.0, dp, use_graph=not args.no_graph, accum=K)
 
     def step_resident(i):
         x, y = resident[i % nbatches]
         return stepper(x, y)
 
     def step_e2e(i):
-        x, y = pinned[i % nbatches]          # pinned host tokens -> static device buffers (H2D inside the step)
+        if spec["char"]:                     # pinned host window starts -> device -> gather kernel -> step
+            x, y = cut(starts_host[i % nbatches].to(dev, non_blocking=True))
+        else:
+            x, y = pinned[i % nbatches]      # pinned host tokens -> static device buffers (H2D inside the step)
         return stepper(x, y).item()          # device -> host read of the loss every step
 
     def step_eager(i):
         x, y = resident[i % nbatches]
-        return m.train_step(model, opt, x, y, 1.0, dp, zero_grad=True)
+        if K == 1:
+            return m.train_step(model, opt, x, y, 1.0, dp, zero_grad=True)
+        for p in model.parameters():
+            p.grad = None
+        for k in range(K):
+            last = k == K - 1
+            m.train_step(model, opt, x[k * B:(k + 1) * B], y[k * B:(k + 1) * B], 1.0, dp, accumulate=not last, loss_div=float(K))
 
     def barrier():
         if world > 1:
@@ -225,8 +284,8 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = t.item()
         n = _lib.launch_count() - n0
-        if n == 0:     # CUDA-graph replays: the kernels were recorded once, at capture
-            n = stepper.launches_per_replay((B, T)) * steps
+        if stepper.use_graph:     # CUDA-graph replays: the kernels were recorded once, at capture
+            n += stepper.launches_per_replay((K * B, T)) * steps
         return ms, n
 
     for i in range(args.warmup):
@@ -244,7 +303,7 @@ def main():
         ms_e2e, _ = timed(step_e2e, args.steps)
     clocks = sampler.stop() if rank == 0 else None
     ms_step = ms_total / args.steps
-    tokens_per_step = world * B * T
+    tokens_per_step = world * K * B * T
     value = tokens_per_step / (ms_step / 1000.0)
     e2e_value = tokens_per_step / (ms_e2e / args.steps / 1000.0)
 
@@ -257,12 +316,12 @@ def main():
 
         def timed_gemm(a, b, out, **kw):
             M, N = out.shape
-            K = a.shape[0] if kw.get("a_mn") else a.shape[1]
+            Kd = a.shape[0] if kw.get("a_mn") else a.shape[1]
             s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             s.record()
             r = orig(a, b, out, **kw)
             e.record()
-            records.append((2.0 * M * N * K, s, e))
+            records.append((2.0 * M * N * Kd, s, e))
             return r
 
         ops.gemm = timed_gemm
@@ -278,48 +337,56 @@ def main():
         finally:
             ops.gemm = orig
         # DRAM traffic per launch from the committed ncu --set full capture of every GEMM shape of the step
-        # (tools/gemm_ncu.py -> profiles/r1_e_gemm_shapes_ncu.json), weighted by how often each shape runs
-        traffic, traffic_alg = None, None
-        tpath = os.path.join(ROOT, "profiles", "r1_e_gemm_shapes_ncu.json")
-        if os.path.exists(tpath) and B == 32 and T == 1024 and args.variant == "mingpt":
-            shapes = json.load(open(tpath))
-            weights = [2 if s["name"].startswith("head") else GPT2["n_layer"] for s in shapes]
-            traffic = sum(w * s["dram_bytes"] for w, s in zip(weights, shapes)) / sum(weights)
-            traffic_alg = sum(w * s["algorithmic_bytes"] for w, s in zip(weights, shapes)) / sum(weights)
+        # (tools/gemm_ncu.py -> profiles/*_gemm_shapes_ncu.json), weighted by how often each shape runs
+        traffic, traffic_alg, tsrc = None, None, None
+        for name in ("r2_gemm_shapes_ncu.json", "r1_e_gemm_shapes_ncu.json"):
+            tpath = os.path.join(ROOT, "profiles", name)
+            if os.path.exists(tpath) and headline:
+                shapes = json.load(open(tpath))
+                weights = [2 if sh["name"].startswith("head") else GPT2["n_layer"] for sh in shapes]
+                traffic = sum(w * sh["dram_bytes"] for w, sh in zip(weights, shapes)) / sum(weights)
+                traffic_alg = sum(w * sh["algorithmic_bytes"] for w, sh in zip(weights, shapes)) / sum(weights)
+                tsrc = f"profiles/{name} (ncu --set full, dram read+write, mean per launch)"
+                break
         flops = sum(r[0] for r in records)
         gemm_ms = sum(r[1].elapsed_time(r[2]) for r in records)
         step_ms_instr = t0.elapsed_time(t1)
         achieved = flops / (gemm_ms / 1000.0) / 1e12
-        roof = dict(bound="tensor", kernel="mgb::gemm::gemm_kernel (all %d launches of a step)" % (len(records) // 2),
+        roof = dict(bound="tensor", kernel="mgb::gemm::gemm_pair_kernel (all %d launches of a step)" % (len(records) // 2),
                     achieved=achieved, peak=peaks["bf16_sustained"], unit="TFLOP/s", frac=achieved / peaks["bf16_sustained"],
                     peak_source=peaks["source"] + " bf16_tflops_sustained (kernel timed inside a long step)",
                     frac_of_nominal=achieved * 1e12 / NOMINAL_BF16, traffic=traffic, traffic_algorithmic=traffic_alg,
-                    traffic_source="profiles/r1_e_gemm_shapes_ncu.json (ncu --set full, dram read+write, mean per launch)",
+                    traffic_source=tsrc,
                     share_of_step=gemm_ms / step_ms_instr, flops_per_launch_avg=flops / max(len(records), 1),
                     ms_per_launch_avg=gemm_ms / max(len(records), 1))
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v_ref, ms_ref, cores, n, sample = cpu_oracle_tokens_per_s("reference", 2, 1, args.cpu_budget)
+        Bc = B if spec["char"] else 1
+        v_ref, ms_ref, cores, n, sample = cpu_oracle_tokens_per_s("reference", 2, 1, args.cpu_budget, B=Bc, T=T, dims=dims)
         cpu = dict(value=v_ref, unit="tokens/s", cores=cores, kind="port",
                    sample="reference's as-written graph via the oracle port: " + sample)
 
     if rank == 0:
-        f_tok = go.flops_per_token(GPT2["n_layer"], GPT2["n_embed"], V, T, args.variant)
+        f_tok = m.flops_per_token(dims["n_layer"], dims["n_embed"], V, T, args.variant)
         line = dict(metric="train_tokens_per_s", value=value, unit="tokens/s", n_gpus=world, steps=args.steps,
                     warmup=args.warmup, ms_per_step=ms_step, higher_is_better=True, scaling="weak", vs_baseline=None,
                     dtype="bf16", data="synthetic",
-                    config=dict(workload=f"gpt2-124M train step (L12 H12 C768 V50257 T{T}), variant={args.variant}, "
-                                         "fp32 master weights + AdamW state, bf16 GEMM/attention operands",
-                                global_batch=world * B, seq_len=T, parallelism=f"dp{world}", dropout=args.dropout,
+                    config=dict(workload=f"{args.model} train step (BASELINE.json config {spec['cfg']}: L{dims['n_layer']} H{dims['n_head']} "
+                                         f"C{dims['n_embed']} V{V} T{T}), variant={args.variant}, "
+                                         "fp32 master weights + AdamW state, bf16 GEMM/attention operands"
+                                         + (", tokens cut from a device-resident synthetic byte corpus (CharDataset)" if spec["char"] else ""),
+                                global_batch=world * K * B, micro_batch_per_gpu=B, accumulation_steps=K, seq_len=T,
+                                parallelism=f"dp{world}", dropout=args.dropout, options=opts,
                                 launch=("eager (one Python call per kernel)" if not stepper.use_graph else
                                         "CUDA graph replay of the whole step" if dp is None else
                                         "CUDA graph segments cut at gradient-bucket boundaries, NCCL all-reduces launched between them"),
-                                l2="per-step working set (>10 GB of activations + 2 GB of parameters/state) is far larger than the 126 MB L2"),
+                                l2="per-step working set (activations + parameters / optimizer state, GBs) is far larger than the 126 MB L2"
+                                   if not spec["char"] else "inputs rotate over 4 batches; working set of the small char-LM configs partly fits the 126 MB L2"),
                     mfu=dict(flops_per_token=f_tok, of_nominal_2p25pf=value * f_tok / (world * NOMINAL_BF16),
                              of_measured_sustained=value * f_tok / (world * peaks["bf16_sustained"] * 1e12)),
                     clocks=clocks,
-                    e2e=dict(value=e2e_value, unit="tokens/s", h2d_bytes_per_step=2 * B * T * 8, d2h_bytes_per_step=4,
+                    e2e=dict(value=e2e_value, unit="tokens/s", h2d_bytes_per_step=h2d_bytes, d2h_bytes_per_step=4,
                              ms_per_step=ms_e2e / args.steps),
                     gpu_launches=launches, roofline=roof, cpu_baseline=cpu)
         sys.stdout.flush()

@@ -169,6 +169,14 @@ int mgb_attention_bwd_colsum(const void* qkv, const void* out, const void* dout,
                              float* dq_accum, void* dqkv, float* dqkv_colsum, int32_t B, int32_t T, int32_t H,
                              int32_t d, int32_t mask_mode, float scale, mgb_stream_t stream);
 
+/* Incremental decode for GPT.generate (mingpt/model.py:322-356; the reference re-runs the whole window for every
+ * new token, :334-339): attention of ONE new position per sequence against cached keys / values.
+ * qkv_cache bf16 [B, Tcap, 3, H, d] -- the packed in-proj layout; row `pos` of every sequence holds the new token's
+ * q / k / v (the caller's qkv GEMM writes it there), rows 0..pos-1 the earlier tokens' k / v. Causal attention of the
+ * last position sees every cached key, so there is no mask. out bf16 [B, H*d]. fp32 softmax. */
+int mgb_attention_decode(const void* qkv_cache, void* out, int32_t B, int32_t Tcap, int32_t pos, int32_t H,
+                         int32_t d, float scale, mgb_stream_t stream);
+
 /* Dropout (the reference trains with p = 0.1 at four sites and never calls eval(): mingpt/model.py:49-51,140,
  * 150,183,215). Masks are counter based (Philox4x32-10 over (seed, site, element)) and never stored: the
  * backward regenerates them. *seed_dev is a DEVICE uint64 the caller changes every step; `site` tells the

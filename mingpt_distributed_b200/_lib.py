@@ -61,6 +61,7 @@ SIGNATURES = {
     "mgb_attention_bwd": [_P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _P],
     "mgb_attention_bwd_colsum": [_P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _P],
     "mgb_attention_bwd_noalloc": [_P, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _P],
+    "mgb_attention_decode": [_P, _P, _I32, _I32, _I32, _I32, _I32, _F, _P],
     "mgb_dropout_bf16": [_P, _P, _P, _I64, _F, _P, C.c_uint32, _P],
     "mgb_attention_fwd_dropout": [_P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _F, _P, C.c_uint32, _P],
     "mgb_attention_bwd_dropout": [_P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _F, _P, C.c_uint32, _P],

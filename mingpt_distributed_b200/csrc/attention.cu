@@ -728,6 +728,111 @@ extern "C" int mgb_attention_bwd_noalloc(const void* qkv, const void* out, const
 }
 
 // =====================================================================================
+// incremental decode: ONE new query per sequence against the cached keys / values
+// (GPT.generate, mingpt/model.py:322-356, which recomputes the whole window for every token)
+// =====================================================================================
+namespace mgb {
+namespace attn {
+constexpr int DEC_THREADS = 128;
+// CTA = one (batch, head). The cache has the packed in-proj layout [B, Tcap, 3, H, d] (what the qkv GEMM writes), the
+// query is row `pos`, keys / values are rows 0 .. pos -- causal attention of the last position, so no mask is needed.
+// fp32 scores in shared memory; thread = key for the scores, thread = (8 features, key group) for P V.
+template <int D>
+__global__ void __launch_bounds__(DEC_THREADS)
+attn_decode_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int Tcap, int pos, int H,
+                   float scale_log2) {
+    extern __shared__ float dsm[];
+    float* sc = dsm;                               // [pos + 1] scores, then probabilities
+    float* qs = sc + ((pos + 1 + 3) & ~3);         // [D] query, pre-scaled
+    float* red = qs + D;                           // [8] block reductions
+    float* part = red + 8;                         // [NG][D] partial outputs
+    constexpr int CH = D / 8, NG = DEC_THREADS / CH;
+    const int b = blockIdx.x / H, h = blockIdx.x - b * H;
+    const int C = H * D;
+    const int64_t row_stride = (int64_t)3 * C;
+    const __nv_bfloat16* base = qkv + (int64_t)b * Tcap * row_stride + (int64_t)h * D;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = pos + 1;
+    if (tid < D) qs[tid] = __bfloat162float(base[(int64_t)pos * row_stride + tid]) * scale_log2;
+    __syncthreads();
+    float mx = -INFINITY;
+    for (int key = tid; key < n; key += DEC_THREADS) {
+        const __nv_bfloat16* kp = base + (int64_t)key * row_stride + C;
+        float dot = 0.f;
+#pragma unroll
+        for (int c = 0; c < CH; ++c) {
+            const uint4 kv = ldg128(kp + c * 8);
+            const uint32_t w[4] = {kv.x, kv.y, kv.z, kv.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 f = unpack_bf16x2(w[e]);
+                dot = fmaf(f.x, qs[c * 8 + 2 * e], dot);
+                dot = fmaf(f.y, qs[c * 8 + 2 * e + 1], dot);
+            }
+        }
+        sc[key] = dot;
+        mx = fmaxf(mx, dot);
+    }
+    mx = warp_max(mx);
+    if (lane == 0) red[warp] = mx;
+    __syncthreads();
+    mx = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
+    float sum = 0.f;
+    for (int key = tid; key < n; key += DEC_THREADS) {
+        const float p = exp2f(sc[key] - mx);
+        sc[key] = p;
+        sum += p;
+    }
+    sum = warp_sum(sum);
+    if (lane == 0) red[4 + warp] = sum;
+    __syncthreads();
+    const float inv = 1.0f / (red[4] + red[5] + red[6] + red[7]);
+    const int ch = tid % CH, grp = tid / CH;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int key = grp; key < n; key += NG) {
+        const uint4 vv = ldg128(base + (int64_t)key * row_stride + 2 * C + ch * 8);
+        const uint32_t w[4] = {vv.x, vv.y, vv.z, vv.w};
+        const float p = sc[key];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const float2 f = unpack_bf16x2(w[e]);
+            acc[2 * e] = fmaf(p, f.x, acc[2 * e]);
+            acc[2 * e + 1] = fmaf(p, f.y, acc[2 * e + 1]);
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) part[grp * D + ch * 8 + e] = acc[e];
+    __syncthreads();
+    if (tid < D) {
+        float o = 0.f;
+        for (int g = 0; g < NG; ++g) o += part[g * D + tid];
+        out[(int64_t)b * C + (int64_t)h * D + tid] = __float2bfloat16(o * inv);
+    }
+}
+}  // namespace attn
+}  // namespace mgb
+
+extern "C" int mgb_attention_decode(const void* qkv_cache, void* out, int32_t B, int32_t Tcap, int32_t pos, int32_t H,
+                                    int32_t d, float scale, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    int rc = check_attn_shape("decode", B, Tcap, H, d, MGB_MASK_CAUSAL);
+    if (rc) return rc;
+    if (pos < 0 || pos >= Tcap) { set_last_error("attention_decode: pos outside the cache"); return kErrBadShape; }
+    if ((uintptr_t)qkv_cache % 16) { set_last_error("attention: pointers must be 16-byte aligned"); return kErrBadAlign; }
+    const int ng = attn::DEC_THREADS / (d / 8);
+    const size_t smem = (size_t)(((pos + 1 + 3) & ~3) + d + 8 + ng * d) * sizeof(float);
+    if (smem > 48 * 1024) { set_last_error("attention_decode: cache too long for the score buffer"); return kErrTooLarge; }
+    const float sl = scale * attn::LOG2E;
+    dim3 grid(B * H);
+    if (d == 64) attn::attn_decode_kernel<64><<<grid, attn::DEC_THREADS, smem, s>>>((const __nv_bfloat16*)qkv_cache, (__nv_bfloat16*)out, Tcap, pos, H, sl);
+    else if (d == 32) attn::attn_decode_kernel<32><<<grid, attn::DEC_THREADS, smem, s>>>((const __nv_bfloat16*)qkv_cache, (__nv_bfloat16*)out, Tcap, pos, H, sl);
+    else attn::attn_decode_kernel<16><<<grid, attn::DEC_THREADS, smem, s>>>((const __nv_bfloat16*)qkv_cache, (__nv_bfloat16*)out, Tcap, pos, H, sl);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+// =====================================================================================
 // attention with dropout on the probabilities (training with attn_drop > 0, the reference's default 0.1)
 // =====================================================================================
 namespace mgb {

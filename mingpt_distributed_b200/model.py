@@ -267,6 +267,24 @@ class _Workspace:
             self.dtmp = torch.empty(M, C, dtype=torch.bfloat16, device=dev)
 
 
+class _DecodeState:
+    """Key / value cache and one-row activations for incremental decoding (GPT.generate with use_cache): per layer a
+    packed qkv buffer [B, block_size, 3C] -- the layout the attention kernels read -- whose row t holds position t."""
+
+    def __init__(self, model: "GPT", B: int):
+        dev = model._flat.device
+        C, L = model.n_embed, model.n_layer
+        bf = lambda *s: torch.empty(*s, dtype=torch.bfloat16, device=dev)
+        f32 = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
+        self.B, self.cap = B, model.block_size
+        self.cache = [bf(B, self.cap, 3 * C) for _ in range(L)]
+        self.x, self.xmid, self.ln, self.att = bf(B, C), bf(B, C), bf(B, C), bf(B, C)
+        self.fc = bf(B, 4 * C)
+        self.mean, self.rstd = f32(B), f32(B)
+        self.logits = f32(B, model.vocab_size)
+        self.err_flag = torch.zeros(1, dtype=torch.int32, device=dev)
+
+
 class _LossFn(torch.autograd.Function):
     """Ties the fused forward to autograd: loss.backward() (mingpt/trainer.py:127) lands here and runs
     the hand-scheduled backward, which writes into the flat gradient buffer and sets p.grad views."""
@@ -850,31 +868,71 @@ class GPT(nn.Module):
                              betas=tuple(getattr(train_config, "betas", (0.9, 0.95))))
         return create_optimizer(self, oc)
 
+    def _decode_step(self, st: _DecodeState, tok: torch.Tensor, pos: int) -> torch.Tensor:
+        """One new token per sequence at position `pos` through the whole stack against the cache: every layer is
+        M = B rows (LayerNorm, the single-CTA tcgen05 GEMM, the decode attention kernel). Returns fp32 logits [B, V]."""
+        C, H, d, L, B = self.n_embed, self.n_head, self.head_dim, self.n_layer, st.B
+        W = lambda r: self._w(r, bf16=True)
+        P = lambda r: self._w(r)
+        wpe = W("wpe").view(-1, C)
+        ops.embedding_fwd(tok.view(B, 1), W("wte"), wpe[pos:pos + 1], st.x.view(B, 1, C), st.err_flag)
+        for l in range(L):
+            ops.layernorm_fwd(st.x, P(f"{l}.ln1_w"), P(f"{l}.ln1_b"), st.ln, st.mean, st.rstd)
+            ops.linear_fwd(st.ln, W(f"{l}.qkv_w"), st.cache[l][:, pos, :], bias=P(f"{l}.qkv_b"))   # q | k | v of the new token
+            ops.attention_decode(st.cache[l], st.att, B, st.cap, pos, H, d)
+            ops.linear_fwd(st.att, W(f"{l}.proj_w"), st.xmid, bias=P(f"{l}.proj_b"), residual=st.x)
+            ops.layernorm_fwd(st.xmid, P(f"{l}.ln2_w"), P(f"{l}.ln2_b"), st.ln, st.mean, st.rstd)
+            ops.linear_fwd(st.ln, W(f"{l}.fc_w"), st.fc, bias=P(f"{l}.fc_b"), act=ops.ACT_GELU_TANH)
+            ops.linear_fwd(st.fc, W(f"{l}.fc2_w"), st.x, bias=P(f"{l}.fc2_b"), residual=st.xmid)
+        ops.layernorm_fwd(st.x, P("lnf_w"), P("lnf_b"), st.ln, st.mean, st.rstd)
+        ops.linear_fwd(st.ln, W("head_w"), st.logits)
+        return st.logits
+
     @torch.no_grad()
-    def generate(self, idx, max_new_tokens, temperature=1.0, do_sample=False, top_k=None):
-        """mingpt/model.py:322-356 (full-window recompute per token, as the reference does), except that
-        only the last position goes through the head GEMM."""
+    def generate(self, idx, max_new_tokens, temperature=1.0, do_sample=False, top_k=None, use_cache=True):
+        """mingpt/model.py:322-356. The reference re-runs the whole window for every new token (:334-339); here the
+        prompt is run once (prefill: the training forward's kernels, keeping every layer's keys / values) and each
+        further token is ONE row through the stack against that cache (`_decode_step`) -- as long as the sequence
+        fits block_size. Beyond it the reference crops to the last block_size tokens (:336-337), which moves every
+        token to a new learned position: the cache is then void by construction and each token is a full-window
+        forward, as in the reference. `variant="reference"` never uses the cache: its attention is not causal
+        (SURVEY Q1), so a new token changes every earlier position's output. Only the last position goes through
+        the head GEMM either way."""
         was_training = self.training
         if any(p > 0 for p in self.drop_p):
             self.eval()
+        cached = use_cache and self.variant == "mingpt"
+        state: Optional[_DecodeState] = None
+
+        def pick(logits):
+            logits = logits / temperature
+            if top_k is not None:
+                v, _ = torch.topk(logits, top_k)
+                logits[logits < v[:, [-1]]] = -float("Inf")
+            probs = torch.softmax(logits, dim=-1)
+            if do_sample:
+                return torch.multinomial(probs, num_samples=1)
+            return torch.topk(probs, k=1, dim=-1)[1]
+
         try:
             for _ in range(max_new_tokens):
-                idx_cond = idx if idx.size(1) <= self.block_size else idx[:, -self.block_size:]
                 self._ensure_device_state()
-                B, T = idx_cond.shape
-                ws = self._ws(B, T)
-                ws.generation += 1
-                self._trunk(ws, idx_cond.contiguous().long())
-                logits = self._head_logits(ws, last_only=True) / temperature
-                if top_k is not None:
-                    v, _ = torch.topk(logits, top_k)
-                    logits[logits < v[:, [-1]]] = -float("Inf")
-                probs = torch.softmax(logits, dim=-1)
-                if do_sample:
-                    idx_next = torch.multinomial(probs, num_samples=1)
+                T_all = idx.size(1)
+                if cached and state is not None and T_all <= self.block_size:
+                    logits = self._decode_step(state, idx[:, -1].contiguous().long(), T_all - 1).clone()
                 else:
-                    _, idx_next = torch.topk(probs, k=1, dim=-1)
-                idx = torch.cat((idx, idx_next), dim=1)
+                    idx_cond = idx if T_all <= self.block_size else idx[:, -self.block_size:]
+                    B, T = idx_cond.shape
+                    ws = self._ws(B, T)
+                    ws.generation += 1
+                    self._trunk(ws, idx_cond.contiguous().long())
+                    logits = self._head_logits(ws, last_only=True)
+                    state = None
+                    if cached and T_all < self.block_size:      # prefill: keep the keys / values of every layer
+                        state = _DecodeState(self, B)
+                        for l in range(self.n_layer):
+                            state.cache[l][:, :T, :].copy_(ws.qkv[l].view(B, T, -1))
+                idx = torch.cat((idx, pick(logits)), dim=1)
         finally:
             self.train(was_training)
         return idx

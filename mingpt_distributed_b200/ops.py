@@ -176,6 +176,14 @@ def attention_bwd(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, d, mask_m
     return dqkv
 
 
+def attention_decode(qkv_cache, out, B, Tcap, pos, H, d, scale=None):
+    """one new query per sequence (row `pos` of the cache) against cached keys / values 0..pos; out bf16 [B, H*d]"""
+    _chk_cuda(qkv_cache, out)
+    scale = 1.0 / math.sqrt(d) if scale is None else scale
+    check(_lib.lib().mgb_attention_decode(_p(qkv_cache), _p(out), B, Tcap, pos, H, d, scale, _stream()), "attention_decode")
+    return out
+
+
 def attention_bwd_noalloc(qkv, out, dout, lse, dqkv, B, T, H, d, mask_mode, scale=None):
     """attention_bwd for callers with no scratch to offer (a plugin in a process with a fixed device pool, a
     pointer-forwarding FFI stub): delta / dQ accumulator come from a fixed array inside the library, so B*T*H*d

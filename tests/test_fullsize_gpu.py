@@ -180,3 +180,14 @@ def test_loss_trajectory_200_steps_head_size_64(variant):
     report(f"traj200_d64_{variant}", max_rel_dev=dev, first=ours[0], last=ours[-1], oracle_last=theirs[-1])
     assert theirs[-1] < 0.5 * theirs[0], "the oracle itself must learn the pattern"
     assert dev < 1e-2, f"trajectory deviates {dev:.4f}"
+    # greedy generation on the trained model: KV-cached decode == full-window recompute == oracle, bit for bit
+    prompt, _ = _periodic_batch(9999, 4, 8, V)
+    osd = {k: v.detach() for k, v in oracle.sd.items()}
+    idx = prompt.clone()
+    for _ in range(40):
+        lg, _ = go.forward(osd, H, idx[:, -blk:], None, variant)
+        idx = torch.cat([idx, lg[:, -1].argmax(-1, keepdim=True)], 1)
+    cached = model.generate(prompt.cuda(), 40).cpu()
+    full = model.generate(prompt.cuda(), 40, use_cache=False).cpu()
+    report(f"generate_d64_{variant}", cached_match=float((cached == idx).float().mean()), uncached_match=float((full == idx).float().mean()))
+    assert torch.equal(full, idx) and torch.equal(cached, idx)

@@ -158,6 +158,19 @@ def test_loss_trajectory_200_steps_and_greedy_generate(variant):
     got = model.generate(prompt.cuda(), 24).cpu()
     report(f"generate_{variant}", match=float((got == idx).float().mean()))
     assert torch.equal(got, idx), f"greedy tokens differ from the oracle's ({variant})"
+    # KV-cached incremental decode (variant "mingpt"; the as-written graph is not causal and never caches) vs the
+    # full-window recompute the reference does, and across the block_size boundary where the window starts to slide
+    uncached = model.generate(prompt.cuda(), 24, use_cache=False).cpu()
+    assert torch.equal(uncached, idx)
+    long_prompt, _ = _periodic_batch(4242, 3, blk - 5, V)
+    idx2 = long_prompt.clone()
+    for _ in range(12):
+        lg, _ = go.forward(osd, H, idx2[:, -blk:], None, variant)
+        idx2 = torch.cat([idx2, lg[:, -1].argmax(-1, keepdim=True)], 1)
+    a = model.generate(long_prompt.cuda(), 12).cpu()
+    b = model.generate(long_prompt.cuda(), 12, use_cache=False).cpu()
+    report(f"generate_sliding_{variant}", cached_match=float((a == idx2).float().mean()), uncached_match=float((b == idx2).float().mean()))
+    assert torch.equal(a, idx2) and torch.equal(b, idx2)
 
 
 def test_fixture_trajectory_and_generate_reference_variant():
