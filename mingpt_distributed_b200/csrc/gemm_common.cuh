@@ -33,6 +33,7 @@ struct Params {
     int32_t tma_store;       // CTA-pair kernel only: D (and preact) leave through smem + TMA
     int32_t m_fast;          // CTA-pair kernel only: tile raster order (1 = m index fastest)
     int32_t tma_aux;         // CTA-pair kernel only: 1 residual / 2 gate arrives through TMA, updated in place
+    int32_t epi_slots;       // CTA-pair kernel only: 4 KiB staging slots per epilogue warp (2, or 3 with an aux tile)
     // epilogue
     void* d;
     int64_t ldd;
