@@ -10,21 +10,18 @@
 // Per CTA:  warp 0 TMA producer (own A rows, own half of B; bytes are credited to the LEADER's barrier),
 //           warp 1 MMA issuer (leader CTA only; commits are multicast to both CTAs' barriers),
 //           warp 2 TMEM allocator, warps 4-11 epilogue for this CTA's 128 rows.
-// Epilogue: eight warps per CTA, each on its OWN: a warp owns 32 output rows (its TMEM lane quarter) of every other
-//           128-byte column slice, stages a slice in a private ring of 128B-swizzled 4 KiB slots and TMA-STORES it
-//           itself (or TMA-reduce-adds it in fp32 for split-K / accumulation) -- no CTA-wide barrier anywhere, so one
-//           warp's store drain overlaps the others' math. TMEM loads run one 32-column chunk ahead of the math. The
-//           residual / gate tile is TMA-LOADED into the slot one slice ahead and updated in place (TMEM ->
-//           registers -> bias, GELU, gate, residual). A second output (the saved pre-activation or GELU') goes out
-//           straight from the registers, 64 contiguous bytes per thread.
+// Epilogue: all global traffic of the epilogue goes through 128B-swizzled shared-memory boxes and TMA:
+//           the residual / gate tile is TMA-LOADED into the box while the tile's MMAs still run, each
+//           thread then updates its own row in place (TMEM -> registers -> bias, GELU, gate, residual) and
+//           one thread TMA-STORES the box (or TMA-reduce-adds it in fp32 for split-K / accumulation).
 #include "gemm_common.cuh"
 
 namespace mgb {
 namespace gemm {
 
 constexpr int kMaxStages = 8;
-constexpr int kSlotBytes = 32 * 128;           // one epilogue warp's staging slot: 32 rows x 128 bytes
-constexpr int kMaxEpiSlots = 3;               // slots per epilogue warp (2 in use without an aux tile)
+constexpr int kBoxBytes = 128 * 128;          // 128 rows x 128 bytes
+constexpr int kNumBoxes = 4;                  // two per epilogue half
 constexpr int kSmemLimit = 232448;            // 227 KiB
 
 // Fallback epilogue for outputs TMA cannot address (row pitch not a multiple of 16 bytes): registers -> global.
@@ -118,16 +115,15 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const int block_n = p.block_n;
     const int nb = block_n >> 1;                               // B columns staged by this CTA
     const uint32_t stage_bytes = BLOCK_M * BLOCK_K * 2 + (uint32_t)nb * BLOCK_K * 2;
-    uint8_t* boxes = smem + p.num_stages * stage_bytes;        // kEpiWarps rings of epi_slots x 4 KiB, 1024-aligned
-    const int kRingBytes = kEpiWarps * p.epi_slots * kSlotBytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(boxes + kRingBytes);
+    uint8_t* boxes = smem + p.num_stages * stage_bytes;        // kNumBoxes x 16 KiB, 1024-aligned
+    uint64_t* bars = reinterpret_cast<uint64_t*>(boxes + kNumBoxes * kBoxBytes);
     uint64_t* full_bar = bars;                       // [kMaxStages]  (leader's copy is the live one)
     uint64_t* empty_bar = bars + kMaxStages;         // [kMaxStages]
     uint64_t* tmem_full = bars + 2 * kMaxStages;     // [2]
     uint64_t* tmem_empty = tmem_full + 2;            // [2]           (leader's copy is the live one)
-    uint64_t* aux_bar = tmem_empty + 2;              // [kEpiWarps][kMaxEpiSlots] residual / gate tile landed in that slot
-    uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(aux_bar + kEpiWarps * kMaxEpiSlots);
-    float* cs_smem = reinterpret_cast<float*>(boxes + kRingBytes + 512);   // [256] (COLSUM only)
+    uint64_t* aux_bar = tmem_empty + 2;              // [kNumBoxes]   residual / gate tile landed in box i
+    uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(aux_bar + kNumBoxes);
+    float* cs_smem = reinterpret_cast<float*>(boxes + kNumBoxes * kBoxBytes + 512);   // [256] (COLSUM only)
     if (COLSUM) {
         for (int c = threadIdx.x; c < 256; c += blockDim.x) cs_smem[c] = 0.f;
     }
@@ -144,6 +140,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         tma_prefetch_desc(&tmap_b);
         if (p.tma_store) {
             tma_prefetch_desc(&tmap_d);
+            if (p.preact) tma_prefetch_desc(&tmap_p);
             if (p.tma_aux) tma_prefetch_desc(&tmap_x);
         }
     }
@@ -156,7 +153,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             mbar_init(&tmem_full[s], 1);
             mbar_init(&tmem_empty[s], 2 * kEpiWarps);   // epilogue warps of BOTH CTAs
         }
-        for (int s = 0; s < kEpiWarps * kMaxEpiSlots; ++s) mbar_init(&aux_bar[s], 1);
+        for (int s = 0; s < kNumBoxes; ++s) mbar_init(&aux_bar[s], 1);
         fence_mbar_init();
     }
     if (warp == 2) tmem_alloc_cg2(tmem_base_ptr, kTmemCols);
@@ -253,98 +250,98 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
     } else if (warp >= 4) {
         // ===================== epilogue (both CTAs, own 128 rows) =====================
-        // Every epilogue warp runs on its own: warp `ew` owns TMEM lanes / output rows 32*(ew&3) .. +31 of the column
-        // slices sl = ew>>2, +2, ... of every tile, stages each 32-row x 128-byte slice in its PRIVATE ring of
-        // swizzled 4 KiB slots and stores it with its own TMA store (one elected lane owns the warp's bulk groups).
-        // Nothing in here synchronises the CTA: the eight warps drift apart, so one warp's TMEM read / math overlaps
-        // another's store drain. TMEM loads run one 32-column chunk ahead of the math.
         const int ew = warp - 4;
         const int quarter = warp & 3;
         const int half = ew >> 2;
-        const bool elected = elect_one();
+        // one lane of warp quarter 0 owns this half's TMA traffic (elect.sync picks the same lane every time, so the
+        // bulk async-groups it commits are the ones it later waits on)
+        const bool elected = (quarter == 0) && elect_one();
         const int r_local = quarter * 32 + lane;
-        const uint32_t swz = (uint32_t)(lane & 7);                // == r_local & 7
+        const uint32_t swz = (uint32_t)(r_local & 7);
         const bool vec_ok = ((p.ldd & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.d) & 15) == 0) &&
                             (!p.residual || (((p.ldr & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.residual) & 15) == 0))) &&
                             (!p.preact || (((p.ldp & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.preact) & 15) == 0))) &&
                             (!p.gate || (((p.ldg & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.gate) & 15) == 0)));
         const bool bias_vec = p.bias && ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
-        const bool two_out = p.tma_store && p.preact != nullptr;  // D through the ring, the second output from registers
-        const int aux = p.tma_aux;                                // 0 none, 1 residual, 2 gate: TMA-loaded into the slot, updated in place
-        const int nslot = p.epi_slots;                            // 2, or 3 with an aux tile (its load runs one slice ahead)
+        const bool two_out = p.tma_store && p.preact != nullptr;
+        const int aux = p.tma_aux;                                // 0 none, 1 residual, 2 gate: TMA-loaded in place
         const int slice_cols = p.d_f32 ? 32 : 64;                 // columns per 128-byte output slice
         const int nslices = block_n / slice_cols;
         const int chunks_per_slice = slice_cols >> 5;
-        uint8_t* ring = boxes + ew * (nslot * kSlotBytes);
-        uint64_t* aux_b = aux_bar + ew * kMaxEpiSlots;
-        const bool has_slices = half < nslices;
-
-        // flat walk over this warp's (tile, slice) pairs; g counts them (slot = g % nslot)
-        auto tile_coords = [&](int u, int& m0, int& n0) {
+        uint8_t* box_base = boxes + half * 2 * kBoxBytes;
+        uint64_t* aux_b = aux_bar + half * 2;
+        uint32_t buf = 0;
+        uint32_t aux_ph = 0;                                      // bit b: parity the next load into box b completes
+        uint32_t acc = 0, acc_phase = 0;
+        for (int u = cluster_id; u < units; u += num_clusters) {
             const int split = u / tiles;
             const int t = u - split * tiles;
             const int mt = p.m_fast ? (t % p.num_m_tiles) : (t / p.num_n_tiles);
             const int nt = p.m_fast ? (t / p.num_m_tiles) : (t % p.num_n_tiles);
-            m0 = mt * (2 * BLOCK_M) + (int)rank * BLOCK_M;
-            n0 = nt * block_n;
-        };
-        auto issue_aux = [&](int u, int sl, uint32_t slot) {      // elected lane only
-            int m0, n0;
-            tile_coords(u, m0, n0);
-            mbar_arrive_expect_tx(&aux_b[slot], kSlotBytes);
-            tma_load_2d(ring + slot * kSlotBytes, &tmap_x, &aux_b[slot], n0 + sl * slice_cols, m0 + quarter * 32);
-        };
-
-        uint32_t slot = 0;
-        uint32_t aux_ph = 0;                                      // bit s: parity of the next load into slot s
-        uint32_t acc = 0, acc_phase = 0;
-        if (aux && has_slices && elected && cluster_id < units) issue_aux(cluster_id, half, 0);
-        for (int u = cluster_id; u < units; u += num_clusters) {
-            int m0, n0;
-            tile_coords(u, m0, n0);
+            const int m0 = mt * (2 * BLOCK_M) + (int)rank * BLOCK_M;
+            const int n0 = nt * block_n;
+            if (aux && elected) {
+                // bf16 output => at most two slices per half and tile, one per box. Fetch their residual / gate
+                // tiles now, while the tile's MMAs still run. Every thread of this half is past the previous
+                // tile's last named barrier, so nobody touches the boxes until the loads land.
+                bulk_wait_read<0>();
+                uint32_t b = buf;
+                for (int sl = half; sl < nslices; sl += 2, b ^= 1) {
+                    mbar_arrive_expect_tx(&aux_b[b], kBoxBytes);
+                    tma_load_2d(box_base + b * kBoxBytes, &tmap_x, &aux_b[b], n0 + sl * slice_cols, m0);
+                }
+            }
             mbar_wait(&tmem_full[acc], acc_phase);
             tc_fence_after();
             const int64_t row = (int64_t)m0 + r_local;
             const bool row_ok = row < p.M;
             const uint32_t taddr_row = tmem_base + acc * kAccStride + ((uint32_t)(quarter * 32) << 16);
-            if (has_slices) {
-                const int nch = ((nslices - half + 1) >> 1) * chunks_per_slice;   // chunks of this warp in the tile
-                // chunk c -> slice half + 2 * (c / chunks_per_slice), 32-column group c % chunks_per_slice
-                auto chunk_col = [&](int c) { return (half + 2 * (c / chunks_per_slice)) * slice_cols + (c % chunks_per_slice) * 32; };
-                auto process = [&](int c, uint32_t (&r)[32]) {
-                    const int sl = half + 2 * (c / chunks_per_slice);
-                    const int ch = c % chunks_per_slice;
-                    const int ccol = sl * slice_cols + ch * 32;
-                    uint8_t* box = ring + slot * kSlotBytes;
-                    uint8_t* rowp = box + lane * 128;
-                    if (ch == 0 && p.tma_store) {
-                        // slot reuse: the store issued from this slot nslot slices ago has been read (one newer group
-                        // may still be in flight); then fetch the NEXT slice's aux tile into the slot after this one
-                        if (elected) {
-                            bulk_wait_read<1>();
-                            if (aux) {
-                                int nu = u, nsl = sl + 2;
-                                if (nsl >= nslices) { nu = u + num_clusters; nsl = half; }
-                                if (nu < units) issue_aux(nu, nsl, (slot + 1 == (uint32_t)nslot) ? 0u : slot + 1);
-                            }
-                        }
-                        __syncwarp();
-                        if (aux) {
-                            mbar_wait(&aux_b[slot], (aux_ph >> slot) & 1u);
-                            aux_ph ^= (1u << slot);
-                        }
-                    }
+            bool released = false;
+            for (int sl = half; sl < nslices; sl += 2) {
+                uint8_t* box = box_base + buf * kBoxBytes;
+                uint8_t* box2 = box_base + (buf ^ 1) * kBoxBytes;
+                // the slice's accumulator columns are requested FIRST, so the TMEM round trip runs under the wait for the
+                // staging box (and the barrier) below instead of after it
+                uint32_t r0[32], r1[32];
+                __syncwarp();
+                tmem_ld_32x32b_x32(taddr_row + (uint32_t)(sl * slice_cols), r0);
+                if (chunks_per_slice == 2) tmem_ld_32x32b_x32(taddr_row + (uint32_t)(sl * slice_cols + 32), r1);
+                if (p.tma_store && !aux) {
+                    // the box written two slices ago (or both, when two outputs share the ring) must have been read
+                    if (elected) { if (two_out) bulk_wait_read<0>(); else bulk_wait_read<1>(); }
+                    named_bar_sync(1 + half, 128);
+                }
+                if (aux) {
+                    mbar_wait(&aux_b[buf], (aux_ph >> buf) & 1u);
+                    aux_ph ^= (1u << buf);
+                }
+                tmem_ld_wait();
+                if (sl + 2 >= nslices) {      // last TMEM read of the tile: the MMAs of the tile after next may overwrite it
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(&tmem_empty[acc], 0);
+                    released = true;
+                }
+                uint8_t* rowp = box + r_local * 128;
+                auto chunk_body = [&](const int ch, uint32_t (&r)[32]) {
+                    const int ccol = sl * slice_cols + ch * 32;      // column inside the tile
                     const int64_t col0 = (int64_t)n0 + ccol;
                     float v[32];
+                    if (p.bias && bias_vec && col0 + 32 <= p.N) {
+                        const float2 al = splat2(p.alpha);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+                        for (int q = 0; q < 8; ++q) {    // v = acc * alpha + bias, two columns per instruction
+                            const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0) + q);
+                            const float2 lo = fma2(make_float2(__uint_as_float(r[q * 4 + 0]), __uint_as_float(r[q * 4 + 1])), al, make_float2(b4.x, b4.y));
+                            const float2 hi = fma2(make_float2(__uint_as_float(r[q * 4 + 2]), __uint_as_float(r[q * 4 + 3])), al, make_float2(b4.z, b4.w));
+                            v[q * 4 + 0] = lo.x; v[q * 4 + 1] = lo.y; v[q * 4 + 2] = hi.x; v[q * 4 + 3] = hi.y;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+                    }
                     if (p.bias) {
                         if (bias_vec && col0 + 32 <= p.N) {
-#pragma unroll
-                            for (int q = 0; q < 8; ++q) {
-                                const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0) + q);
-                                v[q * 4 + 0] += b4.x; v[q * 4 + 1] += b4.y; v[q * 4 + 2] += b4.z; v[q * 4 + 3] += b4.w;
-                            }
                         } else {
 #pragma unroll
                             for (int j = 0; j < 32; ++j)
@@ -355,26 +352,16 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         if (row_ok && col0 < p.N) epilogue_direct(p, v, row, col0, vec_ok);
                         return;
                     }
-                    // ---- staged path ----
+                    // ---- staged path: everything below touches shared memory only ----
                     bool acted = false;
                     if (two_out) {
-                        // second output (pre-activation, or the activation's derivative) straight from registers:
-                        // 64 contiguous bytes of this thread's row
+                        uint8_t* rowp2 = box2 + r_local * 128;
                         uint32_t pw[16];
                         acted = preact_words(v, pw, p.act, p.act_grad);
-                        if (row_ok) {
-                            __nv_bfloat16* dst = p.preact + row * p.ldp + col0;
-                            if (col0 + 32 <= p.N) {
 #pragma unroll
-                                for (int q = 0; q < 4; ++q) stg128(dst + q * 8, make_uint4(pw[q * 4], pw[q * 4 + 1], pw[q * 4 + 2], pw[q * 4 + 3]));
-                            } else {
-#pragma unroll
-                                for (int j = 0; j < 32; ++j)
-                                    if (col0 + j < p.N) {
-                                        const uint32_t w = pw[j >> 1];
-                                        reinterpret_cast<uint16_t*>(dst)[j] = (uint16_t)((j & 1) ? (w >> 16) : (w & 0xffffu));
-                                    }
-                            }
+                        for (int q = 0; q < 4; ++q) {
+                            const uint32_t j = (uint32_t)(ch * 4 + q);
+                            sts128(rowp2 + ((j ^ swz) << 4), make_uint4(pw[q * 4], pw[q * 4 + 1], pw[q * 4 + 2], pw[q * 4 + 3]));
                         }
                     }
                     if (p.act && !acted) act_inplace(v, p.act);
@@ -391,12 +378,12 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         else add_bf16_inplace(v, xw);
                     }
                     if (p.gate && aux != 2 && row_ok) {
-                        const __nv_bfloat16* gp = p.gate + row * p.ldg + col0;
+                        const __nv_bfloat16* g = p.gate + row * p.ldg + col0;
                         uint32_t gw[16];
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
                             uint4 gi = make_uint4(0, 0, 0, 0);
-                            if (col0 + q * 8 < p.N) gi = ldg128(gp + q * 8);
+                            if (col0 + q * 8 < p.N) gi = ldg128(g + q * 8);
                             gw[q * 4 + 0] = gi.x; gw[q * 4 + 1] = gi.y; gw[q * 4 + 2] = gi.z; gw[q * 4 + 3] = gi.w;
                         }
                         gate_inplace(v, gw, p.gate_kind);
@@ -446,48 +433,25 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                                               pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7])));
                         }
                     }
-                    if (ch == chunks_per_slice - 1) {             // slice complete: hand it to the TMA engine
-                        fence_proxy_async_smem();
-                        __syncwarp();
-                        if (elected) {
-                            const int c0 = n0 + sl * slice_cols;
-                            const int r0 = m0 + quarter * 32;
-                            if (c0 < p.N && r0 < p.M) {
-                                if (p.accumulate) tma_reduce_add_2d(&tmap_d, box, c0, r0);
-                                else tma_store_2d(&tmap_d, box, c0, r0);
-                            }
-                            bulk_commit();
-                        }
-                        slot = (slot + 1 == (uint32_t)nslot) ? 0u : slot + 1;
-                    }
                 };
-                // software pipeline over the chunks: the TMEM load of chunk c + 1 is in flight during the math of chunk c
-                uint32_t ra[32], rb[32];
-                __syncwarp();
-                tmem_ld_32x32b_x32(taddr_row + (uint32_t)chunk_col(0), ra);
-                tmem_ld_wait();
-                for (int c = 0; c < nch; c += 2) {
-                    const bool more1 = c + 1 < nch, more2 = c + 2 < nch;
-                    if (more1) tmem_ld_32x32b_x32(taddr_row + (uint32_t)chunk_col(c + 1), rb);
-                    else {       // last TMEM read of the tile is complete: the MMAs of the tile after next may overwrite it
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive_cluster(&tmem_empty[acc], 0);
-                    }
-                    process(c, ra);
-                    if (more1) {
-                        tmem_ld_wait();
-                        if (more2) tmem_ld_32x32b_x32(taddr_row + (uint32_t)chunk_col(c + 2), ra);
-                        else {
-                            tc_fence_before();
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive_cluster(&tmem_empty[acc], 0);
+                chunk_body(0, r0);
+                if (chunks_per_slice == 2) chunk_body(1, r1);
+                if (p.tma_store) {
+                    fence_proxy_async_smem();
+                    named_bar_sync(1 + half, 128);
+                    if (elected) {
+                        const int c0 = n0 + sl * slice_cols;
+                        if (c0 < p.N && m0 < p.M) {
+                            if (p.accumulate) tma_reduce_add_2d(&tmap_d, box, c0, m0);
+                            else tma_store_2d(&tmap_d, box, c0, m0);
+                            if (two_out) tma_store_2d(&tmap_p, box2, c0, m0);
                         }
-                        process(c + 1, rb);
-                        if (more2) tmem_ld_wait();
+                        bulk_commit();
                     }
+                    if (!two_out) buf ^= 1;
                 }
-            } else {   // this half has no slice in the tile (narrow tiles): still hand TMEM back
+            }
+            if (!released) {   // this half had no slice in the tile (narrow tiles): still hand TMEM back
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive_cluster(&tmem_empty[acc], 0);
@@ -584,7 +548,8 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
 
     // D (and the saved pre-activation) leave through TMA when their row pitch allows it; one bf16 side input
     // (gate, else residual) is TMA-loaded in place when the output is bf16 and there is a single output.
-    p.tma_store = tma_ok(a->d, a->ldd, a->d_f32 ? 4 : 2) && !(a->preact && a->d_f32);
+    p.tma_store = tma_ok(a->d, a->ldd, a->d_f32 ? 4 : 2) && (!a->preact || tma_ok(a->preact, a->ldp, 2)) &&
+                  !(a->preact && a->d_f32);
     if (g_opt_gemm_direct_store.load(std::memory_order_relaxed)) p.tma_store = 0;
     p.tma_aux = 0;
     if (p.tma_store && !a->d_f32 && !a->preact) {
@@ -597,8 +562,7 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
     // column sums ride along only on the staged bf16 path; otherwise mgb_gemm_bf16 adds them with a separate pass
     const bool fused_colsum = a->colsum && p.tma_store && !a->d_f32;
     p.colsum = fused_colsum ? a->colsum : nullptr;
-    p.epi_slots = p.tma_aux ? 3 : 2;
-    const int fixed = kEpiWarps * p.epi_slots * kSlotBytes + 1024 + 512 + (fused_colsum ? 1024 : 0);
+    const int fixed = kNumBoxes * kBoxBytes + 1024 + 512 + (fused_colsum ? 1024 : 0);
     int stages = (kSmemLimit - fixed) / (int)stage_bytes;
     if (stages > kMaxStages) stages = kMaxStages;
     p.num_stages = stages;
@@ -614,12 +578,15 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
     if (rc) return rc;
     td = ta; tp = ta; tx = ta;   // placeholders when unused
     if (p.tma_store) {
-        // boxes of 32 rows: every epilogue warp stores (and aux-loads) its own rows
-        rc = make_map_2d(&td, a->d, a->n, a->m, a->ldd, a->d_f32 ? 32 : 64, 32, a->d_f32 != 0);
+        rc = make_map_2d(&td, a->d, a->n, a->m, a->ldd, a->d_f32 ? 32 : 64, BLOCK_M, a->d_f32 != 0);
         if (rc) return rc;
+        if (a->preact) {
+            rc = make_map_2d(&tp, a->preact, a->n, a->m, a->ldp, 64, BLOCK_M);
+            if (rc) return rc;
+        }
         if (p.tma_aux) {
-            rc = p.tma_aux == 2 ? make_map_2d(&tx, a->gate, a->n, a->m, a->ldg, 64, 32)
-                                : make_map_2d(&tx, a->residual, a->n, a->m, a->ldr, 64, 32);
+            rc = p.tma_aux == 2 ? make_map_2d(&tx, a->gate, a->n, a->m, a->ldg, 64, BLOCK_M)
+                                : make_map_2d(&tx, a->residual, a->n, a->m, a->ldr, 64, BLOCK_M);
             if (rc) return rc;
         }
     }

@@ -33,7 +33,6 @@ struct Params {
     int32_t tma_store;       // CTA-pair kernel only: D (and preact) leave through smem + TMA
     int32_t m_fast;          // CTA-pair kernel only: tile raster order (1 = m index fastest)
     int32_t tma_aux;         // CTA-pair kernel only: 1 residual / 2 gate arrives through TMA, updated in place
-    int32_t epi_slots;       // CTA-pair kernel only: 4 KiB staging slots per epilogue warp (2, or 3 with an aux tile)
     // epilogue
     void* d;
     int64_t ldd;
@@ -71,7 +70,10 @@ __device__ __forceinline__ float apply_act_grad(float v, int act) {
 __device__ __forceinline__ void act_inplace(float (&v)[32], int act) {
     if (act == MGB_ACT_GELU_TANH) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = gelu_tanh_f(v[j]);
+        for (int j = 0; j < 16; ++j) {
+            const float2 y = gelu_tanh_2(make_float2(v[2 * j], v[2 * j + 1]));
+            v[2 * j] = y.x; v[2 * j + 1] = y.y;
+        }
     } else if (act == MGB_ACT_GELU_ERF) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = gelu_erf_f(v[j]);
@@ -89,10 +91,10 @@ __device__ __forceinline__ bool preact_words(float (&v)[32], uint32_t (&w)[16], 
     if (act == MGB_ACT_GELU_TANH) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
-            float g0, g1;
-            gelu_tanh_both_f(v[2 * j], v[2 * j], g0);
-            gelu_tanh_both_f(v[2 * j + 1], v[2 * j + 1], g1);
-            w[j] = pack_bf16x2(g0, g1);
+            float2 y, g;
+            gelu_tanh_both_2(make_float2(v[2 * j], v[2 * j + 1]), y, g);
+            v[2 * j] = y.x; v[2 * j + 1] = y.y;
+            w[j] = pack_bf16x2(g.x, g.y);
         }
     } else {
 #pragma unroll
@@ -110,9 +112,8 @@ __device__ __forceinline__ void gate_inplace(float (&v)[32], const uint32_t (&g)
     if (kind == MGB_GATE_MUL) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
-            const float2 f = unpack_bf16x2(g[j]);
-            v[2 * j] *= f.x;
-            v[2 * j + 1] *= f.y;
+            const float2 r = mul2(make_float2(v[2 * j], v[2 * j + 1]), unpack_bf16x2(g[j]));
+            v[2 * j] = r.x; v[2 * j + 1] = r.y;
         }
     } else if (kind == MGB_ACT_GELU_TANH) {
 #pragma unroll
@@ -133,9 +134,8 @@ __device__ __forceinline__ void gate_inplace(float (&v)[32], const uint32_t (&g)
 __device__ __forceinline__ void add_bf16_inplace(float (&v)[32], const uint32_t (&r)[16]) {
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
-        const float2 f = unpack_bf16x2(r[j]);
-        v[2 * j] += f.x;
-        v[2 * j + 1] += f.y;
+        const float2 s = add2(make_float2(v[2 * j], v[2 * j + 1]), unpack_bf16x2(r[j]));
+        v[2 * j] = s.x; v[2 * j + 1] = s.y;
     }
 }
 

@@ -646,16 +646,19 @@ class GPT(nn.Module):
                     ops.linear_fwd(ws.fc_act[l], W(f"{l}.fc2_w"), ws.x[l + 1], bias=P(f"{l}.fc2_b"), residual=ws.xmid[l])
         ops.layernorm_fwd(ws.x[L], P("lnf_w"), P("lnf_b"), ws.lnf, ws.lnf_stats[0], ws.lnf_stats[1])
 
-    def _head_loss(self, ws: _Workspace, targets: torch.Tensor, need_grad: bool):
+    def _head_loss(self, ws: _Workspace, targets: torch.Tensor, need_grad: bool, direct: bool = False):
         """head + cross_entropy (mingpt/model.py:312,316-318) in row chunks; the bf16 logits of a chunk are
         turned into dlogits in place and consumed by the head's dgrad/wgrad right away, so the full
-        (B*T, vocab) logits / dlogits never exist."""
+        (B*T, vocab) logits / dlogits never exist. `direct`: the upstream gradient of the loss is known to be 1
+        (forward_backward), so the head's weight gradient accumulates straight into the flat gradient buffer
+        instead of a scratch copy that backward would scale and add."""
         V, M = self.vocab_size, ws.M
         tg = targets.reshape(-1)
         hw = self._w("head_w", bf16=True)
         ops.count_valid_targets(tg, ws.n_valid)
-        if need_grad:
-            ws.head_dw.zero_()
+        head_dw = self._g("head_w") if direct else ws.head_dw
+        if need_grad and not direct:
+            head_dw.zero_()
         for r0 in range(0, M, ws.chunk):
             rows = min(ws.chunk, M - r0)
             lg_full = ws.logits[:rows]
@@ -665,9 +668,10 @@ class GPT(nn.Module):
                                       write_grad=need_grad, err_flag=ws.err_flag)
             if need_grad:
                 ops.linear_dgrad(lg, hw, ws.dlnf[r0:r0 + rows])
-                ops.linear_wgrad(lg, ws.lnf[r0:r0 + rows], ws.head_dw, accumulate=True)
+                ops.linear_wgrad(lg, ws.lnf[r0:r0 + rows], head_dw, accumulate=True)
         ops.loss_finalize(ws.row_loss, ws.n_valid, ws.loss)
         ws.has_head_grads = need_grad
+        ws.head_direct = direct
 
     def _head_logits(self, ws: _Workspace, last_only: bool = False) -> torch.Tensor:
         V, C = self.vocab_size, self.n_embed
@@ -741,8 +745,11 @@ class GPT(nn.Module):
         ws.generation += 1
         ws.idx = inputs
         self._trunk(ws, inputs)
-        self._head_loss(ws, targets, True)
-        self._backward(ws, self._one if grad_scale is None else grad_scale)
+        direct = grad_scale is None
+        if direct:
+            self._prepare_grads()        # the head's wgrad below already accumulates into the gradient buffer
+        self._head_loss(ws, targets, True, direct=direct)
+        self._backward(ws, self._one if grad_scale is None else grad_scale, publish=not direct)
         return ws.loss
 
     # ------------------------------------------------------------------ backward
@@ -790,9 +797,10 @@ class GPT(nn.Module):
         G = self._g
         if publish:
             self._prepare_grads()
-        # upstream gradient of the scalar loss, applied on the device (no host sync)
-        ops.scale_bf16_dev(ws.dlnf, grad_loss)
-        ops.axpy(G("head_w"), ws.head_dw, grad_loss)
+        if not getattr(ws, "head_direct", False):
+            # upstream gradient of the scalar loss, applied on the device (no host sync)
+            ops.scale_bf16_dev(ws.dlnf, grad_loss)
+            ops.axpy(G("head_w"), ws.head_dw, grad_loss)
         ops.layernorm_bwd(ws.dlnf, ws.x[L], P("lnf_w"), ws.lnf_stats[0], ws.lnf_stats[1], ws.dx_a, G("lnf_w"), G("lnf_b"))
         if self._layer_done_hook is not None:
             self._layer_done_hook(L + 1)

@@ -4,7 +4,7 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from mingpt_distributed_b200 import ops
-B, T, H, d = 8, 1024, 12, 64
+B, T, H, d = int(os.environ.get("ATTN_B", "8")), 1024, 12, 64
 C = H * d
 qkv = torch.randn(B, T, 3 * C, device="cuda").bfloat16()
 dout = torch.randn(B, T, C, device="cuda").bfloat16()
