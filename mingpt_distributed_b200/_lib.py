@@ -136,6 +136,18 @@ def lib() -> C.CDLL:
     with _lock:
         if _lib is not None:
             return _lib
+        override = os.environ.get("MGB_LIB_PATH")      # A/B measurements: load another build of the library as is
+        if override:
+            handle = C.CDLL(override)
+            for table, default in ((SIGNATURES, C.c_int), (INTROSPECTION, None)):
+                for name, spec in table.items():
+                    fn = getattr(handle, name, None)
+                    if fn is None:
+                        continue                             # an older build lacks the newer entry points
+                    fn.argtypes = spec if default is not None else []
+                    fn.restype = default if default is not None else spec
+            _lib = handle
+            return _lib
         if _lib_is_stale():
             # an edited .cu / .cuh / header must never silently run the old binary: rebuild, or refuse to load
             if shutil.which(os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")) is None:

@@ -15,6 +15,7 @@
 #include "dropout.cuh"
 
 namespace mgb {
+extern std::atomic<int> g_opt_attn_poly;   // optim.cu: share of the forward softmax's exponentials on the FMA pipe (0, 1 = 25 %, 2 = 50 %)
 namespace attn_tc {
 
 constexpr int BQ = 128, BKV = 128, D = 64;
@@ -59,7 +60,7 @@ __device__ __forceinline__ void drop_packed(uint32_t* w, uint64_t seed, uint32_t
 
 // DROP: attention-probability dropout (nn.MultiheadAttention dropout=attn_drop: mingpt/model.py:150 ->
 // torch/nn/functional.py:6644-6645). The softmax normaliser keeps every key, P V only the kept ones.
-template <bool DROP>
+template <bool DROP, int POLY>
 __global__ void __launch_bounds__(kThreads, 2)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __restrict__ out,
                    float* __restrict__ lse, int T, int H, int mask_mode, float scale_log2, uint32_t drop_thresh,
@@ -196,7 +197,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
                 // causal diagonal block, all keys present: this warp's rows are 32w..32w+31, so 32-column groups left
                 // of the diagonal group need no mask, the diagonal group a per-element one, and the groups right of
                 // it are entirely masked (no TMEM read, no exponentials). All of it warp-uniform.
-                float mx_raw = -INFINITY;
+                float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
 #pragma unroll 1
                 for (int g = 0; g <= warp; ++g) {
                     uint32_t sv[32];
@@ -204,17 +205,23 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
                     tmem_ld_wait();
                     if (g < warp) {
 #pragma unroll
-                        for (int e = 0; e < 32; e += 2)
-                            mx_raw = fmaxf(mx_raw, fmaxf(__uint_as_float(sv[e]), __uint_as_float(sv[e + 1])));
+                        for (int e = 0; e < 32; e += 8) {
+                            m0 = fmaxf(m0, fmaxf(__uint_as_float(sv[e]), __uint_as_float(sv[e + 1])));
+                            m1 = fmaxf(m1, fmaxf(__uint_as_float(sv[e + 2]), __uint_as_float(sv[e + 3])));
+                            m2 = fmaxf(m2, fmaxf(__uint_as_float(sv[e + 4]), __uint_as_float(sv[e + 5])));
+                            m3 = fmaxf(m3, fmaxf(__uint_as_float(sv[e + 6]), __uint_as_float(sv[e + 7])));
+                        }
                     } else {
 #pragma unroll
                         for (int e = 0; e < 32; ++e)
-                            if (e <= lane) mx_raw = fmaxf(mx_raw, __uint_as_float(sv[e]));
+                            if (e <= lane) m0 = fmaxf(m0, __uint_as_float(sv[e]));
                     }
                 }
-                mx = mx_raw * scale_log2;
+                mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)) * scale_log2;
             } else {
-                // ---- pass 1: row maximum of this block (log2 domain); 64 columns per TMEM round trip ----
+                // ---- pass 1: row maximum of this block (log2 domain); 64 columns per TMEM round trip, four
+                // independent running maxima (one chain would serialise 64 dependent instructions) ----
+                float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
 #pragma unroll 1
                 for (int c = 0; c < 2; ++c) {
                     uint32_t s0[32], s1[32];
@@ -223,7 +230,12 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
                     tmem_ld_wait();
                     if (fast) {
 #pragma unroll
-                        for (int e = 0; e < 32; ++e) mx = fmaxf(mx, fmaxf(__uint_as_float(s0[e]), __uint_as_float(s1[e])));
+                        for (int e = 0; e < 32; e += 4) {
+                            m0 = fmaxf(m0, fmaxf(__uint_as_float(s0[e]), __uint_as_float(s1[e])));
+                            m1 = fmaxf(m1, fmaxf(__uint_as_float(s0[e + 1]), __uint_as_float(s1[e + 1])));
+                            m2 = fmaxf(m2, fmaxf(__uint_as_float(s0[e + 2]), __uint_as_float(s1[e + 2])));
+                            m3 = fmaxf(m3, fmaxf(__uint_as_float(s0[e + 3]), __uint_as_float(s1[e + 3])));
+                        }
                     } else {
 #pragma unroll
                         for (int e = 0; e < 64; ++e) {
@@ -231,10 +243,11 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
                             float x = fmaf(__uint_as_float(e < 32 ? s0[e & 31] : s1[e & 31]), scale_log2, bias_all);
                             if (bias_diag && col <= r) x += LOG2E;
                             if (col >= kvalid || (causal && diag && col > r)) x = -INFINITY;
-                            mx = fmaxf(mx, x);
+                            m0 = fmaxf(m0, x);
                         }
                     }
                 }
+                mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
                 if (fast) mx = fmaf(mx, scale_log2, bias_all);
             }
             // ---- running max with lazy rescale ----
@@ -261,7 +274,11 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
                 }
             }
             // ---- pass 2: P = exp2(x - m_run), row sum, bf16 pairs back into TMEM ----
+            // Everything on fp32 PAIRS (FFMA2 / FADD2: one issue slot for two columns); POLY of every 4 pairs take
+            // their exponential on the FMA pipe (exp2_poly2) instead of the special-function unit.
             const float off = bias_all - m_run;
+            const float2 sc2 = splat2(scale_log2), off2 = splat2(off);
+            float2 acc_a = make_float2(0.f, 0.f), acc_b = make_float2(0.f, 0.f);
             float rs = 0.f;
             if (diag_groups) {
 #pragma unroll 1
@@ -274,16 +291,28 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
                         uint32_t sv[32];
                         tmem_ld_32x32b_x32(taddr + kColS + g * 32, sv);
                         tmem_ld_wait();
+                        if (g < warp) {
 #pragma unroll
-                        for (int e = 0; e < 16; ++e) {
-                            float a0 = exp2f(fmaf(__uint_as_float(sv[2 * e]), scale_log2, off));
-                            float a1 = exp2f(fmaf(__uint_as_float(sv[2 * e + 1]), scale_log2, off));
-                            if (g == warp) {
+                            for (int e = 0; e < 16; e += 2) {
+                                const float2 xa = fma2(make_float2(__uint_as_float(sv[2 * e]), __uint_as_float(sv[2 * e + 1])), sc2, off2);
+                                const float2 xb = fma2(make_float2(__uint_as_float(sv[2 * e + 2]), __uint_as_float(sv[2 * e + 3])), sc2, off2);
+                                const float2 pa = make_float2(exp2f(xa.x), exp2f(xa.y));
+                                const float2 pb = (POLY == 2 || (POLY == 1 && (e & 2))) ? exp2_poly2(xb) : make_float2(exp2f(xb.x), exp2f(xb.y));
+                                acc_a = add2(acc_a, pa);
+                                acc_b = add2(acc_b, pb);
+                                pk[e] = pack_bf16x2(pa.x, pa.y);
+                                pk[e + 1] = pack_bf16x2(pb.x, pb.y);
+                            }
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 16; ++e) {
+                                float a0 = exp2f(fmaf(__uint_as_float(sv[2 * e]), scale_log2, off));
+                                float a1 = exp2f(fmaf(__uint_as_float(sv[2 * e + 1]), scale_log2, off));
                                 if (2 * e > lane) a0 = 0.f;
                                 if (2 * e + 1 > lane) a1 = 0.f;
+                                rs += a0 + a1;
+                                pk[e] = pack_bf16x2(a0, a1);
                             }
-                            rs += a0 + a1;
-                            pk[e] = pack_bf16x2(a0, a1);
                         }
                     }
                     if (DROP && g <= warp) drop_packed<16>(pk, drop_seed, site, drop_row + (uint64_t)(j * (BKV / 8) + g * 4), drop_thresh);
@@ -300,13 +329,14 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
                     if (fast) {
 #pragma unroll
                         for (int e = 0; e < 16; ++e) {
-                            const float a0 = exp2f(fmaf(__uint_as_float(s0[2 * e]), scale_log2, off));
-                            const float a1 = exp2f(fmaf(__uint_as_float(s0[2 * e + 1]), scale_log2, off));
-                            const float b0 = exp2f(fmaf(__uint_as_float(s1[2 * e]), scale_log2, off));
-                            const float b1 = exp2f(fmaf(__uint_as_float(s1[2 * e + 1]), scale_log2, off));
-                            rs += (a0 + a1) + (b0 + b1);
-                            pk[e] = pack_bf16x2(a0, a1);
-                            pk[16 + e] = pack_bf16x2(b0, b1);
+                            const float2 xa = fma2(make_float2(__uint_as_float(s0[2 * e]), __uint_as_float(s0[2 * e + 1])), sc2, off2);
+                            const float2 xb = fma2(make_float2(__uint_as_float(s1[2 * e]), __uint_as_float(s1[2 * e + 1])), sc2, off2);
+                            const float2 pa = make_float2(exp2f(xa.x), exp2f(xa.y));
+                            const float2 pb = (POLY == 2 || (POLY == 1 && (e & 1))) ? exp2_poly2(xb) : make_float2(exp2f(xb.x), exp2f(xb.y));
+                            acc_a = add2(acc_a, pa);
+                            acc_b = add2(acc_b, pb);
+                            pk[e] = pack_bf16x2(pa.x, pa.y);
+                            pk[16 + e] = pack_bf16x2(pb.x, pb.y);
                         }
                     } else {
 #pragma unroll
@@ -329,6 +359,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
                     tmem_st_32x32b_x32(taddr + kColP + c * 32, pk);
                 }
             }
+            rs += (acc_a.x + acc_a.y) + (acc_b.x + acc_b.y);
             l_run += rs;
             tmem_st_wait();
             tc_fence_before();
@@ -372,20 +403,29 @@ int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int 
                cudaStream_t stream, uint32_t drop_thresh, float inv_keep, const uint64_t* seed_dev, uint32_t site) {
     static PerDeviceOnce once;
     once.run([] {
-        cudaFuncSetAttribute(attn_fwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-        cudaFuncSetAttribute(attn_fwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        cudaFuncSetAttribute(attn_fwd_tc_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        cudaFuncSetAttribute(attn_fwd_tc_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        cudaFuncSetAttribute(attn_fwd_tc_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        cudaFuncSetAttribute(attn_fwd_tc_kernel<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        cudaFuncSetAttribute(attn_fwd_tc_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        cudaFuncSetAttribute(attn_fwd_tc_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     });
     CUtensorMap tm;
     const int64_t C3 = (int64_t)3 * H * D;
     int rc = gemm::make_map_2d(&tm, qkv, C3, (int64_t)B * T, C3, 64, 128);
     if (rc) return rc;
     dim3 grid((T + BQ - 1) / BQ, B * H);
-    if (drop_thresh)
-        launch_pdl(attn_fwd_tc_kernel<true>, grid, dim3(kThreads), (size_t)SMEM_BYTES, stream, tm, (__nv_bfloat16*)out, lse, T, H,
-                   mask_mode, scale * LOG2E, drop_thresh, inv_keep, seed_dev, site);
-    else
-        launch_pdl(attn_fwd_tc_kernel<false>, grid, dim3(kThreads), (size_t)SMEM_BYTES, stream, tm, (__nv_bfloat16*)out, lse, T, H,
-                   mask_mode, scale * LOG2E, 0u, 1.0f, (const uint64_t*)nullptr, 0u);
+    const int poly = g_opt_attn_poly.load(std::memory_order_relaxed);
+#define MGB_ATTN_FWD(DROPV, POLYV)                                                                                          \
+    launch_pdl(attn_fwd_tc_kernel<DROPV, POLYV>, grid, dim3(kThreads), (size_t)SMEM_BYTES, stream, tm, (__nv_bfloat16*)out, lse, T, H, \
+               mask_mode, scale * LOG2E, drop_thresh, inv_keep, seed_dev, site)
+    if (drop_thresh) {
+        if (poly == 2) MGB_ATTN_FWD(true, 2); else if (poly == 1) MGB_ATTN_FWD(true, 1); else MGB_ATTN_FWD(true, 0);
+    } else {
+        inv_keep = 1.0f; seed_dev = nullptr; site = 0u;
+        if (poly == 2) MGB_ATTN_FWD(false, 2); else if (poly == 1) MGB_ATTN_FWD(false, 1); else MGB_ATTN_FWD(false, 0);
+    }
+#undef MGB_ATTN_FWD
     return kOk;
 }
 

@@ -129,6 +129,23 @@ __device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
 }
 __device__ __forceinline__ float2 splat2(float a) { return make_float2(a, a); }
 
+// 2^x for a pair WITHOUT the special-function unit: Cody-Waite range reduction (round-to-nearest through the 1.5 * 2^23
+// magic constant) and a cubic minimax polynomial for 2^f on [-0.5, 0.5] (max relative error 7.5e-5, far below the bf16
+// rounding of the probabilities it feeds), the integer part added straight into the exponent field. MUFU.EX2 runs at 16
+// per clock and SM, which is what bounds the attention softmax; a share of the exponentials moved to the FMA pipe
+// (6 packed instructions + 2 integer ones per pair) runs beside it. Inputs are clamped at -126 (result ~1e-38).
+__device__ __forceinline__ float2 exp2_poly2(float2 x) {
+    x.x = fmaxf(x.x, -126.0f);
+    x.y = fmaxf(x.y, -126.0f);
+    const float2 fl = add2(x, splat2(12582912.0f));
+    const float2 f = add2(x, fma2(fl, splat2(-1.0f), splat2(12582912.0f)));      // x - round(x)
+    float2 pl = fma2(splat2(0.0551716648042202f), f, splat2(0.2426111251115799f));
+    pl = fma2(pl, f, splat2(0.6932609677314758f));
+    pl = fma2(pl, f, splat2(0.9999280571937561f));
+    return make_float2(__int_as_float(__float_as_int(pl.x) + (__float_as_int(fl.x) << 23)),
+                       __int_as_float(__float_as_int(pl.y) + (__float_as_int(fl.y) << 23)));
+}
+
 // GELU, both flavours the reference family uses.
 //  tanh ("NewGELU", README.md / north_star MLP) and exact erf (nn.GELU(), mingpt/model.py:182)
 __device__ __forceinline__ float gelu_tanh_f(float x) {
@@ -222,14 +239,29 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return done != 0;
 }
+// try_wait with a suspend-time hint: the hardware may keep the thread asleep for up to `ns` nanoseconds while the
+// phase is incomplete (it is woken by the completing arrive), instead of returning after its short default limit.
+__device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parity, uint32_t ns) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(ns)
+        : "memory");
+    return done != 0;
+}
 // Wait with a watchdog: a protocol bug turns into a trap ("unspecified launch failure")
-// after ~4 s instead of a hung GPU box.
+// after ~4 s instead of a hung GPU box. Waiting warps share their scheduler with the warps that do the math
+// (producer / MMA warps next to epilogue or softmax warps), so the wait must not spin through issue slots: after one
+// plain probe it sleeps in the barrier unit with a long suspend hint.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
     uint64_t t0 = 0;
     uint32_t spins = 0;
-    while (!mbar_try_wait(bar, parity)) {
-        if ((++spins & 0xfffu) == 0) {
+    while (!mbar_try_wait_hint(bar, parity, 100000u)) {
+        if ((++spins & 0x3fu) == 0) {
             uint64_t now;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
             if (t0 == 0) t0 = now;

@@ -311,6 +311,7 @@ std::atomic<int> g_opt_gemm_direct_store{0};
 std::atomic<int> g_opt_pdl{0};   // measured gain on the gpt2-124M step: 0-1 % (within run-to-run noise), so off by default
 bool pdl_enabled() { return g_opt_pdl.load(std::memory_order_relaxed) != 0; }
 std::atomic<int> g_opt_attn_mma{0};
+std::atomic<int> g_opt_attn_poly{1};
 std::atomic<int> g_opt_ln_unstaged{0};
 std::atomic<int> g_opt_ce_unstaged{0};
 }
@@ -320,6 +321,7 @@ extern "C" int mgb_set_option(const char* key, int value) {
     if (!std::strcmp(key, "gemm_direct_store")) return mgb::g_opt_gemm_direct_store.exchange(value);
     if (!std::strcmp(key, "pdl")) return mgb::g_opt_pdl.exchange(value);
     if (!std::strcmp(key, "attn_mma")) return mgb::g_opt_attn_mma.exchange(value);
+    if (!std::strcmp(key, "attn_poly")) return mgb::g_opt_attn_poly.exchange(value);
     if (!std::strcmp(key, "ln_unstaged")) return mgb::g_opt_ln_unstaged.exchange(value);
     if (!std::strcmp(key, "ce_unstaged")) return mgb::g_opt_ce_unstaged.exchange(value);
     if (!std::strcmp(key, "reserved_sms")) return mgb::g_opt_reserved_sms.exchange(value);

@@ -17,65 +17,84 @@ extern std::atomic<int> g_opt_ce_unstaged;   // optim.cu: 1 = cross-entropy stre
 // =====================================================================================
 constexpr int LN_WARPS = 8;
 
-// One warp per row; the row lives in registers (MAXCH 16-byte chunks per lane).
+// One warp per row; the row lives in registers (MAXCH 16-byte chunks per lane). gamma / beta are loaded ONCE per warp
+// (the grid is sized so that a warp walks over many rows) and all elementwise math runs on fp32 pairs (FFMA2): the
+// kernel used to be bound by instruction issue (~420 per row and lane), not by HBM.
 template <int MAXCH>
-__global__ void __launch_bounds__(LN_WARPS * 32)
+__global__ void __launch_bounds__(LN_WARPS * 32, MAXCH <= 4 ? 2 : 1)
 ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
               __nv_bfloat16* __restrict__ y, float* __restrict__ mean, float* __restrict__ rstd, int64_t rows,
               int cols, float eps) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nch = cols >> 3;
     const float inv_cols = 1.0f / (float)cols;
+    float2 gam[MAXCH][4], bet[MAXCH][4];
+#pragma unroll
+    for (int i = 0; i < MAXCH; ++i) {
+        const int ch = lane + 32 * i;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            gam[i][e] = (ch < nch) ? make_float2(gamma[ch * 8 + 2 * e], gamma[ch * 8 + 2 * e + 1]) : make_float2(0.f, 0.f);
+            bet[i][e] = (ch < nch) ? make_float2(beta[ch * 8 + 2 * e], beta[ch * 8 + 2 * e + 1]) : make_float2(0.f, 0.f);
+        }
+    }
     grid_dep_launch();
     grid_dep_wait();                                 // x is the previous kernel's output (programmatic dependent launch)
-    for (int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp; row < rows; row += (int64_t)gridDim.x * LN_WARPS) {
-        const __nv_bfloat16* xr = x + row * cols;
+    const int64_t stride = (int64_t)gridDim.x * LN_WARPS;
+    int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp;
+    uint4 nxt[MAXCH];
+    if (row < rows) {
+#pragma unroll
+        for (int i = 0; i < MAXCH; ++i)
+            if (lane + 32 * i < nch) nxt[i] = ldg128(x + row * cols + (lane + 32 * i) * 8);
+    }
+    for (; row < rows; row += stride) {
         uint4 buf[MAXCH];
-        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < MAXCH; ++i) buf[i] = nxt[i];
+        if (row + stride < rows) {                   // the next row's loads are in flight during this row's math
+#pragma unroll
+            for (int i = 0; i < MAXCH; ++i)
+                if (lane + 32 * i < nch) nxt[i] = ldg128(x + (row + stride) * cols + (lane + 32 * i) * 8);
+        }
+        // mean first, then the centred second moment (two passes over registers: as accurate as torch's)
+        float2 sv = make_float2(0.f, 0.f);
 #pragma unroll
         for (int i = 0; i < MAXCH; ++i) {
-            const int ch = lane + 32 * i;
-            if (ch < nch) {
-                buf[i] = ldg128(xr + ch * 8);
+            if (lane + 32 * i < nch) {
                 const uint32_t w[4] = {buf[i].x, buf[i].y, buf[i].z, buf[i].w};
 #pragma unroll
-                for (int e = 0; e < 4; ++e) { float2 f = unpack_bf16x2(w[e]); s += f.x + f.y; }
+                for (int e = 0; e < 4; ++e) sv = add2(sv, unpack_bf16x2(w[e]));
             }
         }
-        const float mu = warp_sum(s) * inv_cols;
-        float q = 0.f;
+        const float mu = warp_sum(sv.x + sv.y) * inv_cols;
+        const float2 nmu = splat2(-mu);
+        float2 qv = make_float2(0.f, 0.f);
 #pragma unroll
         for (int i = 0; i < MAXCH; ++i) {
-            const int ch = lane + 32 * i;
-            if (ch < nch) {
+            if (lane + 32 * i < nch) {
                 const uint32_t w[4] = {buf[i].x, buf[i].y, buf[i].z, buf[i].w};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    float2 f = unpack_bf16x2(w[e]);
-                    q += (f.x - mu) * (f.x - mu) + (f.y - mu) * (f.y - mu);
+                    const float2 c = add2(unpack_bf16x2(w[e]), nmu);
+                    qv = fma2(c, c, qv);
                 }
             }
         }
-        const float rs = rsqrtf(warp_sum(q) * inv_cols + eps);
+        const float rs = rsqrtf(warp_sum(qv.x + qv.y) * inv_cols + eps);
         if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+        const float2 rs2 = splat2(rs), nmr2 = splat2(-mu * rs);
         __nv_bfloat16* yr = y + row * cols;
 #pragma unroll
         for (int i = 0; i < MAXCH; ++i) {
             const int ch = lane + 32 * i;
             if (ch < nch) {
                 const uint32_t w[4] = {buf[i].x, buf[i].y, buf[i].z, buf[i].w};
-                const float4 g0 = *reinterpret_cast<const float4*>(gamma + ch * 8);
-                const float4 g1 = *reinterpret_cast<const float4*>(gamma + ch * 8 + 4);
-                const float4 b0 = *reinterpret_cast<const float4*>(beta + ch * 8);
-                const float4 b1 = *reinterpret_cast<const float4*>(beta + ch * 8 + 4);
-                const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-                const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
                 uint32_t o[4];
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    float2 f = unpack_bf16x2(w[e]);
-                    o[e] = pack_bf16x2((f.x - mu) * rs * gg[2 * e] + bb[2 * e],
-                                       (f.y - mu) * rs * gg[2 * e + 1] + bb[2 * e + 1]);
+                    const float2 r = fma2(fma2(unpack_bf16x2(w[e]), rs2, nmr2), gam[i][e], bet[i][e]);
+                    o[e] = pack_bf16x2(r.x, r.y);
                 }
                 stg128(yr + ch * 8, make_uint4(o[0], o[1], o[2], o[3]));
             }
@@ -258,16 +277,18 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
         for (int s = 0; s < LNB_STAGES; ++s)
             if (row0 + s < row1) issue(row0 + s, s);
 
-    float gam[MAXCH][8], dg[MAXCH][8], db[MAXCH][8], dr[COLSUM ? MAXCH : 1][8];
+    // All elementwise math on fp32 PAIRS (FFMA2 / FADD2 / FMUL2): the kernel was bound by instruction issue (~21
+    // instructions per element), not by the fp32 pipes or by HBM; packed it needs ~11.
+    float2 gam[MAXCH][4], dg[MAXCH][4], db[MAXCH][4], dr[COLSUM ? MAXCH : 1][4];
 #pragma unroll
     for (int i = 0; i < MAXCH; ++i) {
         const int ch = lane + 32 * i;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            gam[i][e] = (ch < nch) ? gamma[ch * 8 + e] : 0.f;
-            dg[i][e] = 0.f;
-            db[i][e] = 0.f;
-            if (COLSUM) dr[i][e] = 0.f;
+        for (int e = 0; e < 4; ++e) {
+            gam[i][e] = (ch < nch) ? make_float2(gamma[ch * 8 + 2 * e], gamma[ch * 8 + 2 * e + 1]) : make_float2(0.f, 0.f);
+            dg[i][e] = make_float2(0.f, 0.f);
+            db[i][e] = make_float2(0.f, 0.f);
+            if (COLSUM) dr[i][e] = make_float2(0.f, 0.f);
         }
     }
     float mu_n = 0.f, rs_n = 0.f;
@@ -277,11 +298,12 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     for (int64_t row = row0; row < row1; ++row) {
         const float mu = mu_n, rs = rs_n;
         if (row + 1 < row1) { mu_n = mean[row + 1]; rs_n = rstd[row + 1]; }
+        const float2 rs2 = splat2(rs), nmr2 = splat2(-mu * rs);      // xhat = x * rs - mu * rs
         const uint8_t* xs = ring + (size_t)s * 3 * rowbytes;
         const uint8_t* ds = xs + rowbytes;
         const uint8_t* rsd = xs + 2 * rowbytes;
         mbar_wait(&bars[s], ph);
-        float s1 = 0.f, s2 = 0.f;
+        float2 s1 = make_float2(0.f, 0.f), s2 = make_float2(0.f, 0.f);
 #pragma unroll
         for (int i = 0; i < MAXCH; ++i) {
             const int ch = lane + 32 * i;
@@ -291,19 +313,19 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                 const uint32_t wd[4] = {pd.x, pd.y, pd.z, pd.w};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    const float2 fx = unpack_bf16x2(wx[e]);
+                    const float2 h = fma2(unpack_bf16x2(wx[e]), rs2, nmr2);
                     const float2 fd = unpack_bf16x2(wd[e]);
-                    const float h0 = (fx.x - mu) * rs, h1 = (fx.y - mu) * rs;
-                    dg[i][2 * e] += fd.x * h0; dg[i][2 * e + 1] += fd.y * h1;
-                    db[i][2 * e] += fd.x;      db[i][2 * e + 1] += fd.y;
-                    const float g0 = fd.x * gam[i][2 * e], g1 = fd.y * gam[i][2 * e + 1];
-                    s1 += g0 + g1;
-                    s2 += g0 * h0 + g1 * h1;
+                    dg[i][e] = fma2(fd, h, dg[i][e]);
+                    db[i][e] = add2(db[i][e], fd);
+                    const float2 g = mul2(fd, gam[i][e]);
+                    s1 = add2(s1, g);
+                    s2 = fma2(g, h, s2);
                 }
             }
         }
-        const float m1 = warp_sum(s1) * inv_cols;
-        const float m2 = warp_sum(s2) * inv_cols;
+        const float m1 = warp_sum(s1.x + s1.y) * inv_cols;
+        const float m2 = warp_sum(s2.x + s2.y) * inv_cols;
+        const float2 nm1rs = splat2(-m1 * rs), nm2rs = splat2(-m2 * rs);   // dx = rs * (g - m1 - xhat * m2)
 #pragma unroll
         for (int i = 0; i < MAXCH; ++i) {
             const int ch = lane + 32 * i;
@@ -311,14 +333,12 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                 const uint4 px = lds128(xs + ch * 16), pd = lds128(ds + ch * 16);
                 const uint32_t wx[4] = {px.x, px.y, px.z, px.w};
                 const uint32_t wd[4] = {pd.x, pd.y, pd.z, pd.w};
-                float r[8];
+                float2 r[4];
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    const float2 fx = unpack_bf16x2(wx[e]);
-                    const float2 fd = unpack_bf16x2(wd[e]);
-                    const float h0 = (fx.x - mu) * rs, h1 = (fx.y - mu) * rs;
-                    r[2 * e] = rs * (fd.x * gam[i][2 * e] - m1 - h0 * m2);
-                    r[2 * e + 1] = rs * (fd.y * gam[i][2 * e + 1] - m1 - h1 * m2);
+                    const float2 h = fma2(unpack_bf16x2(wx[e]), rs2, nmr2);
+                    const float2 g = mul2(unpack_bf16x2(wd[e]), gam[i][e]);
+                    r[e] = fma2(h, nm2rs, fma2(g, rs2, nm1rs));
                 }
                 if (dres) {
                     const uint4 pr = lds128(rsd + ch * 16);
@@ -326,13 +346,13 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
                         const float2 f = unpack_bf16x2(wr[e]);
-                        r[2 * e] += f.x; r[2 * e + 1] += f.y;
-                        if (COLSUM) { dr[i][2 * e] += f.x; dr[i][2 * e + 1] += f.y; }
+                        r[e] = add2(r[e], f);
+                        if (COLSUM) dr[i][e] = add2(dr[i][e], f);
                     }
                 }
                 stg128(dx + row * cols + ch * 8,
-                       make_uint4(pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]),
-                                  pack_bf16x2(r[6], r[7])));
+                       make_uint4(pack_bf16x2(r[0].x, r[0].y), pack_bf16x2(r[1].x, r[1].y), pack_bf16x2(r[2].x, r[2].y),
+                                  pack_bf16x2(r[3].x, r[3].y)));
             }
         }
         __syncwarp();                                            // every lane is done with this slot
@@ -344,10 +364,15 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
         const int ch = lane + 32 * i;
         if (ch < nch) {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                atomicAdd(&acc[ch * 8 + e], dg[i][e]);
-                atomicAdd(&acc[cols + ch * 8 + e], db[i][e]);
-                if (COLSUM) atomicAdd(&acc[2 * cols + ch * 8 + e], dr[i][e]);
+            for (int e = 0; e < 4; ++e) {
+                atomicAdd(&acc[ch * 8 + 2 * e], dg[i][e].x);
+                atomicAdd(&acc[ch * 8 + 2 * e + 1], dg[i][e].y);
+                atomicAdd(&acc[cols + ch * 8 + 2 * e], db[i][e].x);
+                atomicAdd(&acc[cols + ch * 8 + 2 * e + 1], db[i][e].y);
+                if (COLSUM) {
+                    atomicAdd(&acc[2 * cols + ch * 8 + 2 * e], dr[i][e].x);
+                    atomicAdd(&acc[2 * cols + ch * 8 + 2 * e + 1], dr[i][e].y);
+                }
             }
         }
     }
@@ -743,13 +768,15 @@ extern "C" int mgb_layernorm_fwd(const void* x, const float* gamma, const float*
     cudaStream_t s = (cudaStream_t)s_;
     if (rows < 0 || cols <= 0) { set_last_error("layernorm_fwd: bad shape"); return kErrBadShape; }
     if (rows == 0) return kOk;
-    const int grid = grid_for(rows, LN_WARPS, num_sms() * 8);
+    // two resident CTAs per SM, each warp walking over several rows (gamma / beta stay in its registers)
+    const int grid = grid_for(rows, LN_WARPS * 4, num_sms() * 2);
     auto X = (const __nv_bfloat16*)x; auto Y = (__nv_bfloat16*)y;
     const bool vec = (cols % 8 == 0) && cols <= 2048 && ((uintptr_t)x % 16 == 0) && ((uintptr_t)y % 16 == 0) &&
                      ((uintptr_t)gamma % 16 == 0) && ((uintptr_t)beta % 16 == 0);
     if (!vec) ln_fwd_generic_kernel<<<grid, LN_WARPS * 32, 0, s>>>(X, gamma, beta, Y, mean, rstd, rows, cols, eps);
     else if (cols <= 256) launch_pdl(ln_fwd_kernel<1>, dim3(grid), dim3(LN_WARPS * 32), 0, s, X, gamma, beta, Y, mean, rstd, rows, cols, eps);
     else if (cols <= 512) launch_pdl(ln_fwd_kernel<2>, dim3(grid), dim3(LN_WARPS * 32), 0, s, X, gamma, beta, Y, mean, rstd, rows, cols, eps);
+    else if (cols <= 768) launch_pdl(ln_fwd_kernel<3>, dim3(grid), dim3(LN_WARPS * 32), 0, s, X, gamma, beta, Y, mean, rstd, rows, cols, eps);
     else if (cols <= 1024) launch_pdl(ln_fwd_kernel<4>, dim3(grid), dim3(LN_WARPS * 32), 0, s, X, gamma, beta, Y, mean, rstd, rows, cols, eps);
     else launch_pdl(ln_fwd_kernel<8>, dim3(grid), dim3(LN_WARPS * 32), 0, s, X, gamma, beta, Y, mean, rstd, rows, cols, eps);
     count_launch(1);
