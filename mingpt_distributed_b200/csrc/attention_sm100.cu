@@ -116,13 +116,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
         __syncwarp();
         for (int j = 0; j < nkv; ++j) {
             const uint32_t ph = (uint32_t)(j & 1);
-            mbar_wait(k_empty, ph ^ 1);               // S_{j-1} has consumed the previous K
+            mbar_wait_relaxed(k_empty, ph ^ 1);               // S_{j-1} has consumed the previous K
             if (issuer) {
                 mbar_arrive_expect_tx(k_full, TILE_BYTES);
                 tma_load_2d(sK, &tmap_qkv, k_full, C + h * D, row0 + j * BKV);
             }
             __syncwarp();
-            mbar_wait(v_empty, ph ^ 1);               // P V_{j-1} has consumed the previous V
+            mbar_wait_relaxed(v_empty, ph ^ 1);               // P V_{j-1} has consumed the previous V
             if (issuer) {
                 mbar_arrive_expect_tx(v_full, TILE_BYTES);
                 tma_load_2d(sV, &tmap_qkv, v_full, 2 * C + h * D, row0 + j * BKV);
@@ -147,20 +147,20 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
             }
             __syncwarp();
         };
-        mbar_wait(q_full, 0);
-        mbar_wait(k_full, 0);
+        mbar_wait_relaxed(q_full, 0);
+        mbar_wait_relaxed(k_full, 0);
         tc_fence_after();
         issue_s();
         for (int j = 0; j < nkv; ++j) {
             const uint32_t ph = (uint32_t)(j & 1);
-            mbar_wait(p_ready, ph);               // P_j in TMEM, O rescaled if needed, S consumed
+            mbar_wait_relaxed(p_ready, ph);               // P_j in TMEM, O rescaled if needed, S consumed
             tc_fence_after();
             if (j + 1 < nkv) {                    // S_{j+1} first: the softmax warps start on it while P V_j runs
-                mbar_wait(k_full, ph ^ 1);
+                mbar_wait_relaxed(k_full, ph ^ 1);
                 tc_fence_after();
                 issue_s();
             }
-            mbar_wait(v_full, ph);
+            mbar_wait_relaxed(v_full, ph);
             tc_fence_after();
             if (issuer) {
 #pragma unroll
@@ -190,7 +190,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
             const bool fast = !need_mask && !bias_diag;
             // causal diagonal block with every key present (and no additive bias): handled per 32-column group
             const bool diag_groups = causal && diag && (kvalid == BKV) && !bias_diag;
-            mbar_wait(s_full, ph);
+            mbar_wait_relaxed(s_full, ph);
             tc_fence_after();
             float mx = -INFINITY;
             if (diag_groups) {
@@ -259,7 +259,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
                 l_run *= factor;
             }
             if (j > 0) {
-                mbar_wait(pv_done, ph ^ 1);                      // P V_{j-1} finished: P columns free, O stable
+                mbar_wait_relaxed(pv_done, ph ^ 1);                      // P V_{j-1} finished: P columns free, O stable
                 tc_fence_after();
                 if (__any_sync(0xffffffffu, grow)) {
 #pragma unroll 1
@@ -367,7 +367,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
             if (lane == 0) mbar_arrive(p_ready);
         }
         // ---- epilogue: O / l, log-sum-exp ----
-        mbar_wait(pv_done, (uint32_t)((nkv - 1) & 1));
+        mbar_wait_relaxed(pv_done, (uint32_t)((nkv - 1) & 1));
         tc_fence_after();
         const float inv = l_run > 0.f ? (DROP ? inv_keep : 1.0f) / l_run : 0.f;
         __nv_bfloat16* orow = out + ((int64_t)(row0 + q)) * C + (int64_t)h * D;
@@ -635,12 +635,12 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 const int kv_at = (w > 0) ? 2 : 0;
                 for (int n = 0; n <= nsub; ++n) {
                     if (n == kv_at && have2) {
-                        if (w > 0) mbar_wait(all_done, (w - 1) & 1);
+                        if (w > 0) mbar_wait_relaxed(all_done, (w - 1) & 1);
                         load_kv(it2, (w + 1) & 1);
                     }
                     if (n == nsub) break;
                     const uint32_t slot = g & (kSlots - 1);
-                    mbar_wait(&qdo_empty[slot], ((g >> 2) & 1) ^ 1);
+                    mbar_wait_relaxed(&qdo_empty[slot], ((g >> 2) & 1) ^ 1);
                     const int qrow = row0 + it.i_begin * BQ + n * SUBQ;
                     if (issuer) {
                         mbar_arrive_expect_tx(&qdo_full[slot], 2 * SUB_BYTES);
@@ -671,7 +671,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
             auto issue_scores = [&](uint32_t gg) {    // S^T and dP^T of sub-block gg into buffer gg & 1
                 const uint32_t slot = gg & (kSlots - 1);
                 const uint32_t bcol = (gg & 1) * SUBQ;
-                mbar_wait(&qdo_full[slot], (gg >> 2) & 1);
+                mbar_wait_relaxed(&qdo_full[slot], (gg >> 2) & 1);
                 tc_fence_after();
                 const uint64_t dq_ = dQk0 + slot * kSlotStep, do_ = dq_ + kSubStep;
                 if (issuer) {
@@ -694,13 +694,13 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 if (st == 0) continue;
                 const int nsub = 2 * it.nblk;
                 const uint64_t dKmn = dKmn0 + (uint64_t)(w & 1) * 2 * kAtomStep;   // this item's K tile
-                mbar_wait(kv_ready, w & 1);              // K / V are in TMEM (and the K tile in shared memory)
+                mbar_wait_relaxed(kv_ready, w & 1);              // K / V are in TMEM (and the K tile in shared memory)
                 tc_fence_after();
                 issue_scores(g);
                 for (int n = 0; n < nsub; ++n, ++g) {
                     if (n + 1 < nsub) issue_scores(g + 1);
-                    mbar_wait(&p_ready[g & 1], (g >> 1) & 1);
-                    if (n == 0 && w > 0) mbar_wait(acc_free, (w - 1) & 1);   // dK / dV of the previous item are out
+                    mbar_wait_relaxed(&p_ready[g & 1], (g >> 1) & 1);
+                    if (n == 0 && w > 0) mbar_wait_relaxed(acc_free, (w - 1) & 1);   // dK / dV of the previous item are out
                     tc_fence_after();
                     const uint32_t slot = g & (kSlots - 1);
                     const uint64_t qmn = dQmn0 + slot * kSlotStep, omn = qmn + kSubStep;
@@ -719,7 +719,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                     __syncwarp();
                     if (g & 1) {
                         const uint32_t jg = g >> 1;
-                        if (jg > 0) { mbar_wait(dq_free, (jg - 1) & 1); tc_fence_after(); }
+                        if (jg > 0) { mbar_wait_relaxed(dq_free, (jg - 1) & 1); tc_fence_after(); }
                         const uint64_t dsmn = dSmn0 + (uint64_t)(jg & 1) * 2 * kAtomStep;
                         if (issuer) {
 #pragma unroll
@@ -749,7 +749,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
             if (st < 0) break;
             if (st == 0) continue;
             for (int j = 0; j < it.nblk; ++j, ++jg) {
-                mbar_wait(dq_full, jg & 1);
+                mbar_wait_relaxed(dq_full, jg & 1);
                 tc_fence_after();
                 uint32_t lo[32], hi[32];
                 tmem_ld_32x32b_x32(taddr + cDQ, lo);
@@ -811,7 +811,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
             float2 nxt = fetch_ld(0);
             {   // this item's K and V rows -> TMEM (bf16): 16 features of row r per thread. The previous item's products
                 // are complete (all_done was waited for in its epilogue).
-                mbar_wait(&kv_full[w & 1], (w >> 1) & 1);
+                mbar_wait_relaxed(&kv_full[w & 1], (w >> 1) & 1);
                 const uint8_t* sK = sKV + (w & 1) * 2 * TILE_BYTES;
                 const uint8_t* sV = sK + TILE_BYTES;
                 uint32_t kreg[8], vreg[8];
@@ -842,7 +842,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 if (lane < CPT) ld[lane] = make_float2(((tril && i > kb) ? LOG2E : 0.f) - nxt.x * LOG2E, nxt.y * scale);
                 nxt = fetch_ld(n + 1);
                 __syncwarp();
-                mbar_wait(&s_full[half], jg & 1);
+                mbar_wait_relaxed(&s_full[half], jg & 1);
                 tc_fence_after();
                 const int qc0 = (int)half * SUBQ + wg * CPT;         // first query column (inside the block) of this thread
                 uint32_t sv[CPT], dp[CPT];
@@ -922,7 +922,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 if (lane == 0) mbar_arrive(&p_ready[half]);
             }
             // ---- item epilogue: dK / dV of this key block ----
-            mbar_wait(all_done, w & 1);
+            mbar_wait_relaxed(all_done, w & 1);
             tc_fence_after();
             uint32_t vk[CPT], vv[CPT];
             tmem_ld_cols(taddr + cDK + wg * CPT, vk);

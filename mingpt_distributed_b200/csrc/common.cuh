@@ -253,15 +253,31 @@ __device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parit
     return done != 0;
 }
 // Wait with a watchdog: a protocol bug turns into a trap ("unspecified launch failure")
-// after ~4 s instead of a hung GPU box. Waiting warps share their scheduler with the warps that do the math
-// (producer / MMA warps next to epilogue or softmax warps), so the wait must not spin through issue slots: after one
-// plain probe it sleeps in the barrier unit with a long suspend hint.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+// after ~4 s instead of a hung GPU box.
+// Two flavours (measured on one box against each other, tools/ab_probe.py): the GEMM's producer / MMA / epilogue warps
+// wait on a barrier only while nobody else on their scheduler has work, and their wake-up latency is on the critical
+// path -- spinning on the default try_wait is 6 % faster there. In the attention kernels the waiting warps (TMA, MMA,
+// drain) share schedulers with warps that are busy with the softmax arithmetic: there the wait must not spin through
+// issue slots, and sleeping in the barrier unit with a long suspend hint is 8 % faster (mbar_wait_relaxed).
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
     uint64_t t0 = 0;
     uint32_t spins = 0;
     while (!mbar_try_wait_hint(bar, parity, 100000u)) {
         if ((++spins & 0x3fu) == 0) {
+            uint64_t now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 4000000000ull) { __trap(); }
+        }
+    }
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    if (mbar_try_wait(bar, parity)) return;
+    uint64_t t0 = 0;
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if ((++spins & 0xfffu) == 0) {
             uint64_t now;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
             if (t0 == 0) t0 = now;

@@ -16,6 +16,13 @@
 //           one thread TMA-STORES the box (or TMA-reduce-adds it in fp32 for split-K / accumulation).
 #include "gemm_common.cuh"
 
+#ifndef MGB_EPI_HOIST
+#define MGB_EPI_HOIST 0          // request a slice's accumulator columns before waiting for its staging box
+#endif
+#ifndef MGB_EPI_FFMA2_BIAS
+#define MGB_EPI_FFMA2_BIAS 0     // acc * alpha + bias on fp32 pairs
+#endif
+
 namespace mgb {
 namespace gemm {
 
@@ -303,9 +310,11 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 // the slice's accumulator columns are requested FIRST, so the TMEM round trip runs under the wait for the
                 // staging box (and the barrier) below instead of after it
                 uint32_t r0[32], r1[32];
+#if MGB_EPI_HOIST
                 __syncwarp();
                 tmem_ld_32x32b_x32(taddr_row + (uint32_t)(sl * slice_cols), r0);
                 if (chunks_per_slice == 2) tmem_ld_32x32b_x32(taddr_row + (uint32_t)(sl * slice_cols + 32), r1);
+#endif
                 if (p.tma_store && !aux) {
                     // the box written two slices ago (or both, when two outputs share the ring) must have been read
                     if (elected) { if (two_out) bulk_wait_read<0>(); else bulk_wait_read<1>(); }
@@ -315,6 +324,11 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     mbar_wait(&aux_b[buf], (aux_ph >> buf) & 1u);
                     aux_ph ^= (1u << buf);
                 }
+#if !MGB_EPI_HOIST
+                __syncwarp();
+                tmem_ld_32x32b_x32(taddr_row + (uint32_t)(sl * slice_cols), r0);
+                if (chunks_per_slice == 2) tmem_ld_32x32b_x32(taddr_row + (uint32_t)(sl * slice_cols + 32), r1);
+#endif
                 tmem_ld_wait();
                 if (sl + 2 >= nslices) {      // last TMEM read of the tile: the MMAs of the tile after next may overwrite it
                     tc_fence_before();
@@ -327,7 +341,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     const int ccol = sl * slice_cols + ch * 32;      // column inside the tile
                     const int64_t col0 = (int64_t)n0 + ccol;
                     float v[32];
-                    if (p.bias && bias_vec && col0 + 32 <= p.N) {
+                    if (MGB_EPI_FFMA2_BIAS && p.bias && bias_vec && col0 + 32 <= p.N) {
                         const float2 al = splat2(p.alpha);
 #pragma unroll
                         for (int q = 0; q < 8; ++q) {    // v = acc * alpha + bias, two columns per instruction
@@ -341,7 +355,13 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
                     }
                     if (p.bias) {
-                        if (bias_vec && col0 + 32 <= p.N) {
+                        if (MGB_EPI_FFMA2_BIAS && bias_vec && col0 + 32 <= p.N) {
+                        } else if (bias_vec && col0 + 32 <= p.N) {
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) {
+                                const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0) + q);
+                                v[q * 4 + 0] += b4.x; v[q * 4 + 1] += b4.y; v[q * 4 + 2] += b4.z; v[q * 4 + 3] += b4.w;
+                            }
                         } else {
 #pragma unroll
                             for (int j = 0; j < 32; ++j)

@@ -67,13 +67,21 @@ __device__ __forceinline__ float apply_act_grad(float v, int act) {
 
 // The activation kind is uniform over the launch: branch ONCE around a fully unrolled loop. (Selecting per
 // element makes the compiler evaluate both GELU flavours under predication: measured 2x on the epilogue.)
+#ifndef MGB_GELU_FFMA2
+#define MGB_GELU_FFMA2 1
+#endif
 __device__ __forceinline__ void act_inplace(float (&v)[32], int act) {
     if (act == MGB_ACT_GELU_TANH) {
+#if MGB_GELU_FFMA2
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
             const float2 y = gelu_tanh_2(make_float2(v[2 * j], v[2 * j + 1]));
             v[2 * j] = y.x; v[2 * j + 1] = y.y;
         }
+#else
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = gelu_tanh_f(v[j]);
+#endif
     } else if (act == MGB_ACT_GELU_ERF) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = gelu_erf_f(v[j]);
@@ -91,10 +99,17 @@ __device__ __forceinline__ bool preact_words(float (&v)[32], uint32_t (&w)[16], 
     if (act == MGB_ACT_GELU_TANH) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
+#if MGB_GELU_FFMA2
             float2 y, g;
             gelu_tanh_both_2(make_float2(v[2 * j], v[2 * j + 1]), y, g);
             v[2 * j] = y.x; v[2 * j + 1] = y.y;
             w[j] = pack_bf16x2(g.x, g.y);
+#else
+            float g0, g1;
+            gelu_tanh_both_f(v[2 * j], v[2 * j], g0);
+            gelu_tanh_both_f(v[2 * j + 1], v[2 * j + 1], g1);
+            w[j] = pack_bf16x2(g0, g1);
+#endif
         }
     } else {
 #pragma unroll

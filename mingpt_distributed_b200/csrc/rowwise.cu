@@ -302,7 +302,7 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
         const uint8_t* xs = ring + (size_t)s * 3 * rowbytes;
         const uint8_t* ds = xs + rowbytes;
         const uint8_t* rsd = xs + 2 * rowbytes;
-        mbar_wait(&bars[s], ph);
+        mbar_wait_relaxed(&bars[s], ph);
         float2 s1 = make_float2(0.f, 0.f), s2 = make_float2(0.f, 0.f);
 #pragma unroll
         for (int i = 0; i < MAXCH; ++i) {
@@ -618,7 +618,7 @@ cross_entropy_staged_kernel(__nv_bfloat16* logits, int64_t ld, const int64_t* __
             }
             for (int64_t k = 0; k < nmine; ++k) {
                 const int b = (int)(k & 1);
-                mbar_wait(&done[b], (uint32_t)((k >> 1) & 1));
+                mbar_wait_relaxed(&done[b], (uint32_t)((k >> 1) & 1));
                 bulk_store_1d(logits + (blockIdx.x + k * gridDim.x) * ld, bufs[b], rowbytes);
                 bulk_commit();
                 if (k + 2 < nmine) {
@@ -658,7 +658,7 @@ cross_entropy_staged_kernel(__nv_bfloat16* logits, int64_t ld, const int64_t* __
             if (err_flag && tid == 0) atomicExch(err_flag, 2);
             ignored = true;
         }
-        mbar_wait(&full[b], (uint32_t)((k >> 1) & 1));
+        mbar_wait_relaxed(&full[b], (uint32_t)((k >> 1) & 1));
         if (ignored) {
             if (tid == 0) row_loss[row] = 0.f;
             for (int64_t c = (int64_t)tid * 8; c < ld; c += NT * 8) sts128(lr + c, make_uint4(0, 0, 0, 0));

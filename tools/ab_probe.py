@@ -80,8 +80,10 @@ tg = torch.randint(0, V, (Mc,), device=dev); rl = torch.empty(Mc, device=dev); n
 ops.count_valid_targets(tg, nv)
 cases += [("cross entropy 16384 rows", lambda: ops.cross_entropy_fwd_bwd(lg, tg, rl, nv, V), -(2 * Mc * 50304 * 2))]
 print(f"# {tag}: lib={os.environ.get('MGB_LIB_PATH', 'current')}")
-tot = 0.0
+only = [t for t in os.environ.get("AB_ONLY", "").split(",") if t]
 for name, fn, work in cases:
+    if only and not any(name.startswith(t) for t in only):
+        continue
     t = bench(fn)
     rate = f"{work / t / 1e6:7.0f} TF/s" if work > 0 else f"{-work / t / 1e3:7.0f} GB/s"
     print(f"{tag:10s} {name:32s} {t:8.1f} us {rate}", flush=True)
