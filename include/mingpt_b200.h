@@ -63,7 +63,11 @@ int64_t mgb_launch_count(void);
  * exponentials per logit, instead of staging them in shared memory), "pdl" (default 0; 1 = launch the GEMM,
  * LayerNorm and attention kernels with programmatic stream serialization, so that a kernel's prologue --
  * barrier set-up, TMEM allocation -- overlaps the tail of the kernel before it; every such kernel waits on
- * griddepcontrol before it reads global memory), "reserved_sms" (default 0; n = size the persistent grids -- GEMM,
+ * griddepcontrol before it reads global memory), "gemm_generic" (1 = the CTA-pair GEMM always runs its generic
+ * epilogue instantiation, which decides every epilogue term at run time, instead of the ones specialised at compile
+ * time for the combinations the training step uses), "attn_poly" (default 1: share of the forward softmax's
+ * exponentials computed by a cubic polynomial on the FMA pipe instead of the special-function unit, in quarters of
+ * the 128 keys of a block -- 0, 1 or 2; relative error of the polynomial 7.5e-5), "reserved_sms" (default 0; n = size the persistent grids -- GEMM,
  * attention backward, cross-entropy, LayerNorm backward -- for n fewer SMs than the device has, leaving them to a
  * concurrent communication kernel: the data-parallel trainer sets it while gradient all-reduces are in flight, so no
  * CTA pair of a persistent GEMM waits a whole tile wave for SMs that NCCL occupies). Returns the

@@ -16,13 +16,6 @@
 //           one thread TMA-STORES the box (or TMA-reduce-adds it in fp32 for split-K / accumulation).
 #include "gemm_common.cuh"
 
-#ifndef MGB_EPI_HOIST
-#define MGB_EPI_HOIST 0          // request a slice's accumulator columns before waiting for its staging box
-#endif
-#ifndef MGB_EPI_FFMA2_BIAS
-#define MGB_EPI_FFMA2_BIAS 0     // acc * alpha + bias on fp32 pairs
-#endif
-
 namespace mgb {
 namespace gemm {
 
@@ -112,7 +105,14 @@ __device__ __forceinline__ void epilogue_direct(const Params& p, float (&v)[32],
 // shared-memory atomics per CTA, one global atomic per column and tile) into p.colsum: the bias gradient that
 // goes with an output-gradient GEMM, without another pass over D. A separate instantiation, so the register
 // allocation of the plain kernel is untouched.
-template <bool COLSUM>
+// MODE: the epilogue specialised at compile time for the combinations the training step uses, so that each hot
+// instantiation carries only its own code (the all-in-one epilogue spent ~15 % of its warp time on instruction-cache
+// misses: ncu "no_inst"):
+//   0  generic: everything decided at run time (erf GELU, stores that TMA cannot address, direct gate / residual loads)
+//   1  bf16 D through TMA, one output, no activation; optional bias; optional residual / gate-multiply tile through TMA
+//   2  bf16 D + saved GELU' through TMA, NewGELU(tanh), bias                                   (c_fc forward)
+//   3  fp32 D through TMA store or reduce-add, no epilogue terms                               (weight gradients)
+template <bool COLSUM, int MODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_d, const __grid_constant__ CUtensorMap tmap_p,
@@ -131,6 +131,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     uint64_t* aux_bar = tmem_empty + 2;              // [kNumBoxes]   residual / gate tile landed in box i
     uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(aux_bar + kNumBoxes);
     float* cs_smem = reinterpret_cast<float*>(boxes + kNumBoxes * kBoxBytes + 512);   // [256] (COLSUM only)
+    float* bias_s = cs_smem + 256;                                                     // [2][256] bias of the current / next tile
     if (COLSUM) {
         for (int c = threadIdx.x; c < 256; c += blockDim.x) cs_smem[c] = 0.f;
     }
@@ -145,7 +146,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_a);
         tma_prefetch_desc(&tmap_b);
-        if (p.tma_store) {
+        if (MODE || p.tma_store) {
             tma_prefetch_desc(&tmap_d);
             if (p.preact) tma_prefetch_desc(&tmap_p);
             if (p.tma_aux) tma_prefetch_desc(&tmap_x);
@@ -269,10 +270,17 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                             (!p.residual || (((p.ldr & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.residual) & 15) == 0))) &&
                             (!p.preact || (((p.ldp & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.preact) & 15) == 0))) &&
                             (!p.gate || (((p.ldg & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.gate) & 15) == 0)));
-        const bool bias_vec = p.bias && ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
-        const bool two_out = p.tma_store && p.preact != nullptr;
-        const int aux = p.tma_aux;                                // 0 none, 1 residual, 2 gate: TMA-loaded in place
-        const int slice_cols = p.d_f32 ? 32 : 64;                 // columns per 128-byte output slice
+        // compile-time facts of the specialised instantiations (MODE 0 reads them from the parameters)
+        const bool tma_store = MODE != 0 || p.tma_store;
+        const bool d_f32 = MODE == 3 || (MODE == 0 && p.d_f32);
+        const bool has_bias = MODE != 3 && p.bias != nullptr;
+        const bool two_out = MODE == 2 || (MODE == 0 && p.tma_store && p.preact != nullptr);
+        const int aux = (MODE == 2 || MODE == 3) ? 0 : p.tma_aux;   // 0 none, 1 residual, 2 gate: TMA-loaded in place
+        const int act = MODE == 2 ? (int)MGB_ACT_GELU_TANH : (MODE == 0 ? p.act : 0);
+        const int act_grad = MODE == 2 ? 1 : (MODE == 0 ? p.act_grad : 0);
+        const bool direct_gate = MODE == 0 && p.gate != nullptr;       // gate / residual read from global memory by the thread
+        const bool direct_res = MODE == 0 && p.residual != nullptr;
+        const int slice_cols = d_f32 ? 32 : 64;                   // columns per 128-byte output slice
         const int nslices = block_n / slice_cols;
         const int chunks_per_slice = slice_cols >> 5;
         uint8_t* box_base = boxes + half * 2 * kBoxBytes;
@@ -298,8 +306,17 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     tma_load_2d(box_base + b * kBoxBytes, &tmap_x, &aux_b[b], n0 + sl * slice_cols, m0);
                 }
             }
+            if (has_bias) {
+                // The tile's bias (block_n <= 256 values) goes to shared memory once per tile, while the tile's MMAs
+                // still run: with the shared-memory carve-out at its maximum the L1 holds next to nothing, and eight
+                // 16-byte bias loads per 32-column chunk from L2 were the epilogue's largest stall (ncu: long_sb).
+                // Buffer `acc` is free: its readers finished two tiles ago, before their tmem_empty arrive.
+                const int c = (int)threadIdx.x - 128;
+                bias_s[acc * 256 + c] = (c < block_n && n0 + c < p.N) ? __ldg(p.bias + n0 + c) : 0.f;
+            }
             mbar_wait(&tmem_full[acc], acc_phase);
             tc_fence_after();
+            if (has_bias) named_bar_sync(4, kEpiWarps * 32);      // bias visible to all eight epilogue warps
             const int64_t row = (int64_t)m0 + r_local;
             const bool row_ok = row < p.M;
             const uint32_t taddr_row = tmem_base + acc * kAccStride + ((uint32_t)(quarter * 32) << 16);
@@ -307,15 +324,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             for (int sl = half; sl < nslices; sl += 2) {
                 uint8_t* box = box_base + buf * kBoxBytes;
                 uint8_t* box2 = box_base + (buf ^ 1) * kBoxBytes;
-                // the slice's accumulator columns are requested FIRST, so the TMEM round trip runs under the wait for the
-                // staging box (and the barrier) below instead of after it
-                uint32_t r0[32], r1[32];
-#if MGB_EPI_HOIST
-                __syncwarp();
-                tmem_ld_32x32b_x32(taddr_row + (uint32_t)(sl * slice_cols), r0);
-                if (chunks_per_slice == 2) tmem_ld_32x32b_x32(taddr_row + (uint32_t)(sl * slice_cols + 32), r1);
-#endif
-                if (p.tma_store && !aux) {
+                if (tma_store && !aux) {
                     // the box written two slices ago (or both, when two outputs share the ring) must have been read
                     if (elected) { if (two_out) bulk_wait_read<0>(); else bulk_wait_read<1>(); }
                     named_bar_sync(1 + half, 128);
@@ -324,67 +333,48 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     mbar_wait(&aux_b[buf], (aux_ph >> buf) & 1u);
                     aux_ph ^= (1u << buf);
                 }
-#if !MGB_EPI_HOIST
-                __syncwarp();
-                tmem_ld_32x32b_x32(taddr_row + (uint32_t)(sl * slice_cols), r0);
-                if (chunks_per_slice == 2) tmem_ld_32x32b_x32(taddr_row + (uint32_t)(sl * slice_cols + 32), r1);
-#endif
-                tmem_ld_wait();
-                if (sl + 2 >= nslices) {      // last TMEM read of the tile: the MMAs of the tile after next may overwrite it
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive_cluster(&tmem_empty[acc], 0);
-                    released = true;
-                }
                 uint8_t* rowp = box + r_local * 128;
-                auto chunk_body = [&](const int ch, uint32_t (&r)[32]) {
+                for (int ch = 0; ch < chunks_per_slice; ++ch) {
                     const int ccol = sl * slice_cols + ch * 32;      // column inside the tile
+                    uint32_t r[32];
+                    __syncwarp();
+                    tmem_ld_32x32b_x32(taddr_row + (uint32_t)ccol, r);
+                    tmem_ld_wait();
+                    if (sl + 2 >= nslices && ch == chunks_per_slice - 1) {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive_cluster(&tmem_empty[acc], 0);
+                        released = true;
+                    }
                     const int64_t col0 = (int64_t)n0 + ccol;
                     float v[32];
-                    if (MGB_EPI_FFMA2_BIAS && p.bias && bias_vec && col0 + 32 <= p.N) {
-                        const float2 al = splat2(p.alpha);
 #pragma unroll
-                        for (int q = 0; q < 8; ++q) {    // v = acc * alpha + bias, two columns per instruction
-                            const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0) + q);
-                            const float2 lo = fma2(make_float2(__uint_as_float(r[q * 4 + 0]), __uint_as_float(r[q * 4 + 1])), al, make_float2(b4.x, b4.y));
-                            const float2 hi = fma2(make_float2(__uint_as_float(r[q * 4 + 2]), __uint_as_float(r[q * 4 + 3])), al, make_float2(b4.z, b4.w));
-                            v[q * 4 + 0] = lo.x; v[q * 4 + 1] = lo.y; v[q * 4 + 2] = hi.x; v[q * 4 + 3] = hi.y;
-                        }
-                    } else {
+                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+                    if (has_bias) {      // this tile's bias lives in shared memory (staged once per tile, below)
+                        const float* bs = bias_s + acc * 256 + ccol;
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
-                    }
-                    if (p.bias) {
-                        if (MGB_EPI_FFMA2_BIAS && bias_vec && col0 + 32 <= p.N) {
-                        } else if (bias_vec && col0 + 32 <= p.N) {
-#pragma unroll
-                            for (int q = 0; q < 8; ++q) {
-                                const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0) + q);
-                                v[q * 4 + 0] += b4.x; v[q * 4 + 1] += b4.y; v[q * 4 + 2] += b4.z; v[q * 4 + 3] += b4.w;
-                            }
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (col0 + j < p.N) v[j] += __ldg(p.bias + col0 + j);
+                        for (int q = 0; q < 8; ++q) {
+                            const float4 b4 = lds128f(bs + q * 4);
+                            v[q * 4 + 0] += b4.x; v[q * 4 + 1] += b4.y; v[q * 4 + 2] += b4.z; v[q * 4 + 3] += b4.w;
                         }
                     }
-                    if (!p.tma_store) {
+                    if (!tma_store) {
                         if (row_ok && col0 < p.N) epilogue_direct(p, v, row, col0, vec_ok);
-                        return;
+                        continue;
                     }
                     // ---- staged path: everything below touches shared memory only ----
                     bool acted = false;
                     if (two_out) {
                         uint8_t* rowp2 = box2 + r_local * 128;
                         uint32_t pw[16];
-                        acted = preact_words(v, pw, p.act, p.act_grad);
+                        acted = preact_words(v, pw, act, act_grad);
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
                             const uint32_t j = (uint32_t)(ch * 4 + q);
                             sts128(rowp2 + ((j ^ swz) << 4), make_uint4(pw[q * 4], pw[q * 4 + 1], pw[q * 4 + 2], pw[q * 4 + 3]));
                         }
                     }
-                    if (p.act && !acted) act_inplace(v, p.act);
+                    if (act && !acted) act_inplace(v, act);
                     if (aux) {
                         // this thread's 64 bytes of the TMA-loaded residual / gate tile (swizzled like the output)
                         uint32_t xw[16];
@@ -394,10 +384,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                             const uint4 xi = lds128(rowp + ((j ^ swz) << 4));
                             xw[q * 4 + 0] = xi.x; xw[q * 4 + 1] = xi.y; xw[q * 4 + 2] = xi.z; xw[q * 4 + 3] = xi.w;
                         }
-                        if (aux == 2) gate_inplace(v, xw, p.gate_kind);
+                        if (aux == 2) gate_inplace(v, xw, MODE == 1 ? (int)MGB_GATE_MUL : p.gate_kind);
                         else add_bf16_inplace(v, xw);
                     }
-                    if (p.gate && aux != 2 && row_ok) {
+                    if (direct_gate && aux != 2 && row_ok) {
                         const __nv_bfloat16* g = p.gate + row * p.ldg + col0;
                         uint32_t gw[16];
 #pragma unroll
@@ -408,7 +398,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         }
                         gate_inplace(v, gw, p.gate_kind);
                     }
-                    if (p.residual && aux != 1 && row_ok) {
+                    if (direct_res && aux != 1 && row_ok) {
                         const __nv_bfloat16* rs = p.residual + row * p.ldr + col0;
                         uint32_t rw[16];
 #pragma unroll
@@ -440,7 +430,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         const float tot = (b1 ? t2[1] : t2[0]) + __shfl_xor_sync(0xffffffffu, b1 ? t2[0] : t2[1], 1);
                         atomicAdd(&cs_smem[ccol + lane], tot);
                     }
-                    if (p.d_f32) {
+                    if (d_f32) {
 #pragma unroll
                         for (int q = 0; q < 8; ++q)
                             sts128f(rowp + (((uint32_t)q ^ swz) << 4), make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]));
@@ -453,10 +443,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                                               pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7])));
                         }
                     }
-                };
-                chunk_body(0, r0);
-                if (chunks_per_slice == 2) chunk_body(1, r1);
-                if (p.tma_store) {
+                }
+                if (tma_store) {
                     fence_proxy_async_smem();
                     named_bar_sync(1 + half, 128);
                     if (elected) {
@@ -486,7 +474,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             }
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
-        if (p.tma_store && elected) bulk_wait<0>();
+        if (tma_store && elected) bulk_wait<0>();
     }
 
     __syncwarp();
@@ -530,8 +518,12 @@ static bool tma_ok(const void* base, int64_t ld, int elem_bytes) {
 int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t stream) {
     static PerDeviceOnce once;
     once.run([] {
-        cudaFuncSetAttribute(gemm_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
-        cudaFuncSetAttribute(gemm_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+        cudaFuncSetAttribute(gemm_pair_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+        cudaFuncSetAttribute(gemm_pair_kernel<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+        cudaFuncSetAttribute(gemm_pair_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+        cudaFuncSetAttribute(gemm_pair_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+        cudaFuncSetAttribute(gemm_pair_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+        cudaFuncSetAttribute(gemm_pair_kernel<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     });
     const int num_clusters = num_sms / 2;
     int bn = a->block_n;
@@ -582,7 +574,7 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
     // column sums ride along only on the staged bf16 path; otherwise mgb_gemm_bf16 adds them with a separate pass
     const bool fused_colsum = a->colsum && p.tma_store && !a->d_f32;
     p.colsum = fused_colsum ? a->colsum : nullptr;
-    const int fixed = kNumBoxes * kBoxBytes + 1024 + 512 + (fused_colsum ? 1024 : 0);
+    const int fixed = kNumBoxes * kBoxBytes + 1024 + 512 + 1024 + 2048;   // align slack | barriers | colsum | bias x 2
     int stages = (kSmemLimit - fixed) / (int)stage_bytes;
     if (stages > kMaxStages) stages = kMaxStages;
     p.num_stages = stages;
@@ -612,10 +604,24 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
     }
     const int64_t units = (int64_t)tiles * p.split_k;
     const int clusters = (int)(units < num_clusters ? units : num_clusters);
+    // epilogue specialisation (see the kernel): pick the leanest instantiation that covers this call
+    int mode = 0;
+    if (p.tma_store && !g_opt_gemm_generic.load(std::memory_order_relaxed)) {
+        const bool side_ok = (!a->gate || (p.tma_aux == 2 && a->gate_kind == MGB_GATE_MUL && !a->residual)) &&
+                             (!a->residual || (p.tma_aux == 1 && !a->gate));
+        if (a->d_f32 && !a->bias && !p.act && !a->gate && !a->residual && !a->preact && !fused_colsum) mode = 3;
+        else if (!a->d_f32 && p.preact && p.act == MGB_ACT_GELU_TANH && p.act_grad && a->bias && !a->gate && !a->residual &&
+                 !fused_colsum) mode = 2;
+        else if (!a->d_f32 && !p.preact && !p.act && side_ok) mode = 1;
+    }
     {
-        const cudaError_t e = fused_colsum
-            ? launch_pdl(gemm_pair_kernel<true>, dim3(2 * clusters), dim3(kThreads), (size_t)smem_bytes, stream, ta, tb, td, tp, tx, p)
-            : launch_pdl(gemm_pair_kernel<false>, dim3(2 * clusters), dim3(kThreads), (size_t)smem_bytes, stream, ta, tb, td, tp, tx, p);
+        cudaError_t e;
+#define MGB_PAIR(CS, MD) launch_pdl(gemm_pair_kernel<CS, MD>, dim3(2 * clusters), dim3(kThreads), (size_t)smem_bytes, stream, ta, tb, td, tp, tx, p)
+        if (mode == 3) e = MGB_PAIR(false, 3);
+        else if (mode == 2) e = MGB_PAIR(false, 2);
+        else if (mode == 1) e = fused_colsum ? MGB_PAIR(true, 1) : MGB_PAIR(false, 1);
+        else e = fused_colsum ? MGB_PAIR(true, 0) : MGB_PAIR(false, 0);
+#undef MGB_PAIR
         if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); return kErrLaunch; }
     }
     count_launch(1);

@@ -11,6 +11,7 @@
 namespace mgb {
 extern std::atomic<int> g_opt_gemm_single;
 extern std::atomic<int> g_opt_gemm_direct_store;
+extern std::atomic<int> g_opt_gemm_generic;       // 1 = always the generic (run-time) epilogue instantiation
 namespace gemm {
 
 constexpr int BLOCK_M = 128;   // rows per CTA (a CTA pair covers 256)

@@ -308,6 +308,7 @@ extern "C" int64_t mgb_launch_count(void) { return g_launches.load(std::memory_o
 namespace mgb {
 std::atomic<int> g_opt_gemm_single{0};
 std::atomic<int> g_opt_gemm_direct_store{0};
+std::atomic<int> g_opt_gemm_generic{0};
 std::atomic<int> g_opt_pdl{0};   // measured gain on the gpt2-124M step: 0-1 % (within run-to-run noise), so off by default
 bool pdl_enabled() { return g_opt_pdl.load(std::memory_order_relaxed) != 0; }
 std::atomic<int> g_opt_attn_mma{0};
@@ -319,6 +320,7 @@ extern "C" int mgb_set_option(const char* key, int value) {
     if (!key) return -1;
     if (!std::strcmp(key, "gemm_single")) return mgb::g_opt_gemm_single.exchange(value);
     if (!std::strcmp(key, "gemm_direct_store")) return mgb::g_opt_gemm_direct_store.exchange(value);
+    if (!std::strcmp(key, "gemm_generic")) return mgb::g_opt_gemm_generic.exchange(value);
     if (!std::strcmp(key, "pdl")) return mgb::g_opt_pdl.exchange(value);
     if (!std::strcmp(key, "attn_mma")) return mgb::g_opt_attn_mma.exchange(value);
     if (!std::strcmp(key, "attn_poly")) return mgb::g_opt_attn_poly.exchange(value);
