@@ -117,8 +117,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_d, const __grid_constant__ CUtensorMap tmap_p,
                  const __grid_constant__ CUtensorMap tmap_x, const Params p) {
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    // No static shared memory in this kernel, so the dynamic window starts 1024-aligned (checked): no alignment slack --
+    // the 3 KiB left beside five 32 KiB stages and the staging boxes are needed for the barriers and the bias tiles.
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = smem_raw;
+    if (smem_u32(smem) & 1023u) __trap();
     const int block_n = p.block_n;
     const int nb = block_n >> 1;                               // B columns staged by this CTA
     const uint32_t stage_bytes = BLOCK_M * BLOCK_K * 2 + (uint32_t)nb * BLOCK_K * 2;
@@ -130,8 +133,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     uint64_t* tmem_empty = tmem_full + 2;            // [2]           (leader's copy is the live one)
     uint64_t* aux_bar = tmem_empty + 2;              // [kNumBoxes]   residual / gate tile landed in box i
     uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(aux_bar + kNumBoxes);
-    float* cs_smem = reinterpret_cast<float*>(boxes + kNumBoxes * kBoxBytes + 512);   // [256] (COLSUM only)
-    float* bias_s = cs_smem + 256;                                                     // [2][256] bias of the current / next tile
+    float* bias_s = reinterpret_cast<float*>(boxes + kNumBoxes * kBoxBytes + 256);    // [2][256] bias of the current / next tile
+    float* cs_smem = bias_s + (p.bias ? 512 : 0);                                      // [256] (COLSUM only; behind the bias if both)
     if (COLSUM) {
         for (int c = threadIdx.x; c < 256; c += blockDim.x) cs_smem[c] = 0.f;
     }
@@ -574,7 +577,7 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
     // column sums ride along only on the staged bf16 path; otherwise mgb_gemm_bf16 adds them with a separate pass
     const bool fused_colsum = a->colsum && p.tma_store && !a->d_f32;
     p.colsum = fused_colsum ? a->colsum : nullptr;
-    const int fixed = kNumBoxes * kBoxBytes + 1024 + 512 + 1024 + 2048;   // align slack | barriers | colsum | bias x 2
+    const int fixed = kNumBoxes * kBoxBytes + 256 + ((a->bias && fused_colsum) ? 3072 : 2048);   // barriers | bias x 2 / colsum
     int stages = (kSmemLimit - fixed) / (int)stage_bytes;
     if (stages > kMaxStages) stages = kMaxStages;
     p.num_stages = stages;
