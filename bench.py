@@ -172,6 +172,8 @@ def main():
     ap.add_argument("--dropout", type=float, default=0.0, help="embed/resid/attn dropout (reference default 0.1); headline is 0")
     ap.add_argument("--no-graph", action="store_true", help="issue every kernel from Python instead of replaying a CUDA graph")
     ap.add_argument("--opt", action="append", default=[], help="library option key=value (mgb_set_option), repeatable")
+    ap.add_argument("--grad-wire", default="fp32", choices=["fp32", "bf16"], help="dtype of the gradient all-reduce (N > 1)")
+    ap.add_argument("--comm-sms", type=int, default=0, help="SMs left to NCCL while all-reduces are in flight (N > 1)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -216,7 +218,9 @@ def main():
     model = m.GPT(cfg, verbose=False)
     opt = m.create_optimizer(model, m.OptimizerConfig())
     model = model.to(dev)
-    dp = m.DataParallel(model) if world > 1 else None
+    dp = None
+    if world > 1:
+        dp = m.DataParallel(model, grad_wire_dtype=torch.bfloat16 if args.grad_wire == "bf16" else None, comm_sms=args.comm_sms)
 
     nbatches = 4
     loader = None
@@ -378,6 +382,7 @@ def main():
                                          + (", tokens cut from a device-resident synthetic byte corpus (CharDataset)" if spec["char"] else ""),
                                 global_batch=world * K * B, micro_batch_per_gpu=B, accumulation_steps=K, seq_len=T,
                                 parallelism=f"dp{world}", dropout=args.dropout, options=opts,
+                                grad_allreduce=(None if world == 1 else f"{args.grad_wire} SUM per >=25 MiB bucket, comm_sms={args.comm_sms}"),
                                 launch=("eager (one Python call per kernel)" if not stepper.use_graph else
                                         "CUDA graph replay of the whole step" if dp is None else
                                         "CUDA graph segments cut at gradient-bucket boundaries, NCCL all-reduces launched between them"),

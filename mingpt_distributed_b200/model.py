@@ -174,6 +174,26 @@ class _MinBlock(nn.Module):
 _ALIGN = 64  # elements: every parameter starts 256-byte (fp32) / 128-byte (bf16 shadow) aligned
 
 
+class _Nvtx:
+    """NVTX ranges around the phases of a step (embedding, each block's forward / backward, head + loss) so that an
+    nsys / ncu timeline reads like the model. Off unless MGB_NVTX=1: a range is two host calls per phase."""
+
+    def __init__(self):
+        import os
+        self.on = os.environ.get("MGB_NVTX", "0") == "1"
+
+    def push(self, name: str):
+        if self.on:
+            torch.cuda.nvtx.range_push(name)
+
+    def pop(self):
+        if self.on:
+            torch.cuda.nvtx.range_pop()
+
+
+_nvtx = _Nvtx()
+
+
 class LazyLogits:
     """What forward() returns as `logits` when a loss is requested on the fused path: the full
     (B, T, vocab) tensor is only produced if somebody asks (mingpt/trainer.py:122 discards it)."""
@@ -605,10 +625,14 @@ class GPT(nn.Module):
         wpe = W("wpe").view(-1, C)
         pe, pr, pa = self._dropout_now(ws)
         seed = ws.seed
+        _nvtx.push("embedding")
         ops.embedding_fwd(idx, W("wte"), wpe, ws.x[0], ws.err_flag)
         if pe > 0:   # nn.Dropout(embed_drop), mingpt/model.py:215,231
             ops.dropout(ws.x[0], None, ws.x[0], pe, seed, self.SITE_EMBED)
+        _nvtx.pop()
         for l in range(L):
+            _nvtx.pop() if l else None
+            _nvtx.push(f"block{l}.fwd")
             s = ws.stats[l]
             ops.layernorm_fwd(ws.x[l], P(f"{l}.ln1_w"), P(f"{l}.ln1_b"), ws.ln1[l], s[0], s[1])
             ops.linear_fwd(ws.ln1[l], W(f"{l}.qkv_w"), ws.qkv[l], bias=P(f"{l}.qkv_b"))
@@ -644,6 +668,7 @@ class GPT(nn.Module):
                     ops.dropout(ws.tmp, ws.xmid[l], ws.x[l + 1], pr, seed, 4 * l + 2)
                 else:
                     ops.linear_fwd(ws.fc_act[l], W(f"{l}.fc2_w"), ws.x[l + 1], bias=P(f"{l}.fc2_b"), residual=ws.xmid[l])
+        _nvtx.pop() if L else None
         ops.layernorm_fwd(ws.x[L], P("lnf_w"), P("lnf_b"), ws.lnf, ws.lnf_stats[0], ws.lnf_stats[1])
 
     def _head_loss(self, ws: _Workspace, targets: torch.Tensor, need_grad: bool, direct: bool = False):
@@ -655,6 +680,7 @@ class GPT(nn.Module):
         V, M = self.vocab_size, ws.M
         tg = targets.reshape(-1)
         hw = self._w("head_w", bf16=True)
+        _nvtx.push("head+loss")
         ops.count_valid_targets(tg, ws.n_valid)
         head_dw = self._g("head_w") if direct else ws.head_dw
         if need_grad and not direct:
@@ -670,6 +696,7 @@ class GPT(nn.Module):
                 ops.linear_dgrad(lg, hw, ws.dlnf[r0:r0 + rows])
                 ops.linear_wgrad(lg, ws.lnf[r0:r0 + rows], head_dw, accumulate=True)
         ops.loss_finalize(ws.row_loss, ws.n_valid, ws.loss)
+        _nvtx.pop()
         ws.has_head_grads = need_grad
         ws.head_direct = direct
 
@@ -808,6 +835,7 @@ class GPT(nn.Module):
         pe, pr, pa = ws.drop
         seed = ws.seed
         for l in range(L - 1, -1, -1):
+            _nvtx.push(f"block{l}.bwd")
             s = ws.stats[l]
             dmlp = dx          # gradient of the MLP branch output: through its dropout mask when there is one
             if pr > 0:
@@ -858,6 +886,7 @@ class GPT(nn.Module):
             ops.layernorm_bwd(ws.dln, ws.x[l], P(f"{l}.ln1_w"), s[0], s[1], ws.dx_a, G(f"{l}.ln1_w"), G(f"{l}.ln1_b"), dres=dxm,
                               dres_colsum=G(f"{l}.proj_b") if pr == 0 else None)
             dx = ws.dx_a
+            _nvtx.pop()
             if self._layer_done_hook is not None:
                 self._layer_done_hook(l + 1)
         gwpe = G("wpe").view(-1, C)

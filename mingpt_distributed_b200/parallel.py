@@ -9,6 +9,14 @@ defaults: 25 MiB buckets, reverse registration order, SUM then divide by world s
 The gradients live in ONE flat fp32 buffer laid out by layer (model.GPT._layer_spans), so a bucket is a
 contiguous slice: no flatten/unflatten copies, and the optimizer reads the reduced buffer directly.
 The 1/world_size average is not a separate pass: it is folded into FusedAdamW.step(grad_scale=...).
+
+Two knobs for the NVLink / SM budget (both off by default, so the default exchange is torch DDP's: fp32 SUM):
+  grad_wire_dtype=torch.bfloat16  the bucket is rounded to bf16 for the wire (cast -> all-reduce -> cast back, all on
+                                  the side stream): half the bytes, half the time NCCL's CTAs share the SMs with the
+                                  backward GEMMs. Master gradients, AdamW and its state stay fp32.
+  comm_sms=n                      while all-reduces are in flight the persistent grids of the compute stream (GEMM,
+                                  attention backward, ...) are sized for n fewer SMs (mgb_set_option "reserved_sms"),
+                                  so no CTA pair waits a whole tile wave for an SM that NCCL occupies.
 """
 from __future__ import annotations
 
@@ -42,9 +50,16 @@ class GradBuckets:
     Works on CUDA (NCCL, side stream + events) and on CPU tensors (Gloo, synchronous) -- the latter is
     what the world_size-2 CPU tests drive."""
 
-    def __init__(self, flat_grad: torch.Tensor, layer_spans, bucket_cap_mb: float = 25.0, process_group=None):
+    def __init__(self, flat_grad: torch.Tensor, layer_spans, bucket_cap_mb: float = 25.0, process_group=None,
+                 wire_dtype: Optional[torch.dtype] = None, comm_sms: int = 0):
         self.flat = flat_grad
         self.group = process_group
+        if wire_dtype not in (None, torch.float32, torch.bfloat16):
+            raise ValueError("grad_wire_dtype must be None / torch.float32 / torch.bfloat16")
+        self.wire = None
+        if wire_dtype == torch.bfloat16 and flat_grad.is_cuda:
+            self.wire = torch.empty(flat_grad.numel(), dtype=torch.bfloat16, device=flat_grad.device)
+        self.comm_sms = int(comm_sms)
         self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
         cap = max(1, int(bucket_cap_mb * 1024 * 1024 / flat_grad.element_size()))
         self.buckets = plan_buckets(layer_spans, cap)
@@ -54,28 +69,46 @@ class GradBuckets:
         self.launched = 0
         self.enabled = True   # False = gradient accumulation micro-step (DDP.no_sync)
 
-    def on_group_done(self, g: int):
-        if not self.enabled or self.world == 1:
-            return
-        span = self._by_trigger.get(g)
-        if span is None:
-            return
-        s, e = span
+    def reduce_span(self, s: int, e: int):
+        """SUM all-reduce of flat[s:e] on the side stream, ordered after everything the compute stream has queued"""
         chunk = self.flat[s:e]
         if self.cuda:
             ev = torch.cuda.Event()
             ev.record(torch.cuda.current_stream())
             self.stream.wait_event(ev)
             with torch.cuda.stream(self.stream):
-                dist.all_reduce(chunk, op=dist.ReduceOp.SUM, group=self.group)
+                if self.wire is not None:
+                    from . import ops
+                    w = self.wire[s:e]
+                    ops.cast_f32_to_bf16(chunk, w)
+                    dist.all_reduce(w, op=dist.ReduceOp.SUM, group=self.group)
+                    ops.cast_bf16_to_f32(w, chunk)
+                else:
+                    dist.all_reduce(chunk, op=dist.ReduceOp.SUM, group=self.group)
         else:
             dist.all_reduce(chunk, op=dist.ReduceOp.SUM, group=self.group)
         self.launched += 1
+
+    def reserve_sms(self, on: bool):
+        """size the compute stream's persistent grids for `comm_sms` fewer SMs while all-reduces are in flight"""
+        if self.cuda and self.comm_sms > 0:
+            from . import _lib
+            _lib.set_option("reserved_sms", self.comm_sms if on else 0)
+
+    def on_group_done(self, g: int):
+        if not self.enabled or self.world == 1:
+            return
+        span = self._by_trigger.get(g)
+        if span is None:
+            return
+        self.reduce_span(*span)
+        self.reserve_sms(True)
 
     def finish(self):
         """Make the compute stream wait for every outstanding all-reduce."""
         if self.cuda and self.world > 1:
             torch.cuda.current_stream().wait_stream(self.stream)
+        self.reserve_sms(False)
 
     @property
     def grad_scale(self) -> float:
@@ -88,11 +121,17 @@ class DataParallel(torch.nn.Module):
     `finish_backward()` returns (the Trainer calls it before clipping / stepping)."""
 
     def __init__(self, module, device_ids=None, bucket_cap_mb: float = 25.0, process_group=None,
-                 broadcast_parameters: bool = True):
+                 broadcast_parameters: bool = True, grad_wire_dtype: Optional[torch.dtype] = None, comm_sms: int = 0):
         super().__init__()
         self.module = module
         self.process_group = process_group
         self.bucket_cap_mb = bucket_cap_mb
+        import os
+        if grad_wire_dtype is None and os.environ.get("MGB_GRAD_WIRE", "").lower() in ("bf16", "bfloat16"):
+            grad_wire_dtype = torch.bfloat16          # environment defaults, for launch scripts that cannot pass kwargs
+        if not comm_sms:
+            comm_sms = int(os.environ.get("MGB_COMM_SMS", "0"))
+        self.grad_wire_dtype, self.comm_sms = grad_wire_dtype, comm_sms
         self.buckets: Optional[GradBuckets] = None
         if broadcast_parameters and dist.is_initialized() and dist.get_world_size(process_group) > 1:
             dist.broadcast(module._flat, src=0, group=process_group)      # C2, one message
@@ -102,7 +141,8 @@ class DataParallel(torch.nn.Module):
         m = self.module
         m._ensure_device_state()
         if self.buckets is None or self.buckets.flat.data_ptr() != m._flat_grad.data_ptr():
-            self.buckets = GradBuckets(m._flat_grad, m._layer_spans, self.bucket_cap_mb, self.process_group)
+            self.buckets = GradBuckets(m._flat_grad, m._layer_spans, self.bucket_cap_mb, self.process_group,
+                                       wire_dtype=self.grad_wire_dtype, comm_sms=self.comm_sms)
             m._layer_done_hook = self.buckets.on_group_done
 
     def forward(self, *args, **kwargs):

@@ -184,6 +184,7 @@ class GraphedTrainStep:
                 return
             end()
             segs.append(("allreduce", span))
+            buckets.reserve_sms(True)      # the segments that run beside an all-reduce are captured with smaller grids
             begin()
 
         side = torch.cuda.Stream()
@@ -195,11 +196,13 @@ class GraphedTrainStep:
                 st["loss"] = self._micro_steps(st, last_hook=hook)
                 end()
                 segs.append(("drain", None))
+                buckets.reserve_sms(False)
                 begin()
                 self._optimizer_part(dp.grad_scale / self.accum, True)
                 end()
             finally:
                 model._layer_done_hook = saved
+                buckets.reserve_sms(False)
         torch.cuda.current_stream().wait_stream(side)
         return segs
 
@@ -210,13 +213,7 @@ class GraphedTrainStep:
             if kind == "graph":
                 obj.replay()
             elif kind == "allreduce":
-                s, e = obj
-                ev = torch.cuda.Event()
-                ev.record(cur)
-                buckets.stream.wait_event(ev)
-                with torch.cuda.stream(buckets.stream):
-                    dist.all_reduce(buckets.flat[s:e], op=dist.ReduceOp.SUM, group=buckets.group)
-                buckets.launched += 1
+                buckets.reduce_span(*obj)
             else:
                 cur.wait_stream(buckets.stream)
 

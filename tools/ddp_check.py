@@ -60,6 +60,36 @@ nseg = len([k for k, _ in stp._states[(4, 128)]["graph"] if k == "graph"])
 if rank == 0:
     print(json.dumps(dict(world=world, graph_segments=nseg, graph_vs_eager_param_rel=graph_rel, graph_vs_eager_loss_dev=loss_dev,
                           graph_params_identical_across_ranks=graph_same)))
+
+# (5) bf16 on the wire (grad_wire_dtype) and reserved SMs: gradient still the global-batch gradient to bf16 rounding,
+#     parameters still identical on every rank; (6) k = 2 accumulation micro-steps inside the segmented graph step
+for p_ in model.parameters(): p_.grad = None
+dpw = m.DataParallel(model, bucket_cap_mb=1.0, broadcast_parameters=False, grad_wire_dtype=torch.bfloat16, comm_sms=16)
+_, lw = dpw(xs[4 * rank:4 * rank + 4], ys[4 * rank:4 * rank + 4]); lw.backward()
+dpw.finish_backward(); torch.cuda.synchronize()
+wire_rel = ((model._flat_grad * dpw.grad_scale - want).norm() / want.norm()).item()
+model._layer_done_hook = None
+def run_accum(k, steps=5):
+    torch.manual_seed(0)
+    mdl = m.GPT(cfg, verbose=False).cuda()
+    op = m.create_optimizer(mdl, m.OptimizerConfig(learning_rate=1e-3))
+    d = m.DataParallel(mdl, bucket_cap_mb=1.0, grad_wire_dtype=torch.bfloat16 if k > 1 else None, comm_sms=16 if k > 1 else 0)
+    stepper = m.GraphedTrainStep(mdl, op, 1.0, d, use_graph=True, warmup=2, accum=k)
+    losses = []
+    for s_ in range(steps):
+        gg = torch.Generator().manual_seed(300 + s_)
+        tk = torch.randint(0, 1000, (8 * world, 129), generator=gg)[8 * rank:8 * rank + 8]
+        losses.append(float(stepper(tk[:, :-1].contiguous().pin_memory(), tk[:, 1:].contiguous().pin_memory())))
+    torch.cuda.synchronize()
+    return losses, mdl._flat.clone()
+l1, p1 = run_accum(1)
+l2, p2 = run_accum(2)
+acc_rel = ((p2 - p1).norm() / p1.norm()).item()
+acc_loss = max(abs(a - b) / abs(b) for a, b in zip(l2, l1))
+refa = p2.clone(); dist.broadcast(refa, src=0)
+if rank == 0:
+    print(json.dumps(dict(world=world, bf16_wire_grad_rel_err_vs_global_batch=wire_rel, accum2_bf16wire_vs_accum1_fp32_param_rel=acc_rel,
+                          accum2_vs_accum1_loss_dev=acc_loss, accum2_params_identical_across_ranks=bool(torch.equal(refa, p2)))))
 if rank == 0:
     print(json.dumps(dict(world=world, grad_rel_err_vs_global_batch=rel, params_identical_after_step=same,
                           buckets=len(dp.buckets.buckets), allreduces_launched=dp.buckets.launched)))
