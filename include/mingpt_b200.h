@@ -111,6 +111,13 @@ typedef struct mgb_gemm_args {
     float alpha;       /* 0 is read as 1 */
     float* colsum;     /* optional, bf16 D only: colsum[n] += sum_m D[m,n] (fp32, atomic) -- the bias gradient of the
                           layer below when D is an output gradient; taken from the accumulators before rounding */
+    /* optional "row dot" side output (CTA-pair engine, bf16 D, n a multiple of 64, no gate / residual / preact):
+     * rowdot_out[(b * (n/64) + h) * rowdot_t + t] = sum over the 64 columns of head h of D[m, .] * rowdot_x[m, .] for
+     * row m = b * rowdot_t + t, taken from the fp32 values before D is rounded. With D = dO (the gradient of the
+     * attention output, produced by the out-projection's dgrad) and rowdot_x = O this is flash attention's
+     * delta = rowsum(dO * O) [B, H, T], which the attention backward otherwise computes in a pass of its own. */
+    const void* rowdot_x; int64_t ld_rowdot;
+    float* rowdot_out; int64_t rowdot_t;
 } mgb_gemm_args;
 int mgb_gemm_bf16(const mgb_gemm_args* args, mgb_stream_t stream);
 
@@ -161,6 +168,9 @@ int mgb_embedding_bwd(const int64_t* idx, const void* dx, float* dwte, float* dw
  * ------------------------------------------------------------------------------------------------- */
 int mgb_attention_fwd(const void* qkv, void* out, float* lse, int32_t B, int32_t T, int32_t H, int32_t d,
                       int32_t mask_mode, float scale, mgb_stream_t stream);
+/* OR-ed into mask_mode of the backward entry points: `delta` already holds rowsum(dO * O) -- the out-projection's dgrad
+ * GEMM produced it in its epilogue (mgb_gemm_args.rowdot_*) -- so the backward skips its own pass over O and dO. */
+#define MGB_ATTN_DELTA_GIVEN 0x100
 /* Backward with recompute. delta fp32 [B,H,T] and dq_accum fp32 [B,T,H,d] are caller-provided scratch
  * (dq_accum is zeroed by the call); dqkv bf16 [B,T,3,H,d] is fully overwritten. */
 int mgb_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,

@@ -37,6 +37,8 @@ class GemmArgs(C.Structure):
         ("block_n", C.c_int32),
         ("alpha", C.c_float),
         ("colsum", C.c_void_p),
+        ("rowdot_x", C.c_void_p), ("ld_rowdot", C.c_int64),
+        ("rowdot_out", C.c_void_p), ("rowdot_t", C.c_int64),
     ]
 
 

@@ -541,11 +541,15 @@ static int launch_bwd(const void* qkv, const void* out, const void* dout, const 
                       float p_drop = 0.f, const uint64_t* seed_dev = nullptr, uint32_t site = 0, float* dqkv_colsum = nullptr) {
     const uint32_t thresh = p_drop > 0.f ? dropout_thresh16(p_drop) : 0u;
     const float inv_keep = thresh ? 65536.0f / (65536.0f - (float)thresh) : 1.0f;
-    const int64_t rows = (int64_t)B * T * H * (D / 8);
-    int g = (int)((rows + 255) / 256);
-    if (g > num_sms() * 16) g = num_sms() * 16;
-    launch_pdl(attn_bwd_delta_kernel<D>, dim3(g), dim3(256), 0, s, (const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta,
-               (int64_t)B, (int64_t)T, H);
+    const bool delta_given = (mask_mode & MGB_ATTN_DELTA_GIVEN) != 0;     // the caller's dgrad GEMM already produced it
+    mask_mode &= ~MGB_ATTN_DELTA_GIVEN;
+    if (!delta_given) {
+        const int64_t rows = (int64_t)B * T * H * (D / 8);
+        int g = (int)((rows + 255) / 256);
+        if (g > num_sms() * 16) g = num_sms() * 16;
+        launch_pdl(attn_bwd_delta_kernel<D>, dim3(g), dim3(256), 0, s, (const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta,
+                   (int64_t)B, (int64_t)T, H);
+    }
     constexpr int smem = 4 * 64 * (D + 8) * 2 + 64 * (64 + 8) * 2 + 2 * 64 * 4;
     if (smem > 48 * 1024) {
         static PerDeviceOnce once;
@@ -588,6 +592,7 @@ static int launch_bwd(const void* qkv, const void* out, const void* dout, const 
 using namespace mgb;
 
 static int check_attn_shape(const char* who, int B, int T, int H, int d, int mask_mode) {
+    mask_mode &= ~MGB_ATTN_DELTA_GIVEN;
     if (B <= 0 || T <= 0 || H <= 0) { set_last_error("attention: non-positive B/T/H"); return kErrBadShape; }
     if (d != 16 && d != 32 && d != 64) { set_last_error("attention: head dim must be 16, 32 or 64"); return kErrUnsupported; }
     if (mask_mode < 0 || mask_mode > 2) { set_last_error("attention: bad mask mode"); return kErrBadShape; }
@@ -701,6 +706,7 @@ extern "C" int mgb_attention_bwd_noalloc(const void* qkv, const void* out, const
     cudaStream_t s = (cudaStream_t)s_;
     int rc = check_attn_shape("bwd_noalloc", B, T, H, d, mask_mode);
     if (rc) return rc;
+    if (mask_mode & MGB_ATTN_DELTA_GIVEN) { set_last_error("attention_bwd_noalloc: delta lives in the built-in scratch, it cannot be given"); return kErrUnsupported; }
     if (((uintptr_t)qkv % 16) || ((uintptr_t)out % 16) || ((uintptr_t)dout % 16) || ((uintptr_t)dqkv % 16)) {
         set_last_error("attention: pointers must be 16-byte aligned"); return kErrBadAlign;
     }

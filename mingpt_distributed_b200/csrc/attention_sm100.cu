@@ -838,8 +838,14 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 const bool diag = causal && (i == kb);
                 const bool need_mask = diag || (k0 + BKV > T) || (i * BQ + BQ > T);
                 const bool bias_diag = tril && (i == kb);
-                float2* ld = sLD + warp * CPT;                       // this warp's slot; its last readers passed the __syncwarp below
-                if (lane < CPT) ld[lane] = make_float2(((tril && i > kb) ? LOG2E : 0.f) - nxt.x * LOG2E, nxt.y * scale);
+                // this warp's slot (its last readers passed the __syncwarp below): a[16] = bias - lse * log2e, then
+                // nb[16] = -delta * scale, so that a PAIR of queries is one 8-byte operand of the packed math below
+                float* lda = reinterpret_cast<float*>(sLD + warp * CPT);
+                float* ldb = lda + CPT;
+                if (lane < CPT) {
+                    lda[lane] = ((tril && i > kb) ? LOG2E : 0.f) - nxt.x * LOG2E;
+                    ldb[lane] = -nxt.y * scale;
+                }
                 nxt = fetch_ld(n + 1);
                 __syncwarp();
                 mbar_wait_relaxed(&s_full[half], jg & 1);
@@ -869,30 +875,39 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 }
                 uint32_t pk[CPT / 2], dk[CPT / 2];
                 if (!need_mask && !bias_diag) {
+                    // p = exp2(s * c + a), ds = p * (dp * scale + nb) on fp32 pairs: 3 packed instructions + 2 exponentials
+                    // + 2 packs per pair of queries (the scalar form took 10 issue slots)
+                    const float2 sc2 = splat2(scale_log2), scl2 = splat2(scale);
 #pragma unroll
-                    for (int e = 0; e < CPT / 2; ++e) {
-                        const float4 l4 = lds128f(ld + 2 * e);   // (a0, b0, a1, b1)
-                        const float p0 = exp2f(fmaf(__uint_as_float(sv[2 * e]), scale_log2, l4.x));
-                        const float p1 = exp2f(fmaf(__uint_as_float(sv[2 * e + 1]), scale_log2, l4.z));
-                        pk[e] = pack_bf16x2(p0, p1);
-                        dk[e] = pack_bf16x2(p0 * fmaf(__uint_as_float(dp[2 * e]), scale, -l4.y),
-                                            p1 * fmaf(__uint_as_float(dp[2 * e + 1]), scale, -l4.w));
+                    for (int q4 = 0; q4 < CPT / 4; ++q4) {
+                        const float4 a4 = lds128f(lda + 4 * q4), b4 = lds128f(ldb + 4 * q4);
+#pragma unroll
+                        for (int h2 = 0; h2 < 2; ++h2) {
+                            const int e = 2 * q4 + h2;
+                            const float2 av = h2 ? make_float2(a4.z, a4.w) : make_float2(a4.x, a4.y);
+                            const float2 bv = h2 ? make_float2(b4.z, b4.w) : make_float2(b4.x, b4.y);
+                            const float2 x = fma2(make_float2(__uint_as_float(sv[2 * e]), __uint_as_float(sv[2 * e + 1])), sc2, av);
+                            const float2 pp = make_float2(exp2f(x.x), exp2f(x.y));
+                            const float2 tt = fma2(make_float2(__uint_as_float(dp[2 * e]), __uint_as_float(dp[2 * e + 1])), scl2, bv);
+                            const float2 ds = mul2(pp, tt);
+                            pk[e] = pack_bf16x2(pp.x, pp.y);
+                            dk[e] = pack_bf16x2(ds.x, ds.y);
+                        }
                     }
                 } else {
 #pragma unroll
                     for (int e = 0; e < CPT / 2; ++e) {
                         float pv[2], dsv[2];
-                        const float4 l4 = lds128f(ld + 2 * e);
 #pragma unroll
                         for (int t2 = 0; t2 < 2; ++t2) {
                             const int col = qc0 + 2 * e + t2;          // query column inside the block
-                            const float2 ldv = t2 ? make_float2(l4.z, l4.w) : make_float2(l4.x, l4.y);
+                            const float2 ldv = make_float2(lda[2 * e + t2], ldb[2 * e + t2]);
                             float x = fmaf(__uint_as_float(sv[2 * e + t2]), scale_log2, ldv.x);
                             if (bias_diag && r <= col) x += LOG2E;
                             const bool dead = (key >= T) || (diag && r > col);   // queries >= T carry a = -inf
                             const float p = dead ? 0.f : exp2f(x);
                             pv[t2] = p;
-                            dsv[t2] = p * fmaf(__uint_as_float(dp[2 * e + t2]), scale, -ldv.y);
+                            dsv[t2] = p * fmaf(__uint_as_float(dp[2 * e + t2]), scale, ldv.y);
                         }
                         pk[e] = pack_bf16x2(pv[0], pv[1]);
                         dk[e] = pack_bf16x2(dsv[0], dsv[1]);

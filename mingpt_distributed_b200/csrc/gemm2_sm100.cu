@@ -337,6 +337,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     aux_ph ^= (1u << buf);
                 }
                 uint8_t* rowp = box + r_local * 128;
+                float rowdot_acc = 0.f;
                 for (int ch = 0; ch < chunks_per_slice; ++ch) {
                     const int ccol = sl * slice_cols + ch * 32;      // column inside the tile
                     uint32_t r[32];
@@ -388,6 +389,13 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                             xw[q * 4 + 0] = xi.x; xw[q * 4 + 1] = xi.y; xw[q * 4 + 2] = xi.z; xw[q * 4 + 3] = xi.w;
                         }
                         if (aux == 2) gate_inplace(v, xw, MODE == 1 ? (int)MGB_GATE_MUL : p.gate_kind);
+                        else if (aux == 3) {
+                            // rowdot: sum over this 64-column slice of D * X, from the fp32 values before D is rounded
+                            float2 dacc = make_float2(0.f, 0.f);
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) dacc = fma2(make_float2(v[2 * j], v[2 * j + 1]), unpack_bf16x2(xw[j]), dacc);
+                            rowdot_acc += dacc.x + dacc.y;
+                        }
                         else add_bf16_inplace(v, xw);
                     }
                     if (direct_gate && aux != 2 && row_ok) {
@@ -446,6 +454,12 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                                               pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7])));
                         }
                     }
+                }
+                if (aux == 3 && row_ok && n0 + sl * slice_cols < p.N) {
+                    // out[(b * H + h) * T + t] for row = b * T + t and head h = this 64-column slice
+                    const int64_t bb = row / p.rowdot_T, tt = row - bb * p.rowdot_T;
+                    const int64_t hh = (n0 + sl * slice_cols) >> 6;
+                    p.rowdot_out[(bb * (p.N >> 6) + hh) * p.rowdot_T + tt] = rowdot_acc;
                 }
                 if (tma_store) {
                     fence_proxy_async_smem();
@@ -570,8 +584,18 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
     if (p.tma_store && !a->d_f32 && !a->preact) {
         if (a->gate && tma_ok(a->gate, a->ldg, 2)) p.tma_aux = 2;
         else if (a->residual && tma_ok(a->residual, a->ldr, 2)) p.tma_aux = 1;
+        else if (a->rowdot_x && tma_ok(a->rowdot_x, a->ld_rowdot, 2)) p.tma_aux = 3;
     }
 
+    if (a->rowdot_x) {
+        if (p.tma_aux != 3 || (a->n & 63) || !a->rowdot_out || a->rowdot_t <= 0 || (a->m % a->rowdot_t)) {
+            set_last_error("gemm: rowdot needs a TMA-addressable bf16 D and X, no gate / residual / preact, n a multiple of 64, "
+                           "m a multiple of rowdot_t");
+            return kErrUnsupported;
+        }
+        p.rowdot_out = a->rowdot_out;
+        p.rowdot_T = a->rowdot_t;
+    }
     const int nb = bn / 2;
     const uint32_t stage_bytes = BLOCK_M * BLOCK_K * 2 + (uint32_t)nb * BLOCK_K * 2;
     // column sums ride along only on the staged bf16 path; otherwise mgb_gemm_bf16 adds them with a separate pass
@@ -600,7 +624,8 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
             if (rc) return rc;
         }
         if (p.tma_aux) {
-            rc = p.tma_aux == 2 ? make_map_2d(&tx, a->gate, a->n, a->m, a->ldg, 64, BLOCK_M)
+            rc = p.tma_aux == 3 ? make_map_2d(&tx, a->rowdot_x, a->n, a->m, a->ld_rowdot, 64, BLOCK_M)
+               : p.tma_aux == 2 ? make_map_2d(&tx, a->gate, a->n, a->m, a->ldg, 64, BLOCK_M)
                                 : make_map_2d(&tx, a->residual, a->n, a->m, a->ldr, 64, BLOCK_M);
             if (rc) return rc;
         }
@@ -610,7 +635,7 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
     // epilogue specialisation (see the kernel): pick the leanest instantiation that covers this call
     int mode = 0;
     if (p.tma_store && !g_opt_gemm_generic.load(std::memory_order_relaxed)) {
-        const bool side_ok = (!a->gate || (p.tma_aux == 2 && a->gate_kind == MGB_GATE_MUL && !a->residual)) &&
+        const bool side_ok = (!a->rowdot_x || p.tma_aux == 3) && (!a->gate || (p.tma_aux == 2 && a->gate_kind == MGB_GATE_MUL && !a->residual)) &&
                              (!a->residual || (p.tma_aux == 1 && !a->gate));
         if (a->d_f32 && !a->bias && !p.act && !a->gate && !a->residual && !a->preact && !fused_colsum) mode = 3;
         else if (!a->d_f32 && p.preact && p.act == MGB_ACT_GELU_TANH && p.act_grad && a->bias && !a->gate && !a->residual &&

@@ -51,6 +51,8 @@ struct Params {
     int32_t gate_kind;
     float alpha;
     float* colsum;           // CTA-pair kernel, COLSUM instantiation: column sums of D (fp32, atomic)
+    float* rowdot_out;       // CTA-pair kernel, tma_aux == 3: per (row, 64-column slice) sum of D * X
+    int64_t rowdot_T;
 };
 
 __device__ __forceinline__ float apply_act(float v, int act) {

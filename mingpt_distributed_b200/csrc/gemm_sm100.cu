@@ -356,7 +356,7 @@ extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
     // The epilogue (bias, activation, gate, residual, saved pre-activation, column sums) is applied ONCE per output
     // element. Split-K units each run the whole epilogue on their partial sum, so accumulate + an epilogue term
     // never splits: an automatic split is forced to 1, an explicit one is an error.
-    const bool has_epilogue = a->bias || a->residual || a->gate || a->preact || a->colsum ||
+    const bool has_epilogue = a->bias || a->residual || a->gate || a->preact || a->colsum || a->rowdot_x ||
                               (a->act & ~MGB_ACT_STORE_GRAD) != MGB_ACT_NONE;
     if (has_epilogue && a->split_k > 1) {
         set_last_error("gemm: split_k > 1 cannot be combined with bias / act / gate / residual / preact / colsum");
@@ -386,6 +386,7 @@ extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
     const bool want_pair = engine == MGB_GEMM_ENGINE_PAIR ||
                            (engine == 0 && a->m > BLOCK_M && !g_opt_gemm_single.load(std::memory_order_relaxed));
     if (a->colsum && a->d_f32) { set_last_error("gemm: colsum needs a bf16 D"); return kErrUnsupported; }
+    if (a->rowdot_x && !want_pair) { set_last_error("gemm: rowdot is a CTA-pair engine epilogue (m > 128)"); return kErrUnsupported; }
     if (want_pair) {
         const int rc = launch_gemm_pair(&a_local, p, num_sms, stream);
         if (rc == kFusedColsum) return kOk;

@@ -867,20 +867,24 @@ class GPT(nn.Module):
             if pr > 0:         # (else: fused into the ln_1 backward below, whose dres is this tensor)
                 ops.colsum(dproj, G(f"{l}.proj_b"))
             ops.linear_wgrad(dproj, a_in, G(f"{l}.proj_w"))
-            ops.linear_dgrad(dproj, W(f"{l}.proj_w"), ws.datt)
+            # flash attention's delta = rowsum(dO * O) comes out of the epilogue of the GEMM that produces dO (head size
+            # 64 = one 64-column output slice per head; M > 128 = the CTA-pair engine) instead of a pass over O and dO
+            fuse_delta = d == 64 and M > 128
+            rd = (ws.att[l], ws.delta, T) if fuse_delta else None
+            ops.linear_dgrad(dproj, W(f"{l}.proj_w"), ws.datt, rowdot=None if ref else rd)
             datt = ws.datt
             if ref:
                 ops.colsum(ws.datt, G(f"{l}.o_b"))
                 ops.linear_wgrad(ws.datt, ws.att[l], G(f"{l}.o_w"))
-                ops.linear_dgrad(ws.datt, W(f"{l}.o_w"), ws.datt2)
+                ops.linear_dgrad(ws.datt, W(f"{l}.o_w"), ws.datt2, rowdot=rd)
                 datt = ws.datt2
             if pa > 0:
                 ops.attention_bwd_dropout(ws.qkv[l], ws.att[l], datt, ws.lse[l], ws.delta, ws.dq_acc, ws.dqkv, B, T, H, d,
-                                          mask, pa, seed, 4 * l)
+                                          mask, pa, seed, 4 * l, delta_given=fuse_delta)
                 ops.colsum(ws.dqkv, G(f"{l}.qkv_b"))
             else:      # the qkv bias gradient (column sums of dqkv) comes out of the attention backward itself
                 ops.attention_bwd(ws.qkv[l], ws.att[l], datt, ws.lse[l], ws.delta, ws.dq_acc, ws.dqkv, B, T, H, d, mask,
-                                  dqkv_colsum=G(f"{l}.qkv_b"))
+                                  dqkv_colsum=G(f"{l}.qkv_b"), delta_given=fuse_delta)
             ops.linear_wgrad(ws.dqkv, ws.ln1[l], G(f"{l}.qkv_w"))
             ops.linear_dgrad(ws.dqkv, W(f"{l}.qkv_w"), ws.dln)
             ops.layernorm_bwd(ws.dln, ws.x[l], P(f"{l}.ln1_w"), s[0], s[1], ws.dx_a, G(f"{l}.ln1_w"), G(f"{l}.ln1_b"), dres=dxm,

@@ -53,7 +53,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = Fa
          bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None, act: int = 0,
          preact: Optional[torch.Tensor] = None, gate: Optional[torch.Tensor] = None, gate_kind: int = 0,
          accumulate: bool = False, split_k: int = 0, block_n: int = 0, alpha: float = 1.0,
-         colsum: Optional[torch.Tensor] = None) -> torch.Tensor:
+         colsum: Optional[torch.Tensor] = None, rowdot=None) -> torch.Tensor:
     """out[M,N] = epilogue(alpha * A B^T).  a is [M,K] (or [K,M] if a_mn), b is [N,K] (or [K,N] if b_mn)."""
     _chk_cuda(a, b, out, bias, residual, preact, gate, colsum)
     _chk2d(a, torch.bfloat16, "gemm a")
@@ -88,6 +88,13 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = Fa
         if colsum.dtype != torch.float32 or colsum.numel() != N or not colsum.is_contiguous():
             raise RuntimeError("gemm colsum: expected contiguous fp32 [N]")
         args.colsum = colsum.data_ptr()
+    if rowdot is not None:     # (x bf16 [M,N], out fp32 [B, N/64, T], T): out = per-head row sums of D * x (see mgb_gemm_args)
+        rx, rout, rt = rowdot
+        _chk_cuda(rx, rout)
+        _chk2d(rx, torch.bfloat16, "gemm rowdot x")
+        if tuple(rx.shape) != (M, N) or rout.dtype != torch.float32 or rout.numel() != M * (N // 64) or not rout.is_contiguous():
+            raise RuntimeError("gemm rowdot: x must be [M,N] bf16 and out contiguous fp32 with M * N/64 elements")
+        args.rowdot_x, args.ld_rowdot, args.rowdot_out, args.rowdot_t = rx.data_ptr(), rx.stride(0), rout.data_ptr(), int(rt)
     check(_lib.lib().mgb_gemm_bf16(C.byref(args), _stream()), "gemm")
     return out
 
@@ -164,10 +171,17 @@ def attention_fwd(qkv, out, lse, B, T, H, d, mask_mode, scale=None):
     return out
 
 
-def attention_bwd(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, d, mask_mode, scale=None, dqkv_colsum=None):
-    """dqkv_colsum (fp32 [3*H*d], accumulated): column sums of dqkv, i.e. the qkv projection's bias gradient."""
+ATTN_DELTA_GIVEN = 0x100
+
+
+def attention_bwd(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, d, mask_mode, scale=None, dqkv_colsum=None,
+                  delta_given=False):
+    """dqkv_colsum (fp32 [3*H*d], accumulated): column sums of dqkv, i.e. the qkv projection's bias gradient.
+    delta_given: `delta` already holds rowsum(dout * out) (the dgrad GEMM that produced dout wrote it: gemm rowdot)."""
     _chk_cuda(qkv, out, dout, lse, delta, dq_accum, dqkv, dqkv_colsum)
     scale = 1.0 / math.sqrt(d) if scale is None else scale
+    if delta_given:
+        mask_mode |= ATTN_DELTA_GIVEN
     if dqkv_colsum is not None:
         check(_lib.lib().mgb_attention_bwd_colsum(_p(qkv), _p(out), _p(dout), _p(lse), _p(delta), _p(dq_accum), _p(dqkv),
                                                   _p(dqkv_colsum), B, T, H, d, mask_mode, scale, _stream()), "attention_bwd_colsum")
@@ -207,8 +221,11 @@ def attention_fwd_dropout(qkv, out, lse, B, T, H, d, mask_mode, p, seed_dev, sit
     return out
 
 
-def attention_bwd_dropout(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, d, mask_mode, p, seed_dev, site, scale=None):
+def attention_bwd_dropout(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, d, mask_mode, p, seed_dev, site, scale=None,
+                          delta_given=False):
     scale = 1.0 / math.sqrt(d) if scale is None else scale
+    if delta_given:
+        mask_mode |= ATTN_DELTA_GIVEN
     check(_lib.lib().mgb_attention_bwd_dropout(_p(qkv), _p(out), _p(dout), _p(lse), _p(delta), _p(dq_accum), _p(dqkv), B, T, H, d, mask_mode, scale, float(p), _p(seed_dev), int(site), _stream()), "attention_bwd_dropout")
     return dqkv
 

@@ -196,6 +196,28 @@ def test_gemm_accumulate_with_epilogue_applies_it_once(engine):
         ops.gemm(a, b, out, bias=bias, accumulate=True, split_k=4, block_n=engine)
 
 
+@pytest.mark.parametrize("M,H,T", [(1024, 4, 256), (520, 2, 130), (4096, 12, 1024)])
+def test_gemm_rowdot_side_output_is_flash_attention_delta(M, H, T):
+    """dgrad of the attention out-projection with the rowdot epilogue: D = dY W (bf16) and, per row and head,
+    delta = sum_d D * O from the fp32 accumulators -- what attn_bwd_delta_kernel computes from the rounded D"""
+    from mingpt_distributed_b200 import ops
+    C = H * 64
+    g = torch.Generator(device="cuda").manual_seed(6)
+    dy = torch.randn(M, C, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(C, C, device="cuda", generator=g) * 0.05).bfloat16()
+    o = torch.randn(M, C, device="cuda", generator=g).bfloat16()
+    d = torch.empty(M, C, dtype=torch.bfloat16, device="cuda")
+    delta = torch.full((M // T, H, T), float("nan"), device="cuda")
+    ops.linear_dgrad(dy, w, d, rowdot=(o, delta, T))
+    torch.cuda.synchronize()
+    want_d = dy.float() @ w.float()
+    _check(f"gemm_rowdot_D_{M}x{C}", d, want_d, 2e-2)
+    want = (want_d * o.float()).view(M // T, T, H, 64).sum(-1).transpose(1, 2)
+    _check(f"gemm_rowdot_delta_{M}x{C}", delta, want, 2e-3)
+    with pytest.raises(RuntimeError, match="rowdot"):
+        ops.linear_dgrad(dy, w, d, rowdot=(o, delta, T), residual=o)
+
+
 def test_gemm_strided_views_and_padded_vocab():
     """the head: logits chunk written into a wider (padded) buffer, then used as a K-major A operand whose
     reduction length (the vocabulary) is not a multiple of anything"""

@@ -154,6 +154,13 @@ def test_attention_fwd_bwd(d, mode, B, T, H):
     assert torch.allclose(dqkv2.float(), dqkv.float(), rtol=1.6e-2, atol=1e-3 * dqkv.float().abs().max().item())
     want_cs = qf.grad.reshape(B * T, 3 * C).sum(0)
     assert (cs - 1 - want_cs).abs().max().item() <= 2e-2 * want_cs.abs().max().item() + 2e-2, tag
+    # delta handed in by the caller (the out-projection's dgrad GEMM computes it in its epilogue): same result
+    want_delta = (out.float() * dout.float()).view(B, T, H, d).sum(-1).transpose(1, 2).contiguous()
+    _close("attn_delta_" + tag, delta, want_delta, 1e-3)
+    dqkv3 = torch.full_like(qkv, float("nan"))
+    ops.attention_bwd(qkv, out, dout, lse, want_delta, dq_acc, dqkv3, B, T, H, d, mode, delta_given=True)
+    torch.cuda.synchronize()
+    assert torch.allclose(dqkv3.float(), dqkv.float(), rtol=1.6e-2, atol=1e-3 * dqkv.float().abs().max().item())
 
 
 def test_attention_gpt2_shape_property():
