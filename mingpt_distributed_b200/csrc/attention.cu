@@ -509,13 +509,29 @@ attn_dq_convert_colsum_kernel(const float* __restrict__ dq_accum, __nv_bfloat16*
     grid_dep_wait();                                 // dq_accum is complete once the main backward kernel has finished
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (r < rpb) {
-        for (int64_t row = (int64_t)blockIdx.x * rpb + r; row < BT; row += (int64_t)gridDim.x * rpb) {
-            const float4 a = *reinterpret_cast<const float4*>(dq_accum + row * HD + ch * 8);
-            const float4 c = *reinterpret_cast<const float4*>(dq_accum + row * HD + ch * 8 + 4);
-            acc[0] += a.x; acc[1] += a.y; acc[2] += a.z; acc[3] += a.w;
-            acc[4] += c.x; acc[5] += c.y; acc[6] += c.z; acc[7] += c.w;
-            stg128(dqkv + row * 3 * HD + ch * 8,
-                   make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(c.x, c.y), pack_bf16x2(c.z, c.w)));
+        // four rows per iteration: eight 16-byte loads in flight per thread (the kernel is pure HBM streaming)
+        const int64_t step = (int64_t)gridDim.x * rpb;
+        for (int64_t row0 = (int64_t)blockIdx.x * rpb + r; row0 < BT; row0 += 4 * step) {
+            float4 a[4], c[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int64_t row = row0 + u * step;
+                if (row < BT) {
+                    a[u] = __ldcs(reinterpret_cast<const float4*>(dq_accum + row * HD + ch * 8));
+                    c[u] = __ldcs(reinterpret_cast<const float4*>(dq_accum + row * HD + ch * 8 + 4));
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int64_t row = row0 + u * step;
+                if (row < BT) {
+                    acc[0] += a[u].x; acc[1] += a[u].y; acc[2] += a[u].z; acc[3] += a[u].w;
+                    acc[4] += c[u].x; acc[5] += c[u].y; acc[6] += c[u].z; acc[7] += c[u].w;
+                    stg128(dqkv + row * 3 * HD + ch * 8,
+                           make_uint4(pack_bf16x2(a[u].x, a[u].y), pack_bf16x2(a[u].z, a[u].w), pack_bf16x2(c[u].x, c[u].y),
+                                      pack_bf16x2(c[u].z, c[u].w)));
+                }
+            }
         }
 #pragma unroll
         for (int e = 0; e < 8; ++e) atomicAdd(&cvt_smem[ch * 8 + e], acc[e]);

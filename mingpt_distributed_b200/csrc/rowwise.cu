@@ -234,7 +234,7 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
 // the next rows in flight while the warp works on the current one, so the loads no longer occupy registers and
 // the number of bytes in flight per SM is set by shared memory (2 CTAs x 8 warps x 2 rows x 4.5 KiB at C = 768),
 // not by occupancy. The row is read back from shared memory in both passes (conflict-free 16-byte accesses).
-constexpr int LNB_STAGES = 2;
+constexpr int LNB_STAGES = 4;      // x and dy rows (the two that are read twice) per slot; dres comes through registers
 // COLSUM: additionally dres_colsum[c] += sum over rows of dres[row, c] -- the bias gradient of the linear layer whose
 // output gradient `dres` is (it is being read anyway).
 template <int MAXCH, bool COLSUM>
@@ -248,12 +248,14 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     const int nch = cols >> 3;
     const uint32_t rowbytes = (uint32_t)cols * 2;
     const float inv_cols = 1.0f / (float)cols;
-    constexpr int NACC = COLSUM ? 3 : 2;
-    float* acc = reinterpret_cast<float*>(lnb_smem);                        // [NACC][cols] CTA-level dgamma / dbeta (/ colsum)
-    uint8_t* ring = lnb_smem + (size_t)NACC * cols * sizeof(float) + (size_t)warp * LNB_STAGES * 3 * rowbytes;
+    constexpr int NACC = COLSUM ? 4 : 3;
+    float* acc = reinterpret_cast<float*>(lnb_smem);                        // [NACC - 1][cols] CTA-level dgamma / dbeta (/ colsum)
+    float* gam_s = acc + (size_t)(NACC - 1) * cols;                         // [cols] gamma (read from here: registers are short)
+    uint8_t* ring = lnb_smem + (size_t)NACC * cols * sizeof(float) + (size_t)warp * LNB_STAGES * 2 * rowbytes;
     uint64_t* bars = reinterpret_cast<uint64_t*>(lnb_smem + (size_t)NACC * cols * sizeof(float) +
-                                                 (size_t)LN_WARPS * LNB_STAGES * 3 * rowbytes) + warp * LNB_STAGES;
-    for (int c = threadIdx.x; c < NACC * cols; c += blockDim.x) acc[c] = 0.f;
+                                                 (size_t)LN_WARPS * LNB_STAGES * 2 * rowbytes) + warp * LNB_STAGES;
+    for (int c = threadIdx.x; c < (NACC - 1) * cols; c += blockDim.x) acc[c] = 0.f;
+    for (int c = threadIdx.x; c < cols; c += blockDim.x) gam_s[c] = gamma[c];
     if (lane == 0) {
         for (int s = 0; s < LNB_STAGES; ++s) mbar_init(&bars[s], 1);
         fence_mbar_init();
@@ -265,13 +267,19 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     const int64_t gw = (int64_t)blockIdx.x * LN_WARPS + warp;
     const int64_t row0 = gw * rows_per_warp;
     const int64_t row1 = row0 + rows_per_warp < rows ? row0 + rows_per_warp : rows;
-    const uint32_t tx = (dres ? 3u : 2u) * rowbytes;
+    const uint32_t tx = 2u * rowbytes;
     auto issue = [&](int64_t row, int s) {       // lane 0 only
-        uint8_t* slot = ring + (size_t)s * 3 * rowbytes;
+        uint8_t* slot = ring + (size_t)s * 2 * rowbytes;
         mbar_arrive_expect_tx(&bars[s], tx);
         bulk_load_1d(slot, x + row * cols, rowbytes, &bars[s]);
         bulk_load_1d(slot + rowbytes, dy + row * cols, rowbytes, &bars[s]);
-        if (dres) bulk_load_1d(slot + 2 * rowbytes, dres + row * cols, rowbytes, &bars[s]);
+    };
+    // dres is read once per row: it travels through registers, fetched one row ahead (the ring then holds twice as
+    // many rows in flight for the same shared memory)
+    auto fetch_dres = [&](int64_t row, uint4 (&dst)[MAXCH]) {
+#pragma unroll
+        for (int i = 0; i < MAXCH; ++i)
+            if (lane + 32 * i < nch) dst[i] = __ldcs(reinterpret_cast<const uint4*>(dres + row * cols + (lane + 32 * i) * 8));
     };
     if (lane == 0)
         for (int s = 0; s < LNB_STAGES; ++s)
@@ -279,29 +287,31 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
 
     // All elementwise math on fp32 PAIRS (FFMA2 / FADD2 / FMUL2): the kernel was bound by instruction issue (~21
     // instructions per element), not by the fp32 pipes or by HBM; packed it needs ~11.
-    float2 gam[MAXCH][4], dg[MAXCH][4], db[MAXCH][4], dr[COLSUM ? MAXCH : 1][4];
+    float2 dg[MAXCH][4], db[MAXCH][4], dr[COLSUM ? MAXCH : 1][4];
 #pragma unroll
     for (int i = 0; i < MAXCH; ++i) {
         const int ch = lane + 32 * i;
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-            gam[i][e] = (ch < nch) ? make_float2(gamma[ch * 8 + 2 * e], gamma[ch * 8 + 2 * e + 1]) : make_float2(0.f, 0.f);
             dg[i][e] = make_float2(0.f, 0.f);
             db[i][e] = make_float2(0.f, 0.f);
             if (COLSUM) dr[i][e] = make_float2(0.f, 0.f);
         }
     }
     float mu_n = 0.f, rs_n = 0.f;
-    if (row0 < row1) { mu_n = mean[row0]; rs_n = rstd[row0]; }
+    uint4 dr_n[MAXCH];
+    if (row0 < row1) {
+        mu_n = mean[row0]; rs_n = rstd[row0];
+        if (dres) fetch_dres(row0, dr_n);
+    }
     int s = 0;
     uint32_t ph = 0;
     for (int64_t row = row0; row < row1; ++row) {
         const float mu = mu_n, rs = rs_n;
         if (row + 1 < row1) { mu_n = mean[row + 1]; rs_n = rstd[row + 1]; }
         const float2 rs2 = splat2(rs), nmr2 = splat2(-mu * rs);      // xhat = x * rs - mu * rs
-        const uint8_t* xs = ring + (size_t)s * 3 * rowbytes;
+        const uint8_t* xs = ring + (size_t)s * 2 * rowbytes;
         const uint8_t* ds = xs + rowbytes;
-        const uint8_t* rsd = xs + 2 * rowbytes;
         mbar_wait_relaxed(&bars[s], ph);
         float2 s1 = make_float2(0.f, 0.f), s2 = make_float2(0.f, 0.f);
 #pragma unroll
@@ -311,13 +321,15 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                 const uint4 px = lds128(xs + ch * 16), pd = lds128(ds + ch * 16);
                 const uint32_t wx[4] = {px.x, px.y, px.z, px.w};
                 const uint32_t wd[4] = {pd.x, pd.y, pd.z, pd.w};
+                const float4 ga = lds128f(gam_s + ch * 8), gb = lds128f(gam_s + ch * 8 + 4);
+                const float2 gam[4] = {make_float2(ga.x, ga.y), make_float2(ga.z, ga.w), make_float2(gb.x, gb.y), make_float2(gb.z, gb.w)};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     const float2 h = fma2(unpack_bf16x2(wx[e]), rs2, nmr2);
                     const float2 fd = unpack_bf16x2(wd[e]);
                     dg[i][e] = fma2(fd, h, dg[i][e]);
                     db[i][e] = add2(db[i][e], fd);
-                    const float2 g = mul2(fd, gam[i][e]);
+                    const float2 g = mul2(fd, gam[e]);
                     s1 = add2(s1, g);
                     s2 = fma2(g, h, s2);
                 }
@@ -333,15 +345,17 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                 const uint4 px = lds128(xs + ch * 16), pd = lds128(ds + ch * 16);
                 const uint32_t wx[4] = {px.x, px.y, px.z, px.w};
                 const uint32_t wd[4] = {pd.x, pd.y, pd.z, pd.w};
+                const float4 ga = lds128f(gam_s + ch * 8), gb = lds128f(gam_s + ch * 8 + 4);
+                const float2 gam[4] = {make_float2(ga.x, ga.y), make_float2(ga.z, ga.w), make_float2(gb.x, gb.y), make_float2(gb.z, gb.w)};
                 float2 r[4];
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     const float2 h = fma2(unpack_bf16x2(wx[e]), rs2, nmr2);
-                    const float2 g = mul2(unpack_bf16x2(wd[e]), gam[i][e]);
+                    const float2 g = mul2(unpack_bf16x2(wd[e]), gam[e]);
                     r[e] = fma2(h, nm2rs, fma2(g, rs2, nm1rs));
                 }
                 if (dres) {
-                    const uint4 pr = lds128(rsd + ch * 16);
+                    const uint4 pr = dr_n[i];
                     const uint32_t wr[4] = {pr.x, pr.y, pr.z, pr.w};
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
@@ -355,6 +369,8 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                                   pack_bf16x2(r[3].x, r[3].y)));
             }
         }
+        // next row's dres into the same registers: a whole row's wait + first pass ahead of its use
+        if (dres && row + 1 < row1) fetch_dres(row + 1, dr_n);
         __syncwarp();                                            // every lane is done with this slot
         if (lane == 0 && row + LNB_STAGES < row1) issue(row + LNB_STAGES, s);
         if (++s == LNB_STAGES) { s = 0; ph ^= 1; }
@@ -796,7 +812,7 @@ static int layernorm_bwd_impl(const void* dy, const void* x, const float* gamma,
     const bool vec = (cols % 8 == 0) && cols <= 2048 && ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0) &&
                      ((uintptr_t)dx % 16 == 0) && (!dres || (uintptr_t)dres % 16 == 0);
     // persistent: each CTA owns register accumulators for dgamma/dbeta, flushed once
-    const size_t stage_smem = (size_t)2 * cols * sizeof(float) + (size_t)LN_WARPS * LNB_STAGES * 3 * cols * 2 +
+    const size_t stage_smem = (size_t)3 * cols * sizeof(float) + (size_t)LN_WARPS * LNB_STAGES * 2 * cols * 2 +
                               LN_WARPS * LNB_STAGES * sizeof(uint64_t);
     if (dres_colsum && !dres) { set_last_error("layernorm_bwd: dres_colsum needs dres"); return kErrBadShape; }
     if (vec && stage_smem + (size_t)cols * sizeof(float) <= 227 * 1024 && !g_opt_ln_unstaged.load(std::memory_order_relaxed)) {
