@@ -874,7 +874,17 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                         dp[e] = (keepbits >> e) & 1u ? __float_as_uint(__uint_as_float(dp[e]) * inv_keep) : 0u;
                 }
                 uint32_t pk[CPT / 2], dk[CPT / 2];
-                if (!need_mask && !bias_diag) {
+                // causal diagonal block with every key / query present: key row r sees query column c iff r <= c. This
+                // warp's 32 rows against this thread group's 16 columns [qc0, qc0 + 16) are, warp-uniformly, either all
+                // visible (rows end before qc0: the unmasked path), all hidden (rows start at or after qc0 + 16: zeros, no
+                // exponentials) or -- one warp in four -- mixed (the per-element path below).
+                const bool diag_only = diag && !bias_diag && (k0 + BKV <= T) && (i * BQ + BQ <= T);
+                const bool all_dead = diag_only && (quarter * 32 >= qc0 + CPT);
+                const bool all_live = diag_only && (quarter * 32 + 31 <= qc0);
+                if (all_dead) {
+#pragma unroll
+                    for (int e = 0; e < CPT / 2; ++e) { pk[e] = 0u; dk[e] = 0u; }
+                } else if ((!need_mask && !bias_diag) || all_live) {
                     // p = exp2(s * c + a), ds = p * (dp * scale + nb) on fp32 pairs: 3 packed instructions + 2 exponentials
                     // + 2 packs per pair of queries (the scalar form took 10 issue slots)
                     const float2 sc2 = splat2(scale_log2), scl2 = splat2(scale);

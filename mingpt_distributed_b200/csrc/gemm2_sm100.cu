@@ -125,16 +125,15 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const int block_n = p.block_n;
     const int nb = block_n >> 1;                               // B columns staged by this CTA
     const uint32_t stage_bytes = BLOCK_M * BLOCK_K * 2 + (uint32_t)nb * BLOCK_K * 2;
-    uint8_t* boxes = smem + p.num_stages * stage_bytes;        // num_boxes x 16 KiB, 1024-aligned
-    const int num_boxes = (MODE == 2) ? 6 : kNumBoxes;         // three per half for the two-output epilogue (see there)
-    uint64_t* bars = reinterpret_cast<uint64_t*>(boxes + num_boxes * kBoxBytes);
+    uint8_t* boxes = smem + p.num_stages * stage_bytes;        // kNumBoxes x 16 KiB, 1024-aligned
+    uint64_t* bars = reinterpret_cast<uint64_t*>(boxes + kNumBoxes * kBoxBytes);
     uint64_t* full_bar = bars;                       // [kMaxStages]  (leader's copy is the live one)
     uint64_t* empty_bar = bars + kMaxStages;         // [kMaxStages]
     uint64_t* tmem_full = bars + 2 * kMaxStages;     // [2]
     uint64_t* tmem_empty = tmem_full + 2;            // [2]           (leader's copy is the live one)
     uint64_t* aux_bar = tmem_empty + 2;              // [kNumBoxes]   residual / gate tile landed in box i
     uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(aux_bar + kNumBoxes);
-    float* bias_s = reinterpret_cast<float*>(boxes + num_boxes * kBoxBytes + 256);    // [2][256] bias of the current / next tile
+    float* bias_s = reinterpret_cast<float*>(boxes + kNumBoxes * kBoxBytes + 256);    // [2][256] bias of the current / next tile
     float* cs_smem = bias_s + (p.bias ? 512 : 0);                                      // [256] (COLSUM only; behind the bias if both)
     if (COLSUM) {
         for (int c = threadIdx.x; c < 256; c += blockDim.x) cs_smem[c] = 0.f;
@@ -287,8 +286,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int slice_cols = d_f32 ? 32 : 64;                   // columns per 128-byte output slice
         const int nslices = block_n / slice_cols;
         const int chunks_per_slice = slice_cols >> 5;
-        uint8_t* box_base = boxes + half * (MODE == 2 ? 3 : 2) * kBoxBytes;
-        uint32_t ring3 = 0;                                       // MODE 2: D box of the current slice in the 3-box ring
+        uint8_t* box_base = boxes + half * 2 * kBoxBytes;
         uint64_t* aux_b = aux_bar + half * 2;
         uint32_t buf = 0;
         uint32_t aux_ph = 0;                                      // bit b: parity the next load into box b completes
@@ -327,16 +325,11 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const uint32_t taddr_row = tmem_base + acc * kAccStride + ((uint32_t)(quarter * 32) << 16);
             bool released = false;
             for (int sl = half; sl < nslices; sl += 2) {
-                // MODE 2 (two outputs per slice) rotates through THREE boxes per half: slice s puts D into box 2s mod 3
-                // and the second output into box (2s + 1) mod 3, and commits the two stores as separate bulk groups, D
-                // first. The D box was last used by the second output of slice s - 2, the other one by D of slice
-                // s - 1: waiting until at most ONE group is unread (the second output of s - 1) frees both, so that
-                // store keeps draining under this slice's math instead of being waited for.
-                uint8_t* box = box_base + (MODE == 2 ? ring3 : buf) * kBoxBytes;
-                uint8_t* box2 = box_base + (MODE == 2 ? (ring3 == 2 ? 0u : ring3 + 1) : (buf ^ 1)) * kBoxBytes;
+                uint8_t* box = box_base + buf * kBoxBytes;
+                uint8_t* box2 = box_base + (buf ^ 1) * kBoxBytes;
                 if (tma_store && !aux) {
-                    // the box written two slices ago (or both, when two outputs share a two-box ring) must have been read
-                    if (elected) { if (two_out && MODE != 2) bulk_wait_read<0>(); else bulk_wait_read<1>(); }
+                    // the box written two slices ago (or both, when two outputs share the ring) must have been read
+                    if (elected) { if (two_out) bulk_wait_read<0>(); else bulk_wait_read<1>(); }
                     named_bar_sync(1 + half, 128);
                 }
                 if (aux) {
@@ -476,13 +469,11 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         if (c0 < p.N && m0 < p.M) {
                             if (p.accumulate) tma_reduce_add_2d(&tmap_d, box, c0, m0);
                             else tma_store_2d(&tmap_d, box, c0, m0);
-                            if (MODE == 2) bulk_commit();
                             if (two_out) tma_store_2d(&tmap_p, box2, c0, m0);
-                        } else if (MODE == 2) bulk_commit();     // keep the two-groups-per-slice count
+                        }
                         bulk_commit();
                     }
                     if (!two_out) buf ^= 1;
-                    if (MODE == 2) ring3 = (ring3 + 2) % 3;
                 }
             }
             if (!released) {   // this half had no slice in the tile (narrow tiles): still hand TMEM back
@@ -610,17 +601,7 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
     // column sums ride along only on the staged bf16 path; otherwise mgb_gemm_bf16 adds them with a separate pass
     const bool fused_colsum = a->colsum && p.tma_store && !a->d_f32;
     p.colsum = fused_colsum ? a->colsum : nullptr;
-    // epilogue specialisation (see the kernel): pick the leanest instantiation that covers this call
-    int mode = 0;
-    if (p.tma_store && !g_opt_gemm_generic.load(std::memory_order_relaxed)) {
-        const bool side_ok = (!a->rowdot_x || p.tma_aux == 3) && (!a->gate || (p.tma_aux == 2 && a->gate_kind == MGB_GATE_MUL && !a->residual)) &&
-                             (!a->residual || (p.tma_aux == 1 && !a->gate));
-        if (a->d_f32 && !a->bias && !p.act && !a->gate && !a->residual && !a->preact && !fused_colsum) mode = 3;
-        else if (!a->d_f32 && p.preact && p.act == MGB_ACT_GELU_TANH && p.act_grad && a->bias && !a->gate && !a->residual &&
-                 !fused_colsum) mode = 2;
-        else if (!a->d_f32 && !p.preact && !p.act && side_ok) mode = 1;
-    }
-    const int fixed = (mode == 2 ? 6 : kNumBoxes) * kBoxBytes + 256 + ((a->bias && fused_colsum) ? 3072 : 2048);   // barriers | bias x 2 / colsum
+    const int fixed = kNumBoxes * kBoxBytes + 256 + ((a->bias && fused_colsum) ? 3072 : 2048);   // barriers | bias x 2 / colsum
     int stages = (kSmemLimit - fixed) / (int)stage_bytes;
     if (stages > kMaxStages) stages = kMaxStages;
     p.num_stages = stages;
@@ -651,6 +632,16 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
     }
     const int64_t units = (int64_t)tiles * p.split_k;
     const int clusters = (int)(units < num_clusters ? units : num_clusters);
+    // epilogue specialisation (see the kernel): pick the leanest instantiation that covers this call
+    int mode = 0;
+    if (p.tma_store && !g_opt_gemm_generic.load(std::memory_order_relaxed)) {
+        const bool side_ok = (!a->rowdot_x || p.tma_aux == 3) && (!a->gate || (p.tma_aux == 2 && a->gate_kind == MGB_GATE_MUL && !a->residual)) &&
+                             (!a->residual || (p.tma_aux == 1 && !a->gate));
+        if (a->d_f32 && !a->bias && !p.act && !a->gate && !a->residual && !a->preact && !fused_colsum) mode = 3;
+        else if (!a->d_f32 && p.preact && p.act == MGB_ACT_GELU_TANH && p.act_grad && a->bias && !a->gate && !a->residual &&
+                 !fused_colsum) mode = 2;
+        else if (!a->d_f32 && !p.preact && !p.act && side_ok) mode = 1;
+    }
     {
         cudaError_t e;
 #define MGB_PAIR(CS, MD) launch_pdl(gemm_pair_kernel<CS, MD>, dim3(2 * clusters), dim3(kThreads), (size_t)smem_bytes, stream, ta, tb, td, tp, tx, p)

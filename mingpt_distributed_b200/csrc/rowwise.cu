@@ -264,9 +264,14 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     grid_dep_launch();
     grid_dep_wait();                                 // inputs come from the previous kernels (programmatic dependent launch)
 
+    // Rows are dealt to the warps INTERLEAVED (warp w of the grid takes rows w, w + W, w + 2W, ...): the rows in flight
+    // across the chip at any moment are then neighbours in memory, which keeps the HBM pages open; contiguous per-warp
+    // ranges put 2368 streams 21 KB apart.
     const int64_t gw = (int64_t)blockIdx.x * LN_WARPS + warp;
-    const int64_t row0 = gw * rows_per_warp;
-    const int64_t row1 = row0 + rows_per_warp < rows ? row0 + rows_per_warp : rows;
+    const int64_t stride = (int64_t)gridDim.x * LN_WARPS;
+    const int64_t row0 = gw;
+    const int64_t row1 = rows;
+    (void)rows_per_warp;
     const uint32_t tx = 2u * rowbytes;
     auto issue = [&](int64_t row, int s) {       // lane 0 only
         uint8_t* slot = ring + (size_t)s * 2 * rowbytes;
@@ -283,7 +288,7 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     };
     if (lane == 0)
         for (int s = 0; s < LNB_STAGES; ++s)
-            if (row0 + s < row1) issue(row0 + s, s);
+            if (row0 + s * stride < row1) issue(row0 + s * stride, s);
 
     // All elementwise math on fp32 PAIRS (FFMA2 / FADD2 / FMUL2): the kernel was bound by instruction issue (~21
     // instructions per element), not by the fp32 pipes or by HBM; packed it needs ~11.
@@ -306,9 +311,9 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     }
     int s = 0;
     uint32_t ph = 0;
-    for (int64_t row = row0; row < row1; ++row) {
+    for (int64_t row = row0; row < row1; row += stride) {
         const float mu = mu_n, rs = rs_n;
-        if (row + 1 < row1) { mu_n = mean[row + 1]; rs_n = rstd[row + 1]; }
+        if (row + stride < row1) { mu_n = mean[row + stride]; rs_n = rstd[row + stride]; }
         const float2 rs2 = splat2(rs), nmr2 = splat2(-mu * rs);      // xhat = x * rs - mu * rs
         const uint8_t* xs = ring + (size_t)s * 2 * rowbytes;
         const uint8_t* ds = xs + rowbytes;
@@ -370,9 +375,9 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
             }
         }
         // next row's dres into the same registers: a whole row's wait + first pass ahead of its use
-        if (dres && row + 1 < row1) fetch_dres(row + 1, dr_n);
+        if (dres && row + stride < row1) fetch_dres(row + stride, dr_n);
         __syncwarp();                                            // every lane is done with this slot
-        if (lane == 0 && row + LNB_STAGES < row1) issue(row + LNB_STAGES, s);
+        if (lane == 0 && row + LNB_STAGES * stride < row1) issue(row + LNB_STAGES * stride, s);
         if (++s == LNB_STAGES) { s = 0; ph ^= 1; }
     }
 #pragma unroll
