@@ -63,6 +63,10 @@ if rank == 0:
 
 # (5) bf16 on the wire (grad_wire_dtype) and reserved SMs: gradient still the global-batch gradient to bf16 rounding,
 #     parameters still identical on every rank; (6) k = 2 accumulation micro-steps inside the segmented graph step
+model._layer_done_hook = None
+for p_ in model.parameters(): p_.grad = None
+_, loss_all2 = model(xs, ys); loss_all2.backward()          # the parameters have moved since `want`: a fresh reference
+want = model._flat_grad.clone()
 for p_ in model.parameters(): p_.grad = None
 dpw = m.DataParallel(model, bucket_cap_mb=1.0, broadcast_parameters=False, grad_wire_dtype=torch.bfloat16, comm_sms=16)
 _, lw = dpw(xs[4 * rank:4 * rank + 4], ys[4 * rank:4 * rank + 4]); lw.backward()
