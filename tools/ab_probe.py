@@ -61,6 +61,14 @@ hdw = torch.zeros(V, C, device=dev)
 cases += [("gemm head fwd", lambda: ops.linear_fwd(x[:Mc], hw, lg[:, :V]), 2 * Mc * V * C),
           ("gemm head dgrad", lambda: ops.linear_dgrad(lg[:, :V], hw, o1[:Mc]), 2 * Mc * V * C),
           ("gemm head wgrad", lambda: ops.linear_wgrad(lg[:, :V], x[:Mc], hdw), 2 * Mc * V * C)]
+# cuBLAS (torch.matmul) on the same shapes, plain epilogue: the reference point for the tcgen05 mainloop, not a code path
+of = torch.empty(4 * C, C, device=dev, dtype=torch.bfloat16)
+cases += [("cublas fwd qkv", lambda: torch.matmul(x, w_qkv.t(), out=o3), 2 * M * 3 * C * C),
+          ("cublas fwd fc", lambda: torch.matmul(x, w_fc.t(), out=o4), 2 * M * 4 * C * C),
+          ("cublas fwd fc2", lambda: torch.matmul(x4, w_fc2.t(), out=o1), 2 * M * 4 * C * C),
+          ("cublas dgrad fc2", lambda: torch.matmul(x, w_fc2, out=o4), 2 * M * 4 * C * C),
+          ("cublas wgrad fc (bf16 out)", lambda: torch.matmul(x4.t(), x, out=of), 2 * M * 4 * C * C),
+          ("cublas head fwd", lambda: torch.matmul(x[:Mc], hw.t(), out=lg[:, :V]) if False else torch.matmul(x[:Mc], hw.t()), 2 * Mc * V * C)]
 # attention
 qkv = rn(B, T, 3 * C).bfloat16(); dout = rn(B, T, C).bfloat16()
 out = torch.empty(B, T, C, dtype=torch.bfloat16, device=dev); lse = torch.empty(B, H, T, device=dev)
