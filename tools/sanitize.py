@@ -1,5 +1,7 @@
 #!/usr/bin/env python
-"""Tiny-shape driver for `compute-sanitizer --tool memcheck|racecheck|synccheck python tools/sanitize.py`: one call of
+"""(compute-sanitizer is closed on this GPU pool -- gpurun refuses it -- so this runs as a plain tiny-shape smoke of every
+kernel family; it is kept in the form the sanitizer would take.)
+Tiny-shape driver for `compute-sanitizer --tool memcheck|racecheck|synccheck python tools/sanitize.py`: one call of
 every kernel family through the C ABI (tcgen05 GEMM both engines and every epilogue specialisation, tcgen05 attention
 forward / backward, mma.sync attention, LayerNorm, cross-entropy both kernels, embedding, AdamW, decode, token windows)."""
 import os, sys
@@ -20,7 +22,7 @@ ops.linear_fwd(a, b, o, bias=bias, residual=res)                                
 ops.linear_fwd(a, b, o, bias=bias, act=1 | ops.ACT_STORE_GRAD, preact=p)        # mode 2
 ops.linear_fwd(a, b, o, bias=bias, act=2, preact=p)                             # generic (erf)
 ops.linear_dgrad(o, b, torch.empty(M, K, dtype=torch.bfloat16, device=dev))     # MN-major B
-ops.linear_dgrad(o, b.t().contiguous().t(), torch.empty(M, K, dtype=torch.bfloat16, device=dev), gate=a, gate_kind=ops.GATE_MUL, colsum=torch.zeros(K, device=dev))
+ops.linear_dgrad(o, b, torch.empty(M, K, dtype=torch.bfloat16, device=dev), gate=a, gate_kind=ops.GATE_MUL, colsum=torch.zeros(K, device=dev))
 ops.linear_wgrad(o, a, f)                                                       # mode 3, split-K reduce-add
 ops.linear_fwd(a[:64], b, o[:64], bias=bias)                                    # single-CTA engine
 # attention: tcgen05 (d = 64) and mma.sync (d = 32)
