@@ -802,10 +802,15 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
             // 0-15 fetch them one sub-block ahead into a register and publish them after a __syncwarp -- no CTA-wide
             // rendezvous, the warps drift apart freely.
             // (the fetch returns the RAW values: touching them here would stall on the load it has just issued)
+            // (BQ = 2 SUBQ: sub-block n of the item starts at query i_begin * BQ + n * SUBQ; pointers hoisted per item)
+            const int tq0 = it.i_begin * BQ + wg * CPT + (lane & 15);
+            const float* lse_p = lse + bh_off + tq0;
+            const float* del_p = delta + bh_off + tq0;
+            const int nsub_item = 2 * it.nblk;
             auto fetch_ld = [&](int n_local) {
                 float2 v = make_float2(INFINITY, 0.f);        // queries past the end (and lanes 16-31): lse = +inf -> p = 0
-                const int tq = (it.i_begin + (n_local >> 1)) * BQ + (n_local & 1) * SUBQ + wg * CPT + (lane & 15);
-                if (lane < 16 && n_local < 2 * it.nblk && tq < T) v = make_float2(lse[bh_off + tq], delta[bh_off + tq]);
+                if (lane < 16 && n_local < nsub_item && tq0 + n_local * SUBQ < T)
+                    v = make_float2(lse_p[n_local * SUBQ], del_p[n_local * SUBQ]);
                 return v;
             };
             float2 nxt = fetch_ld(0);

@@ -253,25 +253,10 @@ __device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parit
     return done != 0;
 }
 // Wait with a watchdog: a protocol bug turns into a trap ("unspecified launch failure")
-// after ~4 s instead of a hung GPU box.
-// Two flavours (measured on one box against each other, tools/ab_probe.py): the GEMM's producer / MMA / epilogue warps
-// wait on a barrier only while nobody else on their scheduler has work, and their wake-up latency is on the critical
-// path -- spinning on the default try_wait is 6 % faster there. In the attention kernels the waiting warps (TMA, MMA,
-// drain) share schedulers with warps that are busy with the softmax arithmetic: there the wait must not spin through
-// issue slots, and sleeping in the barrier unit with a long suspend hint is 8 % faster (mbar_wait_relaxed).
-__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
-    if (mbar_try_wait(bar, parity)) return;
-    uint64_t t0 = 0;
-    uint32_t spins = 0;
-    while (!mbar_try_wait_hint(bar, parity, 100000u)) {
-        if ((++spins & 0x3fu) == 0) {
-            uint64_t now;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-            if (t0 == 0) t0 = now;
-            else if (now - t0 > 4000000000ull) { __trap(); }
-        }
-    }
-}
+// after ~4 s instead of a hung GPU box. The plain try_wait already suspends the thread in the barrier unit for a
+// hardware time limit, so most waits end inside the first probe and the loop body runs rarely. (Tried and dropped:
+// try_wait with a large suspend-time hint -- on this part it returns at once instead of sleeping longer, so the
+// loop spun through 28 % of the attention backward's issued instructions: profiles/r2_attn_ncu.md.)
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
     uint64_t t0 = 0;
@@ -285,6 +270,8 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         }
     }
 }
+// (kept as a name: the attention and row kernels' waits, where the waiting warps share schedulers with busy ones)
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) { mbar_wait(bar, parity); }
 
 __device__ __forceinline__ void fence_proxy_async_smem() {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
