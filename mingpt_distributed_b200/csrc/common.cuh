@@ -461,6 +461,36 @@ __device__ __forceinline__ void umma_commit_cg2_mc(uint64_t* bar, uint16_t mask)
 }
 
 // ----------------------------------------------------------------------------
+// Cluster launch control (Blackwell's hardware work queue): a RUNNING cluster asks to cancel a cluster of the same
+// grid that has not started yet and, if it gets one, does that cluster's work itself. The grid is launched with one
+// cluster per work unit; whoever holds SMs pulls units until none is pending, so SMs that are busy with something else
+// (NCCL's CTAs during the gradient all-reduce) simply pull fewer units instead of holding a static share hostage.
+// The 16-byte response lands in shared memory of EVERY CTA of the asking cluster (same offset), each CTA's mbarrier
+// at `bar`'s offset receives 16 transaction bytes.
+// ----------------------------------------------------------------------------
+__device__ __forceinline__ void clc_try_cancel_multicast(void* resp_smem, uint64_t* bar) {
+    asm volatile(
+        "clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.multicast::cluster::all.b128 [%0], [%1];"
+        ::"r"(smem_u32(resp_smem)), "r"(smem_u32(bar))
+        : "memory");
+}
+// true: a pending cluster was cancelled, `ctaid_x` is blockIdx.x of its first CTA; false: nothing left to take
+__device__ __forceinline__ bool clc_decode(const void* resp_smem, uint32_t& ctaid_x) {
+    uint32_t valid = 0, x = 0, y = 0, z = 0;
+    asm volatile(
+        "{\n\t.reg .pred p1;\n\t.reg .b128 resp;\n\t"
+        "ld.shared.b128 resp, [%4];\n\t"
+        "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p1, resp;\n\t"
+        "selp.u32 %3, 1, 0, p1;\n\t"
+        "@p1 clusterlaunchcontrol.query_cancel.get_first_ctaid.v4.b32.b128 {%0, %1, %2, _}, resp;\n\t}"
+        : "=r"(x), "=r"(y), "=r"(z), "=r"(valid)
+        : "r"(smem_u32(resp_smem))
+        : "memory");
+    ctaid_x = x;
+    return valid != 0;
+}
+
+// ----------------------------------------------------------------------------
 // TMA stores (smem -> global), plain and fp32 reduce-add; bulk async-group bookkeeping
 // ----------------------------------------------------------------------------
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, const void* smem_src, int32_t c0, int32_t c1) {

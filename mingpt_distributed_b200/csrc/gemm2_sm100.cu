@@ -23,6 +23,7 @@ constexpr int kMaxStages = 8;
 constexpr int kBoxBytes = 128 * 128;          // 128 rows x 128 bytes
 constexpr int kNumBoxes = 4;                  // two per epilogue half
 constexpr int kSmemLimit = 232448;            // 227 KiB
+constexpr int kBarBytes = 320;                // mbarriers (200 B) + TMEM base + two 16-byte work-queue responses at +256
 
 // Fallback epilogue for outputs TMA cannot address (row pitch not a multiple of 16 bytes): registers -> global.
 __device__ __forceinline__ void epilogue_direct(const Params& p, float (&v)[32], int64_t row, int64_t col0,
@@ -133,7 +134,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     uint64_t* tmem_empty = tmem_full + 2;            // [2]           (leader's copy is the live one)
     uint64_t* aux_bar = tmem_empty + 2;              // [kNumBoxes]   residual / gate tile landed in box i
     uint32_t* tmem_base_ptr = reinterpret_cast<uint32_t*>(aux_bar + kNumBoxes);
-    float* bias_s = reinterpret_cast<float*>(boxes + kNumBoxes * kBoxBytes + 256);    // [2][256] bias of the current / next tile
+    uint64_t* clc_full = aux_bar + kNumBoxes + 1;    // [2]  a work-queue response has landed in this CTA
+    uint64_t* clc_empty = clc_full + 2;              // [2]  (leader's copy is the live one) every reader of both CTAs is done with it
+    uint8_t* clc_resp = reinterpret_cast<uint8_t*>(bars) + 256;                        // [2] x 16 bytes
+    float* bias_s = reinterpret_cast<float*>(boxes + kNumBoxes * kBoxBytes + kBarBytes);   // [2][256] bias of the current / next tile
     float* cs_smem = bias_s + (p.bias ? 512 : 0);                                      // [256] (COLSUM only; behind the bias if both)
     if (COLSUM) {
         for (int c = threadIdx.x; c < 256; c += blockDim.x) cs_smem[c] = 0.f;
@@ -165,6 +169,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             mbar_init(&tmem_empty[s], 2 * kEpiWarps);   // epilogue warps of BOTH CTAs
         }
         for (int s = 0; s < kNumBoxes; ++s) mbar_init(&aux_bar[s], 1);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&clc_full[s], 1);                       // this CTA's scheduler lane arms it (arrive + 16 tx bytes)
+            mbar_init(&clc_empty[s], 2 * (2 + kEpiWarps) + 1);   // per CTA: producer, scheduler, 8 epilogue warps; + the MMA warp
+        }
         fence_mbar_init();
     }
     if (warp == 2) tmem_alloc_cg2(tmem_base_ptr, kTmemCols);
@@ -180,12 +188,54 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const int tiles = p.num_m_tiles * p.num_n_tiles;
     const int units = tiles * p.split_k;
 
+    // Work distribution. Static: cluster c takes units c, c + C, c + 2C, ... of a grid of C persistent clusters.
+    // Dynamic (p.dynamic): the grid has one cluster per unit; a cluster does its own unit and then keeps taking the
+    // units of clusters that have not started yet through cluster launch control (the hardware's work queue) until
+    // none is pending. Warp 3 of both CTAs runs the queue (the leader's asks, the response is multicast into both
+    // CTAs); every other role reads the responses in order through next_unit(). With SMs taken away by a concurrent
+    // kernel (NCCL during the gradient all-reduce) the remaining clusters just take more units, where a static share
+    // would wait for its SM pair.
+    auto next_unit = [&](int& u, uint32_t& k) -> bool {
+        if (!p.dynamic) { u += num_clusters; return u < units; }
+        const uint32_t slot = k & 1u;
+        mbar_wait(&clc_full[slot], (k >> 1) & 1u);
+        uint32_t x;
+        const bool valid = clc_decode(clc_resp + slot * 16, x);
+        fence_proxy_async_smem();                  // this read is ordered before the next response overwrites the slot
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(&clc_empty[slot], 0);
+        ++k;
+        u = (int)(x >> 1);
+        return valid;
+    };
+    if (warp == 3 && p.dynamic) {
+        const bool issuer = elect_one();
+        for (uint32_t k = 0;; ++k) {
+            const uint32_t slot = k & 1u, ph = (k >> 1) & 1u;
+            if (leader) mbar_wait(&clc_empty[slot], ph ^ 1u);          // all readers of both CTAs released the slot
+            if (issuer) {
+                mbar_arrive_expect_tx(&clc_full[slot], 16);
+                if (leader) clc_try_cancel_multicast(clc_resp + slot * 16, &clc_full[slot]);
+            }
+            __syncwarp();
+            mbar_wait(&clc_full[slot], ph);
+            uint32_t x;
+            const bool valid = clc_decode(clc_resp + slot * 16, x);
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(&clc_empty[slot], 0);
+            if (!valid) break;                                          // nothing pending any more: the queue is closed
+        }
+    }
+
     if (warp == 0) {
         // ===================== TMA producer (both CTAs; whole warp runs the loop, one lane issues) ==========
         {
             const bool issuer = elect_one();
             uint32_t stage = 0, phase = 0;
-            for (int u = cluster_id; u < units; u += num_clusters) {
+            int u = cluster_id;
+            uint32_t qk = 0;
+            for (bool more = u < units; more; more = next_unit(u, qk)) {
                 const int split = u / tiles;
                 const int t = u - split * tiles;
                 const int mt = p.m_fast ? (t % p.num_m_tiles) : (t / p.num_n_tiles);
@@ -230,7 +280,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const uint32_t b_kstep = p.b_mn ? UMMA_K * 128 : UMMA_K * 2;
             uint32_t stage = 0, phase = 0;
             uint32_t acc = 0, acc_phase = 0;
-            for (int u = cluster_id; u < units; u += num_clusters) {
+            int u = cluster_id;
+            uint32_t qk = 0;
+            for (bool more = u < units; more; more = next_unit(u, qk)) {
                 const int split = u / tiles;
                 const int kb0 = split * p.k_blocks_per_split;
                 const int kb1 = min(kb0 + p.k_blocks_per_split, p.k_blocks_total);
@@ -291,7 +343,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         uint32_t buf = 0;
         uint32_t aux_ph = 0;                                      // bit b: parity the next load into box b completes
         uint32_t acc = 0, acc_phase = 0;
-        for (int u = cluster_id; u < units; u += num_clusters) {
+        int u = cluster_id;
+        uint32_t qk = 0;
+        for (bool more = u < units; more; more = next_unit(u, qk)) {
             const int split = u / tiles;
             const int t = u - split * tiles;
             const int mt = p.m_fast ? (t % p.num_m_tiles) : (t / p.num_n_tiles);
@@ -601,7 +655,7 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
     // column sums ride along only on the staged bf16 path; otherwise mgb_gemm_bf16 adds them with a separate pass
     const bool fused_colsum = a->colsum && p.tma_store && !a->d_f32;
     p.colsum = fused_colsum ? a->colsum : nullptr;
-    const int fixed = kNumBoxes * kBoxBytes + 256 + ((a->bias && fused_colsum) ? 3072 : 2048);   // barriers | bias x 2 / colsum
+    const int fixed = kNumBoxes * kBoxBytes + kBarBytes + ((a->bias && fused_colsum) ? 3072 : 2048);   // barriers | bias x 2 / colsum
     int stages = (kSmemLimit - fixed) / (int)stage_bytes;
     if (stages > kMaxStages) stages = kMaxStages;
     p.num_stages = stages;
@@ -631,7 +685,9 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
         }
     }
     const int64_t units = (int64_t)tiles * p.split_k;
-    const int clusters = (int)(units < num_clusters ? units : num_clusters);
+    // more units than resident clusters: one cluster per unit, handed out by the hardware work queue (see the kernel)
+    p.dynamic = (units > num_clusters && !g_opt_gemm_static.load(std::memory_order_relaxed)) ? 1 : 0;
+    const int clusters = p.dynamic ? (int)units : (int)(units < num_clusters ? units : num_clusters);
     // epilogue specialisation (see the kernel): pick the leanest instantiation that covers this call
     int mode = 0;
     if (p.tma_store && !g_opt_gemm_generic.load(std::memory_order_relaxed)) {

@@ -11,6 +11,7 @@
 namespace mgb {
 extern std::atomic<int> g_opt_gemm_single;
 extern std::atomic<int> g_opt_gemm_direct_store;
+extern std::atomic<int> g_opt_gemm_static;        // 1 = static persistent tile walk instead of the hardware work queue
 extern std::atomic<int> g_opt_gemm_generic;       // 1 = always the generic (run-time) epilogue instantiation
 namespace gemm {
 
@@ -34,6 +35,7 @@ struct Params {
     int32_t tma_store;       // CTA-pair kernel only: D (and preact) leave through smem + TMA
     int32_t m_fast;          // CTA-pair kernel only: tile raster order (1 = m index fastest)
     int32_t tma_aux;         // CTA-pair kernel only: 1 residual / 2 gate arrives through TMA, updated in place
+    int32_t dynamic;         // CTA-pair kernel only: 1 = one cluster per unit + cluster launch control, 0 = static persistent walk
     // epilogue
     void* d;
     int64_t ldd;

@@ -309,6 +309,7 @@ namespace mgb {
 std::atomic<int> g_opt_gemm_single{0};
 std::atomic<int> g_opt_gemm_direct_store{0};
 std::atomic<int> g_opt_gemm_generic{0};
+std::atomic<int> g_opt_gemm_static{0};
 std::atomic<int> g_opt_pdl{0};   // measured gain on the gpt2-124M step: 0-1 % (within run-to-run noise), so off by default
 bool pdl_enabled() { return g_opt_pdl.load(std::memory_order_relaxed) != 0; }
 std::atomic<int> g_opt_attn_mma{0};
@@ -321,6 +322,7 @@ extern "C" int mgb_set_option(const char* key, int value) {
     if (!std::strcmp(key, "gemm_single")) return mgb::g_opt_gemm_single.exchange(value);
     if (!std::strcmp(key, "gemm_direct_store")) return mgb::g_opt_gemm_direct_store.exchange(value);
     if (!std::strcmp(key, "gemm_generic")) return mgb::g_opt_gemm_generic.exchange(value);
+    if (!std::strcmp(key, "gemm_static")) return mgb::g_opt_gemm_static.exchange(value);
     if (!std::strcmp(key, "pdl")) return mgb::g_opt_pdl.exchange(value);
     if (!std::strcmp(key, "attn_mma")) return mgb::g_opt_attn_mma.exchange(value);
     if (!std::strcmp(key, "attn_poly")) return mgb::g_opt_attn_poly.exchange(value);
