@@ -249,12 +249,11 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     const uint32_t rowbytes = (uint32_t)cols * 2;
     const float inv_cols = 1.0f / (float)cols;
     constexpr int NACC = COLSUM ? 4 : 3;
-    float* acc = reinterpret_cast<float*>(lnb_smem);                        // [NACC - 1][cols] CTA-level dgamma / dbeta (/ colsum)
-    float* gam_s = acc + (size_t)(NACC - 1) * cols;                         // [cols] gamma (read from here: registers are short)
-    uint8_t* ring = lnb_smem + (size_t)NACC * cols * sizeof(float) + (size_t)warp * LNB_STAGES * 2 * rowbytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(lnb_smem + (size_t)NACC * cols * sizeof(float) +
+    static_assert(LNB_STAGES * 2 * 2 >= (NACC - 1) * 4, "the per-warp ring must hold the warp's column partials");
+    float* gam_s = reinterpret_cast<float*>(lnb_smem);                      // [cols] gamma (read from here: registers are short)
+    uint8_t* ring = lnb_smem + (size_t)cols * sizeof(float) + (size_t)warp * LNB_STAGES * 2 * rowbytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(lnb_smem + (size_t)cols * sizeof(float) +
                                                  (size_t)LN_WARPS * LNB_STAGES * 2 * rowbytes) + warp * LNB_STAGES;
-    for (int c = threadIdx.x; c < (NACC - 1) * cols; c += blockDim.x) acc[c] = 0.f;
     for (int c = threadIdx.x; c < cols; c += blockDim.x) gam_s[c] = gamma[c];
     if (lane == 0) {
         for (int s = 0; s < LNB_STAGES; ++s) mbar_init(&bars[s], 1);
@@ -380,28 +379,36 @@ ln_bwd_staged_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
         if (lane == 0 && row + LNB_STAGES * stride < row1) issue(row + LNB_STAGES * stride, s);
         if (++s == LNB_STAGES) { s = 0; ph ^= 1; }
     }
+    // Column sums across the CTA: each warp has ~rows/(8*grid) rows (a handful), so this tail is a visible share of the
+    // kernel. The warp parks its partials in its own (now idle) ring slots with plain 16-byte stores, and after one
+    // barrier each thread adds the eight partials of its columns and sends ONE atomic per column to global memory.
+    float* part = reinterpret_cast<float*>(ring);                          // [NACC - 1][cols] per warp, <= the ring's 16 * cols bytes
 #pragma unroll
     for (int i = 0; i < MAXCH; ++i) {
         const int ch = lane + 32 * i;
         if (ch < nch) {
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                atomicAdd(&acc[ch * 8 + 2 * e], dg[i][e].x);
-                atomicAdd(&acc[ch * 8 + 2 * e + 1], dg[i][e].y);
-                atomicAdd(&acc[cols + ch * 8 + 2 * e], db[i][e].x);
-                atomicAdd(&acc[cols + ch * 8 + 2 * e + 1], db[i][e].y);
-                if (COLSUM) {
-                    atomicAdd(&acc[2 * cols + ch * 8 + 2 * e], dr[i][e].x);
-                    atomicAdd(&acc[2 * cols + ch * 8 + 2 * e + 1], dr[i][e].y);
-                }
+            float4* pg = reinterpret_cast<float4*>(part + ch * 8);
+            pg[0] = make_float4(dg[i][0].x, dg[i][0].y, dg[i][1].x, dg[i][1].y);
+            pg[1] = make_float4(dg[i][2].x, dg[i][2].y, dg[i][3].x, dg[i][3].y);
+            float4* pb = reinterpret_cast<float4*>(part + cols + ch * 8);
+            pb[0] = make_float4(db[i][0].x, db[i][0].y, db[i][1].x, db[i][1].y);
+            pb[1] = make_float4(db[i][2].x, db[i][2].y, db[i][3].x, db[i][3].y);
+            if (COLSUM) {
+                float4* pr = reinterpret_cast<float4*>(part + 2 * cols + ch * 8);
+                pr[0] = make_float4(dr[i][0].x, dr[i][0].y, dr[i][1].x, dr[i][1].y);
+                pr[1] = make_float4(dr[i][2].x, dr[i][2].y, dr[i][3].x, dr[i][3].y);
             }
         }
     }
     __syncthreads();
-    for (int c = threadIdx.x; c < cols; c += blockDim.x) {
-        atomicAdd(dgamma + c, acc[c]);
-        atomicAdd(dbeta + c, acc[cols + c]);
-        if (COLSUM) atomicAdd(dres_colsum + c, acc[2 * cols + c]);
+    const size_t warp_stride = (size_t)LNB_STAGES * 2 * rowbytes / sizeof(float);
+    const float* part0 = reinterpret_cast<const float*>(lnb_smem + (size_t)cols * sizeof(float));
+    for (int c = threadIdx.x; c < (NACC - 1) * cols; c += blockDim.x) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < LN_WARPS; ++w) t += part0[w * warp_stride + c];
+        float* dst = c < cols ? dgamma + c : (c < 2 * cols ? dbeta + (c - cols) : dres_colsum + (c - 2 * cols));
+        atomicAdd(dst, t);
     }
 }
 
@@ -817,13 +824,13 @@ static int layernorm_bwd_impl(const void* dy, const void* x, const float* gamma,
     const bool vec = (cols % 8 == 0) && cols <= 2048 && ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0) &&
                      ((uintptr_t)dx % 16 == 0) && (!dres || (uintptr_t)dres % 16 == 0);
     // persistent: each CTA owns register accumulators for dgamma/dbeta, flushed once
-    const size_t stage_smem = (size_t)3 * cols * sizeof(float) + (size_t)LN_WARPS * LNB_STAGES * 2 * cols * 2 +
+    const size_t stage_smem = (size_t)cols * sizeof(float) + (size_t)LN_WARPS * LNB_STAGES * 2 * cols * 2 +
                               LN_WARPS * LNB_STAGES * sizeof(uint64_t);
     if (dres_colsum && !dres) { set_last_error("layernorm_bwd: dres_colsum needs dres"); return kErrBadShape; }
-    if (vec && stage_smem + (size_t)cols * sizeof(float) <= 227 * 1024 && !g_opt_ln_unstaged.load(std::memory_order_relaxed)) {
+    if (vec && stage_smem <= 227 * 1024 && !g_opt_ln_unstaged.load(std::memory_order_relaxed)) {
         // rows staged through shared memory by bulk copies; every warp owns a contiguous range of rows
         const bool colsum = dres_colsum != nullptr;
-        const size_t smem_used = stage_smem + (colsum ? (size_t)cols * sizeof(float) : 0);
+        const size_t smem_used = stage_smem;
         const int per_sm = (cols <= 768 && 2 * smem_used <= 227 * 1024) ? 2 : 1;
         int grid = num_sms() * per_sm;
         const int64_t warps_wanted = (rows + 3) / 4;                 // at least ~4 rows per warp
