@@ -192,7 +192,7 @@ int mgb_attention_decode(const void* qkv_cache, void* out, int32_t B, int32_t Tc
                          int32_t d, float scale, mgb_stream_t stream);
 
 /* Dropout (the reference trains with p = 0.1 at four sites and never calls eval(): mingpt/model.py:49-51,140,
- * 150,183,215). Masks are counter based (Philox4x32-10 over (seed, site, element)) and never stored: the
+ * 150,183,215). Masks are counter based (Philox4x32, 7 rounds, over (seed, site, element)) and never stored: the
  * backward regenerates them. *seed_dev is a DEVICE uint64 the caller changes every step; `site` tells the
  * dropouts of one step apart. An element is kept with probability 1 - round(p * 65536) / 65536.
  *   mgb_dropout_bf16:   y = (res ? res : 0) + (keep ? x / (1-p) : 0)     (embedding / residual dropouts, and
@@ -211,6 +211,29 @@ int mgb_attention_bwd_dropout(const void* qkv, const void* out, const void* dout
                               mgb_stream_t stream);
 int mgb_attention_dropout_mask(void* keep, int32_t B, int32_t T, int32_t H, float p_drop, const uint64_t* seed_dev,
                                uint32_t site, mgb_stream_t stream);
+/* The same dropout with the keep bits generated ahead of the attention kernels (head size 64 only). The softmax
+ * warps of those kernels are bound by their instruction stream, and the inline Philox calls doubled it; a separate,
+ * well-occupied generator produces the identical bits once per layer and step, and forward AND backward read them.
+ *   mgb_attention_dropout_bits_words: *words = size of the buffer in 32-bit words,
+ *                                     B*H*ceil(T/32) * (roundup(T,16) + roundup(T,32))
+ *   mgb_attention_dropout_bits:       fills it: first [B*H][T/32][roundup(T,16)] words of 32 keys of one query (key
+ *                                     k at bit 16*(k&1) + 15 - (k>>1)) for the forward, then the same bits
+ *                                     transposed, [B*H][T/32][roundup(T,32)] words of 32 queries of one key (query
+ *                                     q at bit q%32) for the backward; for MGB_MASK_CAUSAL the words right of the
+ *                                     diagonal are left untouched
+ *   mgb_attention_fwd_dropout_bits / _bwd_dropout_bits: mgb_attention_fwd_dropout / _bwd_dropout reading that buffer;
+ *                                     the backward also takes dqkv_colsum (or null) like mgb_attention_bwd_colsum.
+ * Same results as the seed-taking entry points above (same mask, same arithmetic). */
+int mgb_attention_dropout_bits_words(int32_t B, int32_t T, int32_t H, int64_t* words);
+int mgb_attention_dropout_bits(uint32_t* bits, int32_t B, int32_t T, int32_t H, int32_t mask_mode, float p_drop,
+                               const uint64_t* seed_dev, uint32_t site, mgb_stream_t stream);
+int mgb_attention_fwd_dropout_bits(const void* qkv, void* out, float* lse, int32_t B, int32_t T, int32_t H, int32_t d,
+                                   int32_t mask_mode, float scale, float p_drop, const uint32_t* bits,
+                                   mgb_stream_t stream);
+int mgb_attention_bwd_dropout_bits(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                                   float* dq_accum, void* dqkv, int32_t B, int32_t T, int32_t H, int32_t d,
+                                   int32_t mask_mode, float scale, float p_drop, const uint32_t* bits,
+                                   float* dqkv_colsum, mgb_stream_t stream);
 
 /* No counterpart in the reference. mgb_attention_bwd for callers that have no scratch to give: a plugin
  * inside a process whose device pool is fixed at start-up, or an FFI stub that only forwards pointers and

@@ -68,6 +68,10 @@ SIGNATURES = {
     "mgb_attention_fwd_dropout": [_P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _F, _P, C.c_uint32, _P],
     "mgb_attention_bwd_dropout": [_P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _F, _P, C.c_uint32, _P],
     "mgb_attention_dropout_mask": [_P, _I32, _I32, _I32, _F, _P, C.c_uint32, _P],
+    "mgb_attention_dropout_bits_words": [_I32, _I32, _I32, _P],
+    "mgb_attention_dropout_bits": [_P, _I32, _I32, _I32, _I32, _F, _P, C.c_uint32, _P],
+    "mgb_attention_fwd_dropout_bits": [_P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _F, _P, _P],
+    "mgb_attention_bwd_dropout_bits": [_P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _F, _P, _P, _P],
     "mgb_cross_entropy_fwd_bwd": [_P, _I64, _P, _P, _P, _I64, _I64, _F, _I32, _P, _P],
     "mgb_count_valid_targets": [_P, _I64, _P, _P],
     "mgb_loss_finalize": [_P, _I64, _P, _P, _P],

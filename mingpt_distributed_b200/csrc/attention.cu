@@ -21,10 +21,11 @@ namespace mgb {
 extern std::atomic<int> g_opt_attn_mma;
 namespace attn_tc {   // tcgen05 / TMEM kernels for head size 64 (attention_sm100.cu)
 int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream,
-               uint32_t drop_thresh, float inv_keep, const uint64_t* seed_dev, uint32_t site);
+               uint32_t drop_thresh, float inv_keep, const uint64_t* seed_dev, uint32_t site, const uint32_t* drop_bits = nullptr);
 int launch_bwd_main(const void* qkv, const void* dout, const float* lse, const float* delta, float* dq_accum,
                     void* dqkv, float* dqkv_colsum, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream,
-                    uint32_t drop_thresh, float inv_keep, const uint64_t* seed_dev, uint32_t site);
+                    uint32_t drop_thresh, float inv_keep, const uint64_t* seed_dev, uint32_t site,
+                    const uint32_t* drop_bits = nullptr);
 }
 namespace attn {
 
@@ -496,7 +497,7 @@ attn_dq_convert_kernel(const float* __restrict__ dq_accum, __nv_bfloat16* __rest
 // Same, and colsum[0 .. HD) += column sums of dQ (the Q third of the qkv bias gradient). The block is
 // (HD/8) x rows_per_block threads: a thread keeps its 8 columns for the whole grid-stride loop, so the sums
 // stay in registers until one shared-memory and one global atomic per column and block.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(512)
 attn_dq_convert_colsum_kernel(const float* __restrict__ dq_accum, __nv_bfloat16* __restrict__ dqkv, int64_t BT, int HD,
                               float* __restrict__ colsum) {
     extern __shared__ float cvt_smem[];              // [HD]
@@ -554,7 +555,8 @@ static int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int 
 template <int D>
 static int launch_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
                       float* dq_accum, void* dqkv, int B, int T, int H, int mask_mode, float scale, cudaStream_t s,
-                      float p_drop = 0.f, const uint64_t* seed_dev = nullptr, uint32_t site = 0, float* dqkv_colsum = nullptr) {
+                      float p_drop = 0.f, const uint64_t* seed_dev = nullptr, uint32_t site = 0, float* dqkv_colsum = nullptr,
+                      const uint32_t* drop_bits = nullptr) {
     const uint32_t thresh = p_drop > 0.f ? dropout_thresh16(p_drop) : 0u;
     const float inv_keep = thresh ? 65536.0f / (65536.0f - (float)thresh) : 1.0f;
     const bool delta_given = (mask_mode & MGB_ATTN_DELTA_GIVEN) != 0;     // the caller's dgrad GEMM already produced it
@@ -575,9 +577,9 @@ static int launch_bwd(const void* qkv, const void* out, const void* dout, const 
     // epilogue, Q third in the convert kernel), a separate pass otherwise
     bool fused_colsum = false;
     if (D == 64 && !g_opt_attn_mma.load(std::memory_order_relaxed)) {
-        fused_colsum = dqkv_colsum != nullptr && (H * D / 8) <= 256;
+        fused_colsum = dqkv_colsum != nullptr && (H * D / 8) <= 512;
         const int rc = attn_tc::launch_bwd_main(qkv, dout, lse, delta, dq_accum, dqkv, fused_colsum ? dqkv_colsum : nullptr, B, T,
-                                                H, mask_mode, scale, s, thresh, inv_keep, seed_dev, site);
+                                                H, mask_mode, scale, s, thresh, inv_keep, seed_dev, site, drop_bits);
         if (rc) return rc;
     } else {
         dim3 grid((T + BN - 1) / BN, B * H);
@@ -587,10 +589,12 @@ static int launch_bwd(const void* qkv, const void* out, const void* dout, const 
     }
     if (fused_colsum) {
         const int nch = H * D / 8;
-        const int threads = (256 / nch) * nch;
+        // few, fat CTAs: every CTA ends with one global atomic per column, and with 8 CTAs per SM those tails were a
+        // third of the kernel (16384 x 768: 19.3 us with 8 x 256-thread CTAs per SM, 13.2 us with 2 x 512)
+        const int threads = (512 / nch) * nch;
         const int64_t rows = (int64_t)B * T;
         int64_t g2 = (rows + (threads / nch) - 1) / (threads / nch);
-        if (g2 > num_sms() * 8) g2 = num_sms() * 8;
+        if (g2 > num_sms() * 2) g2 = num_sms() * 2;
         launch_pdl(attn_dq_convert_colsum_kernel, dim3((int)g2), dim3(threads), H * D * sizeof(float), s, dq_accum,
                    (__nv_bfloat16*)dqkv, rows, H * D, dqkv_colsum);
         return 0;
@@ -875,6 +879,103 @@ attn_dropout_mask_kernel(uint8_t* __restrict__ keep, int64_t BH, int T, uint32_t
 }
 }  // namespace attn
 }  // namespace mgb
+
+namespace mgb {
+namespace attn {
+// Keep words for the tcgen05 kernels (layouts and bit order: dropout.cuh). Thread = 32 keys of one query, a warp =
+// 32 consecutive queries: it stores its query-major words (coalesced) for the forward, transposes the 32 x 32 bits
+// across its lanes and stores the key-major words for the backward. Grid = (query chunks, key words, batch * heads).
+// Causal: words right of the diagonal are never read, and their warps leave at once.
+__global__ void __launch_bounds__(256)
+attn_dropout_bits_kernel(uint32_t* __restrict__ bits, int BH, int T, int causal, uint32_t thresh,
+                         const uint64_t* __restrict__ seed_dev, uint32_t site) {
+    const int kw = (T + 31) >> 5, tp = (T + 15) & ~15, kp = kw * 32;
+    const int w = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const int q = blockIdx.x * 256 + threadIdx.x;
+    const int q0 = q - lane;                                     // first query of this warp: a multiple of 32
+    if (q0 >= T || (causal && w * 32 > q0)) return;              // warp-uniform
+    const uint64_t t8 = (uint64_t)((T + 7) >> 3);
+    const uint64_t seed = *seed_dev;
+    uint32_t* bits_t = bits + dropout_bits_words_q(BH, T);
+    const int key_t = w * 32 + dropout_key_of_bit(lane);         // after the transpose lane b holds the word of the key at bit b
+    for (int bh = blockIdx.z; bh < BH; bh += gridDim.z) {
+        uint32_t word = 0;
+        if (q < T) {
+            word = dropout_keep32_word(seed, site, ((uint64_t)bh * T + (uint64_t)q) * t8 + (uint64_t)w * 4, thresh);
+            bits[((int64_t)bh * kw + w) * tp + q] = word;
+        }
+        const uint32_t wt = warp_transpose32(word, lane);
+        bits_t[((int64_t)bh * kw + (q0 >> 5)) * kp + key_t] = wt;
+    }
+}
+}  // namespace attn
+}  // namespace mgb
+
+static int64_t dropout_bits_words(int32_t B, int32_t T, int32_t H) {
+    return (int64_t)(dropout_bits_words_q((int64_t)B * H, T) + dropout_bits_words_t((int64_t)B * H, T));
+}
+extern "C" int mgb_attention_dropout_bits_words(int32_t B, int32_t T, int32_t H, int64_t* words) {
+    if (B <= 0 || T <= 0 || H <= 0 || !words) { set_last_error("dropout_bits_words: bad arguments"); return kErrBadShape; }
+    *words = dropout_bits_words(B, T, H);
+    return kOk;
+}
+
+extern "C" int mgb_attention_dropout_bits(uint32_t* bits, int32_t B, int32_t T, int32_t H, int32_t mask_mode, float p_drop,
+                                          const uint64_t* seed_dev, uint32_t site, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    if (B <= 0 || T <= 0 || H <= 0 || !bits || !seed_dev || !(p_drop > 0.f && p_drop < 1.f)) { set_last_error("dropout_bits: bad arguments"); return kErrBadShape; }
+    if ((uintptr_t)bits % 16) { set_last_error("dropout_bits: the buffer must be 16-byte aligned"); return kErrBadAlign; }
+    const int64_t bh = (int64_t)B * H;
+    // four (batch, head) pairs per thread: amortises the CTA prologue (the seed load) without starving the tail
+    const int64_t gz = (bh + 3) / 4;
+    dim3 grid((T + 255) / 256, (T + 31) / 32, (unsigned)(gz < 65535 ? gz : 65535));
+    attn::attn_dropout_bits_kernel<<<grid, 256, 0, s>>>(bits, (int)bh, T, (mask_mode & 0xff) == MGB_MASK_CAUSAL ? 1 : 0,
+                                                       dropout_thresh16(p_drop), seed_dev, site);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+extern "C" int mgb_attention_fwd_dropout_bits(const void* qkv, void* out, float* lse, int32_t B, int32_t T, int32_t H,
+                                              int32_t d, int32_t mask_mode, float scale, float p_drop, const uint32_t* bits,
+                                              mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    int rc = check_attn_shape("fwd_dropout_bits", B, T, H, d, mask_mode);
+    if (rc) return rc;
+    if (d != 64 || g_opt_attn_mma.load(std::memory_order_relaxed)) { set_last_error("attention_fwd_dropout_bits: head size 64 (the tcgen05 kernel) only"); return kErrUnsupported; }
+    if (!(p_drop > 0.f && p_drop < 1.f) || !bits) { set_last_error("attention: bad dropout arguments"); return kErrBadShape; }
+    if (((uintptr_t)qkv % 16) || ((uintptr_t)out % 16) || ((uintptr_t)bits % 16)) { set_last_error("attention: pointers must be 16-byte aligned"); return kErrBadAlign; }
+    const uint32_t thresh = dropout_thresh16(p_drop);
+    if (!thresh) return mgb_attention_fwd(qkv, out, lse, B, T, H, d, mask_mode, scale, s_);
+    rc = attn_tc::launch_fwd(qkv, out, lse, B, T, H, mask_mode, scale, s, thresh, 65536.0f / (65536.0f - (float)thresh), nullptr, 0u, bits);
+    if (rc) return rc;
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
+
+extern "C" int mgb_attention_bwd_dropout_bits(const void* qkv, const void* out, const void* dout, const float* lse,
+                                              float* delta, float* dq_accum, void* dqkv, int32_t B, int32_t T, int32_t H,
+                                              int32_t d, int32_t mask_mode, float scale, float p_drop, const uint32_t* bits,
+                                              float* dqkv_colsum, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    int rc = check_attn_shape("bwd_dropout_bits", B, T, H, d, mask_mode);
+    if (rc) return rc;
+    if (d != 64 || g_opt_attn_mma.load(std::memory_order_relaxed)) { set_last_error("attention_bwd_dropout_bits: head size 64 (the tcgen05 kernel) only"); return kErrUnsupported; }
+    if (!(p_drop > 0.f && p_drop < 1.f) || !bits) { set_last_error("attention: bad dropout arguments"); return kErrBadShape; }
+    if (((uintptr_t)qkv % 16) || ((uintptr_t)out % 16) || ((uintptr_t)dout % 16) || ((uintptr_t)dqkv % 16) ||
+        ((uintptr_t)dq_accum % 16) || ((uintptr_t)bits % 16)) {
+        set_last_error("attention: pointers must be 16-byte aligned"); return kErrBadAlign;
+    }
+    cudaMemsetAsync(dq_accum, 0, (size_t)B * T * H * d * sizeof(float), s);
+    const int owed = attn::launch_bwd<64>(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, mask_mode, scale, s, p_drop, nullptr, 0u,
+                                          dqkv_colsum, bits);
+    if (owed < 0) return owed;
+    count_launch(3);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
 
 extern "C" int mgb_attention_fwd_dropout(const void* qkv, void* out, float* lse, int32_t B, int32_t T, int32_t H,
                                          int32_t d, int32_t mask_mode, float scale, float p_drop,

@@ -58,13 +58,25 @@ __device__ __forceinline__ void drop_packed(uint32_t* w, uint64_t seed, uint32_t
     }
 }
 
+// The same on a pre-generated keep word (dropout.cuh): 16 packed pairs = 32 consecutive keys of this query row.
+__device__ __forceinline__ void drop_packed_word(uint32_t* w, uint32_t word) {
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        uint32_t m_s, m_s8;
+        dropout_pair_masks(word, s, m_s, m_s8);
+        w[s] &= m_s;
+        w[s + 8] &= m_s8;
+    }
+}
+
 // DROP: attention-probability dropout (nn.MultiheadAttention dropout=attn_drop: mingpt/model.py:150 ->
 // torch/nn/functional.py:6644-6645). The softmax normaliser keeps every key, P V only the kept ones.
 template <bool DROP, int POLY>
 __global__ void __launch_bounds__(kThreads, 2)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __restrict__ out,
                    float* __restrict__ lse, int T, int H, int mask_mode, float scale_log2, uint32_t drop_thresh,
-                   float inv_keep, const uint64_t* __restrict__ seed_dev, uint32_t site) {
+                   float inv_keep, const uint64_t* __restrict__ seed_dev, uint32_t site,
+                   const uint32_t* __restrict__ drop_bits) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem;
@@ -178,9 +190,24 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
         const int q = q0 + r;
         const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16);
         float m_run = -INFINITY, l_run = 0.f;
-        const uint64_t drop_seed = DROP ? *seed_dev : 0;
+        const uint64_t drop_seed = (DROP && !drop_bits) ? *seed_dev : 0;
         const uint64_t drop_row = ((uint64_t)blockIdx.y * T + (uint64_t)q) * (uint64_t)((T + 7) >> 3);   // first group of this query
+        const int drop_kw = (T + 31) >> 5;                       // keep words per query (pre-generated masks)
+        const uint64_t drop_tp = (uint64_t)((T + 15) & ~15);
+        // pre-generated masks: this row's keep words for a block's 4 x 32 keys, fetched one block ahead
+        uint32_t dwn[4] = {~0u, ~0u, ~0u, ~0u};
+        auto fetch_dw = [&](int jj) {
+            if (q < T && jj < nkv) {
+                const uint32_t* bp = drop_bits + ((uint64_t)blockIdx.y * drop_kw + 4 * jj) * drop_tp + q;
+#pragma unroll
+                for (int g = 0; g < 4; ++g)
+                    if (4 * jj + g < drop_kw) dwn[g] = __ldg(bp + g * drop_tp);
+            }
+        };
+        if (DROP && drop_bits) fetch_dw(0);
         for (int j = 0; j < nkv; ++j) {
+            const uint32_t dw[4] = {dwn[0], dwn[1], dwn[2], dwn[3]};
+            if (DROP && drop_bits) fetch_dw(j + 1);
             const uint32_t ph = (uint32_t)(j & 1);
             const int kvalid = min(BKV, T - j * BKV);            // keys of this block that exist
             const bool diag = (j == qb);
@@ -315,7 +342,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
                             }
                         }
                     }
-                    if (DROP && g <= warp) drop_packed<16>(pk, drop_seed, site, drop_row + (uint64_t)(j * (BKV / 8) + g * 4), drop_thresh);
+                    if (DROP && g <= warp) {
+                        if (drop_bits) drop_packed_word(pk, g == 0 ? dw[0] : (g == 1 ? dw[1] : (g == 2 ? dw[2] : dw[3])));
+                        else drop_packed<16>(pk, drop_seed, site, drop_row + (uint64_t)(j * (BKV / 8) + g * 4), drop_thresh);
+                    }
                     tmem_st_32x32b_x16(taddr + kColP + g * 16, pk);
                 }
             } else {
@@ -355,7 +385,14 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
                             pk[e] = pack_bf16x2(pv[0], pv[1]);
                         }
                     }
-                    if (DROP) drop_packed<32>(pk, drop_seed, site, drop_row + (uint64_t)(j * (BKV / 8) + c * 8), drop_thresh);
+                    if (DROP) {
+                        if (drop_bits) {
+                            drop_packed_word(pk, c ? dw[2] : dw[0]);
+                            drop_packed_word(pk + 16, c ? dw[3] : dw[1]);
+                        } else {
+                            drop_packed<32>(pk, drop_seed, site, drop_row + (uint64_t)(j * (BKV / 8) + c * 8), drop_thresh);
+                        }
+                    }
                     tmem_st_32x32b_x32(taddr + kColP + c * 32, pk);
                 }
             }
@@ -400,7 +437,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
 }
 
 int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int mask_mode, float scale,
-               cudaStream_t stream, uint32_t drop_thresh, float inv_keep, const uint64_t* seed_dev, uint32_t site) {
+               cudaStream_t stream, uint32_t drop_thresh, float inv_keep, const uint64_t* seed_dev, uint32_t site,
+               const uint32_t* drop_bits) {
     static PerDeviceOnce once;
     once.run([] {
         cudaFuncSetAttribute(attn_fwd_tc_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
@@ -418,11 +456,11 @@ int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int 
     const int poly = g_opt_attn_poly.load(std::memory_order_relaxed);
 #define MGB_ATTN_FWD(DROPV, POLYV)                                                                                          \
     launch_pdl(attn_fwd_tc_kernel<DROPV, POLYV>, grid, dim3(kThreads), (size_t)SMEM_BYTES, stream, tm, (__nv_bfloat16*)out, lse, T, H, \
-               mask_mode, scale * LOG2E, drop_thresh, inv_keep, seed_dev, site)
+               mask_mode, scale * LOG2E, drop_thresh, inv_keep, seed_dev, site, drop_bits)
     if (drop_thresh) {
         if (poly == 2) MGB_ATTN_FWD(true, 2); else if (poly == 1) MGB_ATTN_FWD(true, 1); else MGB_ATTN_FWD(true, 0);
     } else {
-        inv_keep = 1.0f; seed_dev = nullptr; site = 0u;
+        inv_keep = 1.0f; seed_dev = nullptr; site = 0u; drop_bits = nullptr;
         if (poly == 2) MGB_ATTN_FWD(false, 2); else if (poly == 1) MGB_ATTN_FWD(false, 1); else MGB_ATTN_FWD(false, 0);
     }
 #undef MGB_ATTN_FWD
@@ -537,11 +575,12 @@ __device__ __forceinline__ int bwd_item(const BwdSched& sc, int q, BwdItem& it) 
     return 1;
 }
 
-// DROP: attention-probability dropout, the forward's mask regenerated (dropout.cuh). In this transposed layout a
-// thread owns ONE key and CPT consecutive queries, while a mask group is 8 consecutive KEYS of one query: the 32
-// lanes of a warp (32 keys = 4 groups) share the 4 x CPT = 64 groups of a sub-block, two Philox calls per lane,
-// and fetch their bits with one shuffle per query. dV uses the kept probabilities (scaled once, in the epilogue),
-// dS = P (keep ? dP / (1-p) : 0 - delta) * scale.
+// DROP: attention-probability dropout with the forward's mask. A thread owns ONE key and CPT consecutive queries:
+//   drop_bits given -- the TRANSPOSED keep words the generator wrote next to the forward's (dropout.cuh; one word =
+//       32 queries of one key): one coalesced 4-byte load per thread and sub-block, 2 instructions per element;
+//   else -- the mask is regenerated: a group is 8 consecutive KEYS of one query, so the 32 lanes of a warp (32 keys =
+//       4 groups) share the 4 x CPT = 64 groups of a sub-block, two Philox calls per lane, one shuffle per query.
+// dS = P (ks dP - delta scale) and dV += (ks P)^T dO / scale with ks = keep ? scale / (1-p) : 0.
 template <bool DROP>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_constant__ CUtensorMap tmap_q,
@@ -549,7 +588,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                    const float* __restrict__ lse, const float* __restrict__ delta,
                    __nv_bfloat16* __restrict__ dqkv, float* __restrict__ kv_colsum, int B, int T, int H, int mask_mode,
                    float scale, float scale_log2, uint32_t drop_thresh, float inv_keep,
-                   const uint64_t* __restrict__ seed_dev, uint32_t site) {
+                   const uint64_t* __restrict__ seed_dev, uint32_t site, const uint32_t* __restrict__ drop_bits) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = smem_raw;
     if (smem_u32(smem) & 1023u) __trap();                      // SWIZZLE_128B tiles need 1024-byte alignment
@@ -787,7 +826,8 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
         const int r = quarter * 32 + lane;               // key row inside the block == TMEM lane
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
         const uint32_t swz = (uint32_t)(r & 7);
-        const uint64_t drop_seed = DROP ? *seed_dev : 0;
+        const uint64_t drop_seed = (DROP && !drop_bits) ? *seed_dev : 0;
+        const uint64_t drop_t_off = dropout_bits_words_q(B * H, T);     // the transposed words follow the query-major ones
         uint32_t g = 0, w = 0;
         for (int q = 0;; ++q) {
             BwdItem it;
@@ -814,6 +854,16 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 return v;
             };
             float2 nxt = fetch_ld(0);
+            // DROP with pre-generated masks: the transposed keep words (dropout.cuh) -- one word = 32 queries of this
+            // thread's key, consecutive lanes = consecutive keys
+            const int kwn = (T + 31) >> 5;
+            const uint32_t* kq_p = (DROP && drop_bits && key < kwn * 32)
+                ? drop_bits + drop_t_off + (uint64_t)(it.b * H + it.h) * kwn * (uint64_t)(kwn * 32) + key : nullptr;
+            auto fetch_kq = [&](int n_local) -> uint32_t {
+                const int qs = it.i_begin * BQ + n_local * SUBQ + wg * CPT;      // first query of this thread in that sub-block
+                return (kq_p && n_local < nsub_item && qs < T) ? __ldg(kq_p + (uint64_t)(qs >> 5) * (uint64_t)(kwn * 32)) : 0u;
+            };
+            uint32_t kq_nxt = (DROP && drop_bits) ? fetch_kq(0) : 0u;
             {   // this item's K and V rows -> TMEM (bf16): 16 features of row r per thread. The previous item's products
                 // are complete (all_done was waited for in its epilogue).
                 mbar_wait_relaxed(&kv_full[w & 1], (w >> 1) & 1);
@@ -853,30 +903,33 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 }
                 nxt = fetch_ld(n + 1);
                 __syncwarp();
+                const int qc0 = (int)half * SUBQ + wg * CPT;         // first query column (inside the block) of this thread
+                // bit e of kq: the probability of query qc0 + e was kept. The word was fetched a sub-block ahead (a load
+                // issued here would sit on this iteration's critical path: the products are usually ready by now).
+                uint32_t kq = (DROP && drop_bits) ? (kq_nxt >> ((n * SUBQ + wg * CPT) & 16)) : 0xffffu;
+                if (DROP && drop_bits) kq_nxt = fetch_kq(n + 1);
                 mbar_wait_relaxed(&s_full[half], jg & 1);
                 tc_fence_after();
-                const int qc0 = (int)half * SUBQ + wg * CPT;         // first query column (inside the block) of this thread
                 uint32_t sv[CPT], dp[CPT];
                 tmem_ld_cols(taddr + cST + half * SUBQ + wg * CPT, sv);
                 tmem_ld_cols(taddr + cDPT + half * SUBQ + wg * CPT, dp);
                 tmem_ld_wait();
-                uint32_t keepbits = 0xffffu;                         // bit e: the probability of query qc0 + e was kept
-                if (DROP) {
+                // DROP: ks = keep ? scale / (1-p) : 0 replaces `scale` in dS = P (ks dP - delta scale) and multiplies P
+                // where it is packed for dV (the item epilogue takes the factor `scale` out again).
+                const float iks = inv_keep * scale;
+                if (DROP && !drop_bits) {
                     static_assert(CPT == 16, "two Philox calls per lane cover 4 key groups x 16 queries");
                     const uint64_t t8 = (uint64_t)((T + 7) >> 3);
                     const uint64_t qrow = ((uint64_t)it.b * H + it.h) * T + (uint64_t)(i * BQ + qc0 + (lane >> 2));
                     const uint64_t kgrp = (uint64_t)((k0 + 32 * quarter) >> 3) + (uint64_t)(lane & 3);
                     const uint32_t m0 = dropout_keep8(drop_seed, site, qrow * t8 + kgrp, drop_thresh);         // queries 0-7
                     const uint32_t m1 = dropout_keep8(drop_seed, site, (qrow + 8) * t8 + kgrp, drop_thresh);   // queries 8-15
-                    keepbits = 0u;
+                    kq = 0u;
 #pragma unroll
                     for (int e = 0; e < CPT; ++e) {
                         const uint32_t v = __shfl_sync(0xffffffffu, e < 8 ? m0 : m1, (e & 7) * 4 + (lane >> 3));
-                        keepbits |= ((v >> (lane & 7)) & 1u) << e;
+                        kq |= ((v >> (lane & 7)) & 1u) << e;
                     }
-#pragma unroll
-                    for (int e = 0; e < CPT; ++e)
-                        dp[e] = (keepbits >> e) & 1u ? __float_as_uint(__uint_as_float(dp[e]) * inv_keep) : 0u;
                 }
                 uint32_t pk[CPT / 2], dk[CPT / 2];
                 // causal diagonal block with every key / query present: key row r sees query column c iff r <= c. This
@@ -903,9 +956,11 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                             const float2 bv = h2 ? make_float2(b4.z, b4.w) : make_float2(b4.x, b4.y);
                             const float2 x = fma2(make_float2(__uint_as_float(sv[2 * e]), __uint_as_float(sv[2 * e + 1])), sc2, av);
                             const float2 pp = make_float2(exp2f(x.x), exp2f(x.y));
-                            const float2 tt = fma2(make_float2(__uint_as_float(dp[2 * e]), __uint_as_float(dp[2 * e + 1])), scl2, bv);
+                            const float2 ks2 = DROP ? make_float2((kq & (1u << (2 * e))) ? iks : 0.f, (kq & (2u << (2 * e))) ? iks : 0.f) : scl2;
+                            const float2 tt = fma2(make_float2(__uint_as_float(dp[2 * e]), __uint_as_float(dp[2 * e + 1])), ks2, bv);
                             const float2 ds = mul2(pp, tt);
-                            pk[e] = pack_bf16x2(pp.x, pp.y);
+                            const float2 pm = DROP ? mul2(pp, ks2) : pp;
+                            pk[e] = pack_bf16x2(pm.x, pm.y);
                             dk[e] = pack_bf16x2(ds.x, ds.y);
                         }
                     }
@@ -921,17 +976,13 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                             if (bias_diag && r <= col) x += LOG2E;
                             const bool dead = (key >= T) || (diag && r > col);   // queries >= T carry a = -inf
                             const float p = dead ? 0.f : exp2f(x);
-                            pv[t2] = p;
-                            dsv[t2] = p * fmaf(__uint_as_float(dp[2 * e + t2]), scale, ldv.y);
+                            const float ks = DROP ? ((kq & (1u << (2 * e + t2))) ? iks : 0.f) : scale;
+                            pv[t2] = DROP ? p * ks : p;
+                            dsv[t2] = p * fmaf(__uint_as_float(dp[2 * e + t2]), ks, ldv.y);
                         }
                         pk[e] = pack_bf16x2(pv[0], pv[1]);
                         dk[e] = pack_bf16x2(dsv[0], dsv[1]);
                     }
-                }
-                if (DROP) {                                          // P^T as it multiplied V: dropped entries are zero
-#pragma unroll
-                    for (int e = 0; e < CPT / 2; ++e)
-                        pk[e] &= ((keepbits >> (2 * e)) & 1u ? 0x0000ffffu : 0u) | ((keepbits >> (2 * e + 1)) & 1u ? 0xffff0000u : 0u);
                 }
                 // bf16 pairs over the first half of this thread's own fp32 columns (both were just read)
                 tmem_st_cols(taddr + cST + half * SUBQ + wg * CPT, pk);
@@ -961,9 +1012,10 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_free);            // the next item may start accumulating
-            if (DROP) {                                      // dV was accumulated from the unscaled kept probabilities
+            if (DROP) {                                      // P carried scale / (1-p) into dV: take `scale` out again
+                const float inv_scale = 1.0f / scale;
 #pragma unroll
-                for (int e = 0; e < CPT; ++e) vv[e] = __float_as_uint(__uint_as_float(vv[e]) * inv_keep);
+                for (int e = 0; e < CPT; ++e) vv[e] = __float_as_uint(__uint_as_float(vv[e]) * inv_scale);
             }
             if (kv_colsum) {
                 // bias gradient of the qkv projection, K and V thirds: column sums over this warp's 32 key rows by a
@@ -1029,7 +1081,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
 // main backward kernel only: delta must be precomputed and dq_accum zeroed by the caller (attention.cu)
 int launch_bwd_main(const void* qkv, const void* dout, const float* lse, const float* delta, float* dq_accum,
                     void* dqkv, float* dqkv_colsum, int B, int T, int H, int mask_mode, float scale, cudaStream_t stream,
-                    uint32_t drop_thresh, float inv_keep, const uint64_t* seed_dev, uint32_t site) {
+                    uint32_t drop_thresh, float inv_keep, const uint64_t* seed_dev, uint32_t site, const uint32_t* drop_bits) {
     static PerDeviceOnce once;
     once.run([] {
         cudaFuncSetAttribute(attn_bwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
@@ -1050,11 +1102,12 @@ int launch_bwd_main(const void* qkv, const void* dout, const float* lse, const f
     const int grid = nunits < num_sms() ? nunits : num_sms();
     if (drop_thresh)
         launch_pdl(attn_bwd_tc_kernel<true>, dim3(grid), dim3(kBwdThreads), (size_t)BWD_SMEM, stream, tkv, tq, td, tdq, lse, delta,
-                   (__nv_bfloat16*)dqkv, dqkv_colsum, B, T, H, mask_mode, scale, scale * LOG2E, drop_thresh, inv_keep, seed_dev, site);
+                   (__nv_bfloat16*)dqkv, dqkv_colsum, B, T, H, mask_mode, scale, scale * LOG2E, drop_thresh, inv_keep, seed_dev, site,
+                   drop_bits);
     else
         launch_pdl(attn_bwd_tc_kernel<false>, dim3(grid), dim3(kBwdThreads), (size_t)BWD_SMEM, stream, tkv, tq, td, tdq, lse, delta,
                    (__nv_bfloat16*)dqkv, dqkv_colsum, B, T, H, mask_mode, scale, scale * LOG2E, 0u, 1.0f,
-                   (const uint64_t*)nullptr, 0u);
+                   (const uint64_t*)nullptr, 0u, (const uint32_t*)nullptr);
     return kOk;
 }
 

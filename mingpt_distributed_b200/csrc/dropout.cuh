@@ -1,4 +1,4 @@
-// Counter-based dropout masks (Philox4x32-10), shared by the elementwise dropout kernel and the attention
+// Counter-based dropout masks (Philox4x32-7), shared by the elementwise dropout kernel and the attention
 // kernels. No mask is ever stored: forward and backward regenerate it from (seed, site, element index).
 //   seed : 64-bit, read from DEVICE memory (so a captured CUDA graph sees a fresh value on every replay)
 //   site : which dropout of the network (layer * 4 + {0 attention probs, 1 attention residual, 2 MLP
@@ -11,10 +11,14 @@
 
 namespace mgb {
 
-__device__ __forceinline__ uint4 philox4x32_10(uint2 key, uint4 ctr) {
+// Philox4x32 (Salmon et al., "Parallel random numbers: as easy as 1, 2, 3", SC'11) with 7 rounds: the smallest round
+// count the paper reports as passing BigCrush (10 is its safety-margin default); a dropout mask needs no more, and
+// every round is 4 of the ~45 instructions of a call.
+constexpr int kPhiloxRounds = 7;
+__device__ __forceinline__ uint4 philox4x32(uint2 key, uint4 ctr) {
     const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
 #pragma unroll
-    for (int r = 0; r < 10; ++r) {
+    for (int r = 0; r < kPhiloxRounds; ++r) {
         const uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
         const uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
         ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
@@ -31,7 +35,7 @@ __host__ __device__ __forceinline__ uint32_t dropout_thresh16(float p) {
 
 // keep flags (bit i = element 8*group + i is kept) for one group of 8 consecutive elements
 __device__ __forceinline__ uint32_t dropout_keep8(uint64_t seed, uint32_t site, uint64_t group, uint32_t thresh16) {
-    const uint4 r = philox4x32_10(make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)),
+    const uint4 r = philox4x32(make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)),
                                   make_uint4((uint32_t)group, (uint32_t)(group >> 32), site, 0x6d677062u));
     const uint32_t w[4] = {r.x, r.y, r.z, r.w};
     uint32_t m = 0;
@@ -41,6 +45,65 @@ __device__ __forceinline__ uint32_t dropout_keep8(uint64_t seed, uint32_t site, 
         m |= ((w[i] >> 16) >= thresh16 ? 1u : 0u) << (2 * i + 1);
     }
     return m;
+}
+
+// ---- pre-generated keep words for the tcgen05 attention kernels ----
+// The attention kernels are bound by the instruction stream of their softmax / elementwise warps, and eight Philox
+// calls per 64 probabilities doubled it. A well-occupied generator kernel produces the same keep bits (same groups,
+// same threshold test as dropout_keep8) at the ALU rate instead, as 32-bit words
+//     bits[(bh * ceil(T/32) + key/32) * Tp + query],   Tp = T rounded up to 16,
+// one word = 32 consecutive keys of one query. Within a word key k sits at bit 16 * (k & 1) + 15 - (k >> 1): that is
+// where the generator's packed 16-bit compare leaves it (below), and shifted left by s the word carries keys 2s, 2s+1
+// in the sign bits of bytes 1 and 3 and keys 2s+16, 2s+17 in those of bytes 0 and 2, which one PRMT each (sign-
+// replicate mode) turns into the AND masks of the packed bf16 pairs s and s + 8.
+// The backward kernels own one KEY and 16 consecutive queries per thread, so the generator also writes the transpose,
+//     bitsT[(bh * ceil(T/32) + query/32) * Kp + key],   Kp = T rounded up to 32,  bit = query % 32,
+// behind the query-major words (a 32 x 32 bit transpose across the warp: five shuffle stages).
+__host__ __device__ __forceinline__ int dropout_bit_of_key(int k) { return 16 * (k & 1) + 15 - (k >> 1); }
+__host__ __device__ __forceinline__ int dropout_key_of_bit(int b) { return 2 * (15 - (b & 15)) + (b >> 4); }
+__host__ __device__ __forceinline__ uint64_t dropout_bits_words_q(int64_t BH, int T) {      // query-major part
+    return (uint64_t)BH * (uint64_t)((T + 31) >> 5) * (uint64_t)((T + 15) & ~15);
+}
+__host__ __device__ __forceinline__ uint64_t dropout_bits_words_t(int64_t BH, int T) {      // transposed part
+    return (uint64_t)BH * (uint64_t)((T + 31) >> 5) * (uint64_t)(((T + 31) >> 5) * 32);
+}
+
+// lane i holds row i of a 32 x 32 bit matrix; returns row i of its transpose (bit j of lane i <- bit i of lane j)
+__device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
+#pragma unroll
+    for (int j = 16; j >= 1; j >>= 1) {
+        const uint32_t m = j == 16 ? 0x0000ffffu : j == 8 ? 0x00ff00ffu : j == 4 ? 0x0f0f0f0fu : j == 2 ? 0x33333333u : 0x55555555u;
+        const uint32_t y = __shfl_xor_sync(0xffffffffu, x, j);
+        x = (lane & j) ? ((x & ~m) | ((y >> j) & m)) : ((x & m) | ((y & m) << j));
+    }
+    return x;
+}
+
+__device__ __forceinline__ uint32_t dropout_keep32_word(uint64_t seed, uint32_t site, uint64_t group0, uint32_t thresh16) {
+    // both 16-bit halves of a Philox word against the threshold in three instructions: with H = 0x80008000,
+    // c = (w | H) - (t & ~H) has bit 15 / 31 set iff the low 15 bits compare >=, and the top bits decide otherwise
+    const uint32_t H = 0x80008000u, tt = thresh16 | (thresh16 << 16), tl = tt & ~H;
+    uint32_t word = 0;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        const uint4 r = philox4x32(make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)),
+                                   make_uint4((uint32_t)(group0 + g), (uint32_t)((group0 + g) >> 32), site, 0x6d677062u));
+        const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t c = (w[i] | H) - tl;
+            const uint32_t ge = ((w[i] & ~tt) | (~(w[i] ^ tt) & c)) & H;    // bit 15: key 8g+2i kept, bit 31: key 8g+2i+1
+            word |= ge >> (4 * g + i);
+        }
+    }
+    return word;
+}
+
+// AND masks for the packed pairs s = (keys 2s, 2s+1) and s + 8 = (keys 2s+16, 2s+17) of a keep word, s = 0 .. 7
+__device__ __forceinline__ void dropout_pair_masks(uint32_t word, int s, uint32_t& m_s, uint32_t& m_s8) {
+    const uint32_t x = word << s;
+    asm("prmt.b32 %0, %1, %1, 0xbb99;" : "=r"(m_s) : "r"(x));
+    asm("prmt.b32 %0, %1, %1, 0xaa88;" : "=r"(m_s8) : "r"(x));
 }
 
 }  // namespace mgb

@@ -277,6 +277,7 @@ class _Workspace:
         self.drop = (0.0, 0.0, 0.0)      # dropout probabilities used by the forward that filled this workspace
         self.seed = torch.zeros(1, dtype=torch.int64, device=dev)   # dropout seed of that forward (backward regenerates its masks)
         self.tmp = self.dtmp = None
+        self.drop_bits = None            # per layer: keep words of the attention-probability dropout (head size 64)
         self._mc = (M, C, dev)
 
     def ensure_dropout_buffers(self):
@@ -285,6 +286,13 @@ class _Workspace:
             M, C, dev = self._mc
             self.tmp = torch.empty(M, C, dtype=torch.bfloat16, device=dev)
             self.dtmp = torch.empty(M, C, dtype=torch.bfloat16, device=dev)
+
+    def ensure_drop_bits(self, L, B, T, H):
+        """one keep-word buffer per layer: written once by the forward's generator launch, read by the attention
+        forward AND backward of that layer (B*H*T*T/8 bytes each; 50 MB at B=32, H=12, T=1024)"""
+        if self.drop_bits is None:
+            words = ops.attention_dropout_bits_words(B, T, H)
+            self.drop_bits = [torch.empty(words, dtype=torch.int32, device=self._mc[2]) for _ in range(L)]
 
 
 class _DecodeState:
@@ -636,7 +644,11 @@ class GPT(nn.Module):
             s = ws.stats[l]
             ops.layernorm_fwd(ws.x[l], P(f"{l}.ln1_w"), P(f"{l}.ln1_b"), ws.ln1[l], s[0], s[1])
             ops.linear_fwd(ws.ln1[l], W(f"{l}.qkv_w"), ws.qkv[l], bias=P(f"{l}.qkv_b"))
-            if pa > 0:   # dropout on the attention probabilities, mingpt/model.py:150
+            if pa > 0 and d == 64:   # dropout on the attention probabilities, mingpt/model.py:150
+                ws.ensure_drop_bits(self.n_layer, B, T, H)
+                ops.attention_dropout_bits(ws.drop_bits[l], B, T, H, mask, pa, seed, 4 * l)
+                ops.attention_fwd_dropout_bits(ws.qkv[l], ws.att[l], ws.lse[l], B, T, H, d, mask, pa, ws.drop_bits[l])
+            elif pa > 0:
                 ops.attention_fwd_dropout(ws.qkv[l], ws.att[l], ws.lse[l], B, T, H, d, mask, pa, seed, 4 * l)
             else:
                 ops.attention_fwd(ws.qkv[l], ws.att[l], ws.lse[l], B, T, H, d, mask)
@@ -878,7 +890,10 @@ class GPT(nn.Module):
                 ops.linear_wgrad(ws.datt, ws.att[l], G(f"{l}.o_w"))
                 ops.linear_dgrad(ws.datt, W(f"{l}.o_w"), ws.datt2, rowdot=rd)
                 datt = ws.datt2
-            if pa > 0:
+            if pa > 0 and d == 64:   # the forward's keep words are still in the workspace
+                ops.attention_bwd_dropout_bits(ws.qkv[l], ws.att[l], datt, ws.lse[l], ws.delta, ws.dq_acc, ws.dqkv, B, T, H, d,
+                                               mask, pa, ws.drop_bits[l], delta_given=fuse_delta, dqkv_colsum=G(f"{l}.qkv_b"))
+            elif pa > 0:
                 ops.attention_bwd_dropout(ws.qkv[l], ws.att[l], datt, ws.lse[l], ws.delta, ws.dq_acc, ws.dqkv, B, T, H, d,
                                           mask, pa, seed, 4 * l, delta_given=fuse_delta)
                 ops.colsum(ws.dqkv, G(f"{l}.qkv_b"))

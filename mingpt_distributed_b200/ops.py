@@ -230,6 +230,38 @@ def attention_bwd_dropout(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, d
     return dqkv
 
 
+def attention_dropout_bits_words(B, T, H) -> int:
+    """uint32 words of the keep-bit buffer of one attention dropout site (mgb_attention_dropout_bits_words)"""
+    import ctypes
+    n = ctypes.c_int64(0)
+    check(_lib.lib().mgb_attention_dropout_bits_words(B, T, H, ctypes.addressof(n)), "attention_dropout_bits_words")
+    return int(n.value)
+
+
+def attention_dropout_bits(bits, B, T, H, mask_mode, p, seed_dev, site):
+    """fills `bits` (int32 [attention_dropout_bits_words]) with the keep words of one site: the mask of
+    attention_fwd_dropout / attention_dropout_mask, laid out for the head-size-64 kernels"""
+    if bits.numel() < attention_dropout_bits_words(B, T, H) or bits.element_size() != 4:
+        raise ValueError("attention_dropout_bits: buffer too small")
+    check(_lib.lib().mgb_attention_dropout_bits(_p(bits), B, T, H, mask_mode, float(p), _p(seed_dev), int(site), _stream()), "attention_dropout_bits")
+    return bits
+
+
+def attention_fwd_dropout_bits(qkv, out, lse, B, T, H, d, mask_mode, p, bits, scale=None):
+    scale = 1.0 / math.sqrt(d) if scale is None else scale
+    check(_lib.lib().mgb_attention_fwd_dropout_bits(_p(qkv), _p(out), _p(lse), B, T, H, d, mask_mode, scale, float(p), _p(bits), _stream()), "attention_fwd_dropout_bits")
+    return out
+
+
+def attention_bwd_dropout_bits(qkv, out, dout, lse, delta, dq_accum, dqkv, B, T, H, d, mask_mode, p, bits, scale=None,
+                               delta_given=False, dqkv_colsum=None):
+    scale = 1.0 / math.sqrt(d) if scale is None else scale
+    if delta_given:
+        mask_mode |= ATTN_DELTA_GIVEN
+    check(_lib.lib().mgb_attention_bwd_dropout_bits(_p(qkv), _p(out), _p(dout), _p(lse), _p(delta), _p(dq_accum), _p(dqkv), B, T, H, d, mask_mode, scale, float(p), _p(bits), _p(dqkv_colsum), _stream()), "attention_bwd_dropout_bits")
+    return dqkv
+
+
 def attention_dropout_mask(keep, B, T, H, p, seed_dev, site):
     check(_lib.lib().mgb_attention_dropout_mask(_p(keep), B, T, H, float(p), _p(seed_dev), int(site), _stream()), "attention_dropout_mask")
     return keep

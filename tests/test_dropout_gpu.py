@@ -82,6 +82,67 @@ def test_attention_dropout_matches_torch_with_the_same_mask(d, mode, B, T, H):
     report(f"attn_dropout_d{d}_m{mode}_{B}x{T}x{H}", out_err=err, grad_err=gerr.max().item(), keep_rate=rate)
 
 
+def _unpack_keep_words(bits, B, T, H):
+    """keep[b,h,q,k] twice, from the two layouts of mgb_attention_dropout_bits (include/mingpt_b200.h, csrc/dropout.cuh):
+    query-major words [(bh, k // 32, q)] with key k at bit 16 * (k & 1) + 15 - (k % 32) // 2, then key-major words
+    [(bh, q // 32, k)] with query q at bit q % 32"""
+    kw, tp = (T + 31) // 32, (T + 15) // 16 * 16
+    nq = B * H * kw * tp
+    w = bits[:nq].view(B, H, kw, tp)[..., :T].to(torch.int64) & 0xffffffff                    # [B,H,kw,q]
+    k = torch.arange(kw * 32, device=bits.device)
+    pos = 16 * (k & 1) + 15 - (k % 32) // 2
+    keep_q = ((w[:, :, k // 32, :] >> pos.view(1, 1, -1, 1)) & 1).permute(0, 1, 3, 2)[..., :T]  # [B,H,q,k]
+    wt = bits[nq:nq + B * H * kw * kw * 32].view(B, H, kw, kw * 32).to(torch.int64) & 0xffffffff   # [B,H,qw,k]
+    q = torch.arange(kw * 32, device=bits.device)
+    keep_t = ((wt[:, :, q // 32, :] >> (q % 32).view(1, 1, -1, 1)) & 1)[:, :, :T, :T]           # [B,H,q,k]
+    return keep_q.to(torch.uint8), keep_t.to(torch.uint8)
+
+
+@pytest.mark.parametrize("B,T,H", [(2, 136, 3), (3, 384, 2), (40, 256, 4), (2, 1024, 2)])
+@pytest.mark.parametrize("mode", [1, 2])
+def test_attention_dropout_from_pregenerated_keep_words(mode, B, T, H):
+    """the keep words generated ahead of the kernels hold exactly the mask the seed-taking entry points draw, and the
+    head-size-64 kernels reading them give the same forward (bit for bit) and backward (fp32 atomics: to rounding)"""
+    from mingpt_distributed_b200 import ops
+    d, p, site = 64, 0.2, 12
+    C = H * d
+    g = torch.Generator(device="cuda").manual_seed(6)
+    qkv = torch.randn(B, T, 3 * C, device="cuda", generator=g).bfloat16()
+    dout = torch.randn(B, T, C, device="cuda", generator=g).bfloat16()
+    seed = _seed(77)
+    keep = torch.empty(B, H, T, T, dtype=torch.uint8, device="cuda")
+    ops.attention_dropout_mask(keep, B, T, H, p, seed, site)
+    words = ops.attention_dropout_bits_words(B, T, H)
+    kw = (T + 31) // 32
+    assert words == B * H * kw * ((T + 15) // 16 * 16) + B * H * kw * kw * 32
+    bits = torch.zeros(words, dtype=torch.int32, device="cuda")
+    ops.attention_dropout_bits(bits, B, T, H, mode, p, seed, site)
+    for got in _unpack_keep_words(bits, B, T, H):
+        if mode == 1:    # causal: words right of the diagonal are not generated; compare what the kernels read
+            qi = torch.arange(T, device="cuda").view(T, 1); ki = torch.arange(T, device="cuda").view(1, T)
+            vis = ki <= qi
+            assert torch.equal(got[..., vis], keep[..., vis])
+        else:
+            assert torch.equal(got, keep)
+    out_a = torch.empty(B, T, C, dtype=torch.bfloat16, device="cuda"); lse_a = torch.empty(B, H, T, device="cuda")
+    out_b = torch.empty_like(out_a); lse_b = torch.empty_like(lse_a)
+    ops.attention_fwd_dropout(qkv, out_a, lse_a, B, T, H, d, mode, p, seed, site)
+    ops.attention_fwd_dropout_bits(qkv, out_b, lse_b, B, T, H, d, mode, p, bits)
+    assert torch.equal(out_a, out_b) and torch.equal(lse_a, lse_b)
+    dq = torch.empty(B, T, C, device="cuda"); delta = torch.empty_like(lse_a)
+    g_a = torch.empty_like(qkv); g_b = torch.empty_like(qkv)
+    ops.attention_bwd_dropout(qkv, out_a, dout, lse_a, delta, dq, g_a, B, T, H, d, mode, p, seed, site)
+    cs = torch.zeros(3 * C, device="cuda")
+    ops.attention_bwd_dropout_bits(qkv, out_a, dout, lse_a, delta, dq, g_b, B, T, H, d, mode, p, bits, dqkv_colsum=cs)
+    torch.cuda.synchronize()
+    err = (g_a.float() - g_b.float()).abs().max().item()
+    scale = g_a.float().abs().max().item()
+    report(f"attn_dropout_bits_m{mode}_{B}x{T}x{H}", grad_dev=err, grad_max=scale)
+    assert err <= 1e-2 * scale
+    want_cs = g_b.float().sum(dim=(0, 1))
+    assert torch.allclose(cs, want_cs, rtol=2e-2, atol=2e-2 * want_cs.abs().max().item())
+
+
 @pytest.mark.parametrize("variant", ["mingpt", "reference"])
 def test_training_step_with_dropout_equals_oracle_with_exported_masks(variant):
     from mingpt_distributed_b200 import ops
