@@ -118,6 +118,12 @@ typedef struct mgb_gemm_args {
      * delta = rowsum(dO * O) [B, H, T], which the attention backward otherwise computes in a pass of its own. */
     const void* rowdot_x; int64_t ld_rowdot;
     float* rowdot_out; int64_t rowdot_t;
+    /* optional (CTA-pair engine, bf16 D, no activation): dropout between the bias and the residual,
+     *   D = residual + (keep ? (alpha * A B^T + bias) / (1 - drop_p) : 0),
+     * with the mask mgb_dropout_bf16 draws for (seed, site) over a contiguous [m, n] tensor (element = row * n +
+     * col; n % 8 == 0): c_proj -> resid_drop -> residual add of the reference's blocks (mingpt/model.py:140,167,183,
+     * 187) in the projection's epilogue. drop_p = 0 or drop_seed = NULL: off. */
+    const uint64_t* drop_seed; float drop_p; uint32_t drop_site;
 } mgb_gemm_args;
 int mgb_gemm_bf16(const mgb_gemm_args* args, mgb_stream_t stream);
 
@@ -202,6 +208,11 @@ int mgb_attention_decode(const void* qkv_cache, void* out, int32_t B, int32_t Tc
  *   mgb_attention_dropout_mask: the uint8 keep mask [B,H,T,T] those kernels use (for tests) */
 int mgb_dropout_bf16(const void* x, const void* res, void* y, int64_t n, float p, const uint64_t* seed_dev,
                      uint32_t site, mgb_stream_t stream);
+/* mgb_dropout_bf16 (res = NULL) over a [rows, cols] gradient, plus colsum[c] += sum over rows of y[:, c]: the
+ * backward of a residual-branch dropout and, in the same pass, the bias gradient of the linear layer in front of
+ * it. Same mask as mgb_dropout_bf16 over the contiguous tensor (element = row * cols + col); cols % 8 == 0. */
+int mgb_dropout_bf16_colsum(const void* x, void* y, int64_t rows, int32_t cols, float p, const uint64_t* seed_dev,
+                            uint32_t site, float* colsum, mgb_stream_t stream);
 int mgb_attention_fwd_dropout(const void* qkv, void* out, float* lse, int32_t B, int32_t T, int32_t H, int32_t d,
                               int32_t mask_mode, float scale, float p_drop, const uint64_t* seed_dev, uint32_t site,
                               mgb_stream_t stream);

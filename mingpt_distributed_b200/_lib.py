@@ -39,6 +39,7 @@ class GemmArgs(C.Structure):
         ("colsum", C.c_void_p),
         ("rowdot_x", C.c_void_p), ("ld_rowdot", C.c_int64),
         ("rowdot_out", C.c_void_p), ("rowdot_t", C.c_int64),
+        ("drop_seed", C.c_void_p), ("drop_p", C.c_float), ("drop_site", C.c_uint32),
     ]
 
 
@@ -65,6 +66,7 @@ SIGNATURES = {
     "mgb_attention_bwd_noalloc": [_P, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _P],
     "mgb_attention_decode": [_P, _P, _I32, _I32, _I32, _I32, _I32, _F, _P],
     "mgb_dropout_bf16": [_P, _P, _P, _I64, _F, _P, C.c_uint32, _P],
+    "mgb_dropout_bf16_colsum": [_P, _P, _I64, _I32, _F, _P, C.c_uint32, _P, _P],
     "mgb_attention_fwd_dropout": [_P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _F, _P, C.c_uint32, _P],
     "mgb_attention_bwd_dropout": [_P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F, _F, _P, C.c_uint32, _P],
     "mgb_attention_dropout_mask": [_P, _I32, _I32, _I32, _F, _P, C.c_uint32, _P],

@@ -41,9 +41,83 @@ dropout_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* res, __
     }
 }
 
+// The backward of a residual-branch dropout, y = keep ? dy / (1-p) : 0 over a [rows, cols] gradient, which is also
+// the output gradient of the linear layer in front of the dropout: its bias gradient = column sums of y come out of
+// the same pass (colsum[c] += sum over rows). The block is (cols/8) x rows_per_block threads; a thread keeps its 8
+// columns for the whole grid-stride loop, so the sums stay in registers until one shared-memory and one global atomic
+// per column and block (few, fat CTAs: those tails are the fixed cost).
+__global__ void __launch_bounds__(512)
+dropout_colsum_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t rows, int cols,
+                      uint32_t thresh, float inv_keep, const uint64_t* __restrict__ seed_dev, uint32_t site,
+                      float* __restrict__ colsum) {
+    extern __shared__ float dcs_smem[];              // [cols]
+    const int nch = cols >> 3;
+    const int rpb = blockDim.x / nch;
+    const int ch = threadIdx.x % nch, r = threadIdx.x / nch;
+    for (int c = threadIdx.x; c < cols; c += blockDim.x) dcs_smem[c] = 0.f;
+    __syncthreads();
+    const uint64_t seed = *seed_dev;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (r < rpb) {
+        const int64_t step = (int64_t)gridDim.x * rpb;
+        for (int64_t row0 = (int64_t)blockIdx.x * rpb + r; row0 < rows; row0 += 2 * step) {
+            uint4 v[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int64_t row = row0 + u * step;
+                if (row < rows) v[u] = __ldcs(reinterpret_cast<const uint4*>(x + row * cols + ch * 8));
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int64_t row = row0 + u * step;
+                if (row >= rows) continue;
+                const uint32_t keep = dropout_keep8(seed, site, (uint64_t)(row * nch + ch), thresh);
+                const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+                uint32_t o[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float2 f = unpack_bf16x2(w[e]);
+                    const float a = ((keep >> (2 * e)) & 1u) ? f.x * inv_keep : 0.f;
+                    const float b = ((keep >> (2 * e + 1)) & 1u) ? f.y * inv_keep : 0.f;
+                    o[e] = pack_bf16x2(a, b);
+                    const float2 q = unpack_bf16x2(o[e]);          // the sums see what the GEMMs will read
+                    acc[2 * e] += q.x;
+                    acc[2 * e + 1] += q.y;
+                }
+                stg128(y + row * cols + ch * 8, make_uint4(o[0], o[1], o[2], o[3]));
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) atomicAdd(&dcs_smem[ch * 8 + e], acc[e]);
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < cols; c += blockDim.x) atomicAdd(colsum + c, dcs_smem[c]);
+}
+
 }  // namespace mgb
 
 using namespace mgb;
+
+extern "C" int mgb_dropout_bf16_colsum(const void* x, void* y, int64_t rows, int32_t cols, float p, const uint64_t* seed_dev,
+                                       uint32_t site, float* colsum, mgb_stream_t s_) {
+    cudaStream_t s = (cudaStream_t)s_;
+    if (rows < 0 || cols <= 0 || (cols % 8) || cols > 4096 || !(p >= 0.f && p < 1.f) || !seed_dev || !colsum) {
+        set_last_error("dropout_colsum: bad arguments (cols must be a multiple of 8, at most 4096)"); return kErrBadShape;
+    }
+    if (((uintptr_t)x % 16) || ((uintptr_t)y % 16)) { set_last_error("dropout: pointers must be 16-byte aligned"); return kErrBadAlign; }
+    if (rows == 0) return kOk;
+    const uint32_t thresh = dropout_thresh16(p);
+    const float inv_keep = 65536.0f / (65536.0f - (float)thresh);
+    const int nch = cols / 8;
+    const int threads = (512 / nch) * nch;
+    int64_t g = (rows + (threads / nch) - 1) / (threads / nch);
+    if (g > (int64_t)num_sms() * 2) g = (int64_t)num_sms() * 2;
+    dropout_colsum_kernel<<<(int)g, threads, cols * sizeof(float), s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, rows, cols, thresh,
+                                                                       inv_keep, seed_dev, site, colsum);
+    count_launch(1);
+    MGB_CHECK_LAUNCH();
+    return kOk;
+}
 
 extern "C" int mgb_dropout_bf16(const void* x, const void* res, void* y, int64_t n, float p, const uint64_t* seed_dev,
                                 uint32_t site, mgb_stream_t s_) {

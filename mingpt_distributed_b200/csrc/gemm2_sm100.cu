@@ -15,6 +15,7 @@
 //           thread then updates its own row in place (TMEM -> registers -> bias, GELU, gate, residual) and
 //           one thread TMA-STORES the box (or TMA-reduce-adds it in fp32 for split-K / accumulation).
 #include "gemm_common.cuh"
+#include "dropout.cuh"
 
 namespace mgb {
 namespace gemm {
@@ -113,6 +114,8 @@ __device__ __forceinline__ void epilogue_direct(const Params& p, float (&v)[32],
 //   1  bf16 D through TMA, one output, no activation; optional bias; optional residual / gate-multiply tile through TMA
 //   2  bf16 D + saved GELU' through TMA, NewGELU(tanh), bias                                   (c_fc forward)
 //   3  fp32 D through TMA store or reduce-add, no epilogue terms                               (weight gradients)
+//   4  mode 1 + dropout between the bias and the residual tile                  (c_proj forward of a block, training
+//      with resid_drop > 0): 4 Philox calls per 32 columns of a row, hidden behind the next tile's main loop
 template <bool COLSUM, int MODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
@@ -335,6 +338,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int act_grad = MODE == 2 ? 1 : (MODE == 0 ? p.act_grad : 0);
         const bool direct_gate = MODE == 0 && p.gate != nullptr;       // gate / residual read from global memory by the thread
         const bool direct_res = MODE == 0 && p.residual != nullptr;
+        const uint64_t drop_seed = MODE == 4 ? *p.drop_seed : 0;
         const int slice_cols = d_f32 ? 32 : 64;                   // columns per 128-byte output slice
         const int nslices = block_n / slice_cols;
         const int chunks_per_slice = slice_cols >> 5;
@@ -433,6 +437,26 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         }
                     }
                     if (act && !acted) act_inplace(v, act);
+                    if (MODE == 4) {
+                        // the mask of mgb_dropout_bf16 over the contiguous [M, N] output: group = 8 consecutive elements,
+                        // element 2i / 2i+1 of a group = low / high 16 bits of Philox word i against the threshold
+                        const uint32_t H = 0x80008000u, tt = p.drop_thresh | (p.drop_thresh << 16), tl = tt & ~H;
+                        const uint64_t g0 = ((uint64_t)row * (uint64_t)p.N + (uint64_t)col0) >> 3;
+                        const float ik = p.drop_inv_keep;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const uint4 rn = philox4x32(make_uint2((uint32_t)drop_seed, (uint32_t)(drop_seed >> 32)),
+                                                        make_uint4((uint32_t)(g0 + q), (uint32_t)((g0 + q) >> 32), p.drop_site, 0x6d677062u));
+                            const uint32_t w[4] = {rn.x, rn.y, rn.z, rn.w};
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                const uint32_t c = (w[i] | H) - tl;
+                                const uint32_t ge = (w[i] & ~tt) | (~(w[i] ^ tt) & c);
+                                v[q * 8 + 2 * i] = (ge & 0x8000u) ? v[q * 8 + 2 * i] * ik : 0.f;
+                                v[q * 8 + 2 * i + 1] = (ge & 0x80000000u) ? v[q * 8 + 2 * i + 1] * ik : 0.f;
+                            }
+                        }
+                    }
                     if (aux) {
                         // this thread's 64 bytes of the TMA-loaded residual / gate tile (swizzled like the output)
                         uint32_t xw[16];
@@ -442,7 +466,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                             const uint4 xi = lds128(rowp + ((j ^ swz) << 4));
                             xw[q * 4 + 0] = xi.x; xw[q * 4 + 1] = xi.y; xw[q * 4 + 2] = xi.z; xw[q * 4 + 3] = xi.w;
                         }
-                        if (aux == 2) gate_inplace(v, xw, MODE == 1 ? (int)MGB_GATE_MUL : p.gate_kind);
+                        if (aux == 2) gate_inplace(v, xw, (MODE == 1 || MODE == 4) ? (int)MGB_GATE_MUL : p.gate_kind);
                         else if (aux == 3) {
                             // rowdot: sum over this 64-column slice of D * X, from the fp32 values before D is rounded
                             float2 dacc = make_float2(0.f, 0.f);
@@ -595,6 +619,7 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
         cudaFuncSetAttribute(gemm_pair_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
         cudaFuncSetAttribute(gemm_pair_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
         cudaFuncSetAttribute(gemm_pair_kernel<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+        cudaFuncSetAttribute(gemm_pair_kernel<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     });
     const int num_clusters = num_sms / 2;
     int bn = a->block_n;
@@ -696,13 +721,18 @@ int launch_gemm_pair(const mgb_gemm_args* a, Params p, int num_sms, cudaStream_t
         if (a->d_f32 && !a->bias && !p.act && !a->gate && !a->residual && !a->preact && !fused_colsum) mode = 3;
         else if (!a->d_f32 && p.preact && p.act == MGB_ACT_GELU_TANH && p.act_grad && a->bias && !a->gate && !a->residual &&
                  !fused_colsum) mode = 2;
-        else if (!a->d_f32 && !p.preact && !p.act && side_ok) mode = 1;
+        else if (!a->d_f32 && !p.preact && !p.act && side_ok) mode = (p.drop_thresh && !fused_colsum) ? 4 : 1;
+    }
+    if (p.drop_thresh && mode != 4) {
+        set_last_error("gemm: the dropout epilogue needs bf16 D through TMA, no activation / colsum / preact, and a residual that TMA can load");
+        return kErrUnsupported;
     }
     {
         cudaError_t e;
 #define MGB_PAIR(CS, MD) launch_pdl(gemm_pair_kernel<CS, MD>, dim3(2 * clusters), dim3(kThreads), (size_t)smem_bytes, stream, ta, tb, td, tp, tx, p)
         if (mode == 3) e = MGB_PAIR(false, 3);
         else if (mode == 2) e = MGB_PAIR(false, 2);
+        else if (mode == 4) e = MGB_PAIR(false, 4);
         else if (mode == 1) e = fused_colsum ? MGB_PAIR(true, 1) : MGB_PAIR(false, 1);
         else e = fused_colsum ? MGB_PAIR(true, 0) : MGB_PAIR(false, 0);
 #undef MGB_PAIR

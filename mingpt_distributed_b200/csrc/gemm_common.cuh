@@ -55,6 +55,9 @@ struct Params {
     float* colsum;           // CTA-pair kernel, COLSUM instantiation: column sums of D (fp32, atomic)
     float* rowdot_out;       // CTA-pair kernel, tma_aux == 3: per (row, 64-column slice) sum of D * X
     int64_t rowdot_T;
+    const uint64_t* drop_seed;   // CTA-pair kernel, MODE 4: dropout between bias and residual (dropout.cuh masks)
+    uint32_t drop_thresh, drop_site;
+    float drop_inv_keep;
 };
 
 __device__ __forceinline__ float apply_act(float v, int act) {

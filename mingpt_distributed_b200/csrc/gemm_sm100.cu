@@ -19,6 +19,8 @@
 //   warps 4-11  epilogue: tcgen05.ld -> bias / GELU / gate / residual -> global stores
 // Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1.
 #include "gemm_common.cuh"
+#include "dropout.cuh"
+static_assert(sizeof(mgb_gemm_args) == 232, "mgb_gemm_args is mirrored field by field in _lib.py (GemmArgs) and INTEGRATION.md");
 
 #include <cstdlib>
 
@@ -375,6 +377,13 @@ extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
     p.act_grad = (a->act & MGB_ACT_STORE_GRAD) ? 1 : 0;
     p.gate = reinterpret_cast<const __nv_bfloat16*>(a->gate); p.ldg = a->ldg; p.gate_kind = a->gate_kind;
     p.alpha = a->alpha == 0.0f ? 1.0f : a->alpha;
+    if (a->drop_p != 0.0f && a->drop_seed) {
+        if (!(a->drop_p > 0.f && a->drop_p < 1.f) || (a->n & 7)) { set_last_error("gemm: dropout needs 0 <= drop_p < 1 and n % 8 == 0"); return kErrBadShape; }
+        p.drop_thresh = dropout_thresh16(a->drop_p);
+        p.drop_inv_keep = 65536.0f / (65536.0f - (float)p.drop_thresh);
+        p.drop_seed = a->drop_seed;
+        p.drop_site = a->drop_site;
+    }
 
     // Two tile engines, chosen by shape: CTA pairs (cta_group::2, 256-row tiles, halves the shared-memory
     // traffic per MMA) whenever there are at least two 128-row tiles; the single-CTA kernel for short M.
@@ -386,6 +395,7 @@ extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
     const bool want_pair = engine == MGB_GEMM_ENGINE_PAIR ||
                            (engine == 0 && a->m > BLOCK_M && !g_opt_gemm_single.load(std::memory_order_relaxed));
     if (a->colsum && a->d_f32) { set_last_error("gemm: colsum needs a bf16 D"); return kErrUnsupported; }
+    if (p.drop_thresh && !want_pair) { set_last_error("gemm: the dropout epilogue is a CTA-pair engine epilogue (m > 128)"); return kErrUnsupported; }
     if (a->rowdot_x && !want_pair) { set_last_error("gemm: rowdot is a CTA-pair engine epilogue (m > 128)"); return kErrUnsupported; }
     if (want_pair) {
         const int rc = launch_gemm_pair(&a_local, p, num_sms, stream);

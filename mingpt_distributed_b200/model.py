@@ -23,6 +23,7 @@ PyTorch-math path on the device side.
 from __future__ import annotations
 
 import math
+import os
 from dataclasses import dataclass
 from typing import Callable, Dict, List, Optional, Tuple
 
@@ -174,6 +175,9 @@ class _MinBlock(nn.Module):
 _ALIGN = 64  # elements: every parameter starts 256-byte (fp32) / 128-byte (bf16 shadow) aligned
 
 
+_DROP_SIDE_STREAM = os.environ.get("MGB_DROP_SIDE_STREAM", "1") != "0"
+
+
 class _Nvtx:
     """NVTX ranges around the phases of a step (embedding, each block's forward / backward, head + loss) so that an
     nsys / ncu timeline reads like the model. Off unless MGB_NVTX=1: a range is two host calls per phase."""
@@ -292,7 +296,11 @@ class _Workspace:
         forward AND backward of that layer (B*H*T*T/8 bytes each; 50 MB at B=32, H=12, T=1024)"""
         if self.drop_bits is None:
             words = ops.attention_dropout_bits_words(B, T, H)
-            self.drop_bits = [torch.empty(words, dtype=torch.int32, device=self._mc[2]) for _ in range(L)]
+            dev = self._mc[2]
+            self.drop_bits = [torch.empty(words, dtype=torch.int32, device=dev) for _ in range(L)]
+            self.drop_stream = torch.cuda.Stream(device=dev)
+            self.drop_fork = torch.cuda.Event()
+            self.drop_ready = [torch.cuda.Event() for _ in range(L)]
 
 
 class _DecodeState:
@@ -638,6 +646,23 @@ class GPT(nn.Module):
         if pe > 0:   # nn.Dropout(embed_drop), mingpt/model.py:215,231
             ops.dropout(ws.x[0], None, ws.x[0], pe, seed, self.SITE_EMBED)
         _nvtx.pop()
+        if pa > 0 and d == 64:
+            # The keep words of every layer's attention dropout depend on the seed alone: they are generated on a side
+            # stream from the start of the step. The generator is pure ALU work in small CTAs without shared memory, so
+            # it shares the SMs with the tensor-bound GEMMs of the first layers instead of standing in the critical path
+            # (12 x ~105 us at gpt2-124M, B = 32). Layer l waits for its own event only.
+            # (MGB_DROP_SIDE_STREAM=0 keeps the generator on the main stream: torch.profiler / CUPTI has been seen to
+            # hang on replayed CUDA graphs with parallel branches.)
+            ws.ensure_drop_bits(self.n_layer, B, T, H)
+            side = ws.drop_stream if _DROP_SIDE_STREAM else None
+            if side is not None:
+                ws.drop_fork.record(torch.cuda.current_stream())
+                side.wait_event(ws.drop_fork)
+            with torch.cuda.stream(side):
+                for l in range(L):
+                    ops.attention_dropout_bits(ws.drop_bits[l], B, T, H, mask, pa, seed, 4 * l)
+                    if side is not None:
+                        ws.drop_ready[l].record(side)
         for l in range(L):
             _nvtx.pop() if l else None
             _nvtx.push(f"block{l}.fwd")
@@ -645,8 +670,8 @@ class GPT(nn.Module):
             ops.layernorm_fwd(ws.x[l], P(f"{l}.ln1_w"), P(f"{l}.ln1_b"), ws.ln1[l], s[0], s[1])
             ops.linear_fwd(ws.ln1[l], W(f"{l}.qkv_w"), ws.qkv[l], bias=P(f"{l}.qkv_b"))
             if pa > 0 and d == 64:   # dropout on the attention probabilities, mingpt/model.py:150
-                ws.ensure_drop_bits(self.n_layer, B, T, H)
-                ops.attention_dropout_bits(ws.drop_bits[l], B, T, H, mask, pa, seed, 4 * l)
+                if _DROP_SIDE_STREAM:
+                    torch.cuda.current_stream().wait_event(ws.drop_ready[l])
                 ops.attention_fwd_dropout_bits(ws.qkv[l], ws.att[l], ws.lse[l], B, T, H, d, mask, pa, ws.drop_bits[l])
             elif pa > 0:
                 ops.attention_fwd_dropout(ws.qkv[l], ws.att[l], ws.lse[l], B, T, H, d, mask, pa, seed, 4 * l)
@@ -656,7 +681,13 @@ class GPT(nn.Module):
             if ref:  # nn.MultiheadAttention's own out_proj, then the extra c_proj (model.py:147-154,167)
                 ops.linear_fwd(ws.att[l], W(f"{l}.o_w"), ws.att_o[l], bias=P(f"{l}.o_b"))
                 a_in = ws.att_o[l]
-            if pr > 0:   # resid_drop after c_proj (model.py:140,167), then the residual add (:187)
+            # resid_drop after c_proj (model.py:140,167), then the residual add (:187): in the projection's epilogue on
+            # the CTA-pair GEMM engine (M > 128), a separate pass otherwise
+            fuse_drop = pr > 0 and B * T > 128 and C % 8 == 0
+            if fuse_drop:
+                ops.linear_fwd(a_in, W(f"{l}.proj_w"), ws.xmid[l], bias=P(f"{l}.proj_b"), residual=ws.x[l],
+                               dropout=(pr, seed, 4 * l + 1))
+            elif pr > 0:
                 ops.linear_fwd(a_in, W(f"{l}.proj_w"), ws.tmp, bias=P(f"{l}.proj_b"))
                 ops.dropout(ws.tmp, ws.x[l], ws.xmid[l], pr, seed, 4 * l + 1)
             else:
@@ -675,7 +706,10 @@ class GPT(nn.Module):
                 # the "pre-activation" buffers (fc_pre here, z above) receive GELU'(pre-activation): all backward needs
                 ops.linear_fwd(ws.ln2[l], W(f"{l}.fc_w"), ws.fc_act[l], bias=P(f"{l}.fc_b"),
                                act=ops.ACT_GELU_TANH | ops.ACT_STORE_GRAD, preact=ws.fc_pre[l])
-                if pr > 0:
+                if fuse_drop:
+                    ops.linear_fwd(ws.fc_act[l], W(f"{l}.fc2_w"), ws.x[l + 1], bias=P(f"{l}.fc2_b"), residual=ws.xmid[l],
+                                   dropout=(pr, seed, 4 * l + 2))
+                elif pr > 0:
                     ops.linear_fwd(ws.fc_act[l], W(f"{l}.fc2_w"), ws.tmp, bias=P(f"{l}.fc2_b"))
                     ops.dropout(ws.tmp, ws.xmid[l], ws.x[l + 1], pr, seed, 4 * l + 2)
                 else:
@@ -850,8 +884,11 @@ class GPT(nn.Module):
             _nvtx.push(f"block{l}.bwd")
             s = ws.stats[l]
             dmlp = dx          # gradient of the MLP branch output: through its dropout mask when there is one
-            if pr > 0:
+            if pr > 0 and ref:
                 ops.dropout(dx, None, ws.dtmp, pr, seed, 4 * l + 2)
+                dmlp = ws.dtmp
+            elif pr > 0:       # the mask, and the c_proj bias gradient = column sums of the masked gradient, in one pass
+                ops.dropout_bwd_colsum(dx.view(-1, C), ws.dtmp, pr, seed, 4 * l + 2, G(f"{l}.fc2_b"))
                 dmlp = ws.dtmp
             if ref:
                 ops.act_bwd(dmlp, ws.z[l], ws.dz, ops.GATE_MUL)
@@ -859,8 +896,8 @@ class GPT(nn.Module):
                 ops.linear_wgrad(ws.dz, ws.fc_pre[l], G(f"{l}.fc2_w"))
                 ops.linear_dgrad(ws.dz, W(f"{l}.fc2_w"), ws.dfc)
             else:
-                if pr > 0:     # (without dropout the bias gradient comes out of the LayerNorm backward below, which reads dx anyway)
-                    ops.colsum(dmlp, G(f"{l}.fc2_b"))
+                # (the c_proj bias gradient: from the dropout backward above, or without dropout from the LayerNorm
+                # backward below, which reads dx anyway)
                 ops.linear_wgrad(dmlp, ws.fc_act[l], G(f"{l}.fc2_w"))
                 # d(c_fc output) and, in the same epilogue, its column sums = the c_fc bias gradient
                 ops.linear_dgrad(dmlp, W(f"{l}.fc2_w"), ws.dfc, gate=ws.fc_pre[l], gate_kind=ops.GATE_MUL, colsum=G(f"{l}.fc_b"))
@@ -873,11 +910,9 @@ class GPT(nn.Module):
             dxm = ws.dx_b
             a_in = ws.att_o[l] if ref else ws.att[l]
             dproj = dxm
-            if pr > 0:
-                ops.dropout(dxm, None, ws.dtmp, pr, seed, 4 * l + 1)
+            if pr > 0:         # (without dropout the bias gradient is fused into the ln_1 backward below, whose dres is this tensor)
+                ops.dropout_bwd_colsum(dxm.view(-1, C), ws.dtmp, pr, seed, 4 * l + 1, G(f"{l}.proj_b"))
                 dproj = ws.dtmp
-            if pr > 0:         # (else: fused into the ln_1 backward below, whose dres is this tensor)
-                ops.colsum(dproj, G(f"{l}.proj_b"))
             ops.linear_wgrad(dproj, a_in, G(f"{l}.proj_w"))
             # flash attention's delta = rowsum(dO * O) comes out of the epilogue of the GEMM that produces dO (head size
             # 64 = one 64-column output slice per head; M > 128 = the CTA-pair engine) instead of a pass over O and dO

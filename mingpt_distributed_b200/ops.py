@@ -53,8 +53,9 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = Fa
          bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None, act: int = 0,
          preact: Optional[torch.Tensor] = None, gate: Optional[torch.Tensor] = None, gate_kind: int = 0,
          accumulate: bool = False, split_k: int = 0, block_n: int = 0, alpha: float = 1.0,
-         colsum: Optional[torch.Tensor] = None, rowdot=None) -> torch.Tensor:
-    """out[M,N] = epilogue(alpha * A B^T).  a is [M,K] (or [K,M] if a_mn), b is [N,K] (or [K,N] if b_mn)."""
+         colsum: Optional[torch.Tensor] = None, rowdot=None, dropout=None) -> torch.Tensor:
+    """out[M,N] = epilogue(alpha * A B^T).  a is [M,K] (or [K,M] if a_mn), b is [N,K] (or [K,N] if b_mn).
+    dropout=(p, seed_dev, site): out = residual + dropout_p(alpha * A B^T + bias), the mask of dropout(..., site)."""
     _chk_cuda(a, b, out, bias, residual, preact, gate, colsum)
     _chk2d(a, torch.bfloat16, "gemm a")
     _chk2d(b, torch.bfloat16, "gemm b")
@@ -95,6 +96,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = Fa
         if tuple(rx.shape) != (M, N) or rout.dtype != torch.float32 or rout.numel() != M * (N // 64) or not rout.is_contiguous():
             raise RuntimeError("gemm rowdot: x must be [M,N] bf16 and out contiguous fp32 with M * N/64 elements")
         args.rowdot_x, args.ld_rowdot, args.rowdot_out, args.rowdot_t = rx.data_ptr(), rx.stride(0), rout.data_ptr(), int(rt)
+    if dropout is not None and dropout[0] > 0:
+        dp, dseed, dsite = dropout
+        _chk_cuda(dseed)
+        args.drop_seed, args.drop_p, args.drop_site = dseed.data_ptr(), float(dp), int(dsite)
     check(_lib.lib().mgb_gemm_bf16(C.byref(args), _stream()), "gemm")
     return out
 
@@ -212,6 +217,16 @@ def dropout(x, res, y, p, seed_dev, site):
     """y = (res or 0) + dropout_p(x); mask = f(*seed_dev, site, element). Also its own backward (res=None)."""
     _chk_cuda(x, res, y, seed_dev)
     check(_lib.lib().mgb_dropout_bf16(_p(x), _p(res), _p(y), x.numel(), float(p), _p(seed_dev), int(site), _stream()), "dropout")
+    return y
+
+
+def dropout_bwd_colsum(dy, y, p, seed_dev, site, colsum):
+    """y = dropout_p mask applied to the 2-D gradient dy (the mask of dropout(..., site)), colsum += y.sum(0)"""
+    _chk_cuda(dy, y, seed_dev, colsum)
+    _chk2d(dy, torch.bfloat16, "dropout_bwd_colsum dy")
+    if dy.stride(0) != dy.shape[1] or y.stride(0) != dy.shape[1]:
+        raise ValueError("dropout_bwd_colsum: contiguous rows only")
+    check(_lib.lib().mgb_dropout_bf16_colsum(_p(dy), _p(y), dy.shape[0], dy.shape[1], float(p), _p(seed_dev), int(site), _p(colsum), _stream()), "dropout_colsum")
     return y
 
 

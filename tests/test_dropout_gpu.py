@@ -143,10 +143,13 @@ def test_attention_dropout_from_pregenerated_keep_words(mode, B, T, H):
     assert torch.allclose(cs, want_cs, rtol=2e-2, atol=2e-2 * want_cs.abs().max().item())
 
 
+@pytest.mark.parametrize("dims", [(2, 2, 64, 97, 64, 3), (2, 2, 128, 97, 96, 3)], ids=["d32", "d64"])
 @pytest.mark.parametrize("variant", ["mingpt", "reference"])
-def test_training_step_with_dropout_equals_oracle_with_exported_masks(variant):
+def test_training_step_with_dropout_equals_oracle_with_exported_masks(variant, dims):
+    """d64 (B*T = 288 rows): the tcgen05 attention kernels read keep words generated on a side stream, the residual
+    dropouts sit in the c_proj GEMM epilogues and their backward carries the bias gradients"""
     from mingpt_distributed_b200 import ops
-    L, H, C, V, T, B = 2, 2, 64, 97, 64, 3
+    L, H, C, V, T, B = dims
     pe, pr, pa = 0.1, 0.15, 0.2
     torch.manual_seed(11)
     cfg = m.GPTConfig(model_type=None, n_layer=L, n_head=H, n_embed=C, vocab_size=V, block_size=T, embed_drop=pe,
@@ -174,7 +177,7 @@ def test_training_step_with_dropout_equals_oracle_with_exported_masks(variant):
     osd = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
     _, oloss = go.forward(osd, H, x, y, variant, masks, (1 - q(pe), 1 - q(pr), 1 - q(pa)))
     oloss.backward()
-    report(f"dropout_step_{variant}", loss=loss.item(), oracle=oloss.item())
+    report(f"dropout_step_{variant}_C{C}", loss=loss.item(), oracle=oloss.item())
     assert abs(loss.item() - oloss.item()) < 1e-2 * oloss.item()
     for n, p in model.named_parameters():
         ref = osd[n].grad
@@ -191,3 +194,45 @@ def test_training_step_with_dropout_equals_oracle_with_exported_masks(variant):
     model.train()
     _, l2 = model(x.cuda(), y.cuda())
     assert int(model._rng_seed.item()) == int(seed.item()) + 1 and abs(l2.item() - loss.item()) > 0
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 768, 768), (1000, 768, 3072), (512, 64, 192)])
+def test_gemm_dropout_epilogue_equals_gemm_then_dropout(M, N, K):
+    """D = residual + dropout(A W^T + bias) in the CTA-pair GEMM's epilogue == the GEMM followed by the elementwise
+    dropout kernel with the same (seed, site): the same mask exactly, values to bf16 rounding of the intermediate"""
+    from mingpt_distributed_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(8)
+    p, site, seed = 0.15, 9, _seed(4242)
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) * 0.05).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    res = torch.randn(M, N, device="cuda", generator=g).bfloat16()
+    fused = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    ops.linear_fwd(a, w, fused, bias=bias, residual=res, dropout=(p, seed, site))
+    tmp = torch.empty_like(fused); two = torch.empty_like(fused)
+    ops.linear_fwd(a, w, tmp, bias=bias)
+    ops.dropout(tmp, res, two, p, seed, site)
+    ones = torch.ones(M * N, device="cuda").bfloat16(); mk = torch.empty_like(ones)
+    ops.dropout(ones, None, mk, p, seed, site)
+    keep = (mk != 0).view(M, N)
+    want = res.float() + torch.where(keep, (a.float() @ w.float().t() + bias) / (1 - round(p * 65536) / 65536), torch.zeros((), device="cuda"))
+    dropped = ~keep
+    assert torch.equal(fused[dropped], res[dropped])                      # dropped entries: the residual alone, exactly
+    err = (fused.float() - want).abs().max().item()
+    err2 = (two.float() - want).abs().max().item()
+    report(f"gemm_dropout_epilogue_{M}x{N}x{K}", fused_err=err, two_pass_err=err2, keep_rate=keep.float().mean().item())
+    assert err <= 2e-2 * want.abs().max().item() and err <= 1.5 * err2 + 1e-3
+
+
+def test_dropout_backward_with_fused_bias_gradient():
+    from mingpt_distributed_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(9)
+    for rows, cols in [(4096, 768), (1000, 192), (77, 1600)]:
+        dy = torch.randn(rows, cols, device="cuda", generator=g).bfloat16()
+        a = torch.empty_like(dy); b = torch.empty_like(dy)
+        cs = torch.zeros(cols, device="cuda")
+        ops.dropout(dy, None, a, 0.1, _seed(5), 3)
+        ops.dropout_bwd_colsum(dy, b, 0.1, _seed(5), 3, cs)
+        assert torch.equal(a, b)
+        want = a.float().sum(0)
+        assert torch.allclose(cs, want, rtol=1e-3, atol=1e-3 * want.abs().max().item())

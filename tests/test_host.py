@@ -153,7 +153,7 @@ def test_cabi_library_exports_every_declared_symbol():
         assert hasattr(handle, name), name
     assert declared == set(_lib.SIGNATURES) | set(_lib.INTROSPECTION)
     assert handle.mgb_version() == 100
-    assert ctypes.sizeof(_lib.GemmArgs) == 216 and ctypes.sizeof(_lib.AdamWChunk) == 16
+    assert ctypes.sizeof(_lib.GemmArgs) == 232 and ctypes.sizeof(_lib.AdamWChunk) == 16
 
 
 def test_device_window_loader_follows_the_distributed_sampler_order():
