@@ -60,26 +60,35 @@ dropout_colsum_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __rest
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (r < rpb) {
         const int64_t step = (int64_t)gridDim.x * rpb;
-        for (int64_t row0 = (int64_t)blockIdx.x * rpb + r; row0 < rows; row0 += 2 * step) {
-            uint4 v[2];
+        // four rows per iteration: the kernel is a stream (2 x M x C x 2 bytes), and 30 KB in flight per SM was not enough
+        for (int64_t row0 = (int64_t)blockIdx.x * rpb + r; row0 < rows; row0 += 4 * step) {
+            uint4 v[4];
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
+            for (int u = 0; u < 4; ++u) {
                 const int64_t row = row0 + u * step;
                 if (row < rows) v[u] = __ldcs(reinterpret_cast<const uint4*>(x + row * cols + ch * 8));
             }
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
+            for (int u = 0; u < 4; ++u) {
                 const int64_t row = row0 + u * step;
                 if (row >= rows) continue;
-                const uint32_t keep = dropout_keep8(seed, site, (uint64_t)(row * nch + ch), thresh);
+                // both 16-bit halves of a Philox word against the threshold at once (dropout.cuh), the result's sign bits
+                // spread over the packed bf16 pair by PRMT
+                const uint32_t H = 0x80008000u, tt = thresh | (thresh << 16), tl = tt & ~H;
+                const uint64_t grp = (uint64_t)(row * nch + ch);
+                const uint4 rn = philox4x32(make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)),
+                                            make_uint4((uint32_t)grp, (uint32_t)(grp >> 32), site, 0x6d677062u));
+                const uint32_t rw[4] = {rn.x, rn.y, rn.z, rn.w};
                 const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
                 uint32_t o[4];
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    const float2 f = unpack_bf16x2(w[e]);
-                    const float a = ((keep >> (2 * e)) & 1u) ? f.x * inv_keep : 0.f;
-                    const float b = ((keep >> (2 * e + 1)) & 1u) ? f.y * inv_keep : 0.f;
-                    o[e] = pack_bf16x2(a, b);
+                    const uint32_t c = (rw[e] | H) - tl;
+                    const uint32_t ge = (rw[e] & ~tt) | (~(rw[e] ^ tt) & c);
+                    uint32_t m;
+                    asm("prmt.b32 %0, %1, %1, 0xbb99;" : "=r"(m) : "r"(ge));
+                    const float2 f = mul2(unpack_bf16x2(w[e] & m), make_float2(inv_keep, inv_keep));
+                    o[e] = pack_bf16x2(f.x, f.y);
                     const float2 q = unpack_bf16x2(o[e]);          // the sums see what the GEMMs will read
                     acc[2 * e] += q.x;
                     acc[2 * e + 1] += q.y;
