@@ -121,7 +121,7 @@ typedef struct mgb_gemm_args {
     /* optional (CTA-pair engine, bf16 D, no activation): dropout between the bias and the residual,
      *   D = residual + (keep ? (alpha * A B^T + bias) / (1 - drop_p) : 0),
      * with the mask mgb_dropout_bf16 draws for (seed, site) over a contiguous [m, n] tensor (element = row * n +
-     * col; n % 8 == 0): c_proj -> resid_drop -> residual add of the reference's blocks (mingpt/model.py:140,167,183,
+     * col; n % 16 == 0): c_proj -> resid_drop -> residual add of the reference's blocks (mingpt/model.py:140,167,183,
      * 187) in the projection's epilogue. drop_p = 0 or drop_seed = NULL: off. */
     const uint64_t* drop_seed; float drop_p; uint32_t drop_site;
 } mgb_gemm_args;

@@ -72,26 +72,28 @@ dropout_colsum_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __rest
             for (int u = 0; u < 4; ++u) {
                 const int64_t row = row0 + u * step;
                 if (row >= rows) continue;
-                // both 16-bit halves of a Philox word against the threshold at once (dropout.cuh), the result's sign bits
-                // spread over the packed bf16 pair by PRMT
-                const uint32_t H = 0x80008000u, tt = thresh | (thresh << 16), tl = tt & ~H;
+                // this thread's 8 elements are half a Philox call (dropout.cuh); the compare leaves the keep flags in the
+                // sign bits of two bytes, which PRMT spreads over the packed bf16 pair
                 const uint64_t grp = (uint64_t)(row * nch + ch);
-                const uint4 rn = philox4x32(make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)),
-                                            make_uint4((uint32_t)grp, (uint32_t)(grp >> 32), site, 0x6d677062u));
-                const uint32_t rw[4] = {rn.x, rn.y, rn.z, rn.w};
+                const uint4 rn = dropout_rand16(seed, site, grp >> 1);
+                const uint32_t rw[2] = {(grp & 1) ? rn.z : rn.x, (grp & 1) ? rn.w : rn.y};
                 const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
                 uint32_t o[4];
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const uint32_t c = (rw[e] | H) - tl;
-                    const uint32_t ge = (rw[e] & ~tt) | (~(rw[e] ^ tt) & c);
-                    uint32_t m;
-                    asm("prmt.b32 %0, %1, %1, 0xbb99;" : "=r"(m) : "r"(ge));
-                    const float2 f = mul2(unpack_bf16x2(w[e] & m), make_float2(inv_keep, inv_keep));
-                    o[e] = pack_bf16x2(f.x, f.y);
-                    const float2 q = unpack_bf16x2(o[e]);          // the sums see what the GEMMs will read
-                    acc[2 * e] += q.x;
-                    acc[2 * e + 1] += q.y;
+                for (int h = 0; h < 2; ++h) {
+                    uint32_t gg[2];
+                    dropout_ge_word(rw[h], thresh, gg[0], gg[1]);
+#pragma unroll
+                    for (int t = 0; t < 2; ++t) {
+                        const int e = 2 * h + t;
+                        uint32_t m;
+                        asm("prmt.b32 %0, %1, %1, 0xbb99;" : "=r"(m) : "r"(gg[t]));
+                        const float2 f = mul2(unpack_bf16x2(w[e] & m), make_float2(inv_keep, inv_keep));
+                        o[e] = pack_bf16x2(f.x, f.y);
+                        const float2 q = unpack_bf16x2(o[e]);          // the sums see what the GEMMs will read
+                        acc[2 * e] += q.x;
+                        acc[2 * e + 1] += q.y;
+                    }
                 }
                 stg128(y + row * cols + ch * 8, make_uint4(o[0], o[1], o[2], o[3]));
             }

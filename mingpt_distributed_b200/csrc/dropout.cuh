@@ -3,8 +3,11 @@
 //   seed : 64-bit, read from DEVICE memory (so a captured CUDA graph sees a fresh value on every replay)
 //   site : which dropout of the network (layer * 4 + {0 attention probs, 1 attention residual, 2 MLP
 //          residual}; 0xffff embeddings): mingpt/model.py:140,150,183,215
-//   one Philox call = 128 random bits = 8 elements x 16 bits; an element is KEPT when its 16 bits >= thresh,
-//   thresh = round(p * 65536), so P(keep) = 1 - thresh / 65536.
+//   one Philox call = 16 random bytes = 16 consecutive elements: element e of a 32-bit Philox word (e = 0..3) draws the
+//   16-bit value (byte e << 8) | byte (e+1)%4 and is KEPT when that value >= thresh = round(p * 65536). Each value is
+//   exactly uniform on [0, 65536), so P(keep) = 1 - thresh / 65536; neighbours share one byte, as the high byte of one
+//   and the low byte of the other, so their decisions are independent except when a high byte ties with the
+//   threshold's (probability 1/256) -- a correlation of order 1e-4 -- for half the Philox calls per element.
 #pragma once
 
 #include <stdint.h>
@@ -33,16 +36,34 @@ __host__ __device__ __forceinline__ uint32_t dropout_thresh16(float p) {
     return t <= 0.f ? 0u : (t >= 65535.f ? 65535u : (uint32_t)t);
 }
 
-// keep flags (bit i = element 8*group + i is kept) for one group of 8 consecutive elements
+__device__ __forceinline__ uint4 dropout_rand16(uint64_t seed, uint32_t site, uint64_t group16) {
+    return philox4x32(make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)),
+                      make_uint4((uint32_t)group16, (uint32_t)(group16 >> 32), site, 0x6d677062u));
+}
+
+// The four elements of one Philox word against the threshold, two per packed 16-bit compare: with H = 0x80008000,
+// c = (x | H) - (t & ~H) has bit 15 / 31 set iff the low 15 bits compare >=, and the top bits decide otherwise.
+// g01: bit 15 = element 0 kept, bit 31 = element 1 kept (other bits arbitrary); g23: elements 2 and 3.
+__device__ __forceinline__ void dropout_ge_word(uint32_t w, uint32_t thresh16, uint32_t& g01, uint32_t& g23) {
+    const uint32_t H = 0x80008000u, tt = thresh16 | (thresh16 << 16), tl = tt & ~H;
+    uint32_t x, y;
+    asm("prmt.b32 %0, %1, %1, 0x1201;" : "=r"(x) : "r"(w));       // lanes (b0:b1), (b1:b2)
+    asm("prmt.b32 %0, %1, %1, 0x3023;" : "=r"(y) : "r"(w));       // lanes (b2:b3), (b3:b0)
+    const uint32_t cx = (x | H) - tl, cy = (y | H) - tl;
+    g01 = (x & ~tt) | (~(x ^ tt) & cx);
+    g23 = (y & ~tt) | (~(y ^ tt) & cy);
+}
+
+// keep flags (bit i = element 8*group + i is kept) for one group of 8 consecutive elements = half a Philox call
 __device__ __forceinline__ uint32_t dropout_keep8(uint64_t seed, uint32_t site, uint64_t group, uint32_t thresh16) {
-    const uint4 r = philox4x32(make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)),
-                                  make_uint4((uint32_t)group, (uint32_t)(group >> 32), site, 0x6d677062u));
-    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+    const uint4 r = dropout_rand16(seed, site, group >> 1);
+    const uint32_t w[2] = {(group & 1) ? r.z : r.x, (group & 1) ? r.w : r.y};
     uint32_t m = 0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        m |= ((w[i] & 0xffffu) >= thresh16 ? 1u : 0u) << (2 * i);
-        m |= ((w[i] >> 16) >= thresh16 ? 1u : 0u) << (2 * i + 1);
+    for (int i = 0; i < 2; ++i) {
+        uint32_t g01, g23;
+        dropout_ge_word(w[i], thresh16, g01, g23);
+        m |= (((g01 >> 15) & 1u) | ((g01 >> 31) << 1) | (((g23 >> 15) & 1u) << 2) | ((g23 >> 31) << 3)) << (4 * i);
     }
     return m;
 }
@@ -53,7 +74,7 @@ __device__ __forceinline__ uint32_t dropout_keep8(uint64_t seed, uint32_t site, 
 // same threshold test as dropout_keep8) at the ALU rate instead, as 32-bit words
 //     bits[(bh * ceil(T/32) + key/32) * Tp + query],   Tp = T rounded up to 16,
 // one word = 32 consecutive keys of one query. Within a word key k sits at bit 16 * (k & 1) + 15 - (k >> 1): that is
-// where the generator's packed 16-bit compare leaves it (below), and shifted left by s the word carries keys 2s, 2s+1
+// where the generator's packed 16-bit compares leave it (below), and shifted left by s the word carries keys 2s, 2s+1
 // in the sign bits of bytes 1 and 3 and keys 2s+16, 2s+17 in those of bytes 0 and 2, which one PRMT each (sign-
 // replicate mode) turns into the AND masks of the packed bf16 pairs s and s + 8.
 // The backward kernels own one KEY and 16 consecutive queries per thread, so the generator also writes the transpose,
@@ -79,21 +100,29 @@ __device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
     return x;
 }
 
+// group0 = the first of the word's four groups of 8 keys (dropout_keep8 numbering)
 __device__ __forceinline__ uint32_t dropout_keep32_word(uint64_t seed, uint32_t site, uint64_t group0, uint32_t thresh16) {
-    // both 16-bit halves of a Philox word against the threshold in three instructions: with H = 0x80008000,
-    // c = (w | H) - (t & ~H) has bit 15 / 31 set iff the low 15 bits compare >=, and the top bits decide otherwise
-    const uint32_t H = 0x80008000u, tt = thresh16 | (thresh16 << 16), tl = tt & ~H;
+    const uint32_t H = 0x80008000u;
     uint32_t word = 0;
+    if ((group0 & 1) == 0) {                       // the usual case (T % 16 == 0): two whole Philox calls
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
-        const uint4 r = philox4x32(make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)),
-                                   make_uint4((uint32_t)(group0 + g), (uint32_t)((group0 + g) >> 32), site, 0x6d677062u));
-        const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+        for (int c = 0; c < 2; ++c) {
+            const uint4 r = dropout_rand16(seed, site, (group0 >> 1) + c);
+            const uint32_t w[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const uint32_t c = (w[i] | H) - tl;
-            const uint32_t ge = ((w[i] & ~tt) | (~(w[i] ^ tt) & c)) & H;    // bit 15: key 8g+2i kept, bit 31: key 8g+2i+1
-            word |= ge >> (4 * g + i);
+            for (int i = 0; i < 4; ++i) {
+                uint32_t g01, g23;
+                dropout_ge_word(w[i], thresh16, g01, g23);       // keys 16c + 4i + {0,1} and + {2,3}
+                word |= (g01 & H) >> (8 * c + 2 * i);
+                word |= (g23 & H) >> (8 * c + 2 * i + 1);
+            }
+        }
+    } else {                                       // a row of an odd number of groups started inside a Philox call
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const uint32_t m = dropout_keep8(seed, site, group0 + g, thresh16);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) word |= ((m >> i) & 1u) << dropout_bit_of_key(8 * g + i);
         }
     }
     return word;

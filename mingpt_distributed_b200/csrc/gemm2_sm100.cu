@@ -115,7 +115,7 @@ __device__ __forceinline__ void epilogue_direct(const Params& p, float (&v)[32],
 //   2  bf16 D + saved GELU' through TMA, NewGELU(tanh), bias                                   (c_fc forward)
 //   3  fp32 D through TMA store or reduce-add, no epilogue terms                               (weight gradients)
 //   4  mode 1 + dropout between the bias and the residual tile                  (c_proj forward of a block, training
-//      with resid_drop > 0): 4 Philox calls per 32 columns of a row, hidden behind the next tile's main loop
+//      with resid_drop > 0): 2 Philox calls per 32 columns of a row, hidden behind the next tile's main loop
 template <bool COLSUM, int MODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
@@ -438,22 +438,23 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     }
                     if (act && !acted) act_inplace(v, act);
                     if (MODE == 4) {
-                        // the mask of mgb_dropout_bf16 over the contiguous [M, N] output: group = 8 consecutive elements,
-                        // element 2i / 2i+1 of a group = low / high 16 bits of Philox word i against the threshold
-                        const uint32_t H = 0x80008000u, tt = p.drop_thresh | (p.drop_thresh << 16), tl = tt & ~H;
-                        const uint64_t g0 = ((uint64_t)row * (uint64_t)p.N + (uint64_t)col0) >> 3;
+                        // the mask of mgb_dropout_bf16 over the contiguous [M, N] output (dropout.cuh): 16 consecutive
+                        // elements per Philox call, so this thread's 32 columns are two calls (N % 16 == 0)
+                        const uint64_t g0 = ((uint64_t)row * (uint64_t)p.N + (uint64_t)col0) >> 4;
                         const float ik = p.drop_inv_keep;
 #pragma unroll
-                        for (int q = 0; q < 4; ++q) {
-                            const uint4 rn = philox4x32(make_uint2((uint32_t)drop_seed, (uint32_t)(drop_seed >> 32)),
-                                                        make_uint4((uint32_t)(g0 + q), (uint32_t)((g0 + q) >> 32), p.drop_site, 0x6d677062u));
+                        for (int c = 0; c < 2; ++c) {
+                            const uint4 rn = dropout_rand16(drop_seed, p.drop_site, g0 + c);
                             const uint32_t w[4] = {rn.x, rn.y, rn.z, rn.w};
 #pragma unroll
                             for (int i = 0; i < 4; ++i) {
-                                const uint32_t c = (w[i] | H) - tl;
-                                const uint32_t ge = (w[i] & ~tt) | (~(w[i] ^ tt) & c);
-                                v[q * 8 + 2 * i] = (ge & 0x8000u) ? v[q * 8 + 2 * i] * ik : 0.f;
-                                v[q * 8 + 2 * i + 1] = (ge & 0x80000000u) ? v[q * 8 + 2 * i + 1] * ik : 0.f;
+                                uint32_t g01, g23;
+                                dropout_ge_word(w[i], p.drop_thresh, g01, g23);
+                                float* vv = v + 16 * c + 4 * i;
+                                vv[0] = (g01 & 0x8000u) ? vv[0] * ik : 0.f;
+                                vv[1] = (g01 & 0x80000000u) ? vv[1] * ik : 0.f;
+                                vv[2] = (g23 & 0x8000u) ? vv[2] * ik : 0.f;
+                                vv[3] = (g23 & 0x80000000u) ? vv[3] * ik : 0.f;
                             }
                         }
                     }

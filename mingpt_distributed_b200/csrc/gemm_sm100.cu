@@ -378,7 +378,7 @@ extern "C" int mgb_gemm_bf16(const mgb_gemm_args* a, mgb_stream_t stream_) {
     p.gate = reinterpret_cast<const __nv_bfloat16*>(a->gate); p.ldg = a->ldg; p.gate_kind = a->gate_kind;
     p.alpha = a->alpha == 0.0f ? 1.0f : a->alpha;
     if (a->drop_p != 0.0f && a->drop_seed) {
-        if (!(a->drop_p > 0.f && a->drop_p < 1.f) || (a->n & 7)) { set_last_error("gemm: dropout needs 0 <= drop_p < 1 and n % 8 == 0"); return kErrBadShape; }
+        if (!(a->drop_p > 0.f && a->drop_p < 1.f) || (a->n & 15)) { set_last_error("gemm: dropout needs 0 <= drop_p < 1 and n % 16 == 0"); return kErrBadShape; }
         p.drop_thresh = dropout_thresh16(a->drop_p);
         p.drop_inv_keep = 65536.0f / (65536.0f - (float)p.drop_thresh);
         p.drop_seed = a->drop_seed;

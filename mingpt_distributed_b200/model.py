@@ -175,7 +175,7 @@ class _MinBlock(nn.Module):
 _ALIGN = 64  # elements: every parameter starts 256-byte (fp32) / 128-byte (bf16 shadow) aligned
 
 
-_DROP_SIDE_STREAM = os.environ.get("MGB_DROP_SIDE_STREAM", "1") != "0"
+_DROP_SIDE_STREAM = os.environ.get("MGB_DROP_SIDE_STREAM", "0") == "1"
 
 
 class _Nvtx:
@@ -647,12 +647,12 @@ class GPT(nn.Module):
             ops.dropout(ws.x[0], None, ws.x[0], pe, seed, self.SITE_EMBED)
         _nvtx.pop()
         if pa > 0 and d == 64:
-            # The keep words of every layer's attention dropout depend on the seed alone: they are generated on a side
-            # stream from the start of the step. The generator is pure ALU work in small CTAs without shared memory, so
-            # it shares the SMs with the tensor-bound GEMMs of the first layers instead of standing in the critical path
-            # (12 x ~105 us at gpt2-124M, B = 32). Layer l waits for its own event only.
-            # (MGB_DROP_SIDE_STREAM=0 keeps the generator on the main stream: torch.profiler / CUPTI has been seen to
-            # hang on replayed CUDA graphs with parallel branches.)
+            # The keep words of every layer's attention dropout depend on the seed alone, so all of them are generated
+            # here, ahead of the blocks. MGB_DROP_SIDE_STREAM=1 moves the generator to a side stream (layer l then waits
+            # for its own event only): it is pure ALU work in small CTAs without shared memory and does share the SMs
+            # with the tensor-bound GEMMs of the first layers, but on a power-capped part the step is bound by energy
+            # rather than by issue slots and the overlap measured 0 (33.35 vs 33.21 ms), and torch.profiler / CUPTI has
+            # been seen to hang on replayed CUDA graphs with parallel branches -- so it is off by default.
             ws.ensure_drop_bits(self.n_layer, B, T, H)
             side = ws.drop_stream if _DROP_SIDE_STREAM else None
             if side is not None:
@@ -683,7 +683,7 @@ class GPT(nn.Module):
                 a_in = ws.att_o[l]
             # resid_drop after c_proj (model.py:140,167), then the residual add (:187): in the projection's epilogue on
             # the CTA-pair GEMM engine (M > 128), a separate pass otherwise
-            fuse_drop = pr > 0 and B * T > 128 and C % 8 == 0
+            fuse_drop = pr > 0 and B * T > 128 and C % 16 == 0
             if fuse_drop:
                 ops.linear_fwd(a_in, W(f"{l}.proj_w"), ws.xmid[l], bias=P(f"{l}.proj_b"), residual=ws.x[l],
                                dropout=(pr, seed, 4 * l + 1))

@@ -2,8 +2,7 @@
 """Kernel table of one training step from torch.profiler (CUPTI activity records: no replay, warm caches) -- a cheap
 companion to the ncu launch list. usage: python tools/step_profile.py [--dropout P] [--batch B] [--model gpt2]"""
 import argparse, os, sys
-if "--graph" in sys.argv:      # torch.profiler hangs on replayed graphs with parallel branches: keep the mask generator in line
-    os.environ.setdefault("MGB_DROP_SIDE_STREAM", "0")
+os.environ["MGB_DROP_SIDE_STREAM"] = "0"     # torch.profiler hangs on replayed graphs with parallel branches
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from torch.profiler import profile, ProfilerActivity
