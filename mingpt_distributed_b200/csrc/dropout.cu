@@ -46,60 +46,73 @@ dropout_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* res, __
 // the same pass (colsum[c] += sum over rows). The block is (cols/8) x rows_per_block threads; a thread keeps its 8
 // columns for the whole grid-stride loop, so the sums stay in registers until one shared-memory and one global atomic
 // per column and block (few, fat CTAs: those tails are the fixed cost).
+// W = 16 columns per thread when cols % 16 == 0 (a whole Philox call = 16 elements per row and thread), else 8 (half).
+template <int W>
 __global__ void __launch_bounds__(512)
 dropout_colsum_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t rows, int cols,
                       uint32_t thresh, float inv_keep, const uint64_t* __restrict__ seed_dev, uint32_t site,
                       float* __restrict__ colsum) {
     extern __shared__ float dcs_smem[];              // [cols]
-    const int nch = cols >> 3;
+    constexpr int NV = W / 8;                        // 16-byte vectors per thread and row
+    constexpr int U = 4 / NV;                        // rows in flight per thread: 64 bytes either way
+    const int nch = cols / W;
     const int rpb = blockDim.x / nch;
     const int ch = threadIdx.x % nch, r = threadIdx.x / nch;
     for (int c = threadIdx.x; c < cols; c += blockDim.x) dcs_smem[c] = 0.f;
     __syncthreads();
     const uint64_t seed = *seed_dev;
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float acc[W];
+#pragma unroll
+    for (int e = 0; e < W; ++e) acc[e] = 0.f;
     if (r < rpb) {
         const int64_t step = (int64_t)gridDim.x * rpb;
-        // four rows per iteration: the kernel is a stream (2 x M x C x 2 bytes), and 30 KB in flight per SM was not enough
-        for (int64_t row0 = (int64_t)blockIdx.x * rpb + r; row0 < rows; row0 += 4 * step) {
-            uint4 v[4];
+        // the kernel is a stream (2 x M x C x 2 bytes): 64 bytes in flight per thread (30 KB per SM was not enough)
+        for (int64_t row0 = (int64_t)blockIdx.x * rpb + r; row0 < rows; row0 += U * step) {
+            uint4 v[U][NV];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < U; ++u) {
                 const int64_t row = row0 + u * step;
-                if (row < rows) v[u] = __ldcs(reinterpret_cast<const uint4*>(x + row * cols + ch * 8));
+                if (row < rows) {
+#pragma unroll
+                    for (int n = 0; n < NV; ++n) v[u][n] = __ldcs(reinterpret_cast<const uint4*>(x + row * cols + ch * W + n * 8));
+                }
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < U; ++u) {
                 const int64_t row = row0 + u * step;
                 if (row >= rows) continue;
-                // this thread's 8 elements are half a Philox call (dropout.cuh); the compare leaves the keep flags in the
-                // sign bits of two bytes, which PRMT spreads over the packed bf16 pair
-                const uint64_t grp = (uint64_t)(row * nch + ch);
-                const uint4 rn = dropout_rand16(seed, site, grp >> 1);
-                const uint32_t rw[2] = {(grp & 1) ? rn.z : rn.x, (grp & 1) ? rn.w : rn.y};
-                const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
-                uint32_t o[4];
+                // 16 consecutive elements = one Philox call (dropout.cuh); the compare leaves the keep flags in the sign bits
+                // of two bytes, which PRMT spreads over the packed bf16 pair
+                const uint64_t e0 = (uint64_t)(row * cols + ch * W);              // first element of this thread in the row
+                const uint4 rn = dropout_rand16(seed, site, e0 >> 4);
+                const bool hi = (W == 8) && (e0 & 8);
+                const uint32_t rw[4] = {hi ? rn.z : rn.x, hi ? rn.w : rn.y, rn.z, rn.w};
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    uint32_t gg[2];
-                    dropout_ge_word(rw[h], thresh, gg[0], gg[1]);
+                for (int n = 0; n < NV; ++n) {
+                    const uint32_t w[4] = {v[u][n].x, v[u][n].y, v[u][n].z, v[u][n].w};
+                    uint32_t o[4];
 #pragma unroll
-                    for (int t = 0; t < 2; ++t) {
-                        const int e = 2 * h + t;
-                        uint32_t m;
-                        asm("prmt.b32 %0, %1, %1, 0xbb99;" : "=r"(m) : "r"(gg[t]));
-                        const float2 f = mul2(unpack_bf16x2(w[e] & m), make_float2(inv_keep, inv_keep));
-                        o[e] = pack_bf16x2(f.x, f.y);
-                        const float2 q = unpack_bf16x2(o[e]);          // the sums see what the GEMMs will read
-                        acc[2 * e] += q.x;
-                        acc[2 * e + 1] += q.y;
+                    for (int h = 0; h < 2; ++h) {
+                        uint32_t gg[2];
+                        dropout_ge_word(rw[2 * n + h], thresh, gg[0], gg[1]);
+#pragma unroll
+                        for (int t = 0; t < 2; ++t) {
+                            const int e = 2 * h + t;
+                            uint32_t m;
+                            asm("prmt.b32 %0, %1, %1, 0xbb99;" : "=r"(m) : "r"(gg[t]));
+                            const float2 f = mul2(unpack_bf16x2(w[e] & m), make_float2(inv_keep, inv_keep));
+                            o[e] = pack_bf16x2(f.x, f.y);
+                            const float2 q = unpack_bf16x2(o[e]);          // the sums see what the GEMMs will read
+                            acc[n * 8 + 2 * e] += q.x;
+                            acc[n * 8 + 2 * e + 1] += q.y;
+                        }
                     }
+                    stg128(y + row * cols + ch * W + n * 8, make_uint4(o[0], o[1], o[2], o[3]));
                 }
-                stg128(y + row * cols + ch * 8, make_uint4(o[0], o[1], o[2], o[3]));
             }
         }
 #pragma unroll
-        for (int e = 0; e < 8; ++e) atomicAdd(&dcs_smem[ch * 8 + e], acc[e]);
+        for (int e = 0; e < W; ++e) atomicAdd(&dcs_smem[ch * W + e], acc[e]);
     }
     __syncthreads();
     for (int c = threadIdx.x; c < cols; c += blockDim.x) atomicAdd(colsum + c, dcs_smem[c]);
@@ -119,12 +132,17 @@ extern "C" int mgb_dropout_bf16_colsum(const void* x, void* y, int64_t rows, int
     if (rows == 0) return kOk;
     const uint32_t thresh = dropout_thresh16(p);
     const float inv_keep = 65536.0f / (65536.0f - (float)thresh);
-    const int nch = cols / 8;
+    const int W = (cols % 16 == 0) ? 16 : 8;
+    const int nch = cols / W;
     const int threads = (512 / nch) * nch;
     int64_t g = (rows + (threads / nch) - 1) / (threads / nch);
     if (g > (int64_t)num_sms() * 2) g = (int64_t)num_sms() * 2;
-    dropout_colsum_kernel<<<(int)g, threads, cols * sizeof(float), s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, rows, cols, thresh,
-                                                                       inv_keep, seed_dev, site, colsum);
+    if (W == 16)
+        dropout_colsum_kernel<16><<<(int)g, threads, cols * sizeof(float), s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, rows, cols,
+                                                                               thresh, inv_keep, seed_dev, site, colsum);
+    else
+        dropout_colsum_kernel<8><<<(int)g, threads, cols * sizeof(float), s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, rows, cols,
+                                                                              thresh, inv_keep, seed_dev, site, colsum);
     count_launch(1);
     MGB_CHECK_LAUNCH();
     return kOk;

@@ -29,6 +29,7 @@ P = model._total
 idx = torch.randint(0, V, (32, 1024), device=dev)
 emb = torch.empty(32, 1024, C, dtype=torch.bfloat16, device=dev)
 seed = torch.tensor([1], dtype=torch.int64, device=dev)
+kbits = torch.empty(ops.attention_dropout_bits_words(32, 1024, 12), dtype=torch.int32, device=dev)
 ops.layernorm_fwd(x, g, b, y, mean, rstd)
 cases = [
     ("layernorm fwd [32768x768]", lambda: ops.layernorm_fwd(x, g, b, y, mean, rstd), 2 * M * C * 2 + 8 * M),
@@ -40,6 +41,9 @@ cases = [
     ("sumsq (163M grads)", lambda: opt.grad_norm_sq(), 4 * P),
     ("embedding fwd [32x1024x768]", lambda: ops.embedding_fwd(idx, model._w("wte", True), model._w("wpe", True).view(-1, C), emb), M * 8 + 2 * M * C * 2),
     ("dropout + residual [32768x768]", lambda: ops.dropout(x, dres, y, 0.1, seed, 3), 3 * M * C * 2),
+    ("dropout backward + bias gradient [32768x768]", lambda: ops.dropout_bwd_colsum(x, y, 0.1, seed, 3, dg), 2 * M * C * 2),
+    ("attention keep words, causal [B32 H12 T1024]", lambda: ops.attention_dropout_bits(kbits, 32, 1024, 12, 1, 0.1, seed, 0),
+     2 * 32 * 12 * (1024 * 1024 // 2) // 8),
 ]
 meta = []
 for name, fn, nbytes in cases:
