@@ -621,7 +621,12 @@ class GPT(nn.Module):
             return ws.drop
         if self._rng_seed is None or self._rng_seed.device != self._flat.device:
             # follows torch.manual_seed(): drawn from the default CPU generator once, then advanced on the device
-            self._rng_seed = torch.randint(0, 2 ** 62, (1,), dtype=torch.int64).to(self._flat.device)
+            # (data-parallel ranks usually call torch.manual_seed with the same value so that they build the same model:
+            # the rank is mixed in, or every rank would draw the same masks for its different shard of the batch)
+            seed0 = int(torch.randint(0, 2 ** 62, (1,), dtype=torch.int64).item())
+            if torch.distributed.is_available() and torch.distributed.is_initialized():
+                seed0 = (seed0 + torch.distributed.get_rank() * 0x9E3779B97F4A7C15) % (2 ** 62)
+            self._rng_seed = torch.tensor([seed0], dtype=torch.int64, device=self._flat.device)
         self._rng_seed += 1
         # the seed travels with the workspace: a training forward of ANOTHER shape between this forward and its
         # backward advances the model-wide seed, and backward must still regenerate THIS forward's masks
