@@ -60,8 +60,8 @@ int64_t mgb_launch_count(void);
  * (1 = head size 64 also uses the mma.sync attention kernels instead of the tcgen05 ones), "ln_unstaged"
  * (1 = LayerNorm backward loads its rows straight into registers instead of staging them through shared
  * memory with bulk copies), "ce_unstaged" (1 = cross-entropy streams its rows from global memory, two
- * exponentials per logit, instead of staging them in shared memory), "pdl" (default 0; 1 = launch the GEMM,
- * LayerNorm and attention kernels with programmatic stream serialization, so that a kernel's prologue --
+ * exponentials per logit, instead of staging them in shared memory), "pdl" (default 1 = launch the GEMM,
+ * LayerNorm and attention kernels with programmatic stream serialization; 0 = ordinary launches, so that a kernel's prologue --
  * barrier set-up, TMEM allocation -- overlaps the tail of the kernel before it; every such kernel waits on
  * griddepcontrol before it reads global memory), "gemm_generic" (1 = the CTA-pair GEMM always runs its generic
  * epilogue instantiation, which decides every epilogue term at run time, instead of the ones specialised at compile

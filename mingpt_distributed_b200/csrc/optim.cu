@@ -310,7 +310,7 @@ std::atomic<int> g_opt_gemm_single{0};
 std::atomic<int> g_opt_gemm_direct_store{0};
 std::atomic<int> g_opt_gemm_generic{0};
 std::atomic<int> g_opt_gemm_static{0};
-std::atomic<int> g_opt_pdl{0};   // measured gain on the gpt2-124M step: 0-1 % (within run-to-run noise), so off by default
+std::atomic<int> g_opt_pdl{1};   // programmatic dependent launch: -3 % on the launch-bound gpt-nano / gpt-mini steps, 0-1 % on gpt2-124M
 bool pdl_enabled() { return g_opt_pdl.load(std::memory_order_relaxed) != 0; }
 std::atomic<int> g_opt_attn_mma{0};
 std::atomic<int> g_opt_attn_poly{1};
