@@ -1,3 +1,6 @@
+"""Soak test: 300 CUDA-graph replays of the gpt2-124M training step with dropout 0.1 at all four sites (the path with
+the most kernels and, with MGB_DROP_SIDE_STREAM=1, a forked side stream inside the graph). Prints the loss every 50 steps;
+run it under `timeout`. env: HB = batch per step (32), HN = steps (300)."""
 import sys, os, time
 sys.path.insert(0, "/root/repo")
 import torch
