@@ -184,3 +184,20 @@ def test_device_window_loader_follows_the_distributed_sampler_order():
     assert torch.equal(ds.codes[s:s + 16], x0) and torch.equal(ds.codes[s + 1:s + 17], y0)
     with pytest.raises(TypeError):
         m.DeviceWindowLoader(torch.utils.data.TensorDataset(torch.zeros(4)), 2, "cpu", None)
+
+
+def test_dropout_keep_word_buffer_size_is_a_host_side_computation():
+    """mgb_attention_dropout_bits_words needs no GPU: B*H*ceil(T/32) * (roundup(T,16) + roundup(T,32)) 32-bit words
+    (query-major words for the forward + the bit-transposed copy for the backward, include/mingpt_b200.h)"""
+    if not os.path.exists(_lib.LIB_PATH):
+        _lib.build()
+    handle = ctypes.CDLL(_lib.LIB_PATH)
+    fn = handle.mgb_attention_dropout_bits_words
+    fn.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
+    fn.restype = ctypes.c_int
+    for B, T, H in [(32, 1024, 12), (2, 136, 3), (1, 1, 1), (3, 33, 5)]:
+        n = ctypes.c_int64(-1)
+        assert fn(B, T, H, ctypes.addressof(n)) == 0
+        kw = (T + 31) // 32
+        assert n.value == B * H * kw * ((T + 15) // 16 * 16 + kw * 32)
+    assert fn(0, 16, 1, ctypes.addressof(n)) != 0 and fn(1, 16, 1, None) != 0
