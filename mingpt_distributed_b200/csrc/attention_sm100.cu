@@ -575,6 +575,9 @@ __device__ __forceinline__ int bwd_item(const BwdSched& sc, int q, BwdItem& it) 
     return 1;
 }
 
+#ifndef MGB_ATTN_BWD_SPLIT_LD
+#define MGB_ATTN_BWD_SPLIT_LD 1
+#endif
 // DROP: attention-probability dropout with the forward's mask. A thread owns ONE key and CPT consecutive queries:
 //   drop_bits given -- the TRANSPOSED keep words the generator wrote next to the forward's (dropout.cuh; one word =
 //       32 queries of one key): one coalesced 4-byte load per thread and sub-block, 2 instructions per element;
@@ -674,12 +677,12 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 const int kv_at = (w > 0) ? 2 : 0;
                 for (int n = 0; n <= nsub; ++n) {
                     if (n == kv_at && have2) {
-                        if (w > 0) mbar_wait_relaxed(all_done, (w - 1) & 1);
+                        if (w > 0) mbar_wait_sleep(all_done, (w - 1) & 1, 256);
                         load_kv(it2, (w + 1) & 1);
                     }
                     if (n == nsub) break;
                     const uint32_t slot = g & (kSlots - 1);
-                    mbar_wait_relaxed(&qdo_empty[slot], ((g >> 2) & 1) ^ 1);
+                    mbar_wait_sleep(&qdo_empty[slot], ((g >> 2) & 1) ^ 1, 256);     // four slots ahead: its wake-up may lag
                     const int qrow = row0 + it.i_begin * BQ + n * SUBQ;
                     if (issuer) {
                         mbar_arrive_expect_tx(&qdo_full[slot], 2 * SUB_BYTES);
@@ -788,7 +791,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
             if (st < 0) break;
             if (st == 0) continue;
             for (int j = 0; j < it.nblk; ++j, ++jg) {
-                mbar_wait_relaxed(dq_full, jg & 1);
+                mbar_wait_sleep(dq_full, jg & 1, 64);
                 tc_fence_after();
                 uint32_t lo[32], hi[32];
                 tmem_ld_32x32b_x32(taddr + cDQ, lo);
@@ -912,8 +915,16 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 tc_fence_after();
                 uint32_t sv[CPT], dp[CPT];
                 tmem_ld_cols(taddr + cST + half * SUBQ + wg * CPT, sv);
+#if MGB_ATTN_BWD_SPLIT_LD
+                // the scores first; dP^T stays in flight while the exponentials of the unmasked path run (it is not
+                // needed before the second half of the arithmetic). Every path waits for it before it touches dp or
+                // stores over those TMEM columns.
+                tmem_ld_wait();
+                tmem_ld_cols(taddr + cDPT + half * SUBQ + wg * CPT, dp);
+#else
                 tmem_ld_cols(taddr + cDPT + half * SUBQ + wg * CPT, dp);
                 tmem_ld_wait();
+#endif
                 // DROP: ks = keep ? scale / (1-p) : 0 replaces `scale` in dS = P (ks dP - delta scale) and multiplies P
                 // where it is packed for dV (the item epilogue takes the factor `scale` out again).
                 const float iks = inv_keep * scale;
@@ -940,8 +951,45 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                 const bool all_dead = diag_only && (quarter * 32 >= qc0 + CPT);
                 const bool all_live = diag_only && (quarter * 32 + 31 <= qc0);
                 if (all_dead) {
+#if MGB_ATTN_BWD_SPLIT_LD
+                    tmem_ld_wait();
+#endif
 #pragma unroll
                     for (int e = 0; e < CPT / 2; ++e) { pk[e] = 0u; dk[e] = 0u; }
+#if MGB_ATTN_BWD_SPLIT_LD
+                } else if ((!need_mask && !bias_diag) || all_live) {
+                    // p = exp2(s * c + a) for all 16 queries, then (dP^T has arrived) ds = p * (dp * scale + nb): fp32 pairs
+                    const float2 sc2 = splat2(scale_log2), scl2 = splat2(scale);
+                    float2 ppv[CPT / 2];
+#pragma unroll
+                    for (int q4 = 0; q4 < CPT / 4; ++q4) {
+                        const float4 a4 = lds128f(lda + 4 * q4);
+#pragma unroll
+                        for (int h2 = 0; h2 < 2; ++h2) {
+                            const int e = 2 * q4 + h2;
+                            const float2 av = h2 ? make_float2(a4.z, a4.w) : make_float2(a4.x, a4.y);
+                            const float2 x = fma2(make_float2(__uint_as_float(sv[2 * e]), __uint_as_float(sv[2 * e + 1])), sc2, av);
+                            ppv[e] = make_float2(exp2f(x.x), exp2f(x.y));
+                        }
+                    }
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int q4 = 0; q4 < CPT / 4; ++q4) {
+                        const float4 b4 = lds128f(ldb + 4 * q4);
+#pragma unroll
+                        for (int h2 = 0; h2 < 2; ++h2) {
+                            const int e = 2 * q4 + h2;
+                            const float2 bv = h2 ? make_float2(b4.z, b4.w) : make_float2(b4.x, b4.y);
+                            const float2 pp = ppv[e];
+                            const float2 ks2 = DROP ? make_float2((kq & (1u << (2 * e))) ? iks : 0.f, (kq & (2u << (2 * e))) ? iks : 0.f) : scl2;
+                            const float2 tt = fma2(make_float2(__uint_as_float(dp[2 * e]), __uint_as_float(dp[2 * e + 1])), ks2, bv);
+                            const float2 ds = mul2(pp, tt);
+                            const float2 pm = DROP ? mul2(pp, ks2) : pp;
+                            pk[e] = pack_bf16x2(pm.x, pm.y);
+                            dk[e] = pack_bf16x2(ds.x, ds.y);
+                        }
+                    }
+#else
                 } else if ((!need_mask && !bias_diag) || all_live) {
                     // p = exp2(s * c + a), ds = p * (dp * scale + nb) on fp32 pairs: 3 packed instructions + 2 exponentials
                     // + 2 packs per pair of queries (the scalar form took 10 issue slots)
@@ -964,7 +1012,11 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_kv, const __grid_con
                             dk[e] = pack_bf16x2(ds.x, ds.y);
                         }
                     }
+#endif
                 } else {
+#if MGB_ATTN_BWD_SPLIT_LD
+                    tmem_ld_wait();
+#endif
 #pragma unroll
                     for (int e = 0; e < CPT / 2; ++e) {
                         float pv[2], dsv[2];

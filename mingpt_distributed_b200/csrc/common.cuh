@@ -272,6 +272,18 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 // (kept as a name: the attention and row kernels' waits, where the waiting warps share schedulers with busy ones)
 __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) { mbar_wait(bar, parity); }
+// For warps that wait most of the time and whose wake-up may lag by ~ns nanoseconds (a TMA producer several stages
+// ahead, drain warps): a failed probe is followed by a real sleep. try_wait alone comes back after a few tens of
+// cycles, and the polling of five such warps was 24 % of the attention backward's issued instructions
+// (profiles/r2b_attn_bwd_ncu.md) -- issue slots and, on a power-capped part, energy taken from the busy warps.
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, uint32_t ns) {
+    if (mbar_try_wait(bar, parity)) return;
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        __nanosleep(ns);
+        if (++spins > (1u << 25)) __trap();          // seconds: a protocol bug, not a wait
+    }
+}
 
 __device__ __forceinline__ void fence_proxy_async_smem() {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
