@@ -550,6 +550,7 @@ struct BwdItem {
 };
 struct BwdSched {
     int H, nq, causal, units_per_bh, nunits, items_per_unit;
+    uint32_t m_upb, m_h;       // ceil(2^32 / units_per_bh), ceil(2^32 / H): x / d == umulhi(x, m) for the unit counts here
 };
 __device__ __forceinline__ BwdSched bwd_sched(int B, int H, int nq, bool causal) {
     BwdSched sc;
@@ -557,18 +558,23 @@ __device__ __forceinline__ BwdSched bwd_sched(int B, int H, int nq, bool causal)
     sc.units_per_bh = causal ? (nq + 1) / 2 : nq;
     sc.nunits = sc.units_per_bh * B * H;
     sc.items_per_unit = causal ? 2 : 1;
+    // every role decodes every item of its CTA, at the start of the item: three integer divisions there were 8 % of the
+    // kernel's warp samples (profiles/r2b_attn_bwd_ncu.md). Exact for x * (m * d - 2^32) < 2^32, i.e. x < 2^32 / d.
+    sc.m_upb = (uint32_t)((0x100000000ull + (uint32_t)sc.units_per_bh - 1) / (uint32_t)sc.units_per_bh);
+    sc.m_h = (uint32_t)((0x100000000ull + (uint32_t)H - 1) / (uint32_t)H);
     return sc;
 }
 // q-th item slot of this CTA: -1 past the end, 0 empty slot (the middle key block of an odd count pairs with
 // itself), 1 valid. Every role walks the same sequence.
 __device__ __forceinline__ int bwd_item(const BwdSched& sc, int q, BwdItem& it) {
-    const int u = (int)blockIdx.x + (q / sc.items_per_unit) * (int)gridDim.x;
+    const int u = (int)blockIdx.x + (sc.causal ? (q >> 1) : q) * (int)gridDim.x;
     if (u >= sc.nunits) return -1;
-    const int second = q % sc.items_per_unit;
-    const int bh = u / sc.units_per_bh, p = u - bh * sc.units_per_bh;
+    const int second = sc.causal ? (q & 1) : 0;
+    const int bh = sc.units_per_bh == 1 ? u : (int)__umulhi((uint32_t)u, sc.m_upb);
+    const int p = u - bh * sc.units_per_bh;
     it.kb = second ? sc.nq - 1 - p : p;
     if (second && it.kb == p) return 0;
-    it.b = bh / sc.H;
+    it.b = sc.H == 1 ? bh : (int)__umulhi((uint32_t)bh, sc.m_h);
     it.h = bh - it.b * sc.H;
     it.i_begin = sc.causal ? it.kb : 0;
     it.nblk = sc.nq - it.i_begin;
