@@ -16,6 +16,9 @@
 //           one thread TMA-STORES the box (or TMA-reduce-adds it in fp32 for split-K / accumulation).
 #include "gemm_common.cuh"
 #include "dropout.cuh"
+#ifndef MGB_GEMM_EPI_SLEEP_NS
+#define MGB_GEMM_EPI_SLEEP_NS 100
+#endif
 
 namespace mgb {
 namespace gemm {
@@ -375,7 +378,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 const int c = (int)threadIdx.x - 128;
                 bias_s[acc * 256 + c] = (c < block_n && n0 + c < p.N) ? __ldg(p.bias + n0 + c) : 0.f;
             }
-            mbar_wait(&tmem_full[acc], acc_phase);
+            // the eight epilogue warps wait here for most of a tile's main loop: sleep between probes instead of polling
+            // (issue slots next to the MMA / TMA threads and, on a power-capped part, energy)
+            mbar_wait_sleep(&tmem_full[acc], acc_phase, MGB_GEMM_EPI_SLEEP_NS);
             tc_fence_after();
             if (has_bias) named_bar_sync(4, kEpiWarps * 32);      // bias visible to all eight epilogue warps
             const int64_t row = (int64_t)m0 + r_local;
