@@ -292,8 +292,23 @@ def main():
             n += stepper.launches_per_replay((K * B, T)) * steps
         return ms, n
 
+    # W warm-up steps, then more of them until the part has been under load for 1.5 s: it is power-capped and sheds clock
+    # over the first second, so a timed leg that starts earlier runs up to 3 % ahead of the legs behind it
+    import time
     for i in range(args.warmup):
         step_resident(i)
+    torch.cuda.synchronize()
+    t_one = time.time()
+    step_resident(args.warmup)          # one more, timed on the host: by now it is a graph replay
+    torch.cuda.synchronize()
+    t_one = max(time.time() - t_one, 1e-4)
+    extra_warm = min(200, int(1.5 / t_one) + 1)
+    if world > 1:                       # every rank must run the same number of (collective) steps
+        t = torch.tensor([extra_warm], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        extra_warm = int(t.item())
+    for i in range(extra_warm):
+        step_resident(args.warmup + 1 + i)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -386,6 +401,7 @@ def main():
                                 launch=("eager (one Python call per kernel)" if not stepper.use_graph else
                                         "CUDA graph replay of the whole step" if dp is None else
                                         "CUDA graph segments cut at gradient-bucket boundaries, NCCL all-reduces launched between them"),
+                                warmup_extra=f"{extra_warm + 1} more untimed steps: load held for 1.5 s before the timed legs (power-capped clocks settle)",
                                 l2="per-step working set (activations + parameters / optimizer state, GBs) is far larger than the 126 MB L2"
                                    if not spec["char"] else "inputs rotate over 4 batches; working set of the small char-LM configs partly fits the 126 MB L2"),
                     mfu=dict(flops_per_token=f_tok, of_nominal_2p25pf=value * f_tok / (world * NOMINAL_BF16),
