@@ -198,8 +198,8 @@ int mgb_attention_decode(const void* qkv_cache, void* out, int32_t B, int32_t Tc
                          int32_t d, float scale, mgb_stream_t stream);
 
 /* Dropout (the reference trains with p = 0.1 at four sites and never calls eval(): mingpt/model.py:49-51,140,
- * 150,183,215). Masks are counter based (Philox4x32, 7 rounds, over (seed, site, element)) and never stored: the
- * backward regenerates them. *seed_dev is a DEVICE uint64 the caller changes every step; `site` tells the
+ * 150,183,215). Masks are counter based (Philox4x32, 7 rounds, over (seed, site, element)): the backward
+ * regenerates them, or reads the packed keep words of mgb_attention_dropout_bits; no mask tensor is kept. *seed_dev is a DEVICE uint64 the caller changes every step; `site` tells the
  * dropouts of one step apart. An element is kept with probability 1 - round(p * 65536) / 65536.
  *   mgb_dropout_bf16:   y = (res ? res : 0) + (keep ? x / (1-p) : 0)     (embedding / residual dropouts, and
  *                       their backward: call it on the incoming gradient with res = NULL)

@@ -1,5 +1,6 @@
 // Counter-based dropout masks (Philox4x32-7), shared by the elementwise dropout kernel and the attention
-// kernels. No mask is ever stored: forward and backward regenerate it from (seed, site, element index).
+// kernels: forward and backward regenerate the mask from (seed, site, element index); only the tcgen05 attention
+// kernels read it from packed keep words a generator kernel wrote from the same function (below).
 //   seed : 64-bit, read from DEVICE memory (so a captured CUDA graph sees a fresh value on every replay)
 //   site : which dropout of the network (layer * 4 + {0 attention probs, 1 attention residual, 2 MLP
 //          residual}; 0xffff embeddings): mingpt/model.py:140,150,183,215

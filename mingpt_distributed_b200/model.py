@@ -615,7 +615,8 @@ class GPT(nn.Module):
     def _dropout_now(self, ws: "_Workspace") -> Tuple[float, float, float]:
         """(embed, resid, attn) dropout probabilities in force for this forward: the config's values in
         training mode (the reference never leaves it: mingpt/trainer.py:118-122,180-183), zeros in eval mode.
-        Draws a fresh seed for the step; masks are regenerated from it in backward (nothing is stored)."""
+        Draws a fresh seed for the step; backward regenerates the masks from it (the head-size-64 attention reads the
+        keep words its forward generated instead)."""
         if not self.training or not any(p > 0 for p in self.drop_p):
             ws.drop = (0.0, 0.0, 0.0)
             return ws.drop
