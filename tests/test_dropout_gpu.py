@@ -236,3 +236,26 @@ def test_dropout_backward_with_fused_bias_gradient():
         assert torch.equal(a, b)
         want = a.float().sum(0)
         assert torch.allclose(cs, want, rtol=1e-3, atol=1e-3 * want.abs().max().item())
+
+
+def test_kernel_masks_equal_the_numpy_restatement():
+    """every way the library draws a mask -- the elementwise kernel, the attention mask export, the pre-generated keep
+    words -- against oracle/dropout_mask.py, bit for bit"""
+    import numpy as np
+    from mingpt_distributed_b200 import ops
+    from oracle import dropout_mask as dm
+    seed_v, site, p = 0x1234567890AB, 9, 0.3
+    seed = _seed(seed_v)
+    n = 100_003
+    ones = torch.ones(n, device="cuda").bfloat16(); y = torch.empty_like(ones)
+    ops.dropout(ones, None, y, p, seed, site)
+    assert np.array_equal((y != 0).cpu().numpy(), dm.elementwise_keep(seed_v, site, n, p))
+    for B, H, T in [(2, 2, 40), (1, 3, 136)]:
+        keep = torch.empty(B, H, T, T, dtype=torch.uint8, device="cuda")
+        ops.attention_dropout_mask(keep, B, T, H, p, seed, site)
+        want = dm.attention_keep(seed_v, site, B, H, T, p)
+        assert np.array_equal(keep.cpu().numpy().astype(bool), want)
+        bits = torch.zeros(ops.attention_dropout_bits_words(B, T, H), dtype=torch.int32, device="cuda")
+        ops.attention_dropout_bits(bits, B, T, H, 2, p, seed, site)
+        for got in _unpack_keep_words(bits, B, T, H):
+            assert np.array_equal(got.cpu().numpy().astype(bool), want)

@@ -91,3 +91,30 @@ def test_live_reference_agrees_with_oracle_and_fixture():
     d = sorted(names[id(p)] for p in opt.param_groups[0]["params"])
     nd = sorted(names[id(p)] for p in opt.param_groups[1]["params"])
     assert (d, nd) == go.decay_split(list(sd))
+
+
+def test_dropout_mask_restatement_philox_known_answers_and_statistics():
+    """oracle/dropout_mask.py: its Philox4x32 reproduces the Random123 known-answer vectors (10 rounds: the published
+    ones), and the mask function built on the 7-round variant keeps each element with probability 1 - round(65536 p) /
+    65536, neighbours (which share a byte of the Philox output) uncorrelated to sampling accuracy"""
+    import numpy as np
+    from oracle import dropout_mask as dm
+    kat = [((0, 0), (0, 0, 0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+           ((0xffffffff, 0xffffffff), (0xffffffff,) * 4, (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+           ((0xa4093822, 0x299f31d0), (0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344),
+            (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1))]
+    for key, ctr, want in kat:
+        got = dm.philox4x32(key[0], key[1], *[[c] for c in ctr], rounds=10)
+        assert tuple(int(g[0]) for g in got) == want
+    n = 1 << 20
+    for p in (0.1, 0.5, 0.73):
+        keep = dm.elementwise_keep(20261107, 5, n, p)
+        q = 1 - dm.thresh16(p) / 65536
+        assert abs(keep.mean() - q) < 5 * np.sqrt(q * (1 - q) / n)
+        a, b = keep[:-1].astype(np.float64), keep[1:].astype(np.float64)
+        corr = ((a - q) * (b - q)).mean() / (q * (1 - q))
+        assert abs(corr) < 5 / np.sqrt(n), corr
+    assert dm.thresh16(0.1) == 6554 and dm.thresh16(0.0) == 0
+    # another seed or site: another mask
+    k0 = dm.elementwise_keep(1, 5, 4096, 0.5)
+    assert (k0 != dm.elementwise_keep(2, 5, 4096, 0.5)).mean() > 0.4 and (k0 != dm.elementwise_keep(1, 6, 4096, 0.5)).mean() > 0.4
