@@ -201,3 +201,32 @@ def test_dropout_keep_word_buffer_size_is_a_host_side_computation():
         kw = (T + 31) // 32
         assert n.value == B * H * kw * ((T + 15) // 16 * 16 + kw * 32)
     assert fn(0, 16, 1, ctypes.addressof(n)) != 0 and fn(1, 16, 1, None) != 0
+
+
+def test_flops_per_token_matches_the_baseline_table():
+    """F_tok = 6 (12 L C^2 + V C) + 6 L C T: the numbers MFU is computed from"""
+    from mingpt_distributed_b200.flops import flops_per_token, mfu
+    assert flops_per_token(12, 768, 50257, 1024) == 797_815_296
+    assert flops_per_token(24, 1024, 50257, 1024) == 2_271_713_280
+    assert flops_per_token(48, 1600, 50257, 1024) == 9_801_686_400
+    assert flops_per_token(6, 192, 65, 256) == 17_769_600
+    assert flops_per_token(3, 48, 65, 128) == 626_976
+    # the as-written graph: two output projections, full-square attention
+    assert flops_per_token(12, 768, 50257, 1024, "reference") == 6 * (13 * 12 * 768 ** 2 + 50257 * 768) + 12 * 12 * 768 * 1024
+    assert abs(mfu(2_820_202, 797_815_296) - 1.0) < 1e-6        # BASELINE.md 3: tokens/s at 100 % of 2.25 PFLOP/s
+
+
+def test_bench_reference_arm_prints_the_contract_line():
+    """`bench.py --impl reference` is CPU-only (the oracle port of the reference's as-written graph): it must run
+    without a GPU and print one JSON line with the contract's keys"""
+    import json
+    import subprocess
+    import sys
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--model", "gpt-nano",
+                          "--steps", "1", "--warmup", "0"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["metric"] == "train_tokens_per_s" and line["unit"] == "tokens/s"
+    assert line["value"] > 0 and line["higher_is_better"] is True and line["n_gpus"] == 1
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["e2e"]["d2h_bytes_per_step"] == 0
+    assert line["cpu_baseline"]["kind"] in ("port", "reference") and line["cpu_baseline"]["cores"] >= 1
